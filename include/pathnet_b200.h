@@ -1,0 +1,199 @@
+/*
+ * pathnet_b200.h -- C ABI of libpathnet_b200.so
+ *
+ * B200 (sm_100a) implementation of the PathNet-gym hot path: population-batched
+ * forward + A3C loss + backward of the module super-net over each genotype's
+ * active path, per-tensor-clipped freeze-masked RMSProp, and the genotype
+ * tournament / mutation.  The reference (jan-hofmeier/pathnet-gym) has no FFI
+ * layer: the path sits behind plain Python call signatures that end in
+ * TensorFlow-1 kernels.  Each entry point below cites the reference interface
+ * it replaces (file:line relative to the reference checkout).
+ *
+ * Conventions
+ *   - return 0 on success, negative pn_status on error; the message is kept per
+ *     handle (pn_last_error) and per thread for handle-less calls
+ *     (pn_last_global_error).  No C++ exception crosses this boundary.
+ *   - pointers named *_dev are device pointers owned by the caller, *_host are
+ *     host pointers.  `stream` is a cudaStream_t passed as void* (NULL = legacy
+ *     default stream).  All work is enqueued on `stream`; no call synchronises
+ *     unless its comment says so.
+ *   - a handle is bound to one device and is not thread-safe.
+ *   - genotypes are bitmasks: masks[p*L + l] bit j  <=>  geopath[l][j] == 1.0 of
+ *     path p (pathnet.py:25-30, game_ac_network.py:158-170).  M <= 32.
+ *   - transitions are laid out path-major: t = p*B + b.
+ */
+#ifndef PATHNET_B200_H
+#define PATHNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PN_API __attribute__((visibility("default")))
+#else
+#define PN_API
+#endif
+
+#define PN_ABI_VERSION 1
+#define PN_MAX_LAYERS 8
+#define PN_MAX_MODULES 32
+
+typedef enum pn_status {
+    PN_OK = 0,
+    PN_ERR_INVALID = -1,   /* bad argument / unsupported configuration */
+    PN_ERR_CUDA = -2,      /* a CUDA runtime call failed */
+    PN_ERR_STATE = -3,     /* call order (e.g. slabs not bound, genotypes not set) */
+    PN_ERR_NOMEM = -4
+} pn_status;
+
+/* Super-net shape.  Mirrors the FLAGS fields and hard-coded sizes read by
+ * GameACPathNetNetwork.__init__ (game_ac_network.py:124-155,180):
+ * L, M, kernel_num, stride_size, feature_num=8, hidden=256, the input shape
+ * and max(ACTION_SIZEZ). */
+typedef struct pn_config {
+    int32_t L;              /* layers incl. the linear last layer (FLAGS.L)        */
+    int32_t M;              /* modules per layer (FLAGS.M), <= 32                  */
+    int32_t H, W, C;        /* frame shape, NHWC (reference fork: 160,120,4)       */
+    int32_t F;              /* conv output channels per module (feature_num) = 8   */
+    int32_t hidden;         /* width of the linear modules = 256                   */
+    int32_t A;              /* policy head width = max(ACTION_SIZEZ), <= 31        */
+    int32_t kernel[PN_MAX_LAYERS];   /* FLAGS.kernel_num, conv layers 0..L-2       */
+    int32_t stride[PN_MAX_LAYERS];   /* FLAGS.stride_size                          */
+    int32_t P;              /* paths (genotypes) evaluated by THIS handle / GPU     */
+    int32_t B_max;          /* max transitions per path per call                   */
+    int32_t device;         /* CUDA device ordinal                                 */
+    int32_t flags;          /* reserved, 0                                         */
+} pn_config;
+
+/* One row per trainable tensor, in get_vars() order with nothing frozen
+ * (game_ac_network.py:239-253): for l<L-1, j<M: W_conv[l,j], b_conv[l,j];
+ * for j<M: W_lin[j], b_lin[j]; W_fc2, b_fc2, W_fc3, b_fc3.
+ * kind: 0 conv W (HWIO), 1 conv b, 2 lin W [in,hidden], 3 lin b, 4 fc2 W, 5 fc2 b,
+ * 6 fc3 W, 7 fc3 b.  offset/length are in floats into the slabs; every offset
+ * is a multiple of 32 floats (the gaps are never read or written). */
+typedef struct pn_tensor_desc {
+    int64_t offset;
+    int64_t length;
+    int32_t layer;
+    int32_t module;         /* -1 for the heads */
+    int32_t kind;
+    int32_t reserved;
+} pn_tensor_desc;
+
+typedef struct pn_handle pn_handle;
+
+/* ---- lifecycle -------------------------------------------------------- */
+
+PN_API int pn_abi_version(void);
+
+/* Replaces GameACPathNetNetwork.__init__ graph construction
+ * (game_ac_network.py:114-204).  Allocates only private workspace
+ * (activations, ReLU masks, gradient partials, module->path lists).
+ * Synchronises the device. */
+PN_API int pn_create(const pn_config* cfg, pn_handle** out);
+PN_API void pn_destroy(pn_handle* h);
+PN_API const char* pn_last_error(const pn_handle* h);
+PN_API const char* pn_last_global_error(void);
+
+/* Layout of the parameter slab == get_vars() order (game_ac_network.py:239-253). */
+PN_API int64_t pn_slab_floats(const pn_handle* h);
+PN_API int pn_num_tensors(const pn_handle* h);
+PN_API int pn_tensor_table(const pn_handle* h, pn_tensor_desc* out, int capacity);
+/* flattened size of the last conv output fed to the linear modules
+ * (`last_lin_num`, game_ac_network.py:133-135) */
+PN_API int pn_last_lin(const pn_handle* h);
+/* bytes of private device workspace held by the handle */
+PN_API int64_t pn_workspace_bytes(const pn_handle* h);
+
+/* Bind caller-owned fp32 device slabs of pn_slab_floats() floats each:
+ * variables, the RMSProp "rms" slot, optional "momentum" slot (NULL when the
+ * momentum coefficient is 0, as in doom_pathnet.py:97-102) and the gradient
+ * slab (tf.gradients output, a3c_training_thread.py:55-60).  Borrowed until
+ * rebound or pn_destroy. */
+PN_API int pn_bind_slabs(pn_handle* h, float* params_dev, float* ms_dev, float* mom_dev, float* grads_dev);
+
+/* Replaces pathnet.geopath_insert: L*M scalar assigns per worker
+ * (pathnet.py:20-23, doom_pathnet.py:216-221,261-266).  masks_host[P*L] are the
+ * EFFECTIVE masks (genotype OR fixed path).  Rebuilds the module->path lists
+ * used by the weight-gradient kernels.  Synchronises `stream`. */
+PN_API int pn_set_genotypes(pn_handle* h, const uint32_t* masks_host, void* stream);
+
+/* Replaces set_fixed_path + get_vars_idx + the op selection in process()
+ * (game_ac_network.py:236-271, a3c_training_thread.py:205-209).
+ * frozen_host[num_tensors]: 1 = the tensor's update op is not run. */
+PN_API int pn_set_frozen(pn_handle* h, const uint8_t* frozen_host);
+
+/* ---- the hot path ------------------------------------------------------ */
+
+/* Replaces sess.run([pi, v]) -- run_policy_and_value / run_policy / run_value
+ * (game_ac_network.py:182-201,209-227) for all P paths at once.
+ * frames_dev [P,B,H,W,C]: uint8 (value k means k/255, game_state.py:49-50) when
+ * frames_are_u8 != 0, else float32.  pi_dev [P,B,A], v_dev [P,B]. */
+PN_API int pn_forward(pn_handle* h, const void* frames_dev, int frames_are_u8, int B,
+               float* pi_dev, float* v_dev, void* stream);
+
+/* Replaces the training sess.run of process() up to (not including) the apply
+ * ops: forward, prepare_loss (game_ac_network.py:20-59), tf.gradients
+ * (a3c_training_thread.py:55-60,205-216) for every path, summed over the P
+ * local paths into the bound gradient slab (overwritten, not accumulated).
+ * actions_dev [P,B] int32 (the one-hot `a` feed), td_dev [P,B], r_dev [P,B].
+ * loss_dev [P] (total_loss per path) may be NULL; pi_dev / v_dev may be NULL. */
+PN_API int pn_train_step(pn_handle* h, const void* frames_dev, int frames_are_u8,
+                  const int32_t* actions_dev, const float* td_dev, const float* r_dev, int B,
+                  float entropy_beta, float* loss_dev, float* pi_dev, float* v_dev, void* stream);
+
+/* Same as pn_train_step but every array is a HOST pointer (pinned memory is
+ * fastest); host->device copies of the inputs and the device->host copy of
+ * loss_host [P] are enqueued on `stream` inside the call.  This is the
+ * reference-facing shape of the call: process() feeds NumPy arrays
+ * (a3c_training_thread.py:210-216).  Synchronises `stream` before returning. */
+PN_API int pn_train_step_host(pn_handle* h, const void* frames_host, int frames_are_u8,
+                       const int32_t* actions_host, const float* td_host, const float* r_host, int B,
+                       float entropy_beta, float* loss_host, void* stream);
+
+/* Replaces RMSPropApplier.apply_gradients for the non-frozen tensors
+ * (rmsprop_applier.py:79-106): per tensor g' = clip_by_norm(g, clip_norm);
+ * ms += (g'^2 - ms)(1-decay); mom = momentum*mom + lr*g'/sqrt(ms+eps);
+ * var -= mom.  Reads the bound gradient slab (all-reduce it first when the
+ * population is sharded over GPUs). */
+PN_API int pn_rmsprop_apply(pn_handle* h, float lr, float decay, float momentum, float epsilon,
+                     float clip_norm, void* stream);
+
+/* Replaces the re-initialisation loop at task switch (doom_pathnet.py:289-293):
+ * every non-frozen tensor <- backup_params_dev (same slab layout).  RMSProp
+ * slots are not reset (as in the reference). */
+PN_API int pn_reinit_unfrozen(pn_handle* h, const float* backup_params_dev, void* stream);
+
+/* ---- genotype ops (no handle needed) ----------------------------------- */
+/* Counter-based RNG: Philox4x32-10, key = seed, counter =
+ * (epoch, path_id, position, domain<<24 | slot); u = (x>>11) * 2^-53. */
+
+/* Replaces pathnet.get_geopath (pathnet.py:78-87) for n_paths genotypes:
+ * masks_dev[(i)*L + l], path ids path_id0 + i. */
+PN_API int pn_geopath_init(uint32_t* masks_dev, int n_paths, int path_id0, int L, int M, int N,
+                    uint64_t seed, uint32_t epoch, void* stream);
+
+/* Replaces pathnet.mutation (pathnet.py:50-63), in place, one genotype per path. */
+PN_API int pn_mutate(uint32_t* masks_dev, int n_paths, int path_id0, int L, int M, int N,
+              uint64_t seed, uint32_t epoch, void* stream);
+
+/* Replaces one controller pass (doom_pathnet.py:225-270) for n_groups disjoint
+ * candidate groups of Bcand paths drawn from a Philox-keyed permutation of the
+ * P_total paths (n_groups = 1 is exactly one reference tournament): a group
+ * with any score == -1000 is skipped; else winner = first arg-max, every other
+ * member <- mutation(copy(winner)), all members' scores <- -1000.
+ * genotypes_dev [P_total,L] raw genotypes (in/out), scores_dev [P_total] (in/out),
+ * fixed_dev [L] frozen-path masks, effective_dev [P_total,L] = genotype | fixed (out),
+ * winners_dev [n_groups] winner path id or -1 (out). */
+PN_API int pn_tournament(uint32_t* genotypes_dev, float* scores_dev, const uint32_t* fixed_dev,
+                  uint32_t* effective_dev, int32_t* winners_dev, int P_total, int L, int M, int N,
+                  int Bcand, int n_groups, uint64_t seed, uint32_t epoch, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PATHNET_B200_H */

@@ -1,0 +1,124 @@
+// Internal declarations shared by the translation units of libpathnet_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "pathnet_b200.h"
+
+#define PN_F 8            // conv output channels per module (feature_num, game_ac_network.py:132)
+#define PN_ALIGN 32       // slab alignment of every tensor, in floats
+#define PN_RMS_CHUNK 2048 // floats per RMSProp work chunk (never straddles a tensor)
+
+struct PnNetDesc {        // passed by value to kernels
+    int L, M, hidden, A, nconv, last_lin;
+    int IH[PN_MAX_LAYERS], IW[PN_MAX_LAYERS], Cin[PN_MAX_LAYERS], k[PN_MAX_LAYERS], s[PN_MAX_LAYERS];
+    int OH[PN_MAX_LAYERS], OW[PN_MAX_LAYERS], KK[PN_MAX_LAYERS];
+    long long convW_base[PN_MAX_LAYERS];   // float offset of W_conv[l,0]
+    int conv_stride[PN_MAX_LAYERS];        // floats between module j and j+1 of layer l
+    int convb_off[PN_MAX_LAYERS];          // b_conv[l,j] = W_conv[l,j] + convb_off[l]
+    long long linW_base; int lin_stride; int linb_off;
+    long long fc2W, fc2b, fc3W, fc3b;
+};
+
+struct PnRmsChunk { int tensor; int len; long long off; };
+
+struct pn_handle {
+    pn_config cfg{};
+    PnNetDesc nd{};
+    int P = 0, Bmax = 0, T = 0;
+    std::vector<pn_tensor_desc> tensors;
+    long long slab_floats = 0;
+    // bound slabs (borrowed)
+    float *params = nullptr, *ms = nullptr, *mom = nullptr, *grads = nullptr;
+    // genotype state
+    bool have_masks = false;
+    std::vector<uint32_t> h_masks;
+    uint32_t* d_masks = nullptr;        // [P*L]
+    int* d_list = nullptr;              // [L*M*P] paths using module (l,j), ascending
+    int* d_list_count = nullptr;        // [L*M]
+    // freeze table
+    std::vector<uint8_t> h_frozen;
+    uint8_t* d_frozen = nullptr;        // [num_tensors]
+    // workspace
+    float* act[PN_MAX_LAYERS] = {};     // conv layer outputs [T, npix, F]
+    float* dact[PN_MAX_LAYERS] = {};    // gradients w.r.t. act[l]
+    uint8_t* rmask[PN_MAX_LAYERS] = {}; // [T][M][npix] one byte = 8 channel bits
+    float* hbuf = nullptr;              // [T, hidden]
+    uint8_t* lmask = nullptr;           // [T][M][hidden] 0/1
+    float* dzv = nullptr;               // [T][32]: dL/dlogits (k<A), dL/dv at k==A
+    float* dh = nullptr;                // [T, hidden] gradient w.r.t. the module sum (already /M)
+    float* loss_t = nullptr;            // [T]
+    float* wpart[PN_MAX_LAYERS] = {};   // conv wgrad partials [P*nch][M][KK*F+F]
+    int nch = 1;                        // transition chunks per path in conv wgrad
+    float* head_part = nullptr;         // [head_chunks][hidden*(A+1) + (A+1)]
+    int head_chunks = 0;
+    // rmsprop
+    std::vector<PnRmsChunk> h_chunks;
+    PnRmsChunk* d_chunks = nullptr;
+    int* d_tensor_chunk0 = nullptr;     // first chunk of each tensor
+    int* d_tensor_nchunks = nullptr;
+    float* d_chunk_ss = nullptr;        // [n_chunks] partial sums of squares
+    // host-call staging
+    void* st_frames = nullptr; size_t st_frames_bytes = 0;
+    int32_t* st_actions = nullptr; float* st_td = nullptr; float* st_r = nullptr; float* st_loss = nullptr;
+    long long workspace_bytes = 0;
+    std::string err;
+};
+
+int pn_fail(pn_handle* h, int code, const char* fmt, ...);
+int pn_fail_global(int code, const char* fmt, ...);
+
+#define PN_CUDA(h, call)                                                                      \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return pn_fail((h), PN_ERR_CUDA, "%s failed: %s (%s:%d)", #call,                  \
+                           cudaGetErrorString(e__), __FILE__, __LINE__);                      \
+    } while (0)
+
+#define PN_LAUNCH_CHECK(h, name)                                                              \
+    do {                                                                                      \
+        cudaError_t e__ = cudaGetLastError();                                                 \
+        if (e__ != cudaSuccess)                                                               \
+            return pn_fail((h), PN_ERR_CUDA, "launch of %s failed: %s", name,                 \
+                           cudaGetErrorString(e__));                                          \
+    } while (0)
+
+// kernels' host launchers (pn_net_kernels.cu)
+int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool training, cudaStream_t st);
+int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, const float* td, const float* r,
+                    float beta, float* pi, float* v, float* loss, cudaStream_t st);
+int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaStream_t st);
+// pn_rmsprop.cu
+int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st);
+int pn_launch_reinit(pn_handle* h, const float* backup, cudaStream_t st);
+
+// ---------------------------------------------------------------------------
+// Philox4x32-10 (Salmon et al.), shared by host-less genotype kernels
+// ---------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ void pn_philox(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                          uint32_t k0, uint32_t k1, uint32_t& o0, uint32_t& o1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    o0 = c0; o1 = c1;
+}
+__device__ __forceinline__ uint64_t pn_philox_u64(uint64_t seed, uint32_t epoch, uint32_t path, uint32_t pos,
+                                                  uint32_t domain, uint32_t slot) {
+    uint32_t o0, o1;
+    pn_philox(epoch, path, pos, (domain << 24) | (slot & 0xFFFFFFu), (uint32_t)seed, (uint32_t)(seed >> 32), o0, o1);
+    return ((uint64_t)o0 << 32) | o1;
+}
+__device__ __forceinline__ double pn_philox_uniform(uint64_t seed, uint32_t epoch, uint32_t path, uint32_t pos,
+                                                    uint32_t domain, uint32_t slot) {
+    return (double)(pn_philox_u64(seed, epoch, path, pos, domain, slot) >> 11) * 0x1.0p-53;
+}
+#endif

@@ -1,0 +1,711 @@
+// Forward / loss / backward kernels of the module super-net (fp32 CUDA-core path).
+//
+// Semantics follow the reference graph (game_ac_network.py:182-201 forward,
+// :38-59 loss, a3c_training_thread.py:55-60 gradients); only the modules a
+// path's genotype enables are evaluated -- the reference multiplies the others
+// by an exact 0.0 gate, so the sums are identical.  Module outputs are summed in
+// ascending module index, like np.sum over the reference's object array.
+//
+// Layouts (t = p*B + b):
+//   act[l]   [T][OH*OW][8]   fp32  sum over active modules of relu(conv+b)
+//   rmask[l] [T][M][OH*OW]   u8    bit c = (pre-activation of channel c > 0)
+//   hbuf     [T][hidden]     fp32  (sum of relu(linear))/M
+//   lmask    [T][M][hidden]  u8    0/1
+#include "pn_internal.cuh"
+
+namespace {
+
+__device__ __forceinline__ float to_f(uint8_t v) { return (float)v; }
+__device__ __forceinline__ float to_f(float v) { return v; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// ---------------------------------------------------------------------------
+// conv layer forward: one CTA = one transition x one band of output rows
+// ---------------------------------------------------------------------------
+template <typename TIn>
+__global__ void __launch_bounds__(128)
+conv_fwd_kernel(const TIn* __restrict__ X, float in_scale, const float* __restrict__ params, PnNetDesc nd, int l,
+                const uint32_t* __restrict__ masks, int B, int rows_per_band, float* __restrict__ Y,
+                uint8_t* __restrict__ R) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int t = blockIdx.x, band = blockIdx.y, p = t / B;
+    const int IH = nd.IH[l], IW = nd.IW[l], Cin = nd.Cin[l], k = nd.k[l], s = nd.s[l];
+    const int OH = nd.OH[l], OW = nd.OW[l], KK = nd.KK[l];
+    const int r0 = band * rows_per_band;
+    const int nrows = min(rows_per_band, OH - r0);
+    const int npix_band = nrows * OW, npix = OH * OW;
+    const int in_rows = (nrows - 1) * s + k, row_elems = IW * Cin;
+    float* Ws = reinterpret_cast<float*>(smem_raw);   // [KK*8]
+    float* bs = Ws + KK * PN_F;                        // [8]
+    TIn* Xs = reinterpret_cast<TIn*>(bs + PN_F);       // [in_rows*row_elems]
+    const TIn* Xg = X + ((size_t)t * IH + (size_t)r0 * s) * row_elems;
+    for (int i = threadIdx.x; i < in_rows * row_elems; i += blockDim.x) Xs[i] = Xg[i];
+    const uint32_t mask = masks[p * nd.L + l];
+    const int iters = (npix_band + blockDim.x - 1) / blockDim.x;
+    const int kc = k * Cin;
+    for (int it = 0; it < iters; ++it) {
+        const int pix = it * blockDim.x + threadIdx.x;
+        const bool live = pix < npix_band;
+        const int oy = live ? pix / OW : 0, ox = live ? pix % OW : 0;
+        float sum[PN_F];
+#pragma unroll
+        for (int c = 0; c < PN_F; ++c) sum[c] = 0.f;
+        for (int j = 0; j < nd.M; ++j) {
+            if (!((mask >> j) & 1u)) continue;   // block-uniform
+            __syncthreads();
+            const float* Wg = params + nd.convW_base[l] + (long long)j * nd.conv_stride[l];
+            for (int i = threadIdx.x; i < KK * PN_F; i += blockDim.x) Ws[i] = Wg[i];
+            if (threadIdx.x < PN_F) bs[threadIdx.x] = Wg[nd.convb_off[l] + threadIdx.x];
+            __syncthreads();
+            if (live) {
+                float acc[PN_F];
+#pragma unroll
+                for (int c = 0; c < PN_F; ++c) acc[c] = 0.f;
+                for (int kh = 0; kh < k; ++kh) {
+                    const TIn* xr = Xs + (oy * s + kh) * row_elems + ox * s * Cin;
+                    const float4* wr = reinterpret_cast<const float4*>(Ws + kh * kc * PN_F);
+                    for (int q = 0; q < kc; ++q) {
+                        const float a = to_f(xr[q]);
+                        const float4 w0 = wr[2 * q], w1 = wr[2 * q + 1];
+                        acc[0] = fmaf(a, w0.x, acc[0]); acc[1] = fmaf(a, w0.y, acc[1]);
+                        acc[2] = fmaf(a, w0.z, acc[2]); acc[3] = fmaf(a, w0.w, acc[3]);
+                        acc[4] = fmaf(a, w1.x, acc[4]); acc[5] = fmaf(a, w1.y, acc[5]);
+                        acc[6] = fmaf(a, w1.z, acc[6]); acc[7] = fmaf(a, w1.w, acc[7]);
+                    }
+                }
+                unsigned bits = 0;
+#pragma unroll
+                for (int c = 0; c < PN_F; ++c) {
+                    const float pre = fmaf(acc[c], in_scale, bs[c]);
+                    if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
+                }
+                R[((size_t)t * nd.M + j) * npix + r0 * OW + pix] = (uint8_t)bits;
+            }
+        }
+        if (live) {
+            float4* yo = reinterpret_cast<float4*>(Y + ((size_t)t * npix + r0 * OW + pix) * PN_F);
+            yo[0] = make_float4(sum[0], sum[1], sum[2], sum[3]);
+            yo[1] = make_float4(sum[4], sum[5], sum[6], sum[7]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// linear modules forward: CTA = (path, 64 hidden units, 32 transitions)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+lin_fwd_kernel(const float* __restrict__ X, const float* __restrict__ params, PnNetDesc nd,
+               const uint32_t* __restrict__ masks, int B, float* __restrict__ Hout, uint8_t* __restrict__ Rl) {
+    __shared__ float Xs[32][33];
+    __shared__ __align__(16) float Ws[32][64];
+    const int p = blockIdx.x, c0 = blockIdx.y * 64, b0 = blockIdx.z * 32;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int K = nd.last_lin, Hd = nd.hidden;
+    const uint32_t mask = masks[p * nd.L + nd.L - 1];
+    float sum[2][4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) sum[a][b] = 0.f;
+    for (int j = 0; j < nd.M; ++j) {
+        if (!((mask >> j) & 1u)) continue;
+        const float* W = params + nd.linW_base + (long long)j * nd.lin_stride;
+        float acc[2][4];
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+        for (int k0 = 0; k0 < K; k0 += 32) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int idx = tid + i * 256, row = idx >> 5, kk = idx & 31, b = b0 + row;
+                Xs[row][kk] = (b < B && k0 + kk < K) ? X[(size_t)(p * B + b) * K + k0 + kk] : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int idx = tid + i * 256, kk = idx >> 6, c = idx & 63;
+                Ws[kk][c] = (k0 + kk < K && c0 + c < Hd) ? W[(size_t)(k0 + kk) * Hd + c0 + c] : 0.f;
+            }
+            __syncthreads();
+#pragma unroll 8
+            for (int kk = 0; kk < 32; ++kk) {
+                const float x0 = Xs[ty * 2][kk], x1 = Xs[ty * 2 + 1][kk];
+                const float4 w = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
+                acc[0][0] = fmaf(x0, w.x, acc[0][0]); acc[0][1] = fmaf(x0, w.y, acc[0][1]);
+                acc[0][2] = fmaf(x0, w.z, acc[0][2]); acc[0][3] = fmaf(x0, w.w, acc[0][3]);
+                acc[1][0] = fmaf(x1, w.x, acc[1][0]); acc[1][1] = fmaf(x1, w.y, acc[1][1]);
+                acc[1][2] = fmaf(x1, w.z, acc[1][2]); acc[1][3] = fmaf(x1, w.w, acc[1][3]);
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const int b = b0 + ty * 2 + a;
+            if (b >= B) continue;
+            const size_t t = (size_t)p * B + b;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int col = c0 + tx * 4 + q;
+                if (col >= Hd) continue;
+                const float pre = acc[a][q] + W[nd.linb_off + col];
+                const bool on = pre > 0.f;
+                if (on) sum[a][q] += pre;
+                Rl[(t * nd.M + j) * Hd + col] = on ? 1 : 0;
+            }
+        }
+    }
+    const float Mf = (float)nd.M;
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        const int b = b0 + ty * 2 + a;
+        if (b >= B) continue;
+        const size_t t = (size_t)p * B + b;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int col = c0 + tx * 4 + q;
+            if (col < Hd) Hout[t * Hd + col] = sum[a][q] / Mf;   // net/FLAGS.M, game_ac_network.py:194
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// heads + A3C loss + closed-form dL/dlogits, dL/dv, dL/dh : one warp per transition
+// (game_ac_network.py:198-201 heads, :38-59 loss)
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnNetDesc nd, int T, int training,
+            const int32_t* __restrict__ actions, const float* __restrict__ td, const float* __restrict__ r,
+            float beta, float* __restrict__ pi_out, float* __restrict__ v_out, float* __restrict__ dzv,
+            float* __restrict__ dh, float* __restrict__ loss_t) {
+    extern __shared__ __align__(16) float hsm[];
+    const int Hd = nd.hidden, A = nd.A;
+    float* W2s = hsm;                 // [Hd*A]
+    float* W3s = W2s + Hd * A;        // [Hd]
+    float* b2s = W3s + Hd;            // [32] (b3 at index A)
+    float* hs = b2s + 32;             // [8][Hd]
+    float* dzs = hs + 8 * Hd;         // [8][32]
+    for (int i = threadIdx.x; i < Hd * A; i += blockDim.x) W2s[i] = params[nd.fc2W + i];
+    for (int i = threadIdx.x; i < Hd; i += blockDim.x) W3s[i] = params[nd.fc3W + i];
+    if (threadIdx.x < 32) b2s[threadIdx.x] = threadIdx.x < A ? params[nd.fc2b + threadIdx.x]
+                                                              : (threadIdx.x == A ? params[nd.fc3b] : 0.f);
+    __syncthreads();
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* hw = hs + w * Hd;
+    float* dzw = dzs + w * 32;
+    const int nwarps = gridDim.x * 8;
+    for (int t = blockIdx.x * 8 + w; t < T; t += nwarps) {
+        for (int i = lane; i < Hd; i += 32) hw[i] = Hin[(size_t)t * Hd + i];
+        __syncwarp();
+        float acc = b2s[lane];
+        if (lane < A) {
+            for (int i = 0; i < Hd; ++i) acc = fmaf(hw[i], W2s[i * A + lane], acc);
+        } else if (lane == A) {
+            for (int i = 0; i < Hd; ++i) acc = fmaf(hw[i], W3s[i], acc);
+        }
+        const float v = __shfl_sync(0xffffffffu, acc, A);
+        const float zk = lane < A ? acc : -INFINITY;
+        const float m = warp_max(zk);
+        const float e = lane < A ? expf(zk - m) : 0.f;
+        const float ssum = warp_sum(e);
+        const float pik = e / ssum;
+        if (pi_out && lane < A) pi_out[(size_t)t * A + lane] = pik;
+        if (v_out && lane == 0) v_out[t] = v;
+        if (training) {
+            const int a = actions[t];
+            const float tdv = td[t], rv = r[t];
+            const float clipped = fminf(fmaxf(pik, 1e-20f), 1.0f);
+            const float logp = lane < A ? logf(clipped) : 0.f;
+            const bool inside = (pik >= 1e-20f) && (pik <= 1.0f);
+            const float Hent = -warp_sum(lane < A ? pik * logp : 0.f);
+            const bool a_ok = a >= 0 && a < A;
+            const float logp_a = __shfl_sync(0xffffffffu, logp, a_ok ? a : 0);
+            const float diff = rv - v;
+            const float loss = -((a_ok ? logp_a * tdv : 0.f) + Hent * beta) + 0.25f * diff * diff;
+            float dpi = 0.f;
+            if (lane < A) {
+                dpi = beta * (logp + (inside ? 1.f : 0.f));
+                if (a_ok && lane == a && inside) dpi -= tdv / clipped;
+            }
+            const float dot = warp_sum(dpi * pik);
+            const float dz = pik * (dpi - dot);
+            const float dv = -0.5f * diff;
+            const float val = lane < A ? dz : (lane == A ? dv : 0.f);
+            dzv[(size_t)t * 32 + lane] = val;
+            dzw[lane] = val;
+            __syncwarp();
+            const float Mf = (float)nd.M;
+            for (int i = lane; i < Hd; i += 32) {
+                float g = dzw[A] * W3s[i];
+                for (int kx = 0; kx < A; ++kx) g = fmaf(dzw[kx], W2s[i * A + kx], g);
+                dh[(size_t)t * Hd + i] = g / Mf;
+            }
+            if (lane == 0) loss_t[t] = loss;
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void path_loss_kernel(const float* __restrict__ loss_t, int P, int B, float* __restrict__ loss) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) s += loss_t[(size_t)p * B + b];
+    loss[p] = s;
+}
+
+// head weight gradients, stage 1: per chunk of 64 transitions
+__global__ void head_wgrad_partial_kernel(const float* __restrict__ Hin, const float* __restrict__ dzv, PnNetDesc nd,
+                                          int T, float* __restrict__ part) {
+    __shared__ float dz[64][32];
+    const int Hd = nd.hidden, A1 = nd.A + 1;
+    const int t0 = blockIdx.x * 64, nt = min(64, T - t0);
+    for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) {
+        const int tt = i >> 5;
+        dz[tt][i & 31] = tt < nt ? dzv[(size_t)(t0 + tt) * 32 + (i & 31)] : 0.f;
+    }
+    __syncthreads();
+    float* out = part + (size_t)blockIdx.x * ((size_t)Hd * A1 + A1);
+    const int i = threadIdx.x;
+    if (i < Hd) {
+        float acc[32];
+#pragma unroll
+        for (int kx = 0; kx < 32; ++kx) acc[kx] = 0.f;
+        for (int tt = 0; tt < nt; ++tt) {
+            const float hv = Hin[(size_t)(t0 + tt) * Hd + i];
+#pragma unroll
+            for (int kx = 0; kx < 32; ++kx) acc[kx] = fmaf(hv, dz[tt][kx], acc[kx]);
+        }
+#pragma unroll
+        for (int kx = 0; kx < 32; ++kx)
+            if (kx < A1) out[(size_t)i * A1 + kx] = acc[kx];
+    }
+    if (i < A1) {
+        float s = 0.f;
+        for (int tt = 0; tt < nt; ++tt) s += dz[tt][i];
+        out[(size_t)Hd * A1 + i] = s;
+    }
+}
+
+// stage 2: fixed-order sum over chunks, scatter into W_fc2/b_fc2/W_fc3/b_fc3
+__global__ void head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc nd,
+                                         float* __restrict__ grads) {
+    const int Hd = nd.hidden, A = nd.A, A1 = A + 1;
+    const int n = Hd * A1 + A1;
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    float s = 0.f;
+    for (int c = 0; c < nchunks; ++c) s += part[(size_t)c * n + e];
+    if (e < Hd * A1) {
+        const int i = e / A1, kx = e % A1;
+        if (kx < A) grads[nd.fc2W + (long long)i * A + kx] = s;
+        else grads[nd.fc3W + i] = s;
+    } else {
+        const int kx = e - Hd * A1;
+        if (kx < A) grads[nd.fc2b + kx] = s;
+        else grads[nd.fc3b] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// linear modules backward
+// ---------------------------------------------------------------------------
+// d(flat)[t][k] = sum_{j active} sum_c dh[t][c]*mask_j[t][c] * W_j[k][c]
+__global__ void __launch_bounds__(256)
+lin_dgrad_kernel(const float* __restrict__ dh, const uint8_t* __restrict__ Rl, const float* __restrict__ params,
+                 PnNetDesc nd, const uint32_t* __restrict__ masks, int B, float* __restrict__ dflat) {
+    __shared__ float Ds[32][33];
+    __shared__ float Wt[64][33];
+    const int p = blockIdx.x, k0 = blockIdx.y * 64, b0 = blockIdx.z * 32;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int K = nd.last_lin, Hd = nd.hidden;
+    const uint32_t mask = masks[p * nd.L + nd.L - 1];
+    float acc[2][4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int j = 0; j < nd.M; ++j) {
+        if (!((mask >> j) & 1u)) continue;
+        const float* W = params + nd.linW_base + (long long)j * nd.lin_stride;
+        for (int c0 = 0; c0 < Hd; c0 += 32) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int idx = tid + i * 256, row = idx >> 5, c = idx & 31, b = b0 + row;
+                float val = 0.f;
+                if (b < B && c0 + c < Hd) {
+                    const size_t t = (size_t)p * B + b;
+                    val = Rl[(t * nd.M + j) * Hd + c0 + c] ? dh[t * Hd + c0 + c] : 0.f;
+                }
+                Ds[row][c] = val;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int idx = tid + i * 256, kk = idx >> 5, c = idx & 31;
+                Wt[kk][c] = (k0 + kk < K && c0 + c < Hd) ? W[(size_t)(k0 + kk) * Hd + c0 + c] : 0.f;
+            }
+            __syncthreads();
+#pragma unroll 8
+            for (int c = 0; c < 32; ++c) {
+                const float d0 = Ds[ty * 2][c], d1 = Ds[ty * 2 + 1][c];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float wv = Wt[tx + 16 * q][c];
+                    acc[0][q] = fmaf(d0, wv, acc[0][q]);
+                    acc[1][q] = fmaf(d1, wv, acc[1][q]);
+                }
+            }
+            __syncthreads();
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+        const int b = b0 + ty * 2 + a;
+        if (b >= B) continue;
+        const size_t t = (size_t)p * B + b;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int kg = k0 + tx + 16 * q;
+            if (kg < K) dflat[t * K + kg] = acc[a][q];
+        }
+    }
+}
+
+// dW_lin[j][k][c] = sum over paths using j (ascending) and their transitions of flat[t][k]*dpre_j[t][c]
+__global__ void __launch_bounds__(256)
+lin_wgrad_kernel(const float* __restrict__ X, const float* __restrict__ dh, const uint8_t* __restrict__ Rl,
+                 PnNetDesc nd, const int* __restrict__ list, const int* __restrict__ list_count, int P, int B,
+                 float* __restrict__ grads) {
+    __shared__ __align__(16) float Xs[16][64];
+    __shared__ __align__(16) float Ds[16][64];
+    const int j = blockIdx.x, k0 = blockIdx.y * 64, c0 = blockIdx.z * 64;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int K = nd.last_lin, Hd = nd.hidden, lm = (nd.L - 1) * nd.M + j;
+    const int total = list_count[lm] * B;
+    const int* lst = list + (size_t)lm * P;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    float bacc = 0.f;
+    const bool do_bias = (blockIdx.y == 0) && tid < 64;
+    for (int r0 = 0; r0 < total; r0 += 16) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = tid + i * 256, rr = idx >> 6, cc = idx & 63, row = r0 + rr;
+            float xv = 0.f, dv = 0.f;
+            if (row < total) {
+                const size_t t = (size_t)lst[row / B] * B + (row % B);
+                if (k0 + cc < K) xv = X[t * K + k0 + cc];
+                if (c0 + cc < Hd) dv = Rl[(t * nd.M + j) * Hd + c0 + cc] ? dh[t * Hd + c0 + cc] : 0.f;
+            }
+            Xs[rr][cc] = xv;
+            Ds[rr][cc] = dv;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int rr = 0; rr < 16; ++rr) {
+            const float4 x4 = *reinterpret_cast<const float4*>(&Xs[rr][ty * 4]);
+            const float4 d4 = *reinterpret_cast<const float4*>(&Ds[rr][tx * 4]);
+            const float xa[4] = {x4.x, x4.y, x4.z, x4.w}, da[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(xa[a], da[b], acc[a][b]);
+            if (do_bias) bacc += Ds[rr][tid];
+        }
+        __syncthreads();
+    }
+    float* G = grads + nd.linW_base + (long long)j * nd.lin_stride;
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int kg = k0 + ty * 4 + a;
+        if (kg >= K) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int col = c0 + tx * 4 + b;
+            if (col < Hd) G[(size_t)kg * Hd + col] = acc[a][b];
+        }
+    }
+    if (do_bias && c0 + tid < Hd) G[nd.linb_off + c0 + tid] = bacc;
+}
+
+// ---------------------------------------------------------------------------
+// conv layers backward
+// ---------------------------------------------------------------------------
+// data gradient of conv layer l >= 1 (Cin == 8): one CTA per transition
+__global__ void __launch_bounds__(256)
+conv_dgrad_kernel(const float* __restrict__ dY, const uint8_t* __restrict__ R, const float* __restrict__ params,
+                  PnNetDesc nd, int l, const uint32_t* __restrict__ masks, int B, float* __restrict__ dX) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int t = blockIdx.x, p = t / B;
+    const int IH = nd.IH[l], IW = nd.IW[l], k = nd.k[l], s = nd.s[l], OH = nd.OH[l], OW = nd.OW[l], KK = nd.KK[l];
+    const int npix = OH * OW;
+    const uint32_t mask = masks[p * nd.L + l];
+    const int nact = __popc(mask);
+    float* dYs = reinterpret_cast<float*>(smem_raw);          // [npix*8]
+    float* Ws = dYs + ((npix * PN_F + 3) & ~3);                // [nact][KK*8]
+    uint8_t* Rs = reinterpret_cast<uint8_t*>(Ws + (size_t)nact * KK * PN_F);   // [nact][npix]
+    for (int i = threadIdx.x; i < npix * PN_F; i += blockDim.x) dYs[i] = dY[(size_t)t * npix * PN_F + i];
+    int slot = 0;
+    for (int j = 0; j < nd.M; ++j) {
+        if (!((mask >> j) & 1u)) continue;
+        const float* Wg = params + nd.convW_base[l] + (long long)j * nd.conv_stride[l];
+        for (int i = threadIdx.x; i < KK * PN_F; i += blockDim.x) Ws[(size_t)slot * KK * PN_F + i] = Wg[i];
+        for (int i = threadIdx.x; i < npix; i += blockDim.x) Rs[slot * npix + i] = R[((size_t)t * nd.M + j) * npix + i];
+        ++slot;
+    }
+    __syncthreads();
+    for (int ipix = threadIdx.x; ipix < IH * IW; ipix += blockDim.x) {
+        const int iy = ipix / IW, ix = ipix % IW;
+        float acc[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+        for (int sl = 0; sl < nact; ++sl) {
+            const float* Wsl = Ws + (size_t)sl * KK * PN_F;
+            for (int kh = 0; kh < k; ++kh) {
+                const int ry = iy - kh;
+                if (ry < 0 || (ry % s) != 0) continue;
+                const int oy = ry / s;
+                if (oy >= OH) continue;
+                for (int kw = 0; kw < k; ++kw) {
+                    const int rx = ix - kw;
+                    if (rx < 0 || (rx % s) != 0) continue;
+                    const int ox = rx / s;
+                    if (ox >= OW) continue;
+                    const int opix = oy * OW + ox;
+                    const unsigned bits = Rs[sl * npix + opix];
+                    if (!bits) continue;
+                    float d[8];
+#pragma unroll
+                    for (int co = 0; co < 8; ++co) d[co] = ((bits >> co) & 1u) ? dYs[opix * PN_F + co] : 0.f;
+                    const float4* w4 = reinterpret_cast<const float4*>(Wsl + (size_t)(kh * k + kw) * 8 * PN_F);
+#pragma unroll
+                    for (int ci = 0; ci < 8; ++ci) {
+                        const float4 a = w4[2 * ci], b = w4[2 * ci + 1];
+                        acc[ci] += d[0] * a.x + d[1] * a.y + d[2] * a.z + d[3] * a.w + d[4] * b.x + d[5] * b.y +
+                                   d[6] * b.z + d[7] * b.w;
+                    }
+                }
+            }
+        }
+        float4* o = reinterpret_cast<float4*>(dX + ((size_t)t * IH * IW + ipix) * 8);
+        o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    }
+}
+
+// weight-gradient partials of conv layer l: CTA = (path, chunk of its transitions),
+// thread = one im2col row kk = (kh, kw, ci); the layer input is read through L1.
+template <typename TIn>
+__global__ void __launch_bounds__(1024)
+conv_wgrad_kernel(const TIn* __restrict__ X, float in_scale, const float* __restrict__ dY,
+                  const uint8_t* __restrict__ R, PnNetDesc nd, int l, const uint32_t* __restrict__ masks, int B,
+                  int cs, int nch_alloc, float* __restrict__ part) {
+    extern __shared__ __align__(16) float Dsm[];   // [npix*8]
+    const int p = blockIdx.x, ch = blockIdx.y;
+    const int IH = nd.IH[l], IW = nd.IW[l], Cin = nd.Cin[l], k = nd.k[l], s = nd.s[l];
+    const int OH = nd.OH[l], OW = nd.OW[l], KK = nd.KK[l], npix = OH * OW;
+    const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
+    const int kk = threadIdx.x;
+    const bool valid = kk < KK;
+    const int kh = valid ? kk / (k * Cin) : 0, rem = valid ? kk % (k * Cin) : 0;
+    const int base = kh * IW * Cin + rem;
+    const uint32_t mask = masks[p * nd.L + l];
+    const int stride_part = KK * PN_F + PN_F;
+    for (int j = 0; j < nd.M; ++j) {
+        if (!((mask >> j) & 1u)) continue;
+        float acc[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+        float bacc = 0.f;
+        for (int b = b_lo; b < b_hi; ++b) {
+            const size_t t = (size_t)p * B + b;
+            __syncthreads();
+            for (int i = threadIdx.x; i < npix * PN_F; i += blockDim.x) {
+                const unsigned bits = R[(t * nd.M + j) * npix + (i >> 3)];
+                Dsm[i] = ((bits >> (i & 7)) & 1u) ? dY[t * npix * PN_F + i] : 0.f;
+            }
+            __syncthreads();
+            if (valid) {
+                const TIn* xt = X + t * (size_t)IH * IW * Cin + base;
+                for (int oy = 0; oy < OH; ++oy) {
+                    const TIn* xr = xt + (size_t)oy * s * IW * Cin;
+                    const float4* d4 = reinterpret_cast<const float4*>(Dsm + (size_t)oy * OW * PN_F);
+                    for (int ox = 0; ox < OW; ++ox) {
+                        const float a = to_f(__ldg(xr + ox * s * Cin));
+                        const float4 d0 = d4[2 * ox], d1 = d4[2 * ox + 1];
+                        acc[0] = fmaf(a, d0.x, acc[0]); acc[1] = fmaf(a, d0.y, acc[1]);
+                        acc[2] = fmaf(a, d0.z, acc[2]); acc[3] = fmaf(a, d0.w, acc[3]);
+                        acc[4] = fmaf(a, d1.x, acc[4]); acc[5] = fmaf(a, d1.y, acc[5]);
+                        acc[6] = fmaf(a, d1.z, acc[6]); acc[7] = fmaf(a, d1.w, acc[7]);
+                    }
+                }
+            }
+            if (threadIdx.x < PN_F) {
+                float sb = 0.f;
+                for (int px = 0; px < npix; ++px) sb += Dsm[px * PN_F + threadIdx.x];
+                bacc += sb;
+            }
+        }
+        float* out = part + ((size_t)(p * nch_alloc + ch) * nd.M + j) * stride_part;
+        if (valid) {
+            float4* o = reinterpret_cast<float4*>(out + (size_t)kk * PN_F);
+            o[0] = make_float4(acc[0] * in_scale, acc[1] * in_scale, acc[2] * in_scale, acc[3] * in_scale);
+            o[1] = make_float4(acc[4] * in_scale, acc[5] * in_scale, acc[6] * in_scale, acc[7] * in_scale);
+        }
+        if (threadIdx.x < PN_F) out[KK * PN_F + threadIdx.x] = bacc;
+    }
+}
+
+// fixed-order reduction of the partials over the paths that use module (l, j)
+__global__ void conv_wgrad_reduce_kernel(const float* __restrict__ part, PnNetDesc nd, int l,
+                                         const int* __restrict__ list, const int* __restrict__ list_count, int P,
+                                         int nch_alloc, int nch_active, float* __restrict__ grads) {
+    const int j = blockIdx.x, KK = nd.KK[l];
+    const int n = KK * PN_F + PN_F;
+    const int e = blockIdx.y * blockDim.x + threadIdx.x;
+    if (e >= n) return;
+    const int lm = l * nd.M + j, cnt = list_count[lm];
+    const int* lst = list + (size_t)lm * P;
+    float s = 0.f;
+    for (int i = 0; i < cnt; ++i) {
+        const int p = lst[i];
+        for (int c = 0; c < nch_active; ++c) s += part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
+    }
+    const long long wb = nd.convW_base[l] + (long long)j * nd.conv_stride[l];
+    if (e < KK * PN_F) grads[wb + e] = s;
+    else grads[wb + nd.convb_off[l] + (e - KK * PN_F)] = s;
+}
+
+template <typename K>
+int set_smem(pn_handle* h, K kern, size_t bytes) {
+    if (bytes > 48 * 1024) {
+        PN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    }
+    return PN_OK;
+}
+
+}  // namespace
+
+// ===========================================================================
+// host launchers
+// ===========================================================================
+int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool training, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    const int T = h->P * B;
+    (void)training;
+    for (int l = 0; l < nd.nconv; ++l) {
+        const int rpb = max(1, 128 / nd.OW[l]);
+        const int nbands = (nd.OH[l] + rpb - 1) / rpb;
+        const int in_rows = (min(rpb, nd.OH[l]) - 1) * nd.s[l] + nd.k[l];
+        const size_t wbytes = ((size_t)nd.KK[l] * PN_F + PN_F) * sizeof(float);
+        dim3 grid(T, nbands);
+        if (l == 0 && is_u8) {
+            const size_t sm = wbytes + (size_t)in_rows * nd.IW[l] * nd.Cin[l];
+            if (int rc = set_smem(h, conv_fwd_kernel<uint8_t>, sm)) return rc;
+            conv_fwd_kernel<uint8_t><<<grid, 128, sm, st>>>((const uint8_t*)frames, 1.0f / 255.0f, h->params, nd, l,
+                                                            h->d_masks, B, rpb, h->act[l], h->rmask[l]);
+        } else {
+            const float* in = l == 0 ? (const float*)frames : h->act[l - 1];
+            const size_t sm = wbytes + (size_t)in_rows * nd.IW[l] * nd.Cin[l] * sizeof(float);
+            if (int rc = set_smem(h, conv_fwd_kernel<float>, sm)) return rc;
+            conv_fwd_kernel<float><<<grid, 128, sm, st>>>(in, 1.0f, h->params, nd, l, h->d_masks, B, rpb, h->act[l],
+                                                          h->rmask[l]);
+        }
+        PN_LAUNCH_CHECK(h, "conv_fwd_kernel");
+    }
+    dim3 grid(h->P, (nd.hidden + 63) / 64, (B + 31) / 32);
+    lin_fwd_kernel<<<grid, 256, 0, st>>>(h->act[nd.nconv - 1], h->params, nd, h->d_masks, B, h->hbuf, h->lmask);
+    PN_LAUNCH_CHECK(h, "lin_fwd_kernel");
+    (void)T;
+    return PN_OK;
+}
+
+int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, const float* td, const float* r,
+                    float beta, float* pi, float* v, float* loss, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    const int T = h->P * B;
+    const size_t sm = ((size_t)nd.hidden * nd.A + nd.hidden + 32 + 8 * (size_t)nd.hidden + 8 * 32) * sizeof(float);
+    if (int rc = set_smem(h, head_kernel, sm)) return rc;
+    const int blocks = max(1, min((T + 7) / 8, 148 * 2));
+    head_kernel<<<blocks, 256, sm, st>>>(h->hbuf, h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v,
+                                         h->dzv, h->dh, h->loss_t);
+    PN_LAUNCH_CHECK(h, "head_kernel");
+    if (training && loss) {
+        path_loss_kernel<<<(h->P + 127) / 128, 128, 0, st>>>(h->loss_t, h->P, B, loss);
+        PN_LAUNCH_CHECK(h, "path_loss_kernel");
+    }
+    return PN_OK;
+}
+
+int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    const int T = h->P * B, P = h->P;
+    // heads
+    {
+        const int nchunks = (T + 63) / 64;
+        const int threads = max(32, (max(nd.hidden, nd.A + 1) + 31) / 32 * 32);
+        head_wgrad_partial_kernel<<<nchunks, threads, 0, st>>>(h->hbuf, h->dzv, nd, T, h->head_part);
+        PN_LAUNCH_CHECK(h, "head_wgrad_partial_kernel");
+        const int n = nd.hidden * (nd.A + 1) + nd.A + 1;
+        head_wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, st>>>(h->head_part, nchunks, nd, h->grads);
+        PN_LAUNCH_CHECK(h, "head_wgrad_reduce_kernel");
+    }
+    // linear modules
+    {
+        const int K = nd.last_lin;
+        dim3 g1(P, (K + 63) / 64, (B + 31) / 32);
+        lin_dgrad_kernel<<<g1, 256, 0, st>>>(h->dh, h->lmask, h->params, nd, h->d_masks, B, h->dact[nd.nconv - 1]);
+        PN_LAUNCH_CHECK(h, "lin_dgrad_kernel");
+        dim3 g2(nd.M, (K + 63) / 64, (nd.hidden + 63) / 64);
+        lin_wgrad_kernel<<<g2, 256, 0, st>>>(h->act[nd.nconv - 1], h->dh, h->lmask, nd, h->d_list, h->d_list_count, P,
+                                             B, h->grads);
+        PN_LAUNCH_CHECK(h, "lin_wgrad_kernel");
+    }
+    // conv layers, last to first
+    const int cs = (B + h->nch - 1) / h->nch;
+    const int nch_active = (B + cs - 1) / cs;
+    for (int l = nd.nconv - 1; l >= 0; --l) {
+        const int npix = nd.OH[l] * nd.OW[l];
+        const int threads = (nd.KK[l] + 31) / 32 * 32;
+        const size_t sm = (size_t)npix * PN_F * sizeof(float);
+        dim3 grid(P, nch_active);
+        if (l == 0 && is_u8) {
+            if (int rc = set_smem(h, conv_wgrad_kernel<uint8_t>, sm)) return rc;
+            conv_wgrad_kernel<uint8_t><<<grid, threads, sm, st>>>((const uint8_t*)frames, 1.0f / 255.0f, h->dact[l],
+                                                                  h->rmask[l], nd, l, h->d_masks, B, cs, h->nch,
+                                                                  h->wpart[l]);
+        } else {
+            const float* in = l == 0 ? (const float*)frames : h->act[l - 1];
+            if (int rc = set_smem(h, conv_wgrad_kernel<float>, sm)) return rc;
+            conv_wgrad_kernel<float><<<grid, threads, sm, st>>>(in, 1.0f, h->dact[l], h->rmask[l], nd, l, h->d_masks,
+                                                                B, cs, h->nch, h->wpart[l]);
+        }
+        PN_LAUNCH_CHECK(h, "conv_wgrad_kernel");
+        const int n = nd.KK[l] * PN_F + PN_F;
+        dim3 gr(nd.M, (n + 255) / 256);
+        conv_wgrad_reduce_kernel<<<gr, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
+                                                     nch_active, h->grads);
+        PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
+        if (l > 0) {
+            const size_t smd = (((size_t)npix * PN_F + 3) & ~(size_t)3) * sizeof(float) +
+                               (size_t)nd.M * nd.KK[l] * PN_F * sizeof(float) + (size_t)nd.M * npix;
+            if (int rc = set_smem(h, conv_dgrad_kernel, smd)) return rc;
+            conv_dgrad_kernel<<<T, 256, smd, st>>>(h->dact[l], h->rmask[l], h->params, nd, l, h->d_masks, B,
+                                                   h->dact[l - 1]);
+            PN_LAUNCH_CHECK(h, "conv_dgrad_kernel");
+        }
+    }
+    return PN_OK;
+}

@@ -1,0 +1,270 @@
+"""Population-batched PathNet engine: thin Python owner of the device slabs that
+calls libpathnet_b200.so through ctypes.  PyTorch is plumbing only (device
+memory, streams, torch.distributed for the gradient all-reduce).
+
+The reference evaluates one path per OS process against parameter servers
+(doom_pathnet.py:59-77,177-201); here the population is a tensor dimension and
+each GPU holds a slice of it.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _native as nat
+
+
+@dataclass(frozen=True)
+class PathNetConfig:
+    """Shape of the super-net; defaults = BASELINE configs C1/C2 (L=3, M=10, N=3, 84x84x4)."""
+    L: int = 3
+    M: int = 10
+    N: int = 3
+    H: int = 84
+    W: int = 84
+    C: int = 4
+    kernels: Tuple[int, ...] = (8, 4, 3)       # FLAGS.kernel_num  (doom_pathnet.py:356-357)
+    strides: Tuple[int, ...] = (4, 2, 1)       # FLAGS.stride_size (doom_pathnet.py:358-359)
+    F: int = 8                                  # feature_num (game_ac_network.py:132)
+    hidden: int = 256                           # game_ac_network.py:146
+    A: int = 18                                 # max(ACTION_SIZEZ) (game_ac_network.py:152)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+class PathNetPopulation:
+    """P paths x (up to) B_max transitions on one GPU.
+
+    Owns four fp32 slabs laid out in get_vars() order (game_ac_network.py:239-253):
+    params, rms (init 1.0, rmsprop_applier.py:34-37), optional momentum (init 0), grads.
+    """
+
+    def __init__(self, cfg: PathNetConfig, P: int, B_max: int, device: int = 0, momentum_slot: bool = False):
+        if not torch.cuda.is_available():
+            raise RuntimeError("pathnet_gym_b200 needs a CUDA device (there is no CPU fallback)")
+        self.lib = nat.load()
+        self.cfg, self.P, self.B_max, self.device_index = cfg, int(P), int(B_max), int(device)
+        self.device = torch.device("cuda", self.device_index)
+        pc = nat.PnConfig()
+        pc.L, pc.M, pc.H, pc.W, pc.C, pc.F, pc.hidden, pc.A = cfg.L, cfg.M, cfg.H, cfg.W, cfg.C, cfg.F, cfg.hidden, cfg.A
+        for i in range(cfg.L - 1):
+            pc.kernel[i], pc.stride[i] = cfg.kernels[i], cfg.strides[i]
+        pc.P, pc.B_max, pc.device, pc.flags = self.P, self.B_max, self.device_index, 0
+        h = C.c_void_p()
+        nat.check(self.lib.pn_create(C.byref(pc), C.byref(h)))
+        self._h = h
+        n = self.lib.pn_num_tensors(h)
+        arr = (nat.PnTensorDesc * n)()
+        nat.check(self.lib.pn_tensor_table(h, arr, n), h)
+        self.tensors = [dict(offset=int(d.offset), length=int(d.length), layer=int(d.layer), module=int(d.module),
+                             kind=int(d.kind)) for d in arr]
+        self.shapes = self._shapes()
+        self.slab_floats = int(self.lib.pn_slab_floats(h))
+        self.last_lin = int(self.lib.pn_last_lin(h))
+        with torch.cuda.device(self.device):
+            self.params = torch.zeros(self.slab_floats, dtype=torch.float32, device=self.device)
+            self.ms = torch.ones(self.slab_floats, dtype=torch.float32, device=self.device)
+            self.grads = torch.zeros(self.slab_floats, dtype=torch.float32, device=self.device)
+            self.mom = torch.zeros(self.slab_floats, dtype=torch.float32, device=self.device) if momentum_slot else None
+        nat.check(self.lib.pn_bind_slabs(h, _ptr(self.params), _ptr(self.ms), _ptr(self.mom), _ptr(self.grads)), h)
+        self.masks = None
+        self.frozen = np.zeros(n, dtype=np.uint8)
+
+    # -- lifecycle -----------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize(self.device)
+            self.lib.pn_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # -- slab layout ---------------------------------------------------------
+    def _shapes(self):
+        cfg = self.cfg
+        shp = []
+        for t in self.tensors:
+            k = t["kind"]
+            if k == 0:
+                cin = cfg.C if t["layer"] == 0 else cfg.F
+                ks = cfg.kernels[t["layer"]]
+                shp.append((ks, ks, cin, cfg.F))
+            elif k == 1:
+                shp.append((cfg.F,))
+            elif k == 2:
+                shp.append((t["length"] // cfg.hidden, cfg.hidden))
+            elif k == 3:
+                shp.append((cfg.hidden,))
+            elif k == 4:
+                shp.append((cfg.hidden, cfg.A))
+            elif k == 5:
+                shp.append((cfg.A,))
+            elif k == 6:
+                shp.append((cfg.hidden, 1))
+            else:
+                shp.append((1,))
+        return shp
+
+    def view(self, slab: torch.Tensor, i: int) -> torch.Tensor:
+        t = self.tensors[i]
+        return slab[t["offset"]:t["offset"] + t["length"]].view(self.shapes[i])
+
+    def load(self, slab: torch.Tensor, arrays: Sequence[np.ndarray]):
+        assert len(arrays) == len(self.tensors)
+        host = slab.detach().cpu().clone()      # keeps the alignment gaps as they are
+        for i, a in enumerate(arrays):
+            t = self.tensors[i]
+            a = np.ascontiguousarray(a, dtype=np.float32)
+            assert a.size == t["length"], (i, a.shape, t)
+            host[t["offset"]:t["offset"] + t["length"]] = torch.from_numpy(a.reshape(-1))
+        slab.copy_(host)
+
+    def dump(self, slab: torch.Tensor) -> List[np.ndarray]:
+        host = slab.detach().cpu().numpy()
+        return [host[t["offset"]:t["offset"] + t["length"]].reshape(self.shapes[i]).copy()
+                for i, t in enumerate(self.tensors)]
+
+    def init_params(self, seed: int = 1):
+        """U(-d, d), d = 1/sqrt(fan_in), bias with the weight's d (game_ac_network.py:89-107)."""
+        rng = np.random.Generator(np.random.PCG64(seed))
+        out, d = [], 1.0
+        for t, shp in zip(self.tensors, self.shapes):
+            if t["kind"] == 0:
+                d = 1.0 / math.sqrt(shp[2] * shp[0] * shp[1])
+            elif t["kind"] in (2, 4, 6):
+                d = 1.0 / math.sqrt(shp[0])
+            out.append(rng.uniform(-d, d, size=shp).astype(np.float32))
+        self.load(self.params, out)
+        return out
+
+    # -- genotype / freeze tables -------------------------------------------
+    def set_genotypes(self, masks):
+        """masks [P, L] uint32 EFFECTIVE masks (genotype | fixed path)."""
+        m = np.ascontiguousarray(np.asarray(masks, dtype=np.uint32).reshape(self.P, self.cfg.L))
+        nat.check(self.lib.pn_set_genotypes(self._h, m.ctypes.data_as(C.c_void_p), self._stream()), self._h)
+        self.masks = m
+
+    def set_frozen(self, flags):
+        f = np.ascontiguousarray(np.asarray(flags, dtype=np.uint8).reshape(len(self.tensors)))
+        nat.check(self.lib.pn_set_frozen(self._h, f.ctypes.data_as(C.c_void_p)), self._h)
+        self.frozen = f
+
+    def set_fixed_path(self, fixed_path):
+        """fixed_path [L, M] of 0/1 -> per-tensor frozen flags (game_ac_network.py:236-271)."""
+        fp = np.asarray(fixed_path)
+        fl = np.zeros(len(self.tensors), dtype=np.uint8)
+        for i, t in enumerate(self.tensors):
+            if t["module"] >= 0:
+                row = t["layer"] if t["layer"] < self.cfg.L - 1 else -1
+                fl[i] = 1 if fp[row, t["module"]] == 1.0 else 0
+        self.set_frozen(fl)
+
+    # -- hot path -------------------------------------------------------------
+    def _check_frames(self, frames: torch.Tensor):
+        cfg = self.cfg
+        if frames.dtype not in (torch.uint8, torch.float32):
+            raise TypeError("frames must be uint8 (k means k/255) or float32")
+        if frames.dim() != 5 or frames.shape[0] != self.P or tuple(frames.shape[2:]) != (cfg.H, cfg.W, cfg.C):
+            raise ValueError("frames must be [P=%d, B, %d, %d, %d], got %s" % (self.P, cfg.H, cfg.W, cfg.C, tuple(frames.shape)))
+        if not frames.is_contiguous():
+            raise ValueError("frames must be contiguous")
+        return int(frames.shape[1]), 1 if frames.dtype == torch.uint8 else 0
+
+    def forward(self, frames: torch.Tensor):
+        """pi [P,B,A], v [P,B] for device frames (run_policy_and_value for all paths)."""
+        B, u8 = self._check_frames(frames)
+        pi = torch.empty(self.P, B, self.cfg.A, dtype=torch.float32, device=self.device)
+        v = torch.empty(self.P, B, dtype=torch.float32, device=self.device)
+        nat.check(self.lib.pn_forward(self._h, _ptr(frames), u8, B, _ptr(pi), _ptr(v), self._stream()), self._h)
+        return pi, v
+
+    def train_step(self, frames, actions, td, r, entropy_beta=0.01, want_outputs=False):
+        """forward + A3C loss + backward for every path; grads slab <- sum over local paths."""
+        B, u8 = self._check_frames(frames)
+        for name, t, dt in (("actions", actions, torch.int32), ("td", td, torch.float32), ("r", r, torch.float32)):
+            if t.dtype != dt or tuple(t.shape) != (self.P, B) or not t.is_contiguous() or t.device != frames.device:
+                raise ValueError("%s must be a contiguous %s [P, B] tensor on the frames' device" % (name, dt))
+        loss = torch.empty(self.P, dtype=torch.float32, device=self.device)
+        pi = v = None
+        if want_outputs:
+            pi = torch.empty(self.P, B, self.cfg.A, dtype=torch.float32, device=self.device)
+            v = torch.empty(self.P, B, dtype=torch.float32, device=self.device)
+        nat.check(self.lib.pn_train_step(self._h, _ptr(frames), u8, _ptr(actions), _ptr(td), _ptr(r), B,
+                                         float(entropy_beta), _ptr(loss), _ptr(pi), _ptr(v), self._stream()), self._h)
+        return (loss, pi, v) if want_outputs else loss
+
+    def train_step_host(self, frames, actions, td, r, entropy_beta=0.01, loss_out: Optional[torch.Tensor] = None):
+        """Same, for HOST tensors (pinned is fastest); copies happen inside the C call."""
+        B, u8 = self._check_frames(frames)
+        if loss_out is None:
+            loss_out = torch.empty(self.P, dtype=torch.float32)
+        nat.check(self.lib.pn_train_step_host(self._h, _ptr(frames), u8, _ptr(actions), _ptr(td), _ptr(r), B,
+                                              float(entropy_beta), _ptr(loss_out), self._stream()), self._h)
+        return loss_out
+
+    def allreduce_grads(self):
+        """Sum the shared-module gradient slab over the GPUs that hold population slices."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            dist.all_reduce(self.grads, op=dist.ReduceOp.SUM)
+
+    def apply_gradients(self, lr, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0):
+        """Per-tensor clip_by_norm + RMSProp on the non-frozen tensors (rmsprop_applier.py:79-106)."""
+        nat.check(self.lib.pn_rmsprop_apply(self._h, float(lr), float(decay), float(momentum), float(epsilon),
+                                            float(clip_norm), self._stream()), self._h)
+
+    def reinit_unfrozen(self, backup: torch.Tensor):
+        """Every non-frozen tensor <- backup (doom_pathnet.py:289-293)."""
+        assert backup.dtype == torch.float32 and backup.numel() == self.slab_floats and backup.is_cuda
+        nat.check(self.lib.pn_reinit_unfrozen(self._h, _ptr(backup), self._stream()), self._h)
+
+    @property
+    def workspace_bytes(self) -> int:
+        return int(self.lib.pn_workspace_bytes(self._h))
+
+
+# ---------------------------------------------------------------------------
+# genotype ops on device bitmasks
+# ---------------------------------------------------------------------------
+def geopath_init(n_paths, L, M, N, seed, epoch, path_id0=0, device=0) -> torch.Tensor:
+    lib = nat.load()
+    dev = torch.device("cuda", device)
+    masks = torch.zeros(n_paths, L, dtype=torch.int32, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    nat.check(lib.pn_geopath_init(_ptr(masks), n_paths, path_id0, L, M, N, int(seed), int(epoch), st))
+    return masks
+
+
+def mutate_(masks: torch.Tensor, M, N, seed, epoch, path_id0=0) -> torch.Tensor:
+    lib = nat.load()
+    assert masks.is_cuda and masks.dtype == torch.int32 and masks.is_contiguous()
+    st = C.c_void_p(torch.cuda.current_stream(masks.device).cuda_stream)
+    nat.check(lib.pn_mutate(_ptr(masks), masks.shape[0], path_id0, masks.shape[1], M, N, int(seed), int(epoch), st))
+    return masks
+
+
+def tournament_(genotypes: torch.Tensor, scores: torch.Tensor, fixed: torch.Tensor, M, N, Bcand, n_groups, seed, epoch):
+    """In-place controller pass; returns (effective masks, winners)."""
+    lib = nat.load()
+    P, L = genotypes.shape
+    assert genotypes.dtype == torch.int32 and scores.dtype == torch.float32 and fixed.dtype == torch.int32
+    eff = torch.empty_like(genotypes)
+    winners = torch.full((max(n_groups, 1),), -1, dtype=torch.int32, device=genotypes.device)
+    st = C.c_void_p(torch.cuda.current_stream(genotypes.device).cuda_stream)
+    nat.check(lib.pn_tournament(_ptr(genotypes), _ptr(scores), _ptr(fixed), _ptr(eff), _ptr(winners), P, L, M, N,
+                                Bcand, n_groups, int(seed), int(epoch), st))
+    return eff, winners[:n_groups]

@@ -1,0 +1,374 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes), against the oracle
+and the committed golden fixtures.  Nothing here reads /root/reference.
+
+Tolerances: integer / genotype work is bit-exact.  Floating point follows north_star:
+1e-3 relative, applied per tensor as max|x - ref| / max|ref| against the fp64 truth
+(REL_TOL below); the fp32 CUDA-core kernels are expected to land near 1e-6.
+"""
+import json
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from oracle import pathnet_oracle as po          # the checker, never the thing measured
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-3
+_report = {}
+
+
+def _note(key, val):
+    _report[key] = float(val)
+    out = os.path.join(hp.GOLDEN, "..", "..", "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_report.json"), "w") as f:
+            json.dump(_report, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
+@pytest.fixture(scope="module")
+def eng_mod(native_lib):
+    from pathnet_gym_b200 import population
+    assert torch.cuda.is_available(), "the gpu-marked tests need a CUDA device"
+    return population
+
+
+def make_pop(eng_mod, cfg, P, B, params=None, masks=None, **kw):
+    pop = eng_mod.PathNetPopulation(hp.to_engine_cfg(cfg), P, B, **kw)
+    if params is not None:
+        pop.load(pop.params, params)
+    if masks is not None:
+        pop.set_genotypes(masks)
+    return pop
+
+
+def dev(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+# ---------------------------------------------------------------------------
+# genotype ops: bit-exact
+# ---------------------------------------------------------------------------
+def test_genotype_golden_bit_exact(eng_mod):
+    g = np.load(os.path.join(hp.GOLDEN, "genotype_golden.npz"))
+    for seed, row in zip(g["seeds"], g["rows"]):
+        L, M, N, epoch, pid = [int(x) for x in row[:5]]
+        m = eng_mod.geopath_init(1, L, M, N, int(seed), epoch, path_id0=pid)
+        assert np.array_equal(m.cpu().numpy().view(np.uint32)[0], row[5:5 + L].astype(np.uint32))
+        eng_mod.mutate_(m, M, N, int(seed), epoch + 1000, path_id0=pid)
+        assert np.array_equal(m.cpu().numpy().view(np.uint32)[0], row[13:13 + L].astype(np.uint32))
+        eng_mod.mutate_(m, M, N, int(seed), epoch + 2000, path_id0=pid)
+        assert np.array_equal(m.cpu().numpy().view(np.uint32)[0], row[21:21 + L].astype(np.uint32))
+
+
+@pytest.mark.parametrize("L,M,N,P", [(3, 10, 3, 512), (4, 10, 4, 256), (5, 32, 7, 97)])
+def test_genotype_population_matches_oracle(eng_mod, L, M, N, P):
+    seed = 0xABCDEF0123
+    m = eng_mod.geopath_init(P, L, M, N, seed, 4, path_id0=3)
+    ref = np.stack([po.get_geopath_masks(L, M, N, seed, 4, 3 + p) for p in range(P)])
+    assert np.array_equal(m.cpu().numpy().view(np.uint32), ref)
+    eng_mod.mutate_(m, M, N, seed, 9, path_id0=3)
+    ref2 = np.stack([po.mutate_masks(ref[p], L, M, N, seed, 9, 3 + p) for p in range(P)])
+    assert np.array_equal(m.cpu().numpy().view(np.uint32), ref2)
+
+
+@pytest.mark.parametrize("P,B,groups", [(512, 3, 170), (64, 3, 1), (10, 4, 2), (256, 2, 128)])
+def test_tournament_matches_oracle(eng_mod, P, B, groups):
+    L, M, N, seed = 4, 10, 4, 77
+    rng = np.random.default_rng(P)
+    geno = np.stack([po.get_geopath_masks(L, M, N, seed, 0, p) for p in range(P)])
+    scores = rng.integers(-5, 5, size=P).astype(np.float32)           # many ties
+    scores[rng.integers(0, P, size=max(1, P // 16))] = -1000.0        # some paths have not reported
+    fixed = np.asarray([0x3, 0x0, 0x210, 0x1], dtype=np.uint32)
+    for epoch in (1, 2, 3):
+        g_ref, eff_ref, sc_ref, win_ref = po.tournament(geno, scores, fixed, L, M, N, B, groups, seed, epoch)
+        gd, sd, fd = dev(geno.view(np.int32)), dev(scores), dev(fixed.view(np.int32))
+        eff, win = eng_mod.tournament_(gd, sd, fd, M, N, B, groups, seed, epoch)
+        assert np.array_equal(gd.cpu().numpy().view(np.uint32), g_ref)
+        assert np.array_equal(eff.cpu().numpy().view(np.uint32), eff_ref)
+        assert np.array_equal(sd.cpu().numpy(), sc_ref)
+        assert np.array_equal(win.cpu().numpy(), win_ref)
+        geno, scores = g_ref, np.where(sc_ref == -1000.0, rng.integers(-5, 5, size=P), sc_ref).astype(np.float32)
+
+
+# ---------------------------------------------------------------------------
+# forward / loss / backward vs golden (fp64 truth)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["float_golden_tiny.npz", "float_golden_tiny4.npz"])
+@pytest.mark.parametrize("as_float", [False, True])
+def test_train_step_matches_golden(eng_mod, name, as_float):
+    g = np.load(os.path.join(hp.GOLDEN, name))
+    cfg = hp.cfg_from_golden(g["cfg"])
+    P, B = g["frames"].shape[:2]
+    params = po.init_params(cfg, 1)
+    pop = make_pop(eng_mod, cfg, P, B, params, g["masks"])
+    frames = dev(po.frames_to_float(g["frames"])) if as_float else dev(g["frames"])
+    # acting forward
+    pi, v = pop.forward(frames)
+    e_pi, e_v = hp.rel_err(pi.cpu().numpy(), g["pi"]), hp.rel_err(v.cpu().numpy(), g["v"])
+    assert e_pi < REL_TOL and e_v < REL_TOL
+    loss, pi2, v2 = pop.train_step(frames, dev(g["actions"]), dev(g["td"]), dev(g["r"]), 0.01, want_outputs=True)
+    assert torch.equal(pi, pi2) and torch.equal(v, v2)
+    e_loss = hp.rel_err(loss.cpu().numpy(), g["loss"])
+    assert e_loss < REL_TOL
+    got = pop.dump(pop.grads)
+    worst = 0.0
+    for a, b, t in zip(got, hp.split_flat(cfg, g["grads"]), po.tensor_table(cfg)):
+        e = hp.rel_err(a, b)
+        worst = max(worst, e)
+        assert e < REL_TOL, (t["name"], e)
+    _note("%s%s.pi" % (name, ".f32" if as_float else ".u8"), e_pi)
+    _note("%s%s.grad_worst" % (name, ".f32" if as_float else ".u8"), worst)
+    # update with module 0 of every layer frozen; tiny4's td is scaled so the clip binds
+    pop.set_frozen(g["frozen"])
+    before_p, before_s = pop.dump(pop.params), pop.dump(pop.ms)
+    pop.apply_gradients(float(g["lr"]))
+    after_p, after_s = pop.dump(pop.params), pop.dump(pop.ms)
+    refp, refs = hp.split_flat(cfg, g["params_after"]), hp.split_flat(cfg, g["ms_after"])
+    for i, t in enumerate(po.tensor_table(cfg)):
+        if g["frozen"][i]:
+            assert np.array_equal(after_p[i], before_p[i]) and np.array_equal(after_s[i], before_s[i]), t["name"]
+        else:
+            # compare the UPDATE (delta), which is what the kernel computes, and the result
+            dref = refp[i] - np.asarray(params[i], dtype=np.float64)
+            dgot = after_p[i].astype(np.float64) - before_p[i].astype(np.float64)
+            assert np.max(np.abs(dgot - dref)) <= REL_TOL * max(np.max(np.abs(dref)), 1e-12) + 1e-9, t["name"]
+            assert hp.rel_err(after_p[i], refp[i]) < REL_TOL
+            assert hp.rel_err(after_s[i], refs[i]) < REL_TOL, t["name"]
+    pop.close()
+
+
+def test_c1_matches_golden(eng_mod):
+    """BASELINE config C1: L=3, M=10, N=3, 84x84x4, one path, B = LOCAL_T_MAX = 20."""
+    g = np.load(os.path.join(hp.GOLDEN, "float_golden_c1.npz"))
+    cfg = hp.cfg_from_golden(g["cfg"])
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, 1, 20, 1234)
+    assert np.uint32(zlib.crc32(frames.tobytes())) == g["frames_crc"]
+    params = po.init_params(cfg, 1)
+    pop = make_pop(eng_mod, cfg, 1, 20, params, masks)
+    # slab layout == oracle tensor table == SURVEY parameter count
+    assert sum(t["length"] for t in pop.tensors) == 1697203
+    loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
+    assert hp.rel_err(pi.cpu().numpy(), g["pi"]) < REL_TOL
+    assert hp.rel_err(v.cpu().numpy(), g["v"]) < REL_TOL
+    assert hp.rel_err(loss.cpu().numpy(), g["loss"]) < REL_TOL
+    got = pop.dump(pop.grads)
+    assert hp.rel_err(np.concatenate([x.ravel()[::97] for x in got]), g["grads_sample"]) < REL_TOL
+    norms = np.asarray([np.sqrt(np.sum(x.astype(np.float64) ** 2)) for x in got])
+    assert np.max(np.abs(norms - g["grad_norms"])) < REL_TOL * np.max(g["grad_norms"])
+    _note("c1.grad_sample", hp.rel_err(np.concatenate([x.ravel()[::97] for x in got]), g["grads_sample"]))
+    pop.set_frozen(g["frozen"])
+    pop.apply_gradients(float(g["lr"]))
+    assert hp.rel_err(np.concatenate([x.ravel()[::97] for x in pop.dump(pop.params)]), g["params_after_sample"]) < REL_TOL
+    assert hp.rel_err(np.concatenate([x.ravel()[::97] for x in pop.dump(pop.ms)]), g["ms_after_sample"]) < REL_TOL
+    pop.close()
+
+
+# ---------------------------------------------------------------------------
+# vs the oracle on fresh seeded inputs, edge cases
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("cfg,P,B", [(hp.TINY, 5, 1), (hp.TINY, 2, 33), (hp.TINY4, 3, 20), (hp.C3, 2, 3)])
+def test_population_vs_oracle(eng_mod, cfg, P, B):
+    params = po.init_params(cfg, 11)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, P, B, 99)
+    full = (1 << cfg.M) - 1
+    masks = masks.copy()
+    masks[0, :] = full                       # every module on (mutation can add modules)
+    if P > 1:
+        masks[1, 0] = 1 << (cfg.M - 1)       # single module in a layer
+    if P > 2:
+        masks[2, cfg.L - 1] = 0              # no module at all in the last layer -> h == 0
+    pi_r, v_r, loss_r, G = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy")
+    pop = make_pop(eng_mod, cfg, P, B, params, masks)
+    loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
+    assert hp.rel_err(pi.cpu().numpy(), pi_r) < REL_TOL
+    assert hp.rel_err(v.cpu().numpy(), v_r) < REL_TOL
+    assert hp.rel_err(loss.cpu().numpy(), loss_r) < REL_TOL
+    for a, b, t in zip(pop.dump(pop.grads), G, po.tensor_table(cfg)):
+        assert hp.rel_err(a, b) < REL_TOL, t["name"]
+    pop.close()
+
+
+def test_pi_underflow_case(eng_mod):
+    cfg = hp.TINY
+    params = po.init_params(cfg, 3)
+    names = [t["name"] for t in po.tensor_table(cfg)]
+    params[names.index("b_fc2")] = np.asarray([200.0, 0, 0, 0, -200.0], dtype=np.float32)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, 1, 3, 5)
+    actions[0, 0] = 4                         # the action whose probability underflows
+    pi_r, v_r, loss_r, G = po.population_step(cfg, params, frames, masks, actions, td, r)
+    pop = make_pop(eng_mod, cfg, 1, 3, params, masks)
+    loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
+    assert float(pi.min()) < 1e-20 and torch.isfinite(loss).all()
+    assert hp.rel_err(loss.cpu().numpy(), loss_r) < REL_TOL
+    for a, b, t in zip(pop.dump(pop.grads), G, po.tensor_table(cfg)):
+        assert np.all(np.isfinite(a)) and hp.rel_err(a, b) < REL_TOL, t["name"]
+    pop.close()
+
+
+def test_rmsprop_semantics(eng_mod):
+    """inactive tensors decay ms with var unchanged; frozen untouched; clip binds per tensor; momentum slot."""
+    cfg = hp.TINY
+    params = po.init_params(cfg, 2)
+    pop = make_pop(eng_mod, cfg, 1, 1, params, np.zeros((1, cfg.L), np.uint32), momentum_slot=True)
+    tt = po.tensor_table(cfg)
+    rng = np.random.default_rng(0)
+    grads = [rng.normal(size=t["shape"]).astype(np.float32) * (50.0 if i % 3 == 0 else 0.01) for i, t in enumerate(tt)]
+    grads[2] = np.zeros_like(grads[2])                    # merely inactive: zero gradient
+    frozen = np.zeros(len(tt), np.uint8)
+    frozen[4] = frozen[5] = 1
+    pop.load(pop.grads, grads)
+    pop.set_frozen(frozen)
+    ms0 = [np.ones(t["shape"], np.float32) for t in tt]
+    mom0 = [np.zeros(t["shape"], np.float32) for t in tt]
+    P1, S1, Q1 = po.apply_gradients(params, ms0, mom0, grads, frozen, 7e-4, 0.99, 0.9, 0.1, 40.0)
+    pop.apply_gradients(7e-4, 0.99, 0.9, 0.1, 40.0)
+    P2, S2, Q2 = po.apply_gradients(P1, S1, Q1, grads, frozen, 5e-4, 0.99, 0.9, 0.1, 40.0)
+    pop.apply_gradients(5e-4, 0.99, 0.9, 0.1, 40.0)
+    gp, gs, gq = pop.dump(pop.params), pop.dump(pop.ms), pop.dump(pop.mom)
+    for i, t in enumerate(tt):
+        assert np.allclose(gp[i], P2[i], rtol=1e-5, atol=1e-7), t["name"]
+        assert np.allclose(gs[i], S2[i], rtol=1e-5, atol=1e-7), t["name"]
+        assert np.allclose(gq[i], Q2[i], rtol=1e-5, atol=1e-8), t["name"]
+    assert np.array_equal(gp[2], params[2]) and np.allclose(gs[2], 0.99 * 0.99, rtol=1e-6)
+    assert np.array_equal(gp[4], params[4]) and np.array_equal(gs[4], ms0[4])
+    # gaps between tensors are never written
+    flat = pop.ms.cpu().numpy()
+    used = np.zeros(pop.slab_floats, bool)
+    for t in pop.tensors:
+        used[t["offset"]:t["offset"] + t["length"]] = True
+    assert np.all(flat[~used] == 1.0)
+    pop.close()
+
+
+def test_reinit_unfrozen_and_fixed_path(eng_mod):
+    cfg = hp.TINY
+    params = po.init_params(cfg, 2)
+    pop = make_pop(eng_mod, cfg, 1, 1, params, np.zeros((1, cfg.L), np.uint32))
+    backup = pop.params.clone()
+    pop.params.mul_(3.0)
+    fixed = np.zeros((cfg.L, cfg.M))
+    fixed[0, 1] = fixed[2, 3] = 1.0
+    pop.set_fixed_path(fixed)
+    assert np.array_equal(pop.frozen, po.frozen_flags(cfg, fixed))
+    pop.reinit_unfrozen(backup)
+    got = pop.dump(pop.params)
+    for i, t in enumerate(po.tensor_table(cfg)):
+        if pop.frozen[i]:
+            assert np.array_equal(got[i], params[i] * np.float32(3.0)), t["name"]
+        else:
+            assert np.array_equal(got[i], params[i]), t["name"]       # heads are re-initialised too
+    pop.close()
+
+
+def test_host_entry_point_equals_device_entry_point(eng_mod):
+    cfg = hp.TINY4
+    params = po.init_params(cfg, 4)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, 3, 7, 42)
+    pop = make_pop(eng_mod, cfg, 3, 8, params, masks)
+    loss_d = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01)
+    g_d = pop.grads.clone()
+    pop.grads.zero_()
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    loss_h = pop.train_step_host(pin(frames), pin(actions), pin(td), pin(r), 0.01)
+    assert torch.equal(loss_h, loss_d.cpu()) and torch.equal(pop.grads, g_d)
+    pop.close()
+
+
+def test_error_paths(eng_mod):
+    from pathnet_gym_b200 import PathNetError
+    cfg = hp.TINY
+    pop = eng_mod.PathNetPopulation(hp.to_engine_cfg(cfg), 2, 4)
+    fr = torch.zeros(2, 4, cfg.H, cfg.W, cfg.C, dtype=torch.uint8, device="cuda")
+    with pytest.raises(PathNetError):              # genotypes not set
+        pop.forward(fr)
+    with pytest.raises(PathNetError):              # bits >= M
+        pop.set_genotypes(np.full((2, cfg.L), 1 << cfg.M, np.uint32))
+    pop.set_genotypes(np.ones((2, cfg.L), np.uint32))
+    with pytest.raises(PathNetError):              # B > B_max
+        pop.forward(torch.zeros(2, 5, cfg.H, cfg.W, cfg.C, dtype=torch.uint8, device="cuda"))
+    with pytest.raises(ValueError):
+        pop.forward(fr[:, :, :-1])
+    pop.close()
+
+
+# ---------------------------------------------------------------------------
+# BASELINE.json's full sizes: size-independent properties
+# ---------------------------------------------------------------------------
+def test_c2_full_size_properties(eng_mod):
+    """C2: 64 paths x 32 transitions.  (1) a path's outputs do not depend on its neighbours;
+    (2) the population gradient is the sum of the single-path gradients; (3) gathered == dense-gated:
+    enabling extra modules whose weights are zero changes nothing; (4) frozen tensors are bit-identical
+    after the update and inactive ones only decay ms."""
+    cfg, P, B = hp.C1, 64, 32
+    params = po.init_params(cfg, 1)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, P, B, 2024)
+    pop = make_pop(eng_mod, cfg, P, B, params, masks)
+    fd, ad, tdd, rd = dev(frames), dev(actions), dev(td), dev(r)
+    loss, pi, v = pop.train_step(fd, ad, tdd, rd, 0.01, want_outputs=True)
+    G = pop.grads.clone()
+    assert torch.isfinite(G).all() and torch.isfinite(pi).all()
+    assert torch.allclose(pi.sum(-1), torch.ones_like(pi.sum(-1)), atol=1e-5)
+    # (1)+(2): three single-path populations
+    one = make_pop(eng_mod, cfg, 1, B, params)
+    acc = torch.zeros_like(G)
+    for p in (0, 17, 63):
+        one.set_genotypes(masks[p:p + 1])
+        l1, pi1, v1 = one.train_step(fd[p:p + 1].contiguous(), ad[p:p + 1].contiguous(), tdd[p:p + 1].contiguous(),
+                                     rd[p:p + 1].contiguous(), 0.01, want_outputs=True)
+        assert torch.equal(pi1[0], pi[p]) and torch.equal(v1[0], v[p]) and torch.equal(l1[0], loss[p])
+        acc += one.grads
+    sub = make_pop(eng_mod, cfg, 3, B, params, masks[[0, 17, 63]])
+    idx = torch.tensor([0, 17, 63], device="cuda")
+    sub.train_step(fd[idx].contiguous(), ad[idx].contiguous(), tdd[idx].contiguous(), rd[idx].contiguous(), 0.01)
+    assert hp.rel_err(sub.grads.cpu().numpy(), acc.cpu().numpy()) < 1e-5
+    # oracle check of one full-size path (fp32 torch CPU finishes in seconds)
+    pi_r, v_r, loss_r, G_r = po.population_step(cfg, params, frames[17:18], masks[17:18], actions[17:18], td[17:18],
+                                                r[17:18], dtype="float64")
+    assert hp.rel_err(pi[17].cpu().numpy(), pi_r[0]) < REL_TOL and hp.rel_err(loss[17:18].cpu().numpy(), loss_r) < REL_TOL
+    one.set_genotypes(masks[17:18])
+    one.train_step(fd[17:18].contiguous(), ad[17:18].contiguous(), tdd[17:18].contiguous(), rd[17:18].contiguous(), 0.01)
+    for a, b, t in zip(one.dump(one.grads), G_r, po.tensor_table(cfg)):
+        assert hp.rel_err(a, b) < REL_TOL, t["name"]
+    # (3) zero-weight modules switched on change nothing in pi / v
+    used = np.bitwise_or.reduce(masks, axis=0)
+    pz = [x.copy() for x in params]
+    tt = po.tensor_table(cfg)
+    for i, t in enumerate(tt):
+        if t["module"] >= 0 and not (int(used[t["layer"]]) >> t["module"]) & 1:
+            pz[i][...] = 0
+    free = [[j for j in range(cfg.M) if not (int(used[l]) >> j) & 1] for l in range(cfg.L)]
+    if all(len(f) > 0 for f in free):
+        pop.load(pop.params, pz)
+        m2 = masks.copy()
+        for l in range(cfg.L):
+            m2[:, l] |= np.uint32(1 << free[l][0])
+        pop.set_genotypes(m2)
+        pi_b, v_b = pop.forward(fd)
+        assert torch.equal(pi_b, pi) and torch.equal(v_b, v)
+        pop.load(pop.params, params)
+        pop.set_genotypes(masks)
+    # (4) update: freeze path 0's modules
+    fixed = po.gates_from_masks(cfg, masks[0])
+    pop.set_fixed_path(fixed)
+    pop.grads.copy_(G)
+    p0, s0 = pop.params.clone(), pop.ms.clone()
+    pop.apply_gradients(7.0016e-4)
+    for i, t in enumerate(pop.tensors):
+        sl = slice(t["offset"], t["offset"] + t["length"])
+        if pop.frozen[i]:
+            assert torch.equal(pop.params[sl], p0[sl]) and torch.equal(pop.ms[sl], s0[sl])
+        elif float(G[sl].abs().max()) == 0.0:
+            assert torch.equal(pop.params[sl], p0[sl]) and torch.allclose(pop.ms[sl], s0[sl] * 0.99, rtol=1e-6)
+        else:
+            assert not torch.equal(pop.params[sl], p0[sl])
+    for q in (pop, one, sub):
+        q.close()
