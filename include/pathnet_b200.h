@@ -168,6 +168,24 @@ PN_API int pn_rmsprop_apply(pn_handle* h, float lr, float decay, float momentum,
  * slots are not reset (as in the reference). */
 PN_API int pn_reinit_unfrozen(pn_handle* h, const float* backup_params_dev, void* stream);
 
+/* ---- measurement support (no counterpart in the reference) ------------- */
+
+/* Kernels launched through this handle since pn_create. */
+PN_API int64_t pn_launch_count(const pn_handle* h);
+
+typedef struct pn_profile_entry {
+    char name[40];
+    float total_ms;         /* summed CUDA-event time of the recorded launches */
+    int32_t launches;       /* launches the sum covers (<= 64 most recent)     */
+} pn_profile_entry;
+
+/* When on, every kernel launch is bracketed by cudaEventRecord on the launch
+ * stream.  Resets the counters. */
+PN_API int pn_profile_enable(pn_handle* h, int on);
+/* Synchronises the device; returns the number of entries written (kernels
+ * that ran at least once). */
+PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int capacity);
+
 /* ---- genotype ops (no handle needed) ----------------------------------- */
 /* Counter-based RNG: Philox4x32-10, key = seed, counter =
  * (epoch, path_id, position, domain<<24 | slot); u = (x>>11) * 2^-53. */

@@ -29,6 +29,10 @@ class PnTensorDesc(C.Structure):
                 ("kind", C.c_int32), ("reserved", C.c_int32)]
 
 
+class PnProfileEntry(C.Structure):
+    _fields_ = [("name", C.c_char * 40), ("total_ms", C.c_float), ("launches", C.c_int32)]
+
+
 class PathNetError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__("libpathnet_b200 error %d: %s" % (code, msg))
@@ -48,6 +52,9 @@ SIGNATURES = {
     "pn_tensor_table": (_i, [_vp, C.POINTER(PnTensorDesc), _i]),
     "pn_last_lin": (_i, [_vp]),
     "pn_workspace_bytes": (C.c_int64, [_vp]),
+    "pn_launch_count": (C.c_int64, [_vp]),
+    "pn_profile_enable": (_i, [_vp, _i]),
+    "pn_profile_read": (_i, [_vp, C.POINTER(PnProfileEntry), _i]),
     "pn_bind_slabs": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "pn_set_genotypes": (_i, [_vp, _vp, _vp]),
     "pn_set_frozen": (_i, [_vp, _vp]),

@@ -196,6 +196,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     cudaFree(h->d_frozen); cudaFree(h->d_chunks); cudaFree(h->d_tensor_chunk0); cudaFree(h->d_tensor_nchunks);
     cudaFree(h->d_chunk_ss); cudaFree(h->st_frames); cudaFree(h->st_actions); cudaFree(h->st_td);
     cudaFree(h->st_r); cudaFree(h->st_loss);
+    for (auto& e : h->prof.ev) cudaEventDestroy(e);
     delete h;
 }
 
@@ -204,6 +205,56 @@ extern "C" PN_API int64_t pn_slab_floats(const pn_handle* h) { return h ? h->sla
 extern "C" PN_API int pn_num_tensors(const pn_handle* h) { return h ? (int)h->tensors.size() : 0; }
 extern "C" PN_API int pn_last_lin(const pn_handle* h) { return h ? h->nd.last_lin : 0; }
 extern "C" PN_API int64_t pn_workspace_bytes(const pn_handle* h) { return h ? h->workspace_bytes : 0; }
+
+extern "C" PN_API int64_t pn_launch_count(const pn_handle* h) { return h ? h->launches : 0; }
+
+extern "C" PN_API int pn_profile_enable(pn_handle* h, int on) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "null handle");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    if (on && h->prof.ev.empty()) {
+        h->prof.ev.resize((size_t)PN_PROF_NSLOTS * PN_PROF_RING * 2);
+        for (auto& e : h->prof.ev) PN_CUDA(h, cudaEventCreate(&e));
+    }
+    for (int& c : h->prof.count) c = 0;
+    h->prof.on = on != 0;
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int capacity) {
+    if (!h || !out) return pn_fail_global(PN_ERR_INVALID, "pn_profile_read: null argument");
+    if (h->prof.ev.empty()) return 0;
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    PN_CUDA(h, cudaDeviceSynchronize());
+    int n = 0;
+    for (int slot = 0; slot < PN_PROF_NSLOTS; ++slot) {
+        const int cnt = std::min(h->prof.count[slot], (int)PN_PROF_RING);
+        if (cnt == 0) continue;
+        if (n >= capacity) return pn_fail(h, PN_ERR_INVALID, "pn_profile_read: capacity %d too small", capacity);
+        float total = 0.f;
+        for (int i = 0; i < cnt; ++i) {
+            float ms = 0.f;
+            PN_CUDA(h, cudaEventElapsedTime(&ms, h->prof.ev[((size_t)slot * PN_PROF_RING + i) * 2],
+                                            h->prof.ev[((size_t)slot * PN_PROF_RING + i) * 2 + 1]));
+            total += ms;
+        }
+        const char* base; int layer = -1;
+        if (slot < PN_PROF_CONV_WGRAD) { base = "conv_fwd"; layer = slot - PN_PROF_CONV_FWD; }
+        else if (slot < PN_PROF_CONV_WGRAD_REDUCE) { base = "conv_wgrad"; layer = slot - PN_PROF_CONV_WGRAD; }
+        else if (slot < PN_PROF_CONV_DGRAD) { base = "conv_wgrad_reduce"; layer = slot - PN_PROF_CONV_WGRAD_REDUCE; }
+        else if (slot < PN_PROF_LIN_FWD) { base = "conv_dgrad"; layer = slot - PN_PROF_CONV_DGRAD; }
+        else {
+            static const char* names[] = {"lin_fwd", "head_loss", "head_wgrad", "lin_dgrad", "lin_wgrad",
+                                          "rms_sumsq", "rms_update"};
+            base = names[slot - PN_PROF_LIN_FWD];
+        }
+        if (layer >= 0) snprintf(out[n].name, sizeof(out[n].name), "%s_l%d", base, layer);
+        else snprintf(out[n].name, sizeof(out[n].name), "%s", base);
+        out[n].total_ms = total;
+        out[n].launches = cnt;
+        ++n;
+    }
+    return n;
+}
 
 extern "C" PN_API int pn_tensor_table(const pn_handle* h, pn_tensor_desc* out, int capacity) {
     if (!h || !out) return pn_fail_global(PN_ERR_INVALID, "pn_tensor_table: null argument");

@@ -24,6 +24,28 @@ struct PnNetDesc {        // passed by value to kernels
 
 struct PnRmsChunk { int tensor; int len; long long off; };
 
+// per-kernel CUDA-event timing (pn_profile_enable / pn_profile_read)
+enum PnProfSlot {
+    PN_PROF_CONV_FWD = 0,                              // + layer
+    PN_PROF_CONV_WGRAD = PN_MAX_LAYERS,                // + layer
+    PN_PROF_CONV_WGRAD_REDUCE = 2 * PN_MAX_LAYERS,     // + layer
+    PN_PROF_CONV_DGRAD = 3 * PN_MAX_LAYERS,            // + layer
+    PN_PROF_LIN_FWD = 4 * PN_MAX_LAYERS,
+    PN_PROF_HEAD,
+    PN_PROF_HEAD_WGRAD,
+    PN_PROF_LIN_DGRAD,
+    PN_PROF_LIN_WGRAD,
+    PN_PROF_RMS_SUMSQ,
+    PN_PROF_RMS_UPDATE,
+    PN_PROF_NSLOTS
+};
+#define PN_PROF_RING 64
+struct PnProf {
+    bool on = false;
+    std::vector<cudaEvent_t> ev;      // [slot][ring][2], created lazily
+    int count[PN_PROF_NSLOTS] = {};
+};
+
 struct pn_handle {
     pn_config cfg{};
     PnNetDesc nd{};
@@ -64,7 +86,22 @@ struct pn_handle {
     void* st_frames = nullptr; size_t st_frames_bytes = 0;
     int32_t* st_actions = nullptr; float* st_td = nullptr; float* st_r = nullptr; float* st_loss = nullptr;
     long long workspace_bytes = 0;
+    long long launches = 0;             // kernels launched through this handle
+    PnProf prof;
     std::string err;
+};
+
+struct PnProfScope {                    // brackets one kernel launch with events when profiling is on
+    pn_handle* h; int slot; cudaStream_t st;
+    PnProfScope(pn_handle* h_, int slot_, cudaStream_t st_) : h(h_), slot(slot_), st(st_) {
+        if (h->prof.on) cudaEventRecord(h->prof.ev[((size_t)slot * PN_PROF_RING + h->prof.count[slot] % PN_PROF_RING) * 2], st);
+    }
+    ~PnProfScope() {
+        if (h->prof.on) {
+            cudaEventRecord(h->prof.ev[((size_t)slot * PN_PROF_RING + h->prof.count[slot] % PN_PROF_RING) * 2 + 1], st);
+            ++h->prof.count[slot];
+        }
+    }
 };
 
 int pn_fail(pn_handle* h, int code, const char* fmt, ...);
@@ -80,6 +117,7 @@ int pn_fail_global(int code, const char* fmt, ...);
 
 #define PN_LAUNCH_CHECK(h, name)                                                              \
     do {                                                                                      \
+        ++(h)->launches;                                                                      \
         cudaError_t e__ = cudaGetLastError();                                                 \
         if (e__ != cudaSuccess)                                                               \
             return pn_fail((h), PN_ERR_CUDA, "launch of %s failed: %s", name,                 \

@@ -611,6 +611,7 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
         const int in_rows = (min(rpb, nd.OH[l]) - 1) * nd.s[l] + nd.k[l];
         const size_t wbytes = ((size_t)nd.KK[l] * PN_F + PN_F) * sizeof(float);
         dim3 grid(T, nbands);
+        PnProfScope prof(h, PN_PROF_CONV_FWD + l, st);
         if (l == 0 && is_u8) {
             const size_t sm = wbytes + (size_t)in_rows * nd.IW[l] * nd.Cin[l];
             if (int rc = set_smem(h, conv_fwd_kernel<uint8_t>, sm)) return rc;
@@ -626,7 +627,10 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
         PN_LAUNCH_CHECK(h, "conv_fwd_kernel");
     }
     dim3 grid(h->P, (nd.hidden + 63) / 64, (B + 31) / 32);
-    lin_fwd_kernel<<<grid, 256, 0, st>>>(h->act[nd.nconv - 1], h->params, nd, h->d_masks, B, h->hbuf, h->lmask);
+    {
+        PnProfScope prof(h, PN_PROF_LIN_FWD, st);
+        lin_fwd_kernel<<<grid, 256, 0, st>>>(h->act[nd.nconv - 1], h->params, nd, h->d_masks, B, h->hbuf, h->lmask);
+    }
     PN_LAUNCH_CHECK(h, "lin_fwd_kernel");
     (void)T;
     return PN_OK;
@@ -639,10 +643,14 @@ int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, 
     const size_t sm = ((size_t)nd.hidden * nd.A + nd.hidden + 32 + 8 * (size_t)nd.hidden + 8 * 32) * sizeof(float);
     if (int rc = set_smem(h, head_kernel, sm)) return rc;
     const int blocks = max(1, min((T + 7) / 8, 148 * 2));
-    head_kernel<<<blocks, 256, sm, st>>>(h->hbuf, h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v,
-                                         h->dzv, h->dh, h->loss_t);
+    {
+        PnProfScope prof(h, PN_PROF_HEAD, st);
+        head_kernel<<<blocks, 256, sm, st>>>(h->hbuf, h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v,
+                                             h->dzv, h->dh, h->loss_t);
+    }
     PN_LAUNCH_CHECK(h, "head_kernel");
     if (training && loss) {
+        PnProfScope prof(h, PN_PROF_HEAD, st);
         path_loss_kernel<<<(h->P + 127) / 128, 128, 0, st>>>(h->loss_t, h->P, B, loss);
         PN_LAUNCH_CHECK(h, "path_loss_kernel");
     }
@@ -656,6 +664,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     {
         const int nchunks = (T + 63) / 64;
         const int threads = max(32, (max(nd.hidden, nd.A + 1) + 31) / 32 * 32);
+        PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
         head_wgrad_partial_kernel<<<nchunks, threads, 0, st>>>(h->hbuf, h->dzv, nd, T, h->head_part);
         PN_LAUNCH_CHECK(h, "head_wgrad_partial_kernel");
         const int n = nd.hidden * (nd.A + 1) + nd.A + 1;
@@ -666,11 +675,17 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     {
         const int K = nd.last_lin;
         dim3 g1(P, (K + 63) / 64, (B + 31) / 32);
-        lin_dgrad_kernel<<<g1, 256, 0, st>>>(h->dh, h->lmask, h->params, nd, h->d_masks, B, h->dact[nd.nconv - 1]);
+        {
+            PnProfScope prof(h, PN_PROF_LIN_DGRAD, st);
+            lin_dgrad_kernel<<<g1, 256, 0, st>>>(h->dh, h->lmask, h->params, nd, h->d_masks, B, h->dact[nd.nconv - 1]);
+        }
         PN_LAUNCH_CHECK(h, "lin_dgrad_kernel");
         dim3 g2(nd.M, (K + 63) / 64, (nd.hidden + 63) / 64);
-        lin_wgrad_kernel<<<g2, 256, 0, st>>>(h->act[nd.nconv - 1], h->dh, h->lmask, nd, h->d_list, h->d_list_count, P,
-                                             B, h->grads);
+        {
+            PnProfScope prof(h, PN_PROF_LIN_WGRAD, st);
+            lin_wgrad_kernel<<<g2, 256, 0, st>>>(h->act[nd.nconv - 1], h->dh, h->lmask, nd, h->d_list, h->d_list_count,
+                                                 P, B, h->grads);
+        }
         PN_LAUNCH_CHECK(h, "lin_wgrad_kernel");
     }
     // conv layers, last to first
@@ -681,27 +696,34 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         const int threads = (nd.KK[l] + 31) / 32 * 32;
         const size_t sm = (size_t)npix * PN_F * sizeof(float);
         dim3 grid(P, nch_active);
+        if (int rc = set_smem(h, conv_wgrad_kernel<uint8_t>, sm)) return rc;
+        if (int rc = set_smem(h, conv_wgrad_kernel<float>, sm)) return rc;
+        {
+        PnProfScope prof(h, PN_PROF_CONV_WGRAD + l, st);
         if (l == 0 && is_u8) {
-            if (int rc = set_smem(h, conv_wgrad_kernel<uint8_t>, sm)) return rc;
             conv_wgrad_kernel<uint8_t><<<grid, threads, sm, st>>>((const uint8_t*)frames, 1.0f / 255.0f, h->dact[l],
                                                                   h->rmask[l], nd, l, h->d_masks, B, cs, h->nch,
                                                                   h->wpart[l]);
         } else {
             const float* in = l == 0 ? (const float*)frames : h->act[l - 1];
-            if (int rc = set_smem(h, conv_wgrad_kernel<float>, sm)) return rc;
             conv_wgrad_kernel<float><<<grid, threads, sm, st>>>(in, 1.0f, h->dact[l], h->rmask[l], nd, l, h->d_masks,
                                                                 B, cs, h->nch, h->wpart[l]);
+        }
         }
         PN_LAUNCH_CHECK(h, "conv_wgrad_kernel");
         const int n = nd.KK[l] * PN_F + PN_F;
         dim3 gr(nd.M, (n + 255) / 256);
-        conv_wgrad_reduce_kernel<<<gr, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
-                                                     nch_active, h->grads);
+        {
+            PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
+            conv_wgrad_reduce_kernel<<<gr, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
+                                                         nch_active, h->grads);
+        }
         PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
         if (l > 0) {
             const size_t smd = (((size_t)npix * PN_F + 3) & ~(size_t)3) * sizeof(float) +
                                (size_t)nd.M * nd.KK[l] * PN_F * sizeof(float) + (size_t)nd.M * npix;
             if (int rc = set_smem(h, conv_dgrad_kernel, smd)) return rc;
+            PnProfScope prof(h, PN_PROF_CONV_DGRAD + l, st);
             conv_dgrad_kernel<<<T, 256, smd, st>>>(h->dact[l], h->rmask[l], h->params, nd, l, h->d_masks, B,
                                                    h->dact[l - 1]);
             PN_LAUNCH_CHECK(h, "conv_dgrad_kernel");

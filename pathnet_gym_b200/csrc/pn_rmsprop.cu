@@ -124,8 +124,12 @@ reinit_kernel(float* __restrict__ params, const float* __restrict__ backup, cons
 
 int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st) {
     const int nchunks = (int)h->h_chunks.size();
-    rms_sumsq_kernel<<<nchunks, kThreads, 0, st>>>(h->grads, h->d_chunks, h->d_frozen, h->d_chunk_ss);
+    {
+        PnProfScope prof(h, PN_PROF_RMS_SUMSQ, st);
+        rms_sumsq_kernel<<<nchunks, kThreads, 0, st>>>(h->grads, h->d_chunks, h->d_frozen, h->d_chunk_ss);
+    }
     PN_LAUNCH_CHECK(h, "rms_sumsq_kernel");
+    PnProfScope prof(h, PN_PROF_RMS_UPDATE, st);
     if (momentum != 0.0f) {
         rms_update_kernel<true><<<nchunks, kThreads, 0, st>>>(h->params, h->ms, h->mom, h->grads, h->d_chunks,
                                                               h->d_frozen, h->d_tensor_chunk0, h->d_tensor_nchunks,

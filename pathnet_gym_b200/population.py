@@ -232,6 +232,20 @@ class PathNetPopulation:
         assert backup.dtype == torch.float32 and backup.numel() == self.slab_floats and backup.is_cuda
         nat.check(self.lib.pn_reinit_unfrozen(self._h, _ptr(backup), self._stream()), self._h)
 
+    # -- measurement support ---------------------------------------------------
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.pn_launch_count(self._h))
+
+    def profile_enable(self, on: bool = True):
+        nat.check(self.lib.pn_profile_enable(self._h, 1 if on else 0), self._h)
+
+    def profile_read(self):
+        """{kernel name: (avg ms per launch, launches)} from CUDA events on the launch stream."""
+        arr = (nat.PnProfileEntry * 64)()
+        n = nat.check(self.lib.pn_profile_read(self._h, arr, 64), self._h)
+        return {arr[i].name.decode(): (arr[i].total_ms / max(arr[i].launches, 1), int(arr[i].launches)) for i in range(n)}
+
     @property
     def workspace_bytes(self) -> int:
         return int(self.lib.pn_workspace_bytes(self._h))
