@@ -168,6 +168,22 @@ PN_API int pn_rmsprop_apply(pn_handle* h, float lr, float decay, float momentum,
  * slots are not reset (as in the reference). */
 PN_API int pn_reinit_unfrozen(pn_handle* h, const float* backup_params_dev, void* stream);
 
+/* No counterpart in the reference.  The same update as pn_rmsprop_apply for hosts
+ * that cannot allocate device memory when they call it (the GPU was handed over
+ * fully reserved, cudaMalloc's device-wide synchronisation is not acceptable, or
+ * the host forbids plugins to own device memory): no handle, no cudaMalloc.  The
+ * caller passes the slabs, the tensor table (pn_tensor_desc rows, host memory) and
+ * optional per-tensor frozen flags (host, may be NULL).  Scratch is a built-in
+ * 64 KiB array per device: at most 128 tensors and 16384 chunks of 2048 floats
+ * (~33.5 M parameters); larger inputs return PN_ERR_INVALID.  The current device
+ * must own the slabs.  All calls on a device share that array: calls that may
+ * overlap on the GPU race and must be serialised by the caller.  The first call on
+ * each device resolves the array's address -- make it before any stream capture. */
+PN_API int pn_rmsprop_apply_noalloc(float* params_dev, float* ms_dev, float* mom_dev, const float* grads_dev,
+                                    const pn_tensor_desc* tensors_host, const uint8_t* frozen_host,
+                                    int num_tensors, float lr, float decay, float momentum, float epsilon,
+                                    float clip_norm, void* stream);
+
 /* ---- measurement support (no counterpart in the reference) ------------- */
 
 /* Kernels launched through this handle since pn_create. */

@@ -282,3 +282,29 @@ def tournament_(genotypes: torch.Tensor, scores: torch.Tensor, fixed: torch.Tens
     nat.check(lib.pn_tournament(_ptr(genotypes), _ptr(scores), _ptr(fixed), _ptr(eff), _ptr(winners), P, L, M, N,
                                 Bcand, n_groups, int(seed), int(epoch), st))
     return eff, winners[:n_groups]
+
+
+def rmsprop_apply_noalloc(params, ms, grads, tensors, lr, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0,
+                          mom=None, frozen=None):
+    """The clipped RMSProp update without a handle and without any device allocation, for hosts that
+    cannot call cudaMalloc when they update (fully reserved GPU, no tolerance for cudaMalloc's
+    device-wide synchronisation, plugins that may not own device memory).  `tensors` is a list of
+    dicts with `offset` and `length` (floats into the slabs), e.g. PathNetPopulation.tensors.
+    Limits: 128 tensors, 16384 chunks of 2048 floats; larger inputs raise PathNetError.  One scratch
+    array per device is shared by all calls: do not let two calls overlap on the same GPU."""
+    lib = nat.load()
+    n = len(tensors)
+    arr = (nat.PnTensorDesc * max(n, 1))()
+    for i, t in enumerate(tensors):
+        arr[i].offset, arr[i].length = int(t["offset"]), int(t["length"])
+        arr[i].layer, arr[i].module, arr[i].kind = int(t.get("layer", 0)), int(t.get("module", -1)), int(t.get("kind", 0))
+    fz = None
+    if frozen is not None:
+        fz = np.ascontiguousarray(np.asarray(frozen, dtype=np.uint8))
+        assert fz.size == n
+    with torch.cuda.device(params.device):
+        st = C.c_void_p(torch.cuda.current_stream(params.device).cuda_stream)
+        nat.check(lib.pn_rmsprop_apply_noalloc(_ptr(params), _ptr(ms), _ptr(mom), _ptr(grads), arr,
+                                               fz.ctypes.data_as(C.c_void_p) if fz is not None else C.c_void_p(0), n,
+                                               float(lr), float(decay), float(momentum), float(epsilon),
+                                               float(clip_norm), st))
