@@ -135,6 +135,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from pathnet_gym_b200.population import PathNetConfig, PathNetPopulation, geopath_init
+    from pathnet_gym_b200.trainer import PopulationTrainer
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -162,10 +163,10 @@ def run_b200(args):
     td = torch.randn(P, B, device=dev, generator=gen)
     r = torch.randn(P, B, device=dev, generator=gen)
 
+    trainer = PopulationTrainer(pop)          # public API: train_step -> all-reduce(grads) -> clipped RMSProp
+
     def step(i):
-        pop.train_step(frames[i % NSETS], actions, td, r, 0.01)
-        pop.allreduce_grads()
-        pop.apply_gradients(LR)
+        trainer.step(frames[i % NSETS], actions, td, r, LR)
 
     def barrier():
         if world > 1:
@@ -202,9 +203,7 @@ def run_b200(args):
     hloss = torch.empty(P, dtype=torch.float32).pin_memory()
 
     def step_host(i):
-        pop.train_step_host(hf[i % NSETS], ha, htd, hr, 0.01, loss_out=hloss)   # H2D inputs, D2H loss, sync
-        pop.allreduce_grads()
-        pop.apply_gradients(LR)
+        trainer.step_host(hf[i % NSETS], ha, htd, hr, LR, loss_out=hloss)       # H2D inputs, D2H loss, sync
 
     for i in range(3):
         step_host(i)

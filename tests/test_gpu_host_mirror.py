@@ -1,0 +1,113 @@
+"""GPU tests of the host-side mirror of the reference interface (pathnet, game_ac_network,
+a3c_training_thread, rmsprop_applier, controller) -- they read like the reference's call sites."""
+import types
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+from oracle import pathnet_oracle as po
+from tests import helpers as hp
+
+pytestmark = pytest.mark.gpu
+
+
+def make_flags(**kw):
+    d = dict(task_index=0, L=3, M=10, N=3, kernel_num="8,4,3", stride_size="4,2,1", worker_hosts_num=4, H=84, W=84,
+             population=1, batch_max=20, B=3)
+    d.update(kw)
+    return types.SimpleNamespace(**d)
+
+
+def test_pathnet_module_matches_oracle(native_lib):
+    from pathnet_gym_b200 import pathnet
+    pathnet.seed(1234, epoch=5)
+    g = pathnet.get_geopath(4, 10, 4)
+    assert g.shape == (4, 10) and np.all(g.sum(axis=1) == 4)
+    assert np.array_equal(pathnet.masks_from_geopath(g), po.get_geopath_masks(4, 10, 4, 1234, 5, 0))
+    g2 = pathnet.mutation(g.copy(), 4, 10, 4)
+    assert np.array_equal(pathnet.masks_from_geopath(g2), po.mutate_masks(pathnet.masks_from_geopath(g), 4, 10, 4, 1234, 6, 0))
+    assert np.array_equal(pathnet.geopath_initializer(3, 4), np.ones((3, 4)))
+
+
+def test_network_thread_applier_like_the_reference_driver(native_lib):
+    """doom_pathnet.py:95-113,186-199: build applier + training thread, set a genotype, run process()."""
+    from pathnet_gym_b200 import pathnet
+    from pathnet_gym_b200.a3c_training_thread import A3CTrainingThread
+    from pathnet_gym_b200.constants import GRAD_NORM_CLIP, MAX_TIME_STEP, RMSP_ALPHA, RMSP_EPSILON
+    from pathnet_gym_b200.rmsprop_applier import RMSPropApplier
+    FLAGS = make_flags()
+    np.random.seed(0)
+    applier = RMSPropApplier(learning_rate=None, decay=RMSP_ALPHA, momentum=0.0, epsilon=RMSP_EPSILON,
+                             clip_norm=GRAD_NORM_CLIP, device="/gpu:0")
+    th = A3CTrainingThread(0, "", 0, 7.0016e-4, None, applier, MAX_TIME_STEP, device="/gpu:0", FLAGS=FLAGS, task_index=0)
+    net = th.local_network
+    assert len(net.get_vars()) == 2 * (2 * 10 + 10) + 4 == len(th.apply_gradients)
+    pathnet.seed(7)
+    geo = pathnet.get_geopath(FLAGS.L, FLAGS.M, FLAGS.N)
+    pathnet.geopath_insert(None, net.geopath_update_placeholders_set[0], net.geopath_update_ops_set[0], geo, FLAGS.L, FLAGS.M)
+    assert np.array_equal(net.get_geopath(None), geo)
+    # acting forward equals the oracle on the same weights
+    s_t = (np.random.randint(0, 256, size=(84, 84, 4)).astype(np.float32)) * np.float32(1 / 255.0)
+    pi, v = net.run_policy_and_value(None, s_t)
+    params = net.pop.dump(net.pop.params)
+    pi_r, v_r, _, _ = po.forward_backward_numpy(hp.C1, params, s_t[None], geo, [0], [0.0], [0.0], want_grads=False)
+    assert hp.rel_err(pi, pi_r[0]) < 1e-3 and abs(v - v_r[0]) < 1e-3 * max(1.0, abs(v_r[0]))
+    assert abs(net.run_value(None, s_t) - v) < 1e-6 and np.allclose(net.run_policy(None, s_t), pi)
+    # freeze module (0,1): its variables leave get_vars() and are untouched by process()
+    fixed = np.zeros((FLAGS.L, FLAGS.M))
+    fixed[0, 1] = 1.0
+    net.set_fixed_path(fixed)
+    assert len(net.get_vars()) == 64 - 2 and net.get_vars_idx()[2:4] == [0, 0]
+    th.set_training_stage(0)
+    before = net.pop.params.clone()
+    ms_before = net.pop.ms.clone()
+    diff = th.process(None, 0, None, None, None, None, None, None, FLAGS, None, None)
+    assert diff == 20 and np.isfinite(th.last_loss)
+    w01 = net.W_conv[0, 1]
+    t = net.pop.tensors[w01.index]
+    sl = slice(t["offset"], t["offset"] + t["length"])
+    assert torch.equal(net.pop.params[sl], before[sl]) and torch.equal(net.pop.ms[sl], ms_before[sl])
+    assert not torch.equal(net.pop.params, before)
+    assert applier.get_slot(net.W_fc2, "rms").shape == (256, 18)
+    assert th._anneal_learning_rate(MAX_TIME_STEP * 2) == 0.0
+    net.pop.close()
+
+
+def test_controller_tournament_freeze_reinit(native_lib):
+    """doom_pathnet.py:212-293 on a 12-path population."""
+    from pathnet_gym_b200.controller import PopulationController
+    from pathnet_gym_b200.population import PathNetPopulation
+    cfg = hp.to_engine_cfg(hp.TINY)
+    P = 12
+    pop = PathNetPopulation(cfg, P, 2)
+    pop.init_params(3)
+    ctl = PopulationController(pop, P, Bcand=3, seed=99)
+    ctl.start_task()
+    g0 = ctl.genotypes.cpu().numpy().view(np.uint32).copy()
+    assert np.array_equal(g0, np.stack([po.get_geopath_masks(cfg.L, cfg.M, cfg.N, 99, 1, p) for p in range(P)]))
+    assert np.all(ctl.tournament_step() == -1)                 # nobody has reported a score yet
+    scores = torch.arange(P, dtype=torch.float32)
+    ctl.report_scores(scores)
+    w = ctl.tournament_step()
+    g_ref, eff_ref, sc_ref, w_ref = po.tournament(g0, scores.numpy(), np.zeros(cfg.L, np.uint32), cfg.L, cfg.M, cfg.N,
+                                                  3, 4, 99, 3)
+    assert np.array_equal(w, w_ref) and np.array_equal(ctl.genotypes.cpu().numpy().view(np.uint32), g_ref)
+    assert np.array_equal(pop.masks, eff_ref) and float(ctl.scores.max()) == -1000.0
+    # task switch: freeze the winner's path, re-initialise the rest, keep the slots
+    pop.params.mul_(2.0)
+    pop.ms.fill_(0.5)
+    fixed = ctl.end_task()
+    assert np.array_equal(fixed, po.gates_from_masks(hp.TINY, g_ref[ctl.winner_idx]))
+    assert np.array_equal(pop.frozen, po.frozen_flags(hp.TINY, fixed))
+    for i, t in enumerate(pop.tensors):
+        sl = slice(t["offset"], t["offset"] + t["length"])
+        if pop.frozen[i]:
+            assert torch.equal(pop.params[sl], ctl.vars_backup[sl] * 2.0)
+        else:
+            assert torch.equal(pop.params[sl], ctl.vars_backup[sl])
+    assert float(pop.ms.min()) == 0.5
+    ctl.start_task()                                           # task 2: new genotypes OR the fixed path
+    assert np.all((pop.masks & g_ref[ctl.winner_idx][None, :]) == g_ref[ctl.winner_idx][None, :])
+    pop.close()
