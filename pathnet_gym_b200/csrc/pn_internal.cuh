@@ -37,6 +37,8 @@ enum PnProfSlot {
     PN_PROF_LIN_WGRAD,
     PN_PROF_RMS_SUMSQ,
     PN_PROF_RMS_UPDATE,
+    PN_PROF_CONV0_WPREP,
+    PN_PROF_CONV0_DQUANT,
     PN_PROF_NSLOTS
 };
 #define PN_PROF_RING 64
@@ -82,6 +84,10 @@ struct pn_handle {
     int* d_tensor_chunk0 = nullptr;     // first chunk of each tensor
     int* d_tensor_nchunks = nullptr;
     float* d_chunk_ss = nullptr;        // [n_chunks] partial sums of squares
+    // tensor-core conv0 (pn_conv0_tc.cu)
+    bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
+    int num_sms = 148;
+    uint8_t* tc_w8 = nullptr;           // [M][6144] int8 weight digits + [M][8] fp32 scales
     // host-call staging
     void* st_frames = nullptr; size_t st_frames_bytes = 0;
     int32_t* st_actions = nullptr; float* st_td = nullptr; float* st_r = nullptr; float* st_loss = nullptr;
@@ -129,6 +135,10 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
 int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, const float* td, const float* r,
                     float beta, float* pi, float* v, float* loss, cudaStream_t st);
 int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaStream_t st);
+// pn_conv0_tc.cu
+bool pn_conv0_tc_supported(const pn_handle* h);
+size_t pn_conv0_tc_scratch_bytes(const pn_handle* h);
+int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 // pn_rmsprop.cu
 int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st);
 int pn_launch_reinit(pn_handle* h, const float* backup, cudaStream_t st);

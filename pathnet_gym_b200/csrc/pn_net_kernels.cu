@@ -606,6 +606,10 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
     const int T = h->P * B;
     (void)training;
     for (int l = 0; l < nd.nconv; ++l) {
+        if (l == 0 && is_u8 && h->tc_conv0) {
+            if (int rc = pn_launch_conv0_fwd_tc(h, (const uint8_t*)frames, B, st)) return rc;
+            continue;
+        }
         const int rpb = max(1, 128 / nd.OW[l]);
         const int nbands = (nd.OH[l] + rpb - 1) / rpb;
         const int in_rows = (min(rpb, nd.OH[l]) - 1) * nd.s[l] + nd.k[l];

@@ -46,7 +46,8 @@ class PathNetPopulation:
     params, rms (init 1.0, rmsprop_applier.py:34-37), optional momentum (init 0), grads.
     """
 
-    def __init__(self, cfg: PathNetConfig, P: int, B_max: int, device: int = 0, momentum_slot: bool = False):
+    def __init__(self, cfg: PathNetConfig, P: int, B_max: int, device: int = 0, momentum_slot: bool = False,
+                 flags: int = 0):
         if not torch.cuda.is_available():
             raise RuntimeError("pathnet_gym_b200 needs a CUDA device (there is no CPU fallback)")
         self.lib = nat.load()
@@ -56,7 +57,7 @@ class PathNetPopulation:
         pc.L, pc.M, pc.H, pc.W, pc.C, pc.F, pc.hidden, pc.A = cfg.L, cfg.M, cfg.H, cfg.W, cfg.C, cfg.F, cfg.hidden, cfg.A
         for i in range(cfg.L - 1):
             pc.kernel[i], pc.stride[i] = cfg.kernels[i], cfg.strides[i]
-        pc.P, pc.B_max, pc.device, pc.flags = self.P, self.B_max, self.device_index, 0
+        pc.P, pc.B_max, pc.device, pc.flags = self.P, self.B_max, self.device_index, int(flags)
         h = C.c_void_p()
         nat.check(self.lib.pn_create(C.byref(pc), C.byref(h)))
         self._h = h

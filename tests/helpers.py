@@ -9,6 +9,8 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 TINY = po.OracleConfig(L=3, M=4, N=2, H=20, W=20, C=4, kernels=(4, 3, 3), strides=(2, 1, 1), F=8, hidden=32, A=5)
 TINY4 = po.OracleConfig(L=4, M=5, N=2, H=28, W=24, C=4, kernels=(4, 4, 3), strides=(2, 2, 1), F=8, hidden=64, A=3)
+# smallest geometry the tensor-core layer-0 path accepts (k = 2*stride, stride*C = 16)
+TC20 = po.OracleConfig(L=3, M=10, N=3, H=20, W=24, C=4, kernels=(8, 2, 3), strides=(4, 1, 1), F=8, hidden=32, A=6)
 C1 = po.OracleConfig(L=3, M=10, N=3, H=84, W=84, C=4, A=18)
 C3 = po.OracleConfig(L=4, M=10, N=4, H=84, W=84, C=4, A=18)
 

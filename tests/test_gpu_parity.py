@@ -175,7 +175,8 @@ def test_c1_matches_golden(eng_mod):
 # ---------------------------------------------------------------------------
 # vs the oracle on fresh seeded inputs, edge cases
 # ---------------------------------------------------------------------------
-@pytest.mark.parametrize("cfg,P,B", [(hp.TINY, 5, 1), (hp.TINY, 2, 33), (hp.TINY4, 3, 20), (hp.C3, 2, 3)])
+@pytest.mark.parametrize("cfg,P,B", [(hp.TINY, 5, 1), (hp.TINY, 2, 33), (hp.TINY4, 3, 20), (hp.C3, 2, 3),
+                                     (hp.TC20, 7, 5), (hp.TC20, 9, 1), (hp.C1, 5, 2)])
 def test_population_vs_oracle(eng_mod, cfg, P, B):
     params = po.init_params(cfg, 11)
     frames, actions, td, r, masks = hp.synth_inputs(cfg, P, B, 99)
@@ -186,6 +187,10 @@ def test_population_vs_oracle(eng_mod, cfg, P, B):
         masks[1, 0] = 1 << (cfg.M - 1)       # single module in a layer
     if P > 2:
         masks[2, cfg.L - 1] = 0              # no module at all in the last layer -> h == 0
+    if P > 3:
+        masks[3, 0] = 0                      # no module in layer 0 -> its output is exactly zero
+    if P > 4:
+        masks[4, 0] = 0b101010101 & full     # five modules: two tensor-core passes
     pi_r, v_r, loss_r, G = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy")
     pop = make_pop(eng_mod, cfg, P, B, params, masks)
     loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
@@ -195,6 +200,30 @@ def test_population_vs_oracle(eng_mod, cfg, P, B):
     for a, b, t in zip(pop.dump(pop.grads), G, po.tensor_table(cfg)):
         assert hp.rel_err(a, b) < REL_TOL, t["name"]
     pop.close()
+
+
+def test_tensor_core_layer0_matches_cuda_core_path(eng_mod):
+    """C2-sized population: the tcgen05 layer-0 kernel (default for u8 frames) against the fp32
+    CUDA-core kernels (flags=1) -- activations agree to fp32 rounding, ReLU masks almost always."""
+    cfg, P, B = hp.C1, 16, 32
+    params = po.init_params(cfg, 1)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, P, B, 77)
+    masks = masks.copy()
+    masks[1, 0] = (1 << cfg.M) - 1
+    fd, ad, tdd, rd = dev(frames), dev(actions), dev(td), dev(r)
+    out = []
+    for flags in (0, 1):
+        pop = make_pop(eng_mod, cfg, P, B, params, masks, flags=flags)
+        loss, pi, v = pop.train_step(fd, ad, tdd, rd, 0.01, want_outputs=True)
+        out.append((pi.clone(), v.clone(), loss.clone(), pop.grads.clone()))
+        pop.close()
+    (pi0, v0, l0, g0), (pi1, v1, l1, g1) = out
+    assert hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()) < 1e-5
+    assert hp.rel_err(v0.cpu().numpy(), v1.cpu().numpy()) < 1e-5
+    assert hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()) < 1e-5
+    assert hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()) < 1e-4
+    _note("tc_vs_simt.pi", hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()))
+    _note("tc_vs_simt.grads", hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()))
 
 
 def test_pi_underflow_case(eng_mod):
