@@ -140,7 +140,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
         PN_TRY(dev_alloc(h, &h->dact[l], T * npix * PN_F));
         PN_TRY(dev_alloc(h, &h->rmask[l], T * c.M * npix));
     }
-    h->nch = std::min(c.B_max, std::max(1, (296 + c.P - 1) / c.P));
+    h->nch = std::min(c.B_max, std::max(8, (296 + c.P - 1) / c.P));
     for (int l = 0; l < nd.nconv; ++l)
         PN_TRY(dev_alloc(h, &h->wpart[l], (size_t)c.P * h->nch * c.M * ((size_t)nd.KK[l] * PN_F + PN_F)));
     PN_TRY(dev_alloc(h, &h->hbuf, T * c.hidden));

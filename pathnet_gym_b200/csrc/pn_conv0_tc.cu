@@ -28,6 +28,8 @@
 #include "pn_internal.cuh"
 #include "pn_tc.cuh"
 
+#include <algorithm>
+
 using namespace pntc;
 
 namespace {
@@ -47,6 +49,7 @@ struct TcGeom {
     int row_bytes, frame_bytes;      // W*C, H*W*C
     int nst;                         // frame stages in the ring
     int ksteps;                      // MMAs (K = 32) per tap = s*16/32
+    int mq;                          // rows of the weight-gradient reduction (block raster, multiple of 32)
 };
 
 // ---- weight split: fp32 -> 3 signed base-256 digits per (module, channel) ---------------------------
@@ -298,6 +301,287 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
     if (warp == 1) tmem_dealloc(td, kAccStages * kAccCols);
 }
 
+
+// =====================================================================================================
+// Layer-0 weight gradient on the tensor cores.
+//   dW_j[kh,kw,ci,co] = sum over the transitions t of the paths that use module j and over output
+//   pixels of  x[t, oy*s+kh, ox*s+kw, ci] * dpre_j[t, oy, ox, co],   dpre_j = dY * relu_mask_j
+// (tf.gradients through Conv2D, a3c_training_thread.py:55-60).  Per tap (dy,dx) this is
+//   D_tap[64 x N] += A_tap^T[64 x m] * dq[m x N]      (m = block raster index, K of the MMA)
+// with A_tap^T the staged frame read MN-major through a shifted descriptor (same buffer as the forward
+// kernel) and dq the masked output gradient quantised to four signed base-256 digits of
+// round(dpre * 2^(30-e)), 2^e >= max|dY| over the batch (one global power-of-two scale, so the integer
+// accumulation is exact and order-independent; resolution 2^-30 of the largest gradient entry).
+// One work item = (path, chunk of its transitions); the four tap accumulators live in TMEM (M = 64,
+// N = 32 columns per module) for the whole chunk and are flushed once into the partial-sum buffer that
+// conv_wgrad_reduce_kernel adds up in a fixed order.
+// Warp roles (192 threads): warp 0 frame producer, warp 1 MMA issue, warps 2-5 quantise dq and flush.
+// =====================================================================================================
+constexpr int kWgDigits = 4;
+constexpr int kWgSlotCols = 8 * kWgDigits;      // 32 accumulator columns per module
+constexpr int kWgTapCols = 128;                  // TMEM columns reserved per tap (4 modules per pass)
+
+__global__ void absmax_kernel(const float* __restrict__ x, size_t n4, unsigned* __restrict__ out) {
+    float m = 0.f;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = reinterpret_cast<const float4*>(x)[i];
+        m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));   // non-negative floats order like uints
+}
+
+__device__ __forceinline__ uint32_t pack4(const int* d) {
+    return (uint32_t)(d[0] & 255) | ((uint32_t)(d[1] & 255) << 8) | ((uint32_t)(d[2] & 255) << 16) |
+           ((uint32_t)(d[3] & 255) << 24);
+}
+__device__ __forceinline__ uint32_t nib_to_bytemask(unsigned nib) {
+    return ((nib & 1u) ? 0xFFu : 0u) | ((nib & 2u) ? 0xFF00u : 0u) | ((nib & 4u) ? 0xFF0000u : 0u) |
+           ((nib & 8u) ? 0xFF000000u : 0u);
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restrict__ dY, const uint8_t* __restrict__ R,
+                      const unsigned* __restrict__ absmax, PnNetDesc nd, const uint32_t* __restrict__ masks, int B,
+                      int P, int cs, int nch, int nch_alloc, TcGeom gm, float* __restrict__ part) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int region_q = gm.mq * 16;                       // bytes of one 16-column group of dq
+    const int dq_stage_bytes = 2 * kPassSlots * region_q;  // up to 4 modules x 2 groups
+    uint8_t* frame_s = smem;
+    uint8_t* dq_s = smem + 2 * (size_t)gm.stage_bytes;
+    // the dq ring doubles as the 16 KB scratch of the bias-gradient reduction at flush time
+    const int dq_total = max(2 * dq_stage_bytes, 128 * 32 * (int)sizeof(float));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(dq_s + dq_total);
+    uint64_t* frame_full = bars;          // [2]
+    uint64_t* frame_empty = bars + 2;     // [2]
+    uint64_t* dq_full = bars + 4;         // [2]
+    uint64_t* dq_empty = bars + 6;        // [2]
+    uint64_t* acc_full = bars + 8;
+    uint64_t* acc_empty = bars + 9;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int npix = gm.OH * gm.OW;
+    const int nitems = P * nch;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1);
+            mbar_init(&dq_full[i], 128); mbar_init(&dq_empty[i], 1);
+        }
+        mbar_init(acc_full, 1);
+        mbar_init(acc_empty, 128);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(&tmem_base_s, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t td = tmem_base_s;
+
+    if (warp == 0) {
+        // ================= frame producer =================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+            const int p = item / nch, ch = item % nch;
+            const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
+            const int ns = __popc(masks[p * nd.L]);
+            const int npass = (ns + kPassSlots - 1) / kPassSlots;
+            for (int pass = 0; pass < npass; ++pass)
+                for (int b = b_lo; b < b_hi; ++b) {
+                    const size_t t = (size_t)p * B + b;
+                    mbar_wait(&frame_empty[stage], phase ^ 1);
+                    if (lane == 0) mbar_expect_tx(&frame_full[stage], (uint32_t)gm.frame_bytes);
+                    __syncwarp();
+                    const uint8_t* src = frames + t * gm.frame_bytes;
+                    uint8_t* dst = frame_s + (size_t)stage * gm.stage_bytes;
+                    for (int ry = lane; ry < gm.H; ry += 32)
+                        bulk_g2s(dst + (ry % gm.s) * gm.region_bytes + (ry / gm.s) * gm.row_bytes,
+                                 src + (size_t)ry * gm.row_bytes, (uint32_t)gm.row_bytes, &frame_full[stage]);
+                    if (++stage == 2) { stage = 0; phase ^= 1; }
+                }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issue =================
+        int stage = 0;
+        uint32_t phase = 0, nflush = 0;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+            const int p = item / nch, ch = item % nch;
+            const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
+            const int ns = __popc(masks[p * nd.L]);
+            const int npass = (ns + kPassSlots - 1) / kPassSlots;
+            for (int pass = 0; pass < npass; ++pass) {
+                if (b_lo >= b_hi) continue;
+                const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                const int N = kWgSlotCols * nsl;
+                const uint32_t idesc = make_idesc_i8(64, N, 0, 1, 1, 1);
+                mbar_wait(acc_empty, (nflush & 1) ^ 1);       // previous flush has drained the accumulators
+                tc_fence_after();
+                uint32_t accum = 0;
+                for (int b = b_lo; b < b_hi; ++b) {
+                    mbar_wait(&frame_full[stage], phase);
+                    mbar_wait(&dq_full[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
+                        const uint32_t qbase = smem_u32(dq_s + (size_t)stage * dq_stage_bytes);
+                        for (int ks = 0; ks < gm.mq / 32; ++ks) {
+                            const uint64_t bd = make_smem_desc(qbase + (uint32_t)(ks * 32 * 16), 128, (uint32_t)region_q);
+                            for (int tap = 0; tap < 4; ++tap) {
+                                const int off = (tap >> 1) * gm.Ws + (tap & 1);
+                                const uint64_t ad = make_smem_desc(fbase + (uint32_t)((ks * 32 + off) * 16), 128,
+                                                                   (uint32_t)gm.region_bytes);
+                                umma_i8(td + tap * kWgTapCols, ad, bd, idesc, accum);
+                            }
+                            accum = 1;
+                        }
+                        umma_commit(&frame_empty[stage]);
+                        umma_commit(&dq_empty[stage]);
+                    }
+                    __syncwarp();
+                    if (++stage == 2) { stage = 0; phase ^= 1; }
+                }
+                if (lane == 0) umma_commit(acc_full);
+                __syncwarp();
+                ++nflush;
+            }
+        }
+    } else {
+        // ================= quantise dq per transition, flush the accumulators per (item, pass) =================
+        const int quad = warp & 3;
+        const int tid = threadIdx.x - 64;                      // 0..127
+        int stage = 0;
+        uint32_t phase = 0, nflush = 0;
+        const unsigned am = *absmax;
+        int e = 0;
+        if (am) frexpf(__uint_as_float(am), &e);                // max = f * 2^e, f in [0.5, 1)  =>  2^e > max
+        const float qscale = am ? ldexpf(1.0f, 30 - e) : 0.f;
+        const double dscale = am ? ldexp(1.0, e - 30) / 255.0 : 0.0;
+        const int stride_part = nd.KK[0] * PN_F + PN_F;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+            const int p = item / nch, ch = item % nch;
+            const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
+            const uint32_t mask = masks[p * nd.L];
+            const int ns = __popc(mask);
+            const int npass = (ns + kPassSlots - 1) / kPassSlots;
+            for (int pass = 0; pass < npass; ++pass) {
+                if (b_lo >= b_hi) continue;
+                const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                int jl[kPassSlots];
+#pragma unroll
+                for (int sl = 0; sl < kPassSlots; ++sl) jl[sl] = sl < nsl ? __fns(mask, 0, pass * kPassSlots + sl + 1) : 0;
+                float bsum[kPassSlots][8];
+#pragma unroll
+                for (int sl = 0; sl < kPassSlots; ++sl)
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) bsum[sl][c] = 0.f;
+                for (int b = b_lo; b < b_hi; ++b) {
+                    const size_t t = (size_t)p * B + b;
+                    mbar_wait(&dq_empty[stage], phase ^ 1);
+                    uint8_t* dq = dq_s + (size_t)stage * dq_stage_bytes;
+                    for (int m = tid; m < gm.mq; m += 128) {
+                        const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
+                        const bool valid = ox < gm.OW && oy < gm.OH;
+                        uint32_t w[4][2];                        // [digit][channels 0-3 / 4-7]
+                        float dv[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) dv[i] = 0.f;
+#pragma unroll
+                        for (int d = 0; d < 4; ++d) w[d][0] = w[d][1] = 0u;
+                        int pix = 0;
+                        if (valid) {
+                            pix = oy * gm.OW + ox;
+                            const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pix) * PN_F);
+                            const float4 a = g4[0], bq = g4[1];
+                            dv[0] = a.x; dv[1] = a.y; dv[2] = a.z; dv[3] = a.w;
+                            dv[4] = bq.x; dv[5] = bq.y; dv[6] = bq.z; dv[7] = bq.w;
+                            int dg[4][8];
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {
+                                int q = __float2int_rn(dv[c] * qscale);
+#pragma unroll
+                                for (int d = 0; d < 3; ++d) {
+                                    const int dd = ((q + 128) & 255) - 128;
+                                    dg[d][c] = dd;
+                                    q = (q - dd) >> 8;
+                                }
+                                dg[3][c] = q;
+                            }
+#pragma unroll
+                            for (int d = 0; d < 4; ++d) { w[d][0] = pack4(&dg[d][0]); w[d][1] = pack4(&dg[d][4]); }
+                        }
+#pragma unroll
+                        for (int sl = 0; sl < kPassSlots; ++sl) {
+                            if (sl >= nsl) break;
+                            unsigned bits = 0;
+                            if (valid) bits = R[(t * nd.M + jl[sl]) * npix + pix];
+                            const uint32_t mlo = nib_to_bytemask(bits & 15u), mhi = nib_to_bytemask(bits >> 4);
+                            uint4 g0 = make_uint4(w[0][0] & mlo, w[0][1] & mhi, w[1][0] & mlo, w[1][1] & mhi);
+                            uint4 g1 = make_uint4(w[2][0] & mlo, w[2][1] & mhi, w[3][0] & mlo, w[3][1] & mhi);
+                            *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl) * region_q + m * 16) = g0;
+                            *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl + 1) * region_q + m * 16) = g1;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c)
+                                if ((bits >> c) & 1u) bsum[sl][c] += dv[c];
+                        }
+                    }
+                    fence_proxy_async();
+                    mbar_arrive(&dq_full[stage]);
+                    if (++stage == 2) { stage = 0; phase ^= 1; }
+                }
+                // ---- flush ----
+                mbar_wait(acc_full, nflush & 1);
+                tc_fence_after();
+                const bool rowvalid = lane < 16;
+                const int r = quad * 16 + lane;                   // accumulator row = (g, byte) of the tap
+                const int g = r >> 4, bb = r & 15;
+                for (int tap = 0; tap < 4; ++tap) {
+                    const int kh = (tap >> 1) * gm.s + g, kw = (tap & 1) * gm.s + bb / gm.C, ci = bb % gm.C;
+                    const int kk = (kh * nd.k[0] + kw) * gm.C + ci;
+                    for (int sl = 0; sl < nsl; ++sl) {
+                        uint32_t d0[8], d1[8], d2[8], d3[8];
+                        const uint32_t ta = td + ((uint32_t)(quad * 32) << 16) + tap * kWgTapCols + sl * kWgSlotCols;
+                        tmem_ld8(ta, d0); tmem_ld8(ta + 8, d1); tmem_ld8(ta + 16, d2); tmem_ld8(ta + 24, d3);
+                        tmem_ld_wait();
+                        if (rowvalid) {
+                            float o[8];
+#pragma unroll
+                            for (int c = 0; c < 8; ++c)
+                                o[c] = (float)(((double)(int)d0[c] + 256.0 * (double)(int)d1[c] + 65536.0 * (double)(int)d2[c] +
+                                                16777216.0 * (double)(int)d3[c]) * dscale);
+                            float4* dst = reinterpret_cast<float4*>(
+                                part + ((size_t)(p * nch_alloc + ch) * nd.M + jl[sl]) * stride_part + (size_t)kk * PN_F);
+                            dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+                            dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+                        }
+                    }
+                }
+                // bias gradient: fixed-order sum of the 128 per-thread partials (dq stage 0 is free now)
+                float* bred = reinterpret_cast<float*>(dq_s);
+#pragma unroll
+                for (int sl = 0; sl < kPassSlots; ++sl)
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) bred[tid * 32 + sl * 8 + c] = bsum[sl][c];
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (tid < nsl * 8) {
+                    float sacc = 0.f;
+                    for (int i = 0; i < 128; ++i) sacc += bred[i * 32 + tid];
+                    part[((size_t)(p * nch_alloc + ch) * nd.M + jl[tid >> 3]) * stride_part + (size_t)nd.KK[0] * PN_F + (tid & 7)] = sacc;
+                }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                tc_fence_before();
+                mbar_arrive(acc_empty);
+                ++nflush;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(td, 512);
+}
+
 bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
     const PnNetDesc& nd = h->nd;
     if (nd.nconv < 1) return false;
@@ -314,7 +598,8 @@ bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
     g.row_bytes = W * C;
     g.frame_bytes = H * W * C;
     g.ksteps = s / 2;
-    if (g.row_bytes % 16 || g.Hs * g.Ws > region_blocks) return false;
+    g.mq = (rows + 31) & ~31;
+    if (g.row_bytes % 16 || g.Hs * g.Ws > region_blocks || g.mq + g.Ws + 1 > region_blocks) return false;
     const size_t fixed = (size_t)(nd.M + 1) * kSlotBytes + (size_t)nd.M * 16 * sizeof(float) + 64 * sizeof(uint64_t);
     for (g.nst = 3; g.nst >= 2; --g.nst) {
         smem_bytes = (size_t)g.nst * g.stage_bytes + fixed;
@@ -331,7 +616,10 @@ bool pn_conv0_tc_supported(const pn_handle* h) {
     return make_geom(h, g, sm);
 }
 
-size_t pn_conv0_tc_scratch_bytes(const pn_handle* h) { return (size_t)h->nd.M * (kSlotBytes + 8 * sizeof(float)); }
+size_t pn_conv0_tc_scratch_bytes(const pn_handle* h) {
+    // int8 weight digits + fp32 scales per module, then 16 bytes for the batch max |dY| of layer 0
+    return (((size_t)h->nd.M * (kSlotBytes + 8 * sizeof(float)) + 15) & ~(size_t)15) + 16;
+}
 
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st) {
     TcGeom g;
@@ -354,5 +642,47 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
                                                                  h->act[0], h->rmask[0]);
     }
     PN_LAUNCH_CHECK(h, "conv0_fwd_tc_kernel");
+    return PN_OK;
+}
+
+int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st) {
+    TcGeom g;
+    size_t fwd_smem = 0;
+    if (!make_geom(h, g, fwd_smem)) return pn_fail(h, PN_ERR_STATE, "tensor-core conv0 not supported for this geometry");
+    const PnNetDesc& nd = h->nd;
+    const int P = h->P, T = P * B;
+    const int npix = g.OH * g.OW;
+    unsigned* absmax = reinterpret_cast<unsigned*>(h->tc_w8 + pn_conv0_tc_scratch_bytes(h) - 16);
+    PN_CUDA(h, cudaMemsetAsync(absmax, 0, sizeof(unsigned), st));
+    {
+        PnProfScope prof(h, PN_PROF_CONV0_DQUANT, st);
+        absmax_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->dact[0], (size_t)T * npix * PN_F / 4, absmax);
+    }
+    PN_LAUNCH_CHECK(h, "absmax_kernel");
+    // chunks per path: balance P*nch items over the SMs, at most 32 transitions per chunk (int32 accumulators)
+    int best_nch = 1;
+    double best_eff = -1.0;
+    for (int nch = 1; nch <= h->nch && nch <= B; ++nch) {
+        const int cs = (B + nch - 1) / nch;
+        if (cs > 32 || (B + cs - 1) / cs != nch) continue;
+        const long long items = (long long)P * nch, rounds = (items + h->num_sms - 1) / h->num_sms;
+        // cost of an item ~ cs transitions of MMAs + one accumulator flush (~0.75 of a transition)
+        const double eff = (double)T / ((double)rounds * h->num_sms * (cs + 0.75));
+        if (eff > best_eff) { best_eff = eff; best_nch = nch; }
+    }
+    if (best_eff < 0) return pn_fail(h, PN_ERR_STATE, "no valid chunking for the conv0 weight-gradient kernel");
+    const int nch = best_nch, cs = (B + nch - 1) / nch;
+    const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), 128 * 32 * sizeof(float));
+    const size_t smem_bytes = 2 * (size_t)g.stage_bytes + dq_total + 16 * sizeof(uint64_t);
+    PN_CUDA(h, cudaFuncSetAttribute(conv0_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    const int items = P * nch;
+    const int grid = items < h->num_sms ? items : h->num_sms;
+    {
+        PnProfScope prof(h, PN_PROF_CONV_WGRAD + 0, st);
+        conv0_wgrad_tc_kernel<<<grid, kTcThreads, smem_bytes, st>>>(frames, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
+                                                                   B, P, cs, nch, h->nch, g, h->wpart[0]);
+    }
+    PN_LAUNCH_CHECK(h, "conv0_wgrad_tc_kernel");
+    h->last_wgrad_nch = nch;
     return PN_OK;
 }

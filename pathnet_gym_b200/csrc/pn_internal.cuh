@@ -87,7 +87,8 @@ struct pn_handle {
     // tensor-core conv0 (pn_conv0_tc.cu)
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
     int num_sms = 148;
-    uint8_t* tc_w8 = nullptr;           // [M][6144] int8 weight digits + [M][8] fp32 scales
+    uint8_t* tc_w8 = nullptr;           // [M][6144] int8 weight digits + [M][8] fp32 scales + batch max|dY|
+    int last_wgrad_nch = 1;             // chunks per path used by the last tensor-core weight-gradient launch
     // host-call staging
     void* st_frames = nullptr; size_t st_frames_bytes = 0;
     int32_t* st_actions = nullptr; float* st_td = nullptr; float* st_r = nullptr; float* st_loss = nullptr;
@@ -139,6 +140,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
 bool pn_conv0_tc_supported(const pn_handle* h);
 size_t pn_conv0_tc_scratch_bytes(const pn_handle* h);
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
+int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 // pn_rmsprop.cu
 int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st);
 int pn_launch_reinit(pn_handle* h, const float* backup, cudaStream_t st);

@@ -13,6 +13,8 @@
 //   lmask    [T][M][hidden]  u8    0/1
 #include "pn_internal.cuh"
 
+#include <algorithm>
+
 namespace {
 
 __device__ __forceinline__ float to_f(uint8_t v) { return (float)v; }
@@ -693,10 +695,23 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         PN_LAUNCH_CHECK(h, "lin_wgrad_kernel");
     }
     // conv layers, last to first
-    const int cs = (B + h->nch - 1) / h->nch;
-    const int nch_active = (B + cs - 1) / cs;
+    const int nch_simt = std::min(h->nch, std::max(1, (296 + P - 1) / P));
+    const int cs = (B + nch_simt - 1) / nch_simt;
+    int nch_active = (B + cs - 1) / cs;
     for (int l = nd.nconv - 1; l >= 0; --l) {
         const int npix = nd.OH[l] * nd.OW[l];
+        if (l == 0 && is_u8 && h->tc_conv0) {
+            if (int rc = pn_launch_conv0_wgrad_tc(h, (const uint8_t*)frames, B, st)) return rc;
+            const int n0 = nd.KK[l] * PN_F + PN_F;
+            dim3 gr0(nd.M, (n0 + 255) / 256);
+            {
+                PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
+                conv_wgrad_reduce_kernel<<<gr0, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
+                                                              h->last_wgrad_nch, h->grads);
+            }
+            PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
+            continue;
+        }
         const int threads = (nd.KK[l] + 31) / 32 * 32;
         const size_t sm = (size_t)npix * PN_F * sizeof(float);
         dim3 grid(P, nch_active);
