@@ -19,12 +19,13 @@
 //    changed the weights).  Integer MMAs are exact, so the only deviation from fp32 arithmetic is the
 //    2^-23 (relative to the channel's largest weight) rounding of that split.  B = [digit][channel]
 //    rows per active module (24 columns per module), gathered per path from the genotype bitmask.
-//  * epilogue (thread = output pixel = TMEM lane): Q = D0 + 256*D1 + 65536*D2 in int64,
-//    pre = Q * scale_c + b_c, ReLU, ascending-j sum, ReLU bit mask for the backward pass.
+//  * epilogue (thread = output pixel = TMEM lane): pre = D2*(65536 s_c) + D1*(256 s_c) + D0*s_c + b_c
+//    in fp32 (the integer sums convert exactly), ReLU, ascending-j sum, ReLU bit mask for backward.
 //
-// Warp roles (192 threads, one CTA per SM, persistent over a contiguous range of transitions):
+// Warp roles (320 threads, one CTA per SM, persistent over a contiguous range of transitions):
 //   warp 0  bulk-copy producer (frames -> smem ring), warp 1  TMEM owner + B gather + MMA issue,
-//   warps 2-5  epilogue (one TMEM lane quadrant each).
+//   warps 2-9  two epilogue groups of four warps (one TMEM lane quadrant each); consecutive 128-row
+//   tiles alternate between the groups and rotate through four TMEM accumulator stages.
 #include "pn_internal.cuh"
 #include "pn_tc.cuh"
 
@@ -34,8 +35,9 @@ using namespace pntc;
 
 namespace {
 
-constexpr int kTcThreads = 192;
-constexpr int kAccStages = 2;
+constexpr int kTcThreads = 192;          // weight-gradient kernel: producer, MMA, 4 quantise/flush warps
+constexpr int kFwdThreads = 320;         // forward kernel: producer, MMA, 2 groups of 4 epilogue warps
+constexpr int kAccStages = 4;            // accumulator ring: tile c uses stage c%4, epilogue group c%2
 constexpr int kAccCols = 128;            // TMEM columns per accumulator stage (max N of one pass = 96)
 constexpr int kSlotBytes = 3 * 2048;     // one module's B rows: 3 digit groups x (8 channels x 256 K bytes)
 constexpr int kPassSlots = 4;            // modules per MMA pass
@@ -103,7 +105,7 @@ conv0_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int s, int8_t
 }
 
 // ---- the convolution -----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict__ w8,
                     const float* __restrict__ wscale, const float* __restrict__ params, PnNetDesc nd,
                     const uint32_t* __restrict__ masks, int B, int T, TcGeom gm, float* __restrict__ Y,
@@ -111,14 +113,16 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* frame_s = smem;
     uint8_t* Bs = smem + (size_t)gm.nst * gm.stage_bytes;
-    float* sbuf = reinterpret_cast<float*>(Bs + (size_t)(nd.M + 1) * kSlotBytes);   // [M][16] scale[8], bias[8]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sbuf + nd.M * 16);
+    float* sbuf = reinterpret_cast<float*>(Bs + (size_t)(nd.M + 1) * kSlotBytes);   // [M][32] s0[8] s1[8] s2[8] bias[8]
+    int* jtab = reinterpret_cast<int*>(sbuf + nd.M * 32);                            // [M] module id of each slot
+    uint64_t* bars = reinterpret_cast<uint64_t*>(jtab + ((nd.M + 1) & ~1));
     uint64_t* frame_full = bars;
     uint64_t* frame_empty = bars + gm.nst;
     uint64_t* acc_full = bars + 2 * gm.nst;
     uint64_t* acc_empty = acc_full + kAccStages;
     uint64_t* path_ready = acc_empty + kAccStages;
     uint64_t* drain = path_ready + 1;
+    uint64_t* b_full = drain + 1;
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -131,6 +135,7 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
         for (int i = 0; i < kAccStages; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
         mbar_init(path_ready, 1);
         mbar_init(drain, 1);
+        mbar_init(b_full, 1);
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(&tmem_base_s, kAccStages * kAccCols);
@@ -156,9 +161,9 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
         }
     } else if (warp == 1) {
         // ================= B gather + MMA issue =================
-        int stage = 0, acc = 0, cur_path = -1, ns = 0;
-        uint32_t fphase = 0, drain_phase = 0;
-        uint32_t fills[kAccStages] = {0, 0};
+        int stage = 0, cur_path = -1, ns = 0;
+        uint32_t fphase = 0, drain_phase = 0, b_phase = 0, tilec = 0;
+        uint32_t fills[kAccStages] = {0, 0, 0, 0};
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
@@ -172,16 +177,19 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
                 }
                 const uint32_t mask = masks[p * nd.L];
                 ns = __popc(mask);
+                if (lane == 0 && ns > 0) mbar_expect_tx(b_full, (uint32_t)(ns * kSlotBytes));
+                __syncwarp();
                 for (int slot = 0; slot < ns; ++slot) {
                     const int j = __fns(mask, 0, slot + 1);
-                    const int4* src = reinterpret_cast<const int4*>(w8 + (size_t)j * kSlotBytes);
-                    int4* dst = reinterpret_cast<int4*>(Bs + (size_t)slot * kSlotBytes);
-                    for (int i = lane; i < kSlotBytes / 16; i += 32) dst[i] = src[i];
-                    if (lane < 8) sbuf[slot * 16 + lane] = wscale[j * 8 + lane];
-                    else if (lane < 16)
-                        sbuf[slot * 16 + lane] = params[nd.convW_base[0] + (long long)j * nd.conv_stride[0] + nd.convb_off[0] + lane - 8];
+                    // the module's digit rows arrive by one bulk copy (async proxy: no staging registers)
+                    if (lane == 0) bulk_g2s(Bs + (size_t)slot * kSlotBytes, w8 + (size_t)j * kSlotBytes, kSlotBytes, b_full);
+                    // digit weights 1, 256, 65536 folded into the per-channel scale (exact: powers of two)
+                    if (lane < 24) sbuf[slot * 32 + lane] = wscale[j * 8 + (lane & 7)] * (float)(1 << (8 * (lane >> 3)));
+                    else
+                        sbuf[slot * 32 + lane] = params[nd.convW_base[0] + (long long)j * nd.conv_stride[0] + nd.convb_off[0] + lane - 24];
+                    if (lane == 0) jtab[slot] = j;
                 }
-                fence_proxy_async();
+                if (ns > 0) { mbar_wait(b_full, b_phase); b_phase ^= 1; }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(path_ready);
                 cur_path = p;
@@ -190,7 +198,8 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
             tc_fence_after();
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
-            for (int tile = 0; tile < gm.tiles; ++tile) {
+            for (int tile = 0; tile < gm.tiles && npass > 0; ++tile, ++tilec) {
+                const int acc = tilec & (kAccStages - 1);
                 for (int pass = 0; pass < npass; ++pass) {
                     mbar_wait(&acc_empty[acc], (fills[acc] & 1) ^ 1);
                     tc_fence_after();
@@ -216,7 +225,6 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
                     }
                     __syncwarp();
                     ++fills[acc];
-                    acc ^= 1;
                 }
             }
             // the frame stage is free once every MMA issued so far has completed
@@ -230,10 +238,11 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
     } else {
         // ================= epilogue: thread = TMEM lane = output pixel of the tile =================
         const int quad = warp & 3;
+        const int group = (warp - 2) >> 2;                    // 0: warps 2-5, 1: warps 6-9
         const int L = quad * 32 + lane;
-        int acc = 0, cur_path = -1, ns = 0;
-        uint32_t path_phase = 0, mask = 0;
-        uint32_t fills[kAccStages] = {0, 0};
+        int cur_path = -1, ns = 0;
+        uint32_t path_phase = 0, mask = 0, tilec = 0;
+        uint32_t fills[kAccStages] = {0, 0, 0, 0};
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
@@ -246,10 +255,12 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             if (npass == 0) {     // no active module in layer 0: the layer output is exactly zero
                 float4* yo = reinterpret_cast<float4*>(Y + (size_t)t * npix * PN_F);
-                for (int i = threadIdx.x - 64; i < npix * 2; i += 128) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = threadIdx.x - 64; i < npix * 2; i += 256) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 continue;
             }
-            for (int tile = 0; tile < gm.tiles; ++tile) {
+            for (int tile = 0; tile < gm.tiles; ++tile, ++tilec) {
+                if ((int)(tilec & 1) != group) continue;
+                const int acc = tilec & (kAccStages - 1);
                 const int m = tile * 128 + L;
                 const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
                 const bool valid = ox < gm.OW && oy < gm.OH;
@@ -269,24 +280,26 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
                         tmem_ld8(tbase + sl * 24 + 16, d2);
                         tmem_ld_wait();
                         const int slot = pass * kPassSlots + sl;
-                        const float* sb = sbuf + slot * 16;
+                        const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
+                        float s0[8], s1[8], s2[8], bi[8];
+                        *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
+                        *reinterpret_cast<float4*>(&s1[0]) = sb[2]; *reinterpret_cast<float4*>(&s1[4]) = sb[3];
+                        *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
+                        *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
                         unsigned bits = 0;
 #pragma unroll
                         for (int c = 0; c < 8; ++c) {
-                            const long long Q = (long long)(int)d0[c] + ((long long)(int)d1[c] << 8) +
-                                                ((long long)(int)d2[c] << 16);
-                            const float pre = fmaf((float)Q, sb[c], sb[8 + c]);
+                            // |D| < 2^24: the int -> float conversions are exact; one rounding per fma
+                            float pre = fmaf((float)(int)d2[c], s2[c], bi[c]);
+                            pre = fmaf((float)(int)d1[c], s1[c], pre);
+                            pre = fmaf((float)(int)d0[c], s0[c], pre);
                             if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
                         }
-                        if (valid) {
-                            const int j = __fns(mask, 0, slot + 1);
-                            R[((size_t)t * nd.M + j) * npix + pix] = (uint8_t)bits;
-                        }
+                        if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
                     }
                     tc_fence_before();
                     mbar_arrive(&acc_empty[acc]);
                     ++fills[acc];
-                    acc ^= 1;
                 }
                 if (valid) {
                     float4* yo = reinterpret_cast<float4*>(Y + ((size_t)t * npix + pix) * PN_F);
@@ -600,7 +613,8 @@ bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
     g.ksteps = s / 2;
     g.mq = (rows + 31) & ~31;
     if (g.row_bytes % 16 || g.Hs * g.Ws > region_blocks || g.mq + g.Ws + 1 > region_blocks) return false;
-    const size_t fixed = (size_t)(nd.M + 1) * kSlotBytes + (size_t)nd.M * 16 * sizeof(float) + 64 * sizeof(uint64_t);
+    const size_t fixed = (size_t)(nd.M + 1) * kSlotBytes + (size_t)nd.M * 32 * sizeof(float) +
+                         (size_t)(nd.M + 2) * sizeof(int) + 64 * sizeof(uint64_t);
     for (g.nst = 3; g.nst >= 2; --g.nst) {
         smem_bytes = (size_t)g.nst * g.stage_bytes + fixed;
         if (smem_bytes <= 220 * 1024) return true;
@@ -638,7 +652,7 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     const int grid = T < h->num_sms ? T : h->num_sms;
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + 0, st);
-        conv0_fwd_tc_kernel<<<grid, kTcThreads, smem_bytes, st>>>(frames, w8, wscale, h->params, nd, h->d_masks, B, T, g,
+        conv0_fwd_tc_kernel<<<grid, kFwdThreads, smem_bytes, st>>>(frames, w8, wscale, h->params, nd, h->d_masks, B, T, g,
                                                                  h->act[0], h->rmask[0]);
     }
     PN_LAUNCH_CHECK(h, "conv0_fwd_tc_kernel");
