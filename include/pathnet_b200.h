@@ -195,6 +195,10 @@ typedef struct pn_profile_entry {
     int32_t launches;       /* launches the sum covers (<= 64 most recent)     */
 } pn_profile_entry;
 
+/* Development aid: with PN_TC_DEBUG=1 in the environment at pn_create, the
+ * tensor-core layer-0 kernel records per-CTA wait cycles; copies them out. */
+PN_API int pn_debug_read(pn_handle* h, long long* out_host, int capacity);
+
 /* When on, every kernel launch is bracketed by cudaEventRecord on the launch
  * stream.  Resets the counters. */
 PN_API int pn_profile_enable(pn_handle* h, int on);

@@ -52,6 +52,7 @@ SIGNATURES = {
     "pn_tensor_table": (_i, [_vp, C.POINTER(PnTensorDesc), _i]),
     "pn_last_lin": (_i, [_vp]),
     "pn_workspace_bytes": (C.c_int64, [_vp]),
+    "pn_debug_read": (_i, [_vp, _vp, _i]),
     "pn_launch_count": (C.c_int64, [_vp]),
     "pn_profile_enable": (_i, [_vp, _i]),
     "pn_profile_read": (_i, [_vp, C.POINTER(PnProfileEntry), _i]),

@@ -1,0 +1,102 @@
+// Development probe: cycles per tcgen05.mma kind::i8 for the operand layouts / shapes of the conv0 kernels.
+#include <cstdio>
+#include <cstdlib>
+#include "../pn_tc.cuh"
+using namespace pntc;
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA error %s at %d\n", cudaGetErrorString(e), __LINE__); exit(1); } } while (0)
+
+// cfg: M, N, a_off (bytes added to the A start), a_lbo, a_sbo, b_lbo, b_sbo, a_mn, b_mn, reps
+// cfg[11]: number of extra warps that hammer TMEM loads (tcgen05.ld) while the MMAs run; cfg[12]: extra warps doing LDS
+__global__ void __launch_bounds__(384) timing(const int* cfg, long long* out) {
+    extern __shared__ __align__(1024) uint8_t sm[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tbase;
+    __shared__ volatile int done;
+    if (threadIdx.x == 0) done = 0;
+    for (int i = threadIdx.x; i < 160 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(sm)[i] = i * 2654435761u;
+    fence_proxy_async();
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); fence_mbar_init(); }
+    if (threadIdx.x < 32) tmem_alloc(&tbase, 512);
+    tc_fence_before(); __syncthreads(); tc_fence_after();
+    const uint32_t td = tbase;
+    if (threadIdx.x == 0) {
+        const int M = cfg[0], N = cfg[1], reps = cfg[9];
+        const uint32_t idesc = make_idesc_i8(M, N, 0, 1, cfg[7], cfg[8]);
+        const uint64_t ad = make_smem_desc(smem_u32(sm) + cfg[2], cfg[3], cfg[4]);
+        const uint64_t bd = make_smem_desc(smem_u32(sm) + 96 * 1024, cfg[5], cfg[6]);
+        const long long t0 = clock64();
+        const int nacc = cfg[10];     // MMAs rotate over this many independent accumulators
+        __shared__ uint64_t bar2;
+        if (cfg[9] == 2001) {          // commit + fence every 8 MMAs, descriptors advanced per MMA (like the conv kernel)
+            mbar_init(&bar2, 1);
+            for (int i = 0; i < reps; i += 8) {
+                tc_fence_after();
+#pragma unroll
+                for (int j = 0; j < 8; ++j) umma_i8(td + ((i >> 3) & 3) * 128, ad + (uint64_t)(j * 8), bd + (uint64_t)(j * 8), idesc, j ? 1u : 0u);
+                umma_commit(&bar2);
+            }
+        } else if (cfg[9] == 2002) {   // as 2001 but additionally wait for every commit before the next group
+            mbar_init(&bar2, 1);
+            uint32_t ph = 0;
+            for (int i = 0; i < reps; i += 8) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) umma_i8(td + ((i >> 3) & 3) * 128, ad + (uint64_t)(j * 8), bd + (uint64_t)(j * 8), idesc, j ? 1u : 0u);
+                umma_commit(&bar2);
+                mbar_wait(&bar2, ph); ph ^= 1;
+                tc_fence_after();
+            }
+        } else
+        if (nacc == 4) { for (int i = 0; i < reps; ++i) umma_i8(td + (i & 3) * 128, ad, bd, idesc, i >= 4); }
+        else if (nacc == 2) { for (int i = 0; i < reps; ++i) umma_i8(td + (i & 1) * 128, ad, bd, idesc, i >= 2); }
+        else { for (int i = 0; i < reps; ++i) umma_i8(td, ad, bd, idesc, i >= 1); }
+        const long long t1 = clock64();
+        umma_commit(&bar);
+        mbar_wait(&bar, 0);
+        const long long t2 = clock64();
+        out[0] = t1 - t0; out[1] = t2 - t0;
+        done = 1;
+    } else if (threadIdx.x >= 128) {
+        const int w = (threadIdx.x >> 5) - 4;            // 0..7
+        unsigned acc = 0;
+        if (w < cfg[11]) {
+            while (!done) {
+                uint32_t r0[8], r1[8], r2[8];
+                const uint32_t ta = td + ((uint32_t)((w & 3) * 32) << 16) + 256;
+                tmem_ld8(ta, r0); tmem_ld8(ta + 8, r1); tmem_ld8(ta + 16, r2);
+                tmem_ld_wait();
+                for (int i = 0; i < 8; ++i) acc += r0[i] ^ r1[i] ^ r2[i];
+            }
+        } else if (w < cfg[11] + cfg[12]) {
+            while (!done) {
+                const uint4 v = reinterpret_cast<const uint4*>(sm)[(threadIdx.x * 37 + acc) & 4095];
+                acc += v.x ^ v.y ^ v.z ^ v.w;
+            }
+        }
+        if (acc == 0x12345) out[2] = acc;
+    }
+    __syncthreads();
+    tc_fence_before(); __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc(td, 512);
+}
+
+int main() {
+    int* cfg_d; long long* out_d;
+    CK(cudaMalloc(&cfg_d, 64)); CK(cudaMalloc(&out_d, 32));
+    CK(cudaFuncSetAttribute(timing, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    struct C { const char* name; int v[13]; };
+    const int R = 7056;
+    C cases[] = {
+        {"M128 N80 back to back, one commit         ", {128, 80, 0, R, 128, 128, 2048, 0, 0, 2000, 4, 0, 0}},
+        {"M128 N80 commit+fence every 8, varying desc", {128, 80, 0, R, 128, 128, 2048, 0, 0, 2001, 4, 0, 0}},
+        {"M128 N80 commit AND WAIT every 8           ", {128, 80, 0, R, 128, 128, 2048, 0, 0, 2002, 4, 0, 0}},
+    };
+    for (auto& c : cases) {
+        CK(cudaMemcpy(cfg_d, c.v, sizeof(c.v), cudaMemcpyHostToDevice));
+        timing<<<1, 384, 160 * 1024>>>(cfg_d, out_d);
+        CK(cudaDeviceSynchronize());
+        long long o[2];
+        CK(cudaMemcpy(o, out_d, 16, cudaMemcpyDeviceToHost));
+        printf("%s issue %.1f cyc/mma, complete %.1f cyc/mma\n", c.name, (double)o[0] / c.v[9], (double)o[1] / c.v[9]);
+    }
+    return 0;
+}

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -180,6 +181,10 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
         h->num_sms = prop.multiProcessorCount;
         h->tc_conv0 = !(c.flags & 1) && prop.major == 10 && pn_conv0_tc_supported(h);
         if (h->tc_conv0) PN_TRY(dev_alloc(h, &h->tc_w8, pn_conv0_tc_scratch_bytes(h)));
+        if (h->tc_conv0 && getenv("PN_TC_DEBUG")) {
+            PN_TRY(dev_alloc(h, &h->tc_dbg, (size_t)h->num_sms * 8));
+            PN_TRYC(cudaMemset(h->tc_dbg, 0, (size_t)h->num_sms * 8 * sizeof(long long)));
+        }
     }
     // staging for the host-pointer entry point
     PN_TRY(dev_alloc(h, &h->st_actions, T));
@@ -202,7 +207,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     cudaFree(h->hbuf); cudaFree(h->lmask); cudaFree(h->dzv); cudaFree(h->dh); cudaFree(h->loss_t);
     cudaFree(h->head_part); cudaFree(h->d_masks); cudaFree(h->d_list); cudaFree(h->d_list_count);
     cudaFree(h->d_frozen); cudaFree(h->d_chunks); cudaFree(h->d_tensor_chunk0); cudaFree(h->d_tensor_nchunks);
-    cudaFree(h->tc_w8);
+    cudaFree(h->tc_w8); cudaFree(h->tc_dbg);
     cudaFree(h->d_chunk_ss); cudaFree(h->st_frames); cudaFree(h->st_actions); cudaFree(h->st_td);
     cudaFree(h->st_r); cudaFree(h->st_loss);
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
@@ -214,6 +219,15 @@ extern "C" PN_API int64_t pn_slab_floats(const pn_handle* h) { return h ? h->sla
 extern "C" PN_API int pn_num_tensors(const pn_handle* h) { return h ? (int)h->tensors.size() : 0; }
 extern "C" PN_API int pn_last_lin(const pn_handle* h) { return h ? h->nd.last_lin : 0; }
 extern "C" PN_API int64_t pn_workspace_bytes(const pn_handle* h) { return h ? h->workspace_bytes : 0; }
+
+extern "C" PN_API int pn_debug_read(pn_handle* h, long long* out_host, int capacity) {
+    if (!h || !h->tc_dbg) return 0;
+    const int n = h->num_sms * 8;
+    if (capacity < n) return -1;
+    cudaDeviceSynchronize();
+    cudaMemcpy(out_host, h->tc_dbg, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost);
+    return n;
+}
 
 extern "C" PN_API int64_t pn_launch_count(const pn_handle* h) { return h ? h->launches : 0; }
 

@@ -8,8 +8,8 @@
 //  * space-to-depth: the 8x8/4 convolution is a 2x2/1 convolution over a 21x21 grid of 4x4x4-byte
 //    blocks.  A frame is staged in shared memory as 4 regions (g = raw row within a block); region g
 //    holds raw rows g, g+4, ... back to back, i.e. 16 bytes per block, blocks in raster order.  The
-//    copy is one cp.async.bulk per raw row: no im2col, no conversion, every frame byte is read from HBM
-//    once.
+//    copy is 16-byte cp.async straight from the u8 frame: no im2col, no conversion, every frame byte
+//    is read from HBM once.
 //  * the A operand of tap (dy,dx) is that SAME buffer read through a shifted descriptor: row m of the
 //    MMA (block index m = oy*21+ox) starts at byte (m + dy*21 + dx)*16 of each region (K-major, no
 //    swizzle: 8 blocks x 16 B core matrices, SBO = 128 B, LBO = region size).  Rows with ox == 20 or
@@ -23,11 +23,13 @@
 //    in fp32 (the integer sums convert exactly), ReLU, ascending-j sum, ReLU bit mask for backward.
 //
 // Warp roles (320 threads, one CTA per SM, persistent over a contiguous range of transitions):
-//   warp 0  bulk-copy producer (frames -> smem ring), warp 1  TMEM owner + B gather + MMA issue,
-//   warps 2-9  two epilogue groups of four warps (one TMEM lane quadrant each); consecutive 128-row
-//   tiles alternate between the groups and rotate through four TMEM accumulator stages.
+//   warps 0-7  two epilogue groups of four warps (one TMEM lane quadrant each); consecutive 128-row
+//   tiles alternate between the groups and rotate through four TMEM accumulator stages,
+//   warp 8  TMA producer (frames -> smem ring), warp 9  TMEM owner + B gather + MMA issue.
 #include "pn_internal.cuh"
 #include "pn_tc.cuh"
+
+#include <cuda.h>
 
 #include <algorithm>
 
@@ -69,7 +71,9 @@ conv0_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int s, int8_t
     float w[8];
 #pragma unroll
     for (int c = 0; c < 8; ++c) w[c] = kk < KK ? W[kk * 8 + c] : 0.f;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // broadcast through a shuffle so that the compiler knows the warp index is warp-uniform (role branches
+    // then count as uniform control flow and the MMA operands can live in uniform registers)
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         float m = fabsf(w[c]);
@@ -104,12 +108,23 @@ conv0_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int s, int8_t
     }
 }
 
+// Stage one frame with ONE 4-D TMA load.  The tensor map views the u8 frames as
+// [t][g = raw row % s][Y = raw row / s][W*C/4 u32] (strides 336*s, 336, H*W*C bytes for 84x84x4), so a box
+// {W*C/4, Hs, s, 1} lands in shared memory as s regions of Hs*Ws 16-byte blocks in raster order.
+// (One cp.async.bulk per 336-byte raw row was measured at ~100 cycles of issue per copy -- 84 copies per
+// frame held the tensor pipe at 16 % -- and a single warp of 16-byte cp.async was slower still.)
+__device__ __forceinline__ void stage_frame_tma(uint8_t* dst, const CUtensorMap* tmap, int t, const TcGeom& gm,
+                                                uint64_t* bar) {
+    mbar_expect_tx(bar, (uint32_t)gm.frame_bytes);
+    tma_load_4d(dst, tmap, 0, 0, 0, t, bar);
+}
+
 // ---- the convolution -----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kFwdThreads, 1)
-conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict__ w8,
+conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __restrict__ w8,
                     const float* __restrict__ wscale, const float* __restrict__ params, PnNetDesc nd,
                     const uint32_t* __restrict__ masks, int B, int T, TcGeom gm, float* __restrict__ Y,
-                    uint8_t* __restrict__ R) {
+                    uint8_t* __restrict__ R, long long* __restrict__ dbg) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* frame_s = smem;
     uint8_t* Bs = smem + (size_t)gm.nst * gm.stage_bytes;
@@ -125,7 +140,9 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
     uint64_t* b_full = drain + 1;
     __shared__ uint32_t tmem_base_s;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // broadcast through a shuffle so that the compiler knows the warp index is warp-uniform (role branches
+    // then count as uniform control flow and the MMA operands can live in uniform registers)
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int t_lo = (int)((long long)T * blockIdx.x / gridDim.x);
     const int t_hi = (int)((long long)T * (blockIdx.x + 1) / gridDim.x);
     const int npix = gm.OH * gm.OW;
@@ -138,46 +155,54 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
         mbar_init(b_full, 1);
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(&tmem_base_s, kAccStages * kAccCols);
+    // Warp ids matter: within an SM sub-partition the scheduler prefers the highest warp id, so the two
+    // single-thread roles that everything else waits for (TMA producer = warp 8, MMA issue = warp 9) sit
+    // above the eight epilogue warps.  (With the MMA warp at id 1 it was measured at ~205 cycles per MMA
+    // against 52 in isolation: it lost arbitration to the epilogue warps of its sub-partition.)
+    if (warp == 9) tmem_alloc(&tmem_base_s, kAccStages * kAccCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
 
-    if (warp == 0) {
-        // ================= producer: one bulk copy per raw frame row =================
+    if (warp == 8) {
+        // ================= producer: one TMA load per frame =================
+        if (lane == 0) tma_prefetch_desc(&tmap);
         int stage = 0;
         uint32_t phase = 0;
+        long long w_empty = 0, t_begin = clock64();
         for (int t = t_lo; t < t_hi; ++t) {
+            const long long c0 = clock64();
             mbar_wait(&frame_empty[stage], phase ^ 1);
-            if (lane == 0) mbar_expect_tx(&frame_full[stage], (uint32_t)gm.frame_bytes);
+            w_empty += clock64() - c0;
+            if (lane == 0) stage_frame_tma(frame_s + (size_t)stage * gm.stage_bytes, &tmap, t, gm, &frame_full[stage]);
             __syncwarp();
-            const uint8_t* src = frames + (size_t)t * gm.frame_bytes;
-            uint8_t* dst = frame_s + (size_t)stage * gm.stage_bytes;
-            for (int ry = lane; ry < gm.H; ry += 32)
-                bulk_g2s(dst + (ry % gm.s) * gm.region_bytes + (ry / gm.s) * gm.row_bytes, src + (size_t)ry * gm.row_bytes,
-                         (uint32_t)gm.row_bytes, &frame_full[stage]);
             if (++stage == gm.nst) { stage = 0; phase ^= 1; }
         }
-    } else if (warp == 1) {
+        if (dbg && lane == 0) { dbg[blockIdx.x * 8 + 0] = w_empty; dbg[blockIdx.x * 8 + 1] = clock64() - t_begin; }
+    } else if (warp == 9) {
         // ================= B gather + MMA issue =================
+        // Everything here is executed by the whole (converged) warp on warp-uniform values; only the
+        // tcgen05 / mbarrier-arrive instructions themselves are elected to one lane (see elect_one()).
         int stage = 0, cur_path = -1, ns = 0;
         uint32_t fphase = 0, drain_phase = 0, b_phase = 0, tilec = 0;
-        uint32_t fills[kAccStages] = {0, 0, 0, 0};
+        uint32_t fill_par = 0;                       // bit a = parity of the number of fills of accumulator stage a
+        const long long t_begin = clock64();
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
                 if (cur_path >= 0) {
                     // every MMA that reads the old B has completed, every accumulator has been drained
-                    if (lane == 0) umma_commit(drain);
+                    if (elect_one()) umma_commit(drain);
                     __syncwarp();
                     mbar_wait(drain, drain_phase);
                     drain_phase ^= 1;
-                    for (int a = 0; a < kAccStages; ++a) mbar_wait(&acc_empty[a], (fills[a] & 1) ^ 1);
+                    for (int a = 0; a < kAccStages; ++a) mbar_wait(&acc_empty[a], ((fill_par >> a) & 1u) ^ 1u);
                 }
-                const uint32_t mask = masks[p * nd.L];
+                // the OR-reduction hands the compiler a value it knows to be warp-uniform
+                const uint32_t mask = __reduce_or_sync(0xffffffffu, masks[p * nd.L]);
                 ns = __popc(mask);
-                if (lane == 0 && ns > 0) mbar_expect_tx(b_full, (uint32_t)(ns * kSlotBytes));
+                if (ns > 0 && elect_one()) mbar_expect_tx(b_full, (uint32_t)(ns * kSlotBytes));
                 __syncwarp();
                 for (int slot = 0; slot < ns; ++slot) {
                     const int j = __fns(mask, 0, slot + 1);
@@ -191,58 +216,56 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
                 }
                 if (ns > 0) { mbar_wait(b_full, b_phase); b_phase ^= 1; }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(path_ready);
+                if (elect_one()) mbar_arrive(path_ready);
                 cur_path = p;
             }
             mbar_wait(&frame_full[stage], fphase);
             tc_fence_after();
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
+            const uint32_t bsm = smem_u32(Bs);
             for (int tile = 0; tile < gm.tiles && npass > 0; ++tile, ++tilec) {
-                const int acc = tilec & (kAccStages - 1);
+                const uint32_t acc = tilec & (kAccStages - 1);
                 for (int pass = 0; pass < npass; ++pass) {
-                    mbar_wait(&acc_empty[acc], (fills[acc] & 1) ^ 1);
+                    mbar_wait(&acc_empty[acc], ((fill_par >> acc) & 1u) ^ 1u);
                     tc_fence_after();
-                    if (lane == 0) {
-                        const int nsl = min(kPassSlots, ns - pass * kPassSlots);
-                        const int N = (24 * nsl + 15) & ~15;
-                        const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
-                        const uint32_t bbase = smem_u32(Bs + (size_t)pass * kPassSlots * kSlotBytes);
-                        uint32_t accum = 0;
-                        for (int tap = 0; tap < 4; ++tap) {
-                            const int off = (tap >> 1) * gm.Ws + (tap & 1);
-                            for (int ks = 0; ks < gm.ksteps; ++ks) {
-                                const uint64_t ad = make_smem_desc(
-                                    fbase + (uint32_t)(2 * ks * gm.region_bytes + (tile * 128 + off) * 16),
-                                    (uint32_t)gm.region_bytes, 128);
-                                const uint64_t bd =
-                                    make_smem_desc(bbase + (uint32_t)((tap * gm.s + 2 * ks) * 128), 128, 2048);
-                                umma_i8(td + acc * kAccCols, ad, bd, idesc, accum);
-                                accum = 1;
-                            }
-                        }
-                        umma_commit(&acc_full[acc]);
+                    const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                    const int N = (24 * nsl + 15) & ~15;
+                    const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
+                    const uint32_t dcol = td + acc * kAccCols;
+                    const uint32_t bpass = bsm + (uint32_t)(pass * kPassSlots * kSlotBytes);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int tap = i >> 1, ks = i & 1;                  // 2 K-steps of 32 bytes per tap (s = 4)
+                        const int off = (tap >> 1) * gm.Ws + (tap & 1);
+                        const uint64_t ad = make_smem_desc(
+                            fbase + (uint32_t)(2 * ks * gm.region_bytes + (tile * 128 + off) * 16), (uint32_t)gm.region_bytes, 128);
+                        const uint64_t bd = make_smem_desc(bpass + (uint32_t)((tap * gm.s + 2 * ks) * 128), 128, 2048);
+                        if (i < 4 * gm.ksteps && elect_one()) umma_i8(dcol, ad, bd, idesc, i ? 1u : 0u);
                     }
+                    if (elect_one()) umma_commit(&acc_full[acc]);
                     __syncwarp();
-                    ++fills[acc];
+                    fill_par ^= 1u << acc;
                 }
             }
             // the frame stage is free once every MMA issued so far has completed
-            if (lane == 0) {
+            if (elect_one()) {
                 if (npass > 0) umma_commit(&frame_empty[stage]);
                 else mbar_arrive(&frame_empty[stage]);
             }
             __syncwarp();
             if (++stage == gm.nst) { stage = 0; fphase ^= 1; }
         }
+        if (dbg && lane == 0) dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
     } else {
         // ================= epilogue: thread = TMEM lane = output pixel of the tile =================
         const int quad = warp & 3;
-        const int group = (warp - 2) >> 2;                    // 0: warps 2-5, 1: warps 6-9
+        const int group = warp >> 2;                          // 0: warps 0-3, 1: warps 4-7
         const int L = quad * 32 + lane;
         int cur_path = -1, ns = 0;
         uint32_t path_phase = 0, mask = 0, tilec = 0;
         uint32_t fills[kAccStages] = {0, 0, 0, 0};
+        long long w_full = 0, t_begin = clock64();
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
@@ -255,7 +278,7 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             if (npass == 0) {     // no active module in layer 0: the layer output is exactly zero
                 float4* yo = reinterpret_cast<float4*>(Y + (size_t)t * npix * PN_F);
-                for (int i = threadIdx.x - 64; i < npix * 2; i += 256) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = threadIdx.x; i < npix * 2; i += 256) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 continue;
             }
             for (int tile = 0; tile < gm.tiles; ++tile, ++tilec) {
@@ -269,7 +292,9 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
 #pragma unroll
                 for (int c = 0; c < 8; ++c) sum[c] = 0.f;
                 for (int pass = 0; pass < npass; ++pass) {
+                    const long long ce0 = clock64();
                     mbar_wait(&acc_full[acc], fills[acc] & 1);
+                    w_full += clock64() - ce0;
                     tc_fence_after();
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const uint32_t tbase = td + ((uint32_t)(quad * 32) << 16) + acc * kAccCols;
@@ -308,10 +333,11 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
                 }
             }
         }
+        if (dbg && threadIdx.x == 0) { dbg[blockIdx.x * 8 + 6] = w_full; dbg[blockIdx.x * 8 + 7] = clock64() - t_begin; }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(td, kAccStages * kAccCols);
+    if (warp == 9) tmem_dealloc(td, kAccStages * kAccCols);
 }
 
 
@@ -328,7 +354,7 @@ conv0_fwd_tc_kernel(const uint8_t* __restrict__ frames, const int8_t* __restrict
 // One work item = (path, chunk of its transitions); the four tap accumulators live in TMEM (M = 64,
 // N = 32 columns per module) for the whole chunk and are flushed once into the partial-sum buffer that
 // conv_wgrad_reduce_kernel adds up in a fixed order.
-// Warp roles (192 threads): warp 0 frame producer, warp 1 MMA issue, warps 2-5 quantise dq and flush.
+// Warp roles (192 threads): warps 0-3 quantise dq and flush, warp 4 frame producer, warp 5 MMA issue.
 // =====================================================================================================
 constexpr int kWgDigits = 4;
 constexpr int kWgSlotCols = 8 * kWgDigits;      // 32 accumulator columns per module
@@ -355,7 +381,7 @@ __device__ __forceinline__ uint32_t nib_to_bytemask(unsigned nib) {
 }
 
 __global__ void __launch_bounds__(kTcThreads, 1)
-conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restrict__ dY, const uint8_t* __restrict__ R,
+conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ dY, const uint8_t* __restrict__ R,
                       const unsigned* __restrict__ absmax, PnNetDesc nd, const uint32_t* __restrict__ masks, int B,
                       int P, int cs, int nch, int nch_alloc, TcGeom gm, float* __restrict__ part) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -374,7 +400,9 @@ conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restric
     uint64_t* acc_empty = bars + 9;
     __shared__ uint32_t tmem_base_s;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // broadcast through a shuffle so that the compiler knows the warp index is warp-uniform (role branches
+    // then count as uniform control flow and the MMA operands can live in uniform registers)
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int npix = gm.OH * gm.OW;
     const int nitems = P * nch;
 
@@ -387,14 +415,16 @@ conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restric
         mbar_init(acc_empty, 128);
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(&tmem_base_s, 512);
+    // roles: warps 0-3 quantise + flush, warp 4 frame producer, warp 5 MMA issue (highest id = scheduler priority)
+    if (warp == 5) tmem_alloc(&tmem_base_s, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
 
-    if (warp == 0) {
+    if (warp == 4) {
         // ================= frame producer =================
+        if (lane == 0) tma_prefetch_desc(&tmap);
         int stage = 0;
         uint32_t phase = 0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
@@ -406,24 +436,21 @@ conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restric
                 for (int b = b_lo; b < b_hi; ++b) {
                     const size_t t = (size_t)p * B + b;
                     mbar_wait(&frame_empty[stage], phase ^ 1);
-                    if (lane == 0) mbar_expect_tx(&frame_full[stage], (uint32_t)gm.frame_bytes);
+                    if (lane == 0)
+                        stage_frame_tma(frame_s + (size_t)stage * gm.stage_bytes, &tmap, (int)t, gm, &frame_full[stage]);
                     __syncwarp();
-                    const uint8_t* src = frames + t * gm.frame_bytes;
-                    uint8_t* dst = frame_s + (size_t)stage * gm.stage_bytes;
-                    for (int ry = lane; ry < gm.H; ry += 32)
-                        bulk_g2s(dst + (ry % gm.s) * gm.region_bytes + (ry / gm.s) * gm.row_bytes,
-                                 src + (size_t)ry * gm.row_bytes, (uint32_t)gm.row_bytes, &frame_full[stage]);
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
         }
-    } else if (warp == 1) {
+    } else if (warp == 5) {
         // ================= MMA issue =================
+        // whole-warp, warp-uniform code; only the tcgen05 instructions are elected to one lane
         int stage = 0;
         uint32_t phase = 0, nflush = 0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int p = item / nch, ch = item % nch;
             const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
-            const int ns = __popc(masks[p * nd.L]);
+            const int ns = __popc(__reduce_or_sync(0xffffffffu, masks[p * nd.L]));
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             for (int pass = 0; pass < npass; ++pass) {
                 if (b_lo >= b_hi) continue;
@@ -437,26 +464,27 @@ conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restric
                     mbar_wait(&frame_full[stage], phase);
                     mbar_wait(&dq_full[stage], phase);
                     tc_fence_after();
-                    if (lane == 0) {
-                        const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
-                        const uint32_t qbase = smem_u32(dq_s + (size_t)stage * dq_stage_bytes);
-                        for (int ks = 0; ks < gm.mq / 32; ++ks) {
-                            const uint64_t bd = make_smem_desc(qbase + (uint32_t)(ks * 32 * 16), 128, (uint32_t)region_q);
-                            for (int tap = 0; tap < 4; ++tap) {
-                                const int off = (tap >> 1) * gm.Ws + (tap & 1);
-                                const uint64_t ad = make_smem_desc(fbase + (uint32_t)((ks * 32 + off) * 16), 128,
-                                                                   (uint32_t)gm.region_bytes);
-                                umma_i8(td + tap * kWgTapCols, ad, bd, idesc, accum);
-                            }
-                            accum = 1;
+                    const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
+                    const uint32_t qbase = smem_u32(dq_s + (size_t)stage * dq_stage_bytes);
+                    for (int ks = 0; ks < gm.mq / 32; ++ks) {
+                        const uint64_t bd = make_smem_desc(qbase + (uint32_t)(ks * 32 * 16), 128, (uint32_t)region_q);
+#pragma unroll
+                        for (int tap = 0; tap < 4; ++tap) {
+                            const int off = (tap >> 1) * gm.Ws + (tap & 1);
+                            const uint64_t ad = make_smem_desc(fbase + (uint32_t)((ks * 32 + off) * 16), 128,
+                                                               (uint32_t)gm.region_bytes);
+                            if (elect_one()) umma_i8(td + tap * kWgTapCols, ad, bd, idesc, accum);
                         }
+                        accum = 1;
+                    }
+                    if (elect_one()) {
                         umma_commit(&frame_empty[stage]);
                         umma_commit(&dq_empty[stage]);
                     }
                     __syncwarp();
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
-                if (lane == 0) umma_commit(acc_full);
+                if (elect_one()) umma_commit(acc_full);
                 __syncwarp();
                 ++nflush;
             }
@@ -464,7 +492,7 @@ conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restric
     } else {
         // ================= quantise dq per transition, flush the accumulators per (item, pass) =================
         const int quad = warp & 3;
-        const int tid = threadIdx.x - 64;                      // 0..127
+        const int tid = threadIdx.x;                           // 0..127
         int stage = 0;
         uint32_t phase = 0, nflush = 0;
         const unsigned am = *absmax;
@@ -592,7 +620,7 @@ conv0_wgrad_tc_kernel(const uint8_t* __restrict__ frames, const float* __restric
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 1) tmem_dealloc(td, 512);
+    if (warp == 5) tmem_dealloc(td, 512);
 }
 
 bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
@@ -605,14 +633,18 @@ bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
     if (g.OH != g.Hs - 1 || g.OW != g.Ws - 1) return false;
     const int rows = (g.OH - 1) * g.Ws + g.OW;
     g.tiles = (rows + 127) / 128;
-    const int region_blocks = (g.tiles * 128 + g.Ws + 1 + 7) & ~7;
+    // regions are packed (TMA box layout); shifted descriptors read up to `extent` blocks from a region's
+    // start, running into the next region / the padding behind the last one: any bytes are harmless there
+    // because those MMA rows are discarded (forward) or multiplied by zero gradients (weight gradient)
+    const int region_blocks = g.Hs * g.Ws;
     g.region_bytes = region_blocks * 16;
-    g.stage_bytes = s * g.region_bytes;
+    g.mq = (rows + 31) & ~31;
+    const int extent = std::max(g.tiles * 128, g.mq) + g.Ws + 2;
+    g.stage_bytes = (((s - 1) * g.region_bytes + extent * 16) + 1023) & ~1023;
     g.row_bytes = W * C;
     g.frame_bytes = H * W * C;
     g.ksteps = s / 2;
-    g.mq = (rows + 31) & ~31;
-    if (g.row_bytes % 16 || g.Hs * g.Ws > region_blocks || g.mq + g.Ws + 1 > region_blocks) return false;
+    if (g.row_bytes % 16 || g.row_bytes / 4 > 256 || g.Hs > 256) return false;
     const size_t fixed = (size_t)(nd.M + 1) * kSlotBytes + (size_t)nd.M * 32 * sizeof(float) +
                          (size_t)(nd.M + 2) * sizeof(int) + 64 * sizeof(uint64_t);
     for (g.nst = 3; g.nst >= 2; --g.nst) {
@@ -620,6 +652,32 @@ bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
         if (smem_bytes <= 220 * 1024) return true;
     }
     return false;
+}
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T, CUtensorMap* out) {
+    static PFN_encodeTiled encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+            return pn_fail(h, PN_ERR_CUDA, "cuTensorMapEncodeTiled is not available: %s", cudaGetErrorString(e));
+        encode = reinterpret_cast<PFN_encodeTiled>(fn);
+    }
+    if (reinterpret_cast<uintptr_t>(frames) & 15) return pn_fail(h, PN_ERR_INVALID, "frames must be 16-byte aligned");
+    const cuuint64_t dims[4] = {(cuuint64_t)(g.row_bytes / 4), (cuuint64_t)g.Hs, (cuuint64_t)g.s, (cuuint64_t)T};
+    const cuuint64_t strides[3] = {(cuuint64_t)g.row_bytes * g.s, (cuuint64_t)g.row_bytes, (cuuint64_t)g.frame_bytes};
+    const cuuint32_t box[4] = {(cuuint32_t)(g.row_bytes / 4), (cuuint32_t)g.Hs, (cuuint32_t)g.s, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<uint8_t*>(frames), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return pn_fail(h, PN_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return PN_OK;
 }
 
 }  // namespace
@@ -650,10 +708,12 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     PN_LAUNCH_CHECK(h, "conv0_wprep_kernel");
     PN_CUDA(h, cudaFuncSetAttribute(conv0_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int grid = T < h->num_sms ? T : h->num_sms;
+    CUtensorMap tmap;
+    if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + 0, st);
-        conv0_fwd_tc_kernel<<<grid, kFwdThreads, smem_bytes, st>>>(frames, w8, wscale, h->params, nd, h->d_masks, B, T, g,
-                                                                 h->act[0], h->rmask[0]);
+        conv0_fwd_tc_kernel<<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g,
+                                                                 h->act[0], h->rmask[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_fwd_tc_kernel");
     return PN_OK;
@@ -691,9 +751,11 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     PN_CUDA(h, cudaFuncSetAttribute(conv0_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int items = P * nch;
     const int grid = items < h->num_sms ? items : h->num_sms;
+    CUtensorMap tmap;
+    if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + 0, st);
-        conv0_wgrad_tc_kernel<<<grid, kTcThreads, smem_bytes, st>>>(frames, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
+        conv0_wgrad_tc_kernel<<<grid, kTcThreads, smem_bytes, st>>>(tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
                                                                    B, P, cs, nch, h->nch, g, h->wpart[0]);
     }
     PN_LAUNCH_CHECK(h, "conv0_wgrad_tc_kernel");

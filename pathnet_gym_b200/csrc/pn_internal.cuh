@@ -88,6 +88,7 @@ struct pn_handle {
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
     int num_sms = 148;
     uint8_t* tc_w8 = nullptr;           // [M][6144] int8 weight digits + [M][8] fp32 scales + batch max|dY|
+    long long* tc_dbg = nullptr;        // optional [num_sms][8] cycle counters (PN_TC_DEBUG=1), else null
     int last_wgrad_nch = 1;             // chunks per path used by the last tensor-core weight-gradient launch
     // host-call staging
     void* st_frames = nullptr; size_t st_frames_bytes = 0;

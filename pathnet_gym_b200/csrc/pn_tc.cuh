@@ -35,8 +35,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// The spin loop lives INSIDE the asm block: a C++ `while (!try_wait())` has a per-thread exit condition, which
+// makes nvcc treat everything after it as potentially divergent and keeps warp-uniform values (MMA
+// descriptors, loop counters) out of the uniform registers.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    while (!mbar_try_wait(bar, parity)) {}
+    asm volatile(
+        "{\n.reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
 }
 
 // ---- async (bulk) copies and proxy fence ----------------------------------------------------------
@@ -47,8 +58,39 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                  "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// 4-D tiled TMA load (tensor map built on the host with cuTensorMapEncodeTiled); completion on `bar`
+__device__ __forceinline__ void tma_load_4d(void* dst_smem, const void* tmap, int c0, int c1, int c2, int c3,
+                                            uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5}], [%6];" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(tmap), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const void* tmap) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+// 16-byte LDGSTS; completion of all of a thread's earlier cp.async is reported to `bar` by
+// cp_async_arrive_noinc (the barrier's expected count must include one arrival per issuing thread)
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src_gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 // make generic-proxy shared-memory writes visible to the async proxy (tensor core / bulk copy)
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// One lane of a converged warp.  tcgen05.mma / tcgen05.commit take their operands from UNIFORM registers:
+// when the surrounding code is executed by the whole warp on warp-uniform values and only the instruction
+// itself is guarded by elect_one(), nvcc keeps the descriptors in uniform registers and issues UTC*MMA back to
+// back.  Issuing from inside an `if (lane == 0)` region instead costs an ELECT + 7 x R2UR.BROADCAST + branch
+// loop per MMA (measured: ~140 cycles per MMA against a 52-cycle MMA).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n.reg .b32 rx;\n.reg .pred px;\nelect.sync rx|px, 0xffffffff;\nselp.u32 %0, 1, 0, px;\n}\n" : "=r"(pred));
+    return pred != 0;
+}
 
 // ---- TMEM ---------------------------------------------------------------------------------------------
 // one full warp; ncols power of two >= 32; the base address is written to *dst_smem
