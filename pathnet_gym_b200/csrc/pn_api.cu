@@ -181,6 +181,8 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
         h->num_sms = prop.multiProcessorCount;
         h->tc_conv0 = !(c.flags & 1) && prop.major == 10 && pn_conv0_tc_supported(h);
         if (h->tc_conv0) PN_TRY(dev_alloc(h, &h->tc_w8, pn_conv0_tc_scratch_bytes(h)));
+        h->tc_lin = !(c.flags & 2) && prop.major == 10 && pn_lin_tc_supported(h);
+        if (h->tc_lin) PN_TRY(dev_alloc(h, &h->tc_lin_buf, pn_lin_tc_scratch_bytes(h)));
         if (h->tc_conv0 && getenv("PN_TC_DEBUG")) {
             PN_TRY(dev_alloc(h, &h->tc_dbg, (size_t)h->num_sms * 8));
             PN_TRYC(cudaMemset(h->tc_dbg, 0, (size_t)h->num_sms * 8 * sizeof(long long)));
@@ -207,7 +209,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     cudaFree(h->hbuf); cudaFree(h->lmask); cudaFree(h->dzv); cudaFree(h->dh); cudaFree(h->loss_t);
     cudaFree(h->head_part); cudaFree(h->d_masks); cudaFree(h->d_list); cudaFree(h->d_list_count);
     cudaFree(h->d_frozen); cudaFree(h->d_chunks); cudaFree(h->d_tensor_chunk0); cudaFree(h->d_tensor_nchunks);
-    cudaFree(h->tc_w8); cudaFree(h->tc_dbg);
+    cudaFree(h->tc_w8); cudaFree(h->tc_dbg); cudaFree(h->tc_lin_buf);
     cudaFree(h->d_chunk_ss); cudaFree(h->st_frames); cudaFree(h->st_actions); cudaFree(h->st_td);
     cudaFree(h->st_r); cudaFree(h->st_loss);
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
@@ -267,7 +269,7 @@ extern "C" PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int c
         else if (slot < PN_PROF_LIN_FWD) { base = "conv_dgrad"; layer = slot - PN_PROF_CONV_DGRAD; }
         else {
             static const char* names[] = {"lin_fwd", "head_loss", "head_wgrad", "lin_dgrad", "lin_wgrad",
-                                          "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant"};
+                                          "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant", "lin_prep"};
             base = names[slot - PN_PROF_LIN_FWD];
         }
         if (layer >= 0) snprintf(out[n].name, sizeof(out[n].name), "%s_l%d", base, layer);

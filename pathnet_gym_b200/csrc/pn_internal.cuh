@@ -39,6 +39,7 @@ enum PnProfSlot {
     PN_PROF_RMS_UPDATE,
     PN_PROF_CONV0_WPREP,
     PN_PROF_CONV0_DQUANT,
+    PN_PROF_LIN_PREP,
     PN_PROF_NSLOTS
 };
 #define PN_PROF_RING 64
@@ -88,6 +89,8 @@ struct pn_handle {
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
     int num_sms = 148;
     uint8_t* tc_w8 = nullptr;           // [M][6144] int8 weight digits + [M][8] fp32 scales + batch max|dY|
+    bool tc_lin = false;                // tensor-core linear modules (pn_lin_tc.cu)
+    uint8_t* tc_lin_buf = nullptr;      // Wp | Xp | Dp  bf16 hi/lo block buffers
     long long* tc_dbg = nullptr;        // optional [num_sms][8] cycle counters (PN_TC_DEBUG=1), else null
     int last_wgrad_nch = 1;             // chunks per path used by the last tensor-core weight-gradient launch
     // host-call staging
@@ -142,6 +145,11 @@ bool pn_conv0_tc_supported(const pn_handle* h);
 size_t pn_conv0_tc_scratch_bytes(const pn_handle* h);
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
+// pn_lin_tc.cu
+bool pn_lin_tc_supported(const pn_handle* h);
+size_t pn_lin_tc_scratch_bytes(const pn_handle* h);
+int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st);
+int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st);
 // pn_rmsprop.cu
 int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st);
 int pn_launch_reinit(pn_handle* h, const float* backup, cudaStream_t st);

@@ -632,6 +632,7 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
         }
         PN_LAUNCH_CHECK(h, "conv_fwd_kernel");
     }
+    if (h->tc_lin) return pn_launch_lin_fwd_tc(h, B, st);
     dim3 grid(h->P, (nd.hidden + 63) / 64, (B + 31) / 32);
     {
         PnProfScope prof(h, PN_PROF_LIN_FWD, st);
@@ -678,7 +679,9 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         PN_LAUNCH_CHECK(h, "head_wgrad_reduce_kernel");
     }
     // linear modules
-    {
+    if (h->tc_lin) {
+        if (int rc = pn_launch_lin_bwd_tc(h, B, st)) return rc;
+    } else {
         const int K = nd.last_lin;
         dim3 g1(P, (K + 63) / 64, (B + 31) / 32);
         {

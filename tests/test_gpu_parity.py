@@ -212,7 +212,7 @@ def test_tensor_core_layer0_matches_cuda_core_path(eng_mod):
     masks[1, 0] = (1 << cfg.M) - 1
     fd, ad, tdd, rd = dev(frames), dev(actions), dev(td), dev(r)
     out = []
-    for flags in (0, 1):
+    for flags in (0, 3):
         pop = make_pop(eng_mod, cfg, P, B, params, masks, flags=flags)
         loss, pi, v = pop.train_step(fd, ad, tdd, rd, 0.01, want_outputs=True)
         out.append((pi.clone(), v.clone(), loss.clone(), pop.grads.clone()))
