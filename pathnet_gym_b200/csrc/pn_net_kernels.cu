@@ -612,6 +612,10 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
             if (int rc = pn_launch_conv0_fwd_tc(h, (const uint8_t*)frames, B, st)) return rc;
             continue;
         }
+        if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
+            if (int rc = pn_launch_conv_mid_fwd(h, l, B, st)) return rc;
+            continue;
+        }
         const int rpb = max(1, 128 / nd.OW[l]);
         const int nbands = (nd.OH[l] + rpb - 1) / rpb;
         const int in_rows = (min(rpb, nd.OH[l]) - 1) * nd.s[l] + nd.k[l];
@@ -703,6 +707,19 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     int nch_active = (B + cs - 1) / cs;
     for (int l = nd.nconv - 1; l >= 0; --l) {
         const int npix = nd.OH[l] * nd.OW[l];
+        if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
+            int nch_used = 1;
+            if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used)) return rc;
+            const int n1 = nd.KK[l] * PN_F + PN_F;
+            dim3 gr1(nd.M, (n1 + 255) / 256);
+            {
+                PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
+                conv_wgrad_reduce_kernel<<<gr1, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
+                                                              nch_used, h->grads);
+            }
+            PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
+            continue;
+        }
         if (l == 0 && is_u8 && h->tc_conv0) {
             if (int rc = pn_launch_conv0_wgrad_tc(h, (const uint8_t*)frames, B, st)) return rc;
             const int n0 = nd.KK[l] * PN_F + PN_F;
