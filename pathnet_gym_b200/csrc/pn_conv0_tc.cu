@@ -37,7 +37,7 @@ using namespace pntc;
 
 namespace {
 
-constexpr int kTcThreads = 192;          // weight-gradient kernel: producer, MMA, 4 quantise/flush warps
+constexpr int kTcThreads = 320;          // weight-gradient kernel: 8 quantise/flush warps, producer, MMA
 constexpr int kFwdThreads = 320;         // forward kernel: producer, MMA, 2 groups of 4 epilogue warps
 constexpr int kAccStages = 4;            // accumulator ring: tile c uses stage c%4, epilogue group c%2
 constexpr int kAccCols = 128;            // TMEM columns per accumulator stage (max N of one pass = 96)
@@ -138,6 +138,8 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
     uint64_t* path_ready = acc_empty + kAccStages;
     uint64_t* drain = path_ready + 1;
     uint64_t* b_full = drain + 1;
+    uint64_t* epi_idle = b_full + 1;      // all epilogue threads have finished the previous path (they still read
+                                          // its scales / module ids after releasing the accumulator stage)
     __shared__ uint32_t tmem_base_s;
 
     // broadcast through a shuffle so that the compiler knows the warp index is warp-uniform (role branches
@@ -153,6 +155,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         mbar_init(path_ready, 1);
         mbar_init(drain, 1);
         mbar_init(b_full, 1);
+        mbar_init(epi_idle, 256);
         fence_mbar_init();
     }
     // Warp ids matter: within an SM sub-partition the scheduler prefers the highest warp id, so the two
@@ -185,7 +188,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         // Everything here is executed by the whole (converged) warp on warp-uniform values; only the
         // tcgen05 / mbarrier-arrive instructions themselves are elected to one lane (see elect_one()).
         int stage = 0, cur_path = -1, ns = 0;
-        uint32_t fphase = 0, drain_phase = 0, b_phase = 0, tilec = 0;
+        uint32_t fphase = 0, drain_phase = 0, b_phase = 0, idle_phase = 0, tilec = 0;
         uint32_t fill_par = 0;                       // bit a = parity of the number of fills of accumulator stage a
         const long long t_begin = clock64();
         for (int t = t_lo; t < t_hi; ++t) {
@@ -198,6 +201,8 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     mbar_wait(drain, drain_phase);
                     drain_phase ^= 1;
                     for (int a = 0; a < kAccStages; ++a) mbar_wait(&acc_empty[a], ((fill_par >> a) & 1u) ^ 1u);
+                    mbar_wait(epi_idle, idle_phase);
+                    idle_phase ^= 1;
                 }
                 // the OR-reduction hands the compiler a value it knows to be warp-uniform
                 const uint32_t mask = __reduce_or_sync(0xffffffffu, masks[p * nd.L]);
@@ -269,6 +274,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
+                if (cur_path >= 0) mbar_arrive(epi_idle);
                 mbar_wait(path_ready, path_phase);
                 path_phase ^= 1;
                 cur_path = p;
@@ -298,33 +304,42 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     tc_fence_after();
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const uint32_t tbase = td + ((uint32_t)(quad * 32) << 16) + acc * kAccCols;
-                    for (int sl = 0; sl < nsl; ++sl) {
-                        uint32_t d0[8], d1[8], d2[8];
-                        tmem_ld8(tbase + sl * 24, d0);
-                        tmem_ld8(tbase + sl * 24 + 8, d1);
-                        tmem_ld8(tbase + sl * 24 + 16, d2);
-                        tmem_ld_wait();
-                        const int slot = pass * kPassSlots + sl;
-                        const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
-                        float s0[8], s1[8], s2[8], bi[8];
-                        *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
-                        *reinterpret_cast<float4*>(&s1[0]) = sb[2]; *reinterpret_cast<float4*>(&s1[4]) = sb[3];
-                        *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
-                        *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
-                        unsigned bits = 0;
+                    uint32_t dd[kPassSlots][3][8];              // every digit plane of the pass, one wait
 #pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            // |D| < 2^24: the int -> float conversions are exact; one rounding per fma
-                            float pre = fmaf((float)(int)d2[c], s2[c], bi[c]);
-                            pre = fmaf((float)(int)d1[c], s1[c], pre);
-                            pre = fmaf((float)(int)d0[c], s0[c], pre);
-                            if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
+                    for (int sl = 0; sl < kPassSlots; ++sl) {
+                        if (sl < nsl) {
+                            tmem_ld8(tbase + sl * 24, dd[sl][0]);
+                            tmem_ld8(tbase + sl * 24 + 8, dd[sl][1]);
+                            tmem_ld8(tbase + sl * 24 + 16, dd[sl][2]);
                         }
-                        if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
                     }
+                    tmem_ld_wait();
+                    // the accumulator stage can be refilled while this thread does its arithmetic
                     tc_fence_before();
                     mbar_arrive(&acc_empty[acc]);
                     ++fills[acc];
+#pragma unroll
+                    for (int sl = 0; sl < kPassSlots; ++sl) {
+                        if (sl < nsl) {
+                            const int slot = pass * kPassSlots + sl;
+                            const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
+                            float s0[8], s1[8], s2[8], bi[8];
+                            *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
+                            *reinterpret_cast<float4*>(&s1[0]) = sb[2]; *reinterpret_cast<float4*>(&s1[4]) = sb[3];
+                            *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
+                            *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
+                            unsigned bits = 0;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {
+                                // |D| < 2^24: the int -> float conversions are exact; one rounding per fma
+                                float pre = fmaf((float)(int)dd[sl][2][c], s2[c], bi[c]);
+                                pre = fmaf((float)(int)dd[sl][1][c], s1[c], pre);
+                                pre = fmaf((float)(int)dd[sl][0][c], s0[c], pre);
+                                if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
+                            }
+                            if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
+                        }
+                    }
                 }
                 if (valid) {
                     float4* yo = reinterpret_cast<float4*>(Y + ((size_t)t * npix + pix) * PN_F);
@@ -354,7 +369,8 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
 // One work item = (path, chunk of its transitions); the four tap accumulators live in TMEM (M = 64,
 // N = 32 columns per module) for the whole chunk and are flushed once into the partial-sum buffer that
 // conv_wgrad_reduce_kernel adds up in a fixed order.
-// Warp roles (192 threads): warps 0-3 quantise dq and flush, warp 4 frame producer, warp 5 MMA issue.
+// Warp roles (320 threads): warps 0-7 quantise dq and flush (two groups of four: a group flushes two of the
+// four tap accumulators), warp 8 frame producer, warp 9 MMA issue.
 // =====================================================================================================
 constexpr int kWgDigits = 4;
 constexpr int kWgSlotCols = 8 * kWgDigits;      // 32 accumulator columns per module
@@ -390,7 +406,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     uint8_t* frame_s = smem;
     uint8_t* dq_s = smem + 2 * (size_t)gm.stage_bytes;
     // the dq ring doubles as the 16 KB scratch of the bias-gradient reduction at flush time
-    const int dq_total = max(2 * dq_stage_bytes, 128 * 32 * (int)sizeof(float));
+    const int dq_total = max(2 * dq_stage_bytes, 256 * 32 * (int)sizeof(float));
     uint64_t* bars = reinterpret_cast<uint64_t*>(dq_s + dq_total);
     uint64_t* frame_full = bars;          // [2]
     uint64_t* frame_empty = bars + 2;     // [2]
@@ -409,20 +425,20 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
             mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1);
-            mbar_init(&dq_full[i], 128); mbar_init(&dq_empty[i], 1);
+            mbar_init(&dq_full[i], 256); mbar_init(&dq_empty[i], 1);
         }
         mbar_init(acc_full, 1);
-        mbar_init(acc_empty, 128);
+        mbar_init(acc_empty, 256);
         fence_mbar_init();
     }
-    // roles: warps 0-3 quantise + flush, warp 4 frame producer, warp 5 MMA issue (highest id = scheduler priority)
-    if (warp == 5) tmem_alloc(&tmem_base_s, 512);
+    // roles: warps 0-7 quantise + flush, warp 8 frame producer, warp 9 MMA issue (highest id = scheduler priority)
+    if (warp == 9) tmem_alloc(&tmem_base_s, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
 
-    if (warp == 4) {
+    if (warp == 8) {
         // ================= frame producer =================
         if (lane == 0) tma_prefetch_desc(&tmap);
         int stage = 0;
@@ -442,7 +458,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
         }
-    } else if (warp == 5) {
+    } else if (warp == 9) {
         // ================= MMA issue =================
         // whole-warp, warp-uniform code; only the tcgen05 instructions are elected to one lane
         int stage = 0;
@@ -491,8 +507,8 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
         }
     } else {
         // ================= quantise dq per transition, flush the accumulators per (item, pass) =================
-        const int quad = warp & 3;
-        const int tid = threadIdx.x;                           // 0..127
+        const int quad = warp & 3, fgroup = warp >> 2;         // TMEM lane quadrant; flush group (taps 2*fgroup, +1)
+        const int tid = threadIdx.x;                           // 0..255
         int stage = 0;
         uint32_t phase = 0, nflush = 0;
         const unsigned am = *absmax;
@@ -522,22 +538,35 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     const size_t t = (size_t)p * B + b;
                     mbar_wait(&dq_empty[stage], phase ^ 1);
                     uint8_t* dq = dq_s + (size_t)stage * dq_stage_bytes;
-                    for (int m = tid; m < gm.mq; m += 128) {
-                        const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
-                        const bool valid = ox < gm.OW && oy < gm.OH;
-                        uint32_t w[4][2];                        // [digit][channels 0-3 / 4-7]
-                        float dv[8];
+                    for (int base = 0; base < gm.mq; base += 512) {
+                        // two raster rows per thread; all global loads are issued before either is processed
+                        int mm[2], pixv[2];
+                        bool val[2];
+                        float4 ga[2], gb[2];
+                        uint32_t rb[2];
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) dv[i] = 0.f;
+                        for (int u = 0; u < 2; ++u) {
+                            const int m = base + u * 256 + tid;
+                            mm[u] = m;
+                            const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
+                            val[u] = m < gm.mq && ox < gm.OW && oy < gm.OH;
+                            pixv[u] = oy * gm.OW + ox;
+                            ga[u] = gb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            rb[u] = 0;
+                            if (val[u]) {
+                                const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pixv[u]) * PN_F);
+                                ga[u] = g4[0]; gb[u] = g4[1];
 #pragma unroll
-                        for (int d = 0; d < 4; ++d) w[d][0] = w[d][1] = 0u;
-                        int pix = 0;
-                        if (valid) {
-                            pix = oy * gm.OW + ox;
-                            const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pix) * PN_F);
-                            const float4 a = g4[0], bq = g4[1];
-                            dv[0] = a.x; dv[1] = a.y; dv[2] = a.z; dv[3] = a.w;
-                            dv[4] = bq.x; dv[5] = bq.y; dv[6] = bq.z; dv[7] = bq.w;
+                                for (int sl = 0; sl < kPassSlots; ++sl)
+                                    if (sl < nsl) rb[u] |= (uint32_t)R[(t * nd.M + jl[sl]) * npix + pixv[u]] << (8 * sl);
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            const int m = mm[u];
+                            if (m >= gm.mq) continue;
+                            const float dv[8] = {ga[u].x, ga[u].y, ga[u].z, ga[u].w, gb[u].x, gb[u].y, gb[u].z, gb[u].w};
+                            uint32_t w[4][2];                    // [digit][channels 0-3 / 4-7]
                             int dg[4][8];
 #pragma unroll
                             for (int c = 0; c < 8; ++c) {
@@ -552,20 +581,19 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                             }
 #pragma unroll
                             for (int d = 0; d < 4; ++d) { w[d][0] = pack4(&dg[d][0]); w[d][1] = pack4(&dg[d][4]); }
-                        }
 #pragma unroll
-                        for (int sl = 0; sl < kPassSlots; ++sl) {
-                            if (sl >= nsl) break;
-                            unsigned bits = 0;
-                            if (valid) bits = R[(t * nd.M + jl[sl]) * npix + pix];
-                            const uint32_t mlo = nib_to_bytemask(bits & 15u), mhi = nib_to_bytemask(bits >> 4);
-                            uint4 g0 = make_uint4(w[0][0] & mlo, w[0][1] & mhi, w[1][0] & mlo, w[1][1] & mhi);
-                            uint4 g1 = make_uint4(w[2][0] & mlo, w[2][1] & mhi, w[3][0] & mlo, w[3][1] & mhi);
-                            *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl) * region_q + m * 16) = g0;
-                            *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl + 1) * region_q + m * 16) = g1;
+                            for (int sl = 0; sl < kPassSlots; ++sl) {
+                                if (sl >= nsl) break;
+                                const unsigned bits = (rb[u] >> (8 * sl)) & 255u;     // 0 for rows outside the output grid
+                                const uint32_t mlo = nib_to_bytemask(bits & 15u), mhi = nib_to_bytemask(bits >> 4);
+                                const uint4 g0 = make_uint4(w[0][0] & mlo, w[0][1] & mhi, w[1][0] & mlo, w[1][1] & mhi);
+                                const uint4 g1 = make_uint4(w[2][0] & mlo, w[2][1] & mhi, w[3][0] & mlo, w[3][1] & mhi);
+                                *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl) * region_q + m * 16) = g0;
+                                *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl + 1) * region_q + m * 16) = g1;
 #pragma unroll
-                            for (int c = 0; c < 8; ++c)
-                                if ((bits >> c) & 1u) bsum[sl][c] += dv[c];
+                                for (int c = 0; c < 8; ++c)
+                                    if ((bits >> c) & 1u) bsum[sl][c] += dv[c];
+                            }
                         }
                     }
                     fence_proxy_async();
@@ -578,7 +606,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 const bool rowvalid = lane < 16;
                 const int r = quad * 16 + lane;                   // accumulator row = (g, byte) of the tap
                 const int g = r >> 4, bb = r & 15;
-                for (int tap = 0; tap < 4; ++tap) {
+                for (int tap = 2 * fgroup; tap < 2 * fgroup + 2; ++tap) {
                     const int kh = (tap >> 1) * gm.s + g, kw = (tap & 1) * gm.s + bb / gm.C, ci = bb % gm.C;
                     const int kk = (kh * nd.k[0] + kw) * gm.C + ci;
                     for (int sl = 0; sl < nsl; ++sl) {
@@ -599,19 +627,19 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                         }
                     }
                 }
-                // bias gradient: fixed-order sum of the 128 per-thread partials (dq stage 0 is free now)
+                // bias gradient: fixed-order sum of the 256 per-thread partials (the dq ring is free now)
                 float* bred = reinterpret_cast<float*>(dq_s);
 #pragma unroll
                 for (int sl = 0; sl < kPassSlots; ++sl)
 #pragma unroll
                     for (int c = 0; c < 8; ++c) bred[tid * 32 + sl * 8 + c] = bsum[sl][c];
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (tid < nsl * 8) {
                     float sacc = 0.f;
-                    for (int i = 0; i < 128; ++i) sacc += bred[i * 32 + tid];
+                    for (int i = 0; i < 256; ++i) sacc += bred[i * 32 + tid];
                     part[((size_t)(p * nch_alloc + ch) * nd.M + jl[tid >> 3]) * stride_part + (size_t)nd.KK[0] * PN_F + (tid & 7)] = sacc;
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 tc_fence_before();
                 mbar_arrive(acc_empty);
                 ++nflush;
@@ -620,7 +648,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) tmem_dealloc(td, 512);
+    if (warp == 9) tmem_dealloc(td, 512);
 }
 
 bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
@@ -746,7 +774,7 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     }
     if (best_eff < 0) return pn_fail(h, PN_ERR_STATE, "no valid chunking for the conv0 weight-gradient kernel");
     const int nch = best_nch, cs = (B + nch - 1) / nch;
-    const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), 128 * 32 * sizeof(float));
+    const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), 256 * 32 * sizeof(float));
     const size_t smem_bytes = 2 * (size_t)g.stage_bytes + dq_total + 16 * sizeof(uint64_t);
     PN_CUDA(h, cudaFuncSetAttribute(conv0_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     const int items = P * nch;
