@@ -184,8 +184,10 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
         h->tc_lin = !(c.flags & 2) && prop.major == 10 && pn_lin_tc_supported(h);
         if (h->tc_lin) PN_TRY(dev_alloc(h, &h->tc_lin_buf, pn_lin_tc_scratch_bytes(h)));
         if (h->tc_conv0 && getenv("PN_TC_DEBUG")) {
-            PN_TRY(dev_alloc(h, &h->tc_dbg, (size_t)h->num_sms * 8));
-            PN_TRYC(cudaMemset(h->tc_dbg, 0, (size_t)h->num_sms * 8 * sizeof(long long)));
+            PN_TRY(dev_alloc(h, &h->tc_dbg, (size_t)h->num_sms * 8 + 8));
+            PN_TRYC(cudaMemset(h->tc_dbg, 0, ((size_t)h->num_sms * 8 + 8) * sizeof(long long)));
+            const long long mode = atoll(getenv("PN_TC_DEBUG"));
+            PN_TRYC(cudaMemcpy(h->tc_dbg + (size_t)h->num_sms * 8, &mode, sizeof(mode), cudaMemcpyHostToDevice));
         }
     }
     // staging for the host-pointer entry point

@@ -23,9 +23,9 @@
 //    in fp32 (the integer sums convert exactly), ReLU, ascending-j sum, ReLU bit mask for backward.
 //
 // Warp roles (320 threads, one CTA per SM, persistent over a contiguous range of transitions):
-//   warps 0-7  two epilogue groups of four warps (one TMEM lane quadrant each); consecutive 128-row
-//   tiles alternate between the groups and rotate through four TMEM accumulator stages,
-//   warp 8  TMA producer (frames -> smem ring), warp 9  TMEM owner + B gather + MMA issue.
+//   warps 0-15  four epilogue groups of four warps (one TMEM lane quadrant each); consecutive 128-row
+//   tiles rotate over the groups, each group owning one TMEM accumulator stage,
+//   warp 16  TMA producer (frames -> smem ring), warp 17  TMEM owner + B gather + MMA issue.
 #include "pn_internal.cuh"
 #include "pn_tc.cuh"
 
@@ -38,8 +38,12 @@ using namespace pntc;
 namespace {
 
 constexpr int kTcThreads = 320;          // weight-gradient kernel: 8 quantise/flush warps, producer, MMA
-constexpr int kFwdThreads = 320;         // forward kernel: producer, MMA, 2 groups of 4 epilogue warps
-constexpr int kAccStages = 4;            // accumulator ring: tile c uses stage c%4, epilogue group c%2
+constexpr int kEpiGroups = 4;            // forward kernel: 4 groups of 4 epilogue warps, then producer and MMA warps
+constexpr int kFwdThreads = (4 * kEpiGroups + 2) * 32;
+// One TMEM accumulator stage per epilogue group: tile c -> group c%4 -> stage c%4.  (A stage must not be shared
+// between groups: mbarrier parity waits only distinguish the current from the preceding phase, so a group that
+// ran ahead would take another group's older phase for its own.)
+constexpr int kAccStages = kEpiGroups;
 constexpr int kAccCols = 128;            // TMEM columns per accumulator stage (max N of one pass = 96)
 constexpr int kSlotBytes = 3 * 2048;     // one module's B rows: 3 digit groups x (8 channels x 256 K bytes)
 constexpr int kPassSlots = 4;            // modules per MMA pass
@@ -54,6 +58,7 @@ struct TcGeom {
     int nst;                         // frame stages in the ring
     int ksteps;                      // MMAs (K = 32) per tap = s*16/32
     int mq;                          // rows of the weight-gradient reduction (block raster, multiple of 32)
+    int rcp_ws;                      // ceil(65536 / Ws): m / Ws == (m * rcp_ws) >> 16 for every row index used
 };
 
 // ---- weight split: fp32 -> 3 signed base-256 digits per (module, channel) ---------------------------
@@ -155,20 +160,20 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         mbar_init(path_ready, 1);
         mbar_init(drain, 1);
         mbar_init(b_full, 1);
-        mbar_init(epi_idle, 256);
+        mbar_init(epi_idle, 128 * kEpiGroups);
         fence_mbar_init();
     }
     // Warp ids matter: within an SM sub-partition the scheduler prefers the highest warp id, so the two
-    // single-thread roles that everything else waits for (TMA producer = warp 8, MMA issue = warp 9) sit
-    // above the eight epilogue warps.  (With the MMA warp at id 1 it was measured at ~205 cycles per MMA
+    // single-thread roles that everything else waits for (TMA producer = warp 16, MMA issue = warp 17) sit
+    // above the sixteen epilogue warps.  (With the MMA warp at id 1 it was measured at ~205 cycles per MMA
     // against 52 in isolation: it lost arbitration to the epilogue warps of its sub-partition.)
-    if (warp == 9) tmem_alloc(&tmem_base_s, kAccStages * kAccCols);
+    if (warp == 4 * kEpiGroups + 1) tmem_alloc(&tmem_base_s, kAccStages * kAccCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
 
-    if (warp == 8) {
+    if (warp == 4 * kEpiGroups) {
         // ================= producer: one TMA load per frame =================
         if (lane == 0) tma_prefetch_desc(&tmap);
         int stage = 0;
@@ -183,14 +188,15 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             if (++stage == gm.nst) { stage = 0; phase ^= 1; }
         }
         if (dbg && lane == 0) { dbg[blockIdx.x * 8 + 0] = w_empty; dbg[blockIdx.x * 8 + 1] = clock64() - t_begin; }
-    } else if (warp == 9) {
+    } else if (warp == 4 * kEpiGroups + 1) {
         // ================= B gather + MMA issue =================
         // Everything here is executed by the whole (converged) warp on warp-uniform values; only the
         // tcgen05 / mbarrier-arrive instructions themselves are elected to one lane (see elect_one()).
         int stage = 0, cur_path = -1, ns = 0;
-        uint32_t fphase = 0, drain_phase = 0, b_phase = 0, idle_phase = 0, tilec = 0;
-        uint32_t fill_par = 0;                       // bit a = parity of the number of fills of accumulator stage a
+        uint32_t fphase = 0, drain_phase = 0, b_phase = 0, idle_phase = 0;
+        uint32_t tilec = 0, fill_par = 0;            // tiles issued; bit a = parity of the fills of accumulator stage a
         const long long t_begin = clock64();
+        long long w_frame = 0, w_acc = 0;
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
@@ -200,7 +206,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     __syncwarp();
                     mbar_wait(drain, drain_phase);
                     drain_phase ^= 1;
-                    for (int a = 0; a < kAccStages; ++a) mbar_wait(&acc_empty[a], ((fill_par >> a) & 1u) ^ 1u);
+                    for (uint32_t a = 0; a < kAccStages; ++a) mbar_wait(&acc_empty[a], ((fill_par >> a) & 1u) ^ 1u);
                     mbar_wait(epi_idle, idle_phase);
                     idle_phase ^= 1;
                 }
@@ -224,30 +230,41 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                 if (elect_one()) mbar_arrive(path_ready);
                 cur_path = p;
             }
+            const long long cf0 = dbg ? clock64() : 0;
             mbar_wait(&frame_full[stage], fphase);
+            if (dbg) w_frame += clock64() - cf0;
             tc_fence_after();
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
             const uint32_t bsm = smem_u32(Bs);
+            // low descriptor words of tile 0 / pass 0 for the 8 (tap, K-step) MMAs; a tile advances A by 128
+            // blocks, a pass advances B by 4 modules (units of 16 bytes) -- one uniform add per MMA
+            uint32_t alo[8], blo[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int tap = i >> 1, ks = i & 1;                          // 2 K-steps of 32 bytes per tap (s = 4)
+                alo[i] = desc_lo(fbase + (uint32_t)(2 * ks * gm.region_bytes + ((tap >> 1) * gm.Ws + (tap & 1)) * 16),
+                                 (uint32_t)gm.region_bytes);
+                blo[i] = desc_lo(bsm + (uint32_t)((tap * gm.s + 2 * ks) * 128), 128);
+            }
+            const uint32_t ahi = desc_hi(128), bhi = desc_hi(2048);
+            const int nmma = 4 * gm.ksteps;
             for (int tile = 0; tile < gm.tiles && npass > 0; ++tile, ++tilec) {
                 const uint32_t acc = tilec & (kAccStages - 1);
                 for (int pass = 0; pass < npass; ++pass) {
+                    const long long ca0 = dbg ? clock64() : 0;
                     mbar_wait(&acc_empty[acc], ((fill_par >> acc) & 1u) ^ 1u);
+                    if (dbg) w_acc += clock64() - ca0;
                     tc_fence_after();
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const int N = (24 * nsl + 15) & ~15;
                     const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
                     const uint32_t dcol = td + acc * kAccCols;
-                    const uint32_t bpass = bsm + (uint32_t)(pass * kPassSlots * kSlotBytes);
+                    const uint32_t a_adv = (uint32_t)(tile * 128), b_adv = (uint32_t)((pass * kPassSlots * kSlotBytes) >> 4);
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int tap = i >> 1, ks = i & 1;                  // 2 K-steps of 32 bytes per tap (s = 4)
-                        const int off = (tap >> 1) * gm.Ws + (tap & 1);
-                        const uint64_t ad = make_smem_desc(
-                            fbase + (uint32_t)(2 * ks * gm.region_bytes + (tile * 128 + off) * 16), (uint32_t)gm.region_bytes, 128);
-                        const uint64_t bd = make_smem_desc(bpass + (uint32_t)((tap * gm.s + 2 * ks) * 128), 128, 2048);
-                        if (i < 4 * gm.ksteps && elect_one()) umma_i8(dcol, ad, bd, idesc, i ? 1u : 0u);
-                    }
+                    for (int i = 0; i < 8; ++i)
+                        if (i < nmma && elect_one())
+                            umma_i8(dcol, desc_join(alo[i] + a_adv, ahi), desc_join(blo[i] + b_adv, bhi), idesc, i ? 1u : 0u);
                     if (elect_one()) umma_commit(&acc_full[acc]);
                     __syncwarp();
                     fill_par ^= 1u << acc;
@@ -261,15 +278,16 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             __syncwarp();
             if (++stage == gm.nst) { stage = 0; fphase ^= 1; }
         }
-        if (dbg && lane == 0) dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
+        if (dbg && lane == 0) {
+            dbg[blockIdx.x * 8 + 2] = w_frame; dbg[blockIdx.x * 8 + 3] = w_acc; dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
+        }
     } else {
         // ================= epilogue: thread = TMEM lane = output pixel of the tile =================
         const int quad = warp & 3;
-        const int group = warp >> 2;                          // 0: warps 0-3, 1: warps 4-7
+        const int group = warp >> 2;                          // warps 4g .. 4g+3
         const int L = quad * 32 + lane;
         int cur_path = -1, ns = 0;
-        uint32_t path_phase = 0, mask = 0, tilec = 0;
-        uint32_t fills[kAccStages] = {0, 0, 0, 0};
+        uint32_t path_phase = 0, mask = 0, tilec = 0, gi = 0;   // gi: items this group has consumed from its stage
         long long w_full = 0, t_begin = clock64();
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
@@ -284,61 +302,59 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             if (npass == 0) {     // no active module in layer 0: the layer output is exactly zero
                 float4* yo = reinterpret_cast<float4*>(Y + (size_t)t * npix * PN_F);
-                for (int i = threadIdx.x; i < npix * 2; i += 256) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int i = threadIdx.x; i < npix * 2; i += 128 * kEpiGroups) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 continue;
             }
             for (int tile = 0; tile < gm.tiles; ++tile, ++tilec) {
-                if ((int)(tilec & 1) != group) continue;
-                const int acc = tilec & (kAccStages - 1);
+                if ((int)(tilec & (kEpiGroups - 1)) != group) continue;
                 const int m = tile * 128 + L;
-                const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
+                const int oy = (int)(((uint32_t)m * (uint32_t)gm.rcp_ws) >> 16), ox = m - oy * gm.Ws;   // m / Ws
                 const bool valid = ox < gm.OW && oy < gm.OH;
                 const int pix = oy * gm.OW + ox;
                 float sum[8];
 #pragma unroll
                 for (int c = 0; c < 8; ++c) sum[c] = 0.f;
-                for (int pass = 0; pass < npass; ++pass) {
+                for (int pass = 0; pass < npass; ++pass, ++gi) {
+                    const uint32_t acc = (uint32_t)group;
                     const long long ce0 = clock64();
-                    mbar_wait(&acc_full[acc], fills[acc] & 1);
+                    mbar_wait(&acc_full[acc], gi & 1u);
                     w_full += clock64() - ce0;
                     tc_fence_after();
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const uint32_t tbase = td + ((uint32_t)(quad * 32) << 16) + acc * kAccCols;
-                    uint32_t dd[kPassSlots][3][8];              // every digit plane of the pass, one wait
-#pragma unroll
-                    for (int sl = 0; sl < kPassSlots; ++sl) {
-                        if (sl < nsl) {
-                            tmem_ld8(tbase + sl * 24, dd[sl][0]);
-                            tmem_ld8(tbase + sl * 24 + 8, dd[sl][1]);
-                            tmem_ld8(tbase + sl * 24 + 16, dd[sl][2]);
-                        }
+                    if (dbg && dbg[gridDim.x * 8] == 2) {          // experiment: handshake only
+                        tc_fence_before();
+                        mbar_arrive(&acc_empty[acc]);
+                        continue;
                     }
-                    tmem_ld_wait();
-                    // the accumulator stage can be refilled while this thread does its arithmetic
-                    tc_fence_before();
-                    mbar_arrive(&acc_empty[acc]);
-                    ++fills[acc];
-#pragma unroll
-                    for (int sl = 0; sl < kPassSlots; ++sl) {
-                        if (sl < nsl) {
-                            const int slot = pass * kPassSlots + sl;
-                            const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
-                            float s0[8], s1[8], s2[8], bi[8];
-                            *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
-                            *reinterpret_cast<float4*>(&s1[0]) = sb[2]; *reinterpret_cast<float4*>(&s1[4]) = sb[3];
-                            *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
-                            *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
-                            unsigned bits = 0;
-#pragma unroll
-                            for (int c = 0; c < 8; ++c) {
-                                // |D| < 2^24: the int -> float conversions are exact; one rounding per fma
-                                float pre = fmaf((float)(int)dd[sl][2][c], s2[c], bi[c]);
-                                pre = fmaf((float)(int)dd[sl][1][c], s1[c], pre);
-                                pre = fmaf((float)(int)dd[sl][0][c], s0[c], pre);
-                                if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
-                            }
-                            if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
+#pragma unroll 1
+                    for (int sl = 0; sl < nsl; ++sl) {
+                        uint32_t d0[8], d1[8], d2[8];
+                        tmem_ld8(tbase + sl * 24, d0);
+                        tmem_ld8(tbase + sl * 24 + 8, d1);
+                        tmem_ld8(tbase + sl * 24 + 16, d2);
+                        const int slot = pass * kPassSlots + sl;
+                        const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
+                        float s0[8], s1[8], s2[8], bi[8];
+                        *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
+                        *reinterpret_cast<float4*>(&s1[0]) = sb[2]; *reinterpret_cast<float4*>(&s1[4]) = sb[3];
+                        *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
+                        *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
+                        tmem_ld_wait();
+                        if (sl == nsl - 1) {        // last read of this accumulator stage: hand it back to the MMA warp
+                            tc_fence_before();
+                            mbar_arrive(&acc_empty[acc]);
                         }
+                        unsigned bits = 0;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            // |D| < 2^24: the int -> float conversions are exact; one rounding per fma
+                            float pre = fmaf((float)(int)d2[c], s2[c], bi[c]);
+                            pre = fmaf((float)(int)d1[c], s1[c], pre);
+                            pre = fmaf((float)(int)d0[c], s0[c], pre);
+                            if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
+                        }
+                        if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
                     }
                 }
                 if (valid) {
@@ -352,7 +368,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) tmem_dealloc(td, kAccStages * kAccCols);
+    if (warp == 4 * kEpiGroups + 1) tmem_dealloc(td, kAccStages * kAccCols);
 }
 
 
@@ -482,15 +498,20 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     tc_fence_after();
                     const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
                     const uint32_t qbase = smem_u32(dq_s + (size_t)stage * dq_stage_bytes);
+                    // a K step advances both start addresses by 32 blocks (descriptor unit: 16 bytes): one add each
+                    uint32_t alo[4];
+#pragma unroll
+                    for (int tap = 0; tap < 4; ++tap) alo[tap] = desc_lo(fbase + (uint32_t)(((tap >> 1) * gm.Ws + (tap & 1)) * 16), 128);
+                    uint32_t blo = desc_lo(qbase, 128);
+                    const uint32_t ahi = desc_hi((uint32_t)gm.region_bytes), bhi = desc_hi((uint32_t)region_q);
                     for (int ks = 0; ks < gm.mq / 32; ++ks) {
-                        const uint64_t bd = make_smem_desc(qbase + (uint32_t)(ks * 32 * 16), 128, (uint32_t)region_q);
+                        const uint64_t bd = desc_join(blo, bhi);
 #pragma unroll
                         for (int tap = 0; tap < 4; ++tap) {
-                            const int off = (tap >> 1) * gm.Ws + (tap & 1);
-                            const uint64_t ad = make_smem_desc(fbase + (uint32_t)((ks * 32 + off) * 16), 128,
-                                                               (uint32_t)gm.region_bytes);
-                            if (elect_one()) umma_i8(td + tap * kWgTapCols, ad, bd, idesc, accum);
+                            if (elect_one()) umma_i8(td + tap * kWgTapCols, desc_join(alo[tap], ahi), bd, idesc, accum);
+                            alo[tap] += 32;
                         }
+                        blo += 32;
                         accum = 1;
                     }
                     if (elect_one()) {
@@ -672,6 +693,9 @@ bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
     g.row_bytes = W * C;
     g.frame_bytes = H * W * C;
     g.ksteps = s / 2;
+    g.rcp_ws = (65536 + g.Ws - 1) / g.Ws;
+    for (int m = 0; m < g.tiles * 128; ++m)
+        if ((int)(((unsigned)m * (unsigned)g.rcp_ws) >> 16) != m / g.Ws) return false;
     if (g.row_bytes % 16 || g.row_bytes / 4 > 256 || g.Hs > 256) return false;
     const size_t fixed = (size_t)(nd.M + 1) * kSlotBytes + (size_t)nd.M * 32 * sizeof(float) +
                          (size_t)(nd.M + 2) * sizeof(int) + 64 * sizeof(uint64_t);

@@ -115,6 +115,17 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
     d |= (uint64_t)1 << 46;                       // descriptor version (Blackwell)
     return d;                                     // base_offset = 0, lbo_mode = 0, layout_type = 0 (no swizzle)
 }
+// The same descriptor as two 32-bit halves.  Only the low word changes when the start address advances
+// (units of 16 bytes), so an issue loop keeps `hi` fixed and spends one uniform add per MMA on `lo`.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+    return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+__device__ __forceinline__ uint64_t desc_join(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
+}
 // instruction descriptor. kind::i8: A u8 (0) / s8 (1), B likewise, D s32.  major: 0 = K-major, 1 = MN-major
 __host__ __device__ constexpr uint32_t make_idesc_i8(int M, int N, int a_signed, int b_signed, int a_mn_major,
                                                      int b_mn_major) {
