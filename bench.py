@@ -28,6 +28,7 @@ METRIC = "env-steps/sec (population fwd+bwd+RMSProp)"
 UNIT = "env-steps/s"
 P_PER_GPU, BATCH, NSETS = 64, 32, 4
 LR = 7.0016e-4
+DTYPE = "u8 x s8 -> s32 (layer 0), bf16 hi/lo x3 -> f32 (linear), f32 elsewhere"
 FALLBACK_PEAKS = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}
 
 
@@ -135,7 +136,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from pathnet_gym_b200.population import PathNetConfig, PathNetPopulation, geopath_init
-    from pathnet_gym_b200.trainer import PopulationTrainer
+    from pathnet_gym_b200.trainer import PipelinedHostTrainer, PopulationTrainer
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -202,16 +203,19 @@ def run_b200(args):
     ha, htd, hr = actions.cpu().pin_memory(), td.cpu().pin_memory(), r.cpu().pin_memory()
     hloss = torch.empty(P, dtype=torch.float32).pin_memory()
 
-    def step_host(i):
-        trainer.step_host(hf[i % NSETS], ha, htd, hr, LR, loss_out=hloss)       # H2D inputs, D2H loss, sync
-
+    # The repo's public host-buffer API: batch i+1 is staged (pinned host -> device, own copy stream) while step i
+    # runs; every step's inputs cross PCIe inside the timed region and every step's losses are read back.
+    pipe = PipelinedHostTrainer(pop)
+    batch = lambda i: (hf[i % NSETS], ha, htd, hr)
+    pipe.prime(batch(0))
     for i in range(3):
-        step_host(i)
+        pipe.step(batch(i + 1), LR, loss_out=hloss)
+    torch.cuda.synchronize()
     sampler.active.set()
     barrier()
     ev0.record()
     for i in range(K):
-        step_host(3 + i)
+        pipe.step(batch(3 + i + 1) if i + 1 < K else None, LR, loss_out=hloss)
     ev1.record()
     barrier()
     sampler.active.clear()
@@ -246,6 +250,14 @@ def run_b200(args):
         roof = {"kernel": dom, "bound": bound, "achieved": round(ach, 3), "peak": peak, "unit": runit,
                 "frac": round(ach / peak, 5), "traffic": traffic, "peak_source": peak_src,
                 "work_per_launch": work, "avg_launch_ms": round(prof[dom][0], 5)}
+        tensor_rows = []
+        for kn in ("conv_fwd_l0", "conv_wgrad_l0", "lin_fwd", "lin_dgrad", "lin_wgrad"):
+            if kn in prof:
+                _, wk = kernel_work(kn, pop, B)
+                a = wk / (prof[kn][0] * 1e-3) / 1e12
+                tensor_rows.append({"kernel": kn, "bound": "tensor", "achieved": round(a, 2), "peak": peaks["bf16_tflops_sustained"],
+                                    "unit": "TFLOP/s", "frac": round(a / peaks["bf16_tflops_sustained"], 4),
+                                    "avg_launch_ms": round(prof[kn][0], 5)})
         rb, rwork = kernel_work("rms_update", pop, B)
         rms = prof.get("rms_update")
         roof_rms = None
@@ -257,19 +269,21 @@ def run_b200(args):
         fbytes = P * B * cfg.H * cfg.W * cfg.C
         line = {"metric": METRIC, "value": round(units * K / (ms_total * 1e-3), 1), "unit": UNIT, "n_gpus": world,
                 "steps": K, "warmup": W, "ms_per_step": round(ms_total / K, 4), "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "scaling": "weak", "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
                 "config": workload_config(world), "clocks": sampler.summary(),
                 "e2e": {"value": round(units * K / (e2e_ms * 1e-3), 1), "unit": UNIT,
                         "h2d_bytes_per_step": fbytes + 3 * P * B * 4, "d2h_bytes_per_step": P * 4,
                         "ms_per_step": round(e2e_ms / K, 4),
-                        "api": "pn_train_step_host (pinned host buffers) + pn_rmsprop_apply"},
-                "gpu_launches": int(launches), "roofline": roof, "roofline_rmsprop": roof_rms, "kernels": kern,
+                        "api": "PipelinedHostTrainer: pn_stage_inputs_host (pinned host buffers, copy stream) + "
+                               "pn_train_step_staged + pn_rmsprop_apply; losses copied back every step"},
+                "gpu_launches": int(launches), "roofline": roof, "roofline_rmsprop": roof_rms,
+                "roofline_tensor_kernels": tensor_rows, "kernels": kern,
                 "workspace_mb": round(pop.workspace_bytes / 1e6, 1)}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(target_seconds=12.0)
         else:
             line["cpu_baseline"] = None
-        print(json.dumps(line), flush=True)
+        emit(line)
     pop.close()
     if world > 1:
         dist.barrier()
@@ -306,16 +320,33 @@ def run_reference(args):
     n = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
     line = {"impl": "reference", "metric": METRIC, "value": round(v, 1), "unit": UNIT, "n_gpus": n, "steps": K,
             "warmup": W, "ms_per_step": round(dt / K * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(n),
+            "vs_baseline": None, "dtype": "f32 (torch CPU)", "data": "synthetic", "config": workload_config(n),
             "cpu_baseline": {"value": round(v, 1), "unit": UNIT, "cores": thr, "kind": "port",
                              "sample": "each step = %d single-path updates of batch %d of the C2 workload on the host "
                                        "cores (all M modules evaluated and gated, torch-CPU fp32)" % (per_step, BATCH)},
             "e2e": {"value": round(v, 1), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line goes to the process's original stdout; everything else (NCCL banners, warnings) to stderr."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, data)
+    else:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)

@@ -156,6 +156,19 @@ PN_API int pn_train_step_host(pn_handle* h, const void* frames_host, int frames_
                        const int32_t* actions_host, const float* td_host, const float* r_host, int B,
                        float entropy_beta, float* loss_host, void* stream);
 
+/* Pipelined form of pn_train_step_host for callers that feed a stream of batches
+ * (process() is called in a loop, doom_pathnet.py:197-201): pn_stage_inputs_host
+ * enqueues the host->device copies of one batch on `copy_stream` into staging slot
+ * 0 or 1 and returns; pn_train_step_staged makes `stream` wait for that slot, runs
+ * the step and enqueues the device->host copy of loss_host [P] (no synchronisation:
+ * read loss_host after synchronising `stream`).  Staging batch i+1 while step i
+ * runs hides the PCIe transfer behind the kernels.  Host arrays must stay valid
+ * (and should be pinned) until their copies have completed. */
+PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* frames_host, int frames_are_u8,
+                                const int32_t* actions_host, const float* td_host, const float* r_host, int B,
+                                void* copy_stream);
+PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, float* loss_host, void* stream);
+
 /* Replaces RMSPropApplier.apply_gradients for the non-frozen tensors
  * (rmsprop_applier.py:79-106): per tensor g' = clip_by_norm(g, clip_norm);
  * ms += (g'^2 - ms)(1-decay); mom = momentum*mom + lr*g'/sqrt(ms+eps);

@@ -214,6 +214,11 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     cudaFree(h->tc_w8); cudaFree(h->tc_dbg); cudaFree(h->tc_lin_buf);
     cudaFree(h->d_chunk_ss); cudaFree(h->st_frames); cudaFree(h->st_actions); cudaFree(h->st_td);
     cudaFree(h->st_r); cudaFree(h->st_loss);
+    for (auto& sl : h->slot) {
+        cudaFree(sl.frames); cudaFree(sl.actions); cudaFree(sl.td); cudaFree(sl.r); cudaFree(sl.loss);
+        if (sl.copied) cudaEventDestroy(sl.copied);
+        if (sl.consumed) cudaEventDestroy(sl.consumed);
+    }
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
     delete h;
 }
@@ -384,6 +389,62 @@ extern "C" PN_API int pn_train_step_host(pn_handle* h, const void* frames_host, 
     if (loss_host)
         PN_CUDA(h, cudaMemcpyAsync(loss_host, h->st_loss, (size_t)h->P * sizeof(float), cudaMemcpyDeviceToHost, st));
     PN_CUDA(h, cudaStreamSynchronize(st));
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* frames_host, int frames_are_u8,
+                                           const int32_t* actions_host, const float* td_host, const float* r_host, int B,
+                                           void* copy_stream) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "null handle");
+    if (slot < 0 || slot > 1) return pn_fail(h, PN_ERR_INVALID, "slot must be 0 or 1");
+    if (int rc = check_B(h, B)) return rc;
+    if (!frames_host || !actions_host || !td_host || !r_host) return pn_fail(h, PN_ERR_INVALID, "null input array");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    pn_handle::StageSlot& s = h->slot[slot];
+    cudaStream_t cs = (cudaStream_t)copy_stream;
+    const size_t Tmax = (size_t)h->T, T = (size_t)h->P * B;
+    const size_t esz = frames_are_u8 ? 1 : sizeof(float);
+    const size_t want = Tmax * h->cfg.H * h->cfg.W * h->cfg.C * esz, fbytes = T * h->cfg.H * h->cfg.W * h->cfg.C * esz;
+    if (!s.copied) {
+        PN_CUDA(h, cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
+        PN_CUDA(h, cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
+        PN_CUDA(h, cudaMalloc(&s.actions, Tmax * sizeof(int32_t)));
+        PN_CUDA(h, cudaMalloc(&s.td, Tmax * sizeof(float)));
+        PN_CUDA(h, cudaMalloc(&s.r, Tmax * sizeof(float)));
+        PN_CUDA(h, cudaMalloc(&s.loss, (size_t)h->P * sizeof(float)));
+        h->workspace_bytes += (long long)(Tmax * 12 + (size_t)h->P * 4);
+    }
+    if (s.frames_bytes < want) {
+        PN_CUDA(h, cudaDeviceSynchronize());
+        cudaFree(s.frames);
+        s.frames = nullptr; s.frames_bytes = 0;
+        cudaError_t e = cudaMalloc(&s.frames, want);
+        if (e != cudaSuccess) return pn_fail(h, PN_ERR_NOMEM, "frame staging cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
+        s.frames_bytes = want;
+        h->workspace_bytes += (long long)want;
+    }
+    // do not overwrite the slot while the step that last used it is still reading it
+    if (s.used) PN_CUDA(h, cudaStreamWaitEvent(cs, s.consumed, 0));
+    PN_CUDA(h, cudaMemcpyAsync(s.frames, frames_host, fbytes, cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaMemcpyAsync(s.actions, actions_host, T * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaMemcpyAsync(s.td, td_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaMemcpyAsync(s.r, r_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaEventRecord(s.copied, cs));
+    s.B = B; s.is_u8 = frames_are_u8; s.used = true;
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, float* loss_host, void* stream) {
+    if (int rc = check_ready(h, true)) return rc;
+    if (slot < 0 || slot > 1 || !h->slot[slot].used) return pn_fail(h, PN_ERR_STATE, "slot %d has not been staged", slot);
+    pn_handle::StageSlot& s = h->slot[slot];
+    cudaStream_t st = (cudaStream_t)stream;
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    PN_CUDA(h, cudaStreamWaitEvent(st, s.copied, 0));
+    if (int rc = pn_train_step(h, s.frames, s.is_u8, s.actions, s.td, s.r, s.B, entropy_beta, s.loss, nullptr, nullptr, stream))
+        return rc;
+    PN_CUDA(h, cudaEventRecord(s.consumed, st));
+    if (loss_host) PN_CUDA(h, cudaMemcpyAsync(loss_host, s.loss, (size_t)h->P * sizeof(float), cudaMemcpyDeviceToHost, st));
     return PN_OK;
 }
 

@@ -96,6 +96,13 @@ struct pn_handle {
     // host-call staging
     void* st_frames = nullptr; size_t st_frames_bytes = 0;
     int32_t* st_actions = nullptr; float* st_td = nullptr; float* st_r = nullptr; float* st_loss = nullptr;
+    // double-buffered staging for the pipelined host path (pn_stage_inputs_host / pn_train_step_staged)
+    struct StageSlot {
+        void* frames = nullptr; size_t frames_bytes = 0;
+        int32_t* actions = nullptr; float* td = nullptr; float* r = nullptr; float* loss = nullptr;
+        cudaEvent_t copied = nullptr, consumed = nullptr;
+        bool used = false; int B = 0; int is_u8 = 1;
+    } slot[2];
     long long workspace_bytes = 0;
     long long launches = 0;             // kernels launched through this handle
     PnProf prof;

@@ -217,6 +217,19 @@ class PathNetPopulation:
                                               float(entropy_beta), _ptr(loss_out), self._stream()), self._h)
         return loss_out
 
+    def stage_host(self, slot, frames, actions, td, r, copy_stream: Optional[torch.cuda.Stream] = None):
+        """Enqueue the H2D copies of one batch (pinned host tensors) into staging slot 0/1 on `copy_stream`."""
+        B, u8 = self._check_frames(frames)
+        cs = copy_stream if copy_stream is not None else torch.cuda.current_stream(self.device)
+        nat.check(self.lib.pn_stage_inputs_host(self._h, int(slot), _ptr(frames), u8, _ptr(actions), _ptr(td), _ptr(r), B,
+                                                C.c_void_p(cs.cuda_stream)), self._h)
+
+    def train_step_staged(self, slot, entropy_beta=0.01, loss_out: Optional[torch.Tensor] = None):
+        """Run the step on a staged slot; the D2H copy of the losses is enqueued, not awaited."""
+        nat.check(self.lib.pn_train_step_staged(self._h, int(slot), float(entropy_beta), _ptr(loss_out), self._stream()),
+                  self._h)
+        return loss_out
+
     def allreduce_grads(self):
         """Sum the shared-module gradient slab over the GPUs that hold population slices."""
         import torch.distributed as dist

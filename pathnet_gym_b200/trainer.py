@@ -22,3 +22,34 @@ class PopulationTrainer(object):
         parallel.allreduce_sum_(self.pop.grads)
         self.pop.apply_gradients(lr, self.decay, self.momentum, self.epsilon, self.clip_norm)
         return loss
+
+
+class PipelinedHostTrainer(object):
+    """Feeds host (pinned) batches through the double-buffered staging slots of the C ABI: while step i runs,
+    batch i+1 crosses PCIe on a separate copy stream."""
+
+    def __init__(self, pop, entropy_beta=0.01, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0):
+        import torch
+        self.pop, self.beta = pop, entropy_beta
+        self.decay, self.momentum, self.epsilon, self.clip_norm = decay, momentum, epsilon, clip_norm
+        self.copy_stream = torch.cuda.Stream(device=pop.device)
+        self.i = 0
+        self.primed = False
+
+    def prime(self, batch):
+        """Stage the first batch (frames, actions, td, r)."""
+        self.pop.stage_host(self.i & 1, *batch, copy_stream=self.copy_stream)
+        self.primed = True
+
+    def step(self, next_batch, lr, loss_out=None):
+        """Train on the batch staged last, and start staging `next_batch` (or None at the end)."""
+        assert self.primed, "call prime() with the first batch"
+        cur = self.i & 1
+        if next_batch is not None:
+            self.pop.stage_host(cur ^ 1, *next_batch, copy_stream=self.copy_stream)
+        self.pop.train_step_staged(cur, self.beta, loss_out)
+        parallel.allreduce_sum_(self.pop.grads)
+        self.pop.apply_gradients(lr, self.decay, self.momentum, self.epsilon, self.clip_norm)
+        self.i += 1
+        self.primed = next_batch is not None
+        return loss_out

@@ -314,6 +314,31 @@ def test_host_entry_point_equals_device_entry_point(eng_mod):
     pop.close()
 
 
+def test_pipelined_host_trainer_equals_device_steps(eng_mod):
+    """Staged double-buffered host path (copy stream) == the plain device-tensor step, three steps in a row."""
+    from pathnet_gym_b200.trainer import PipelinedHostTrainer, PopulationTrainer
+    cfg = hp.TC20
+    params = po.init_params(cfg, 4)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    batches = [hp.synth_inputs(cfg, 4, 6, 50 + i) for i in range(3)]
+    masks = batches[0][4]
+    ref = make_pop(eng_mod, cfg, 4, 8, params, masks)
+    tr = PopulationTrainer(ref)
+    ref_losses = [tr.step(dev(f), dev(a), dev(td), dev(r), 7e-4).cpu() for (f, a, td, r, _) in batches]
+    pop = make_pop(eng_mod, cfg, 4, 8, params, masks)
+    pipe = PipelinedHostTrainer(pop)
+    hb = [(pin(f), pin(a), pin(td), pin(r)) for (f, a, td, r, _) in batches]
+    outs = [torch.empty(4).pin_memory() for _ in batches]
+    pipe.prime(hb[0])
+    for i in range(3):
+        pipe.step(hb[i + 1] if i + 1 < 3 else None, 7e-4, loss_out=outs[i])
+    torch.cuda.synchronize()
+    for a, b in zip(outs, ref_losses):
+        assert torch.equal(a, b)
+    assert torch.equal(pop.params, ref.params) and torch.equal(pop.ms, ref.ms)
+    pop.close(); ref.close()
+
+
 def test_error_paths(eng_mod):
     from pathnet_gym_b200 import PathNetError
     cfg = hp.TINY
