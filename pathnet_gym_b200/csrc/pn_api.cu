@@ -149,7 +149,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
     PN_TRY(dev_alloc(h, &h->dzv, T * 32));
     PN_TRY(dev_alloc(h, &h->dh, T * c.hidden));
     PN_TRY(dev_alloc(h, &h->loss_t, T));
-    h->head_chunks = (int)((T + 63) / 64);
+    h->head_chunks = (int)((T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK);
     PN_TRY(dev_alloc(h, &h->head_part, (size_t)h->head_chunks * ((size_t)c.hidden * (c.A + 1) + c.A + 1)));
     PN_TRY(dev_alloc(h, &h->d_masks, (size_t)c.P * c.L));
     PN_TRY(dev_alloc(h, &h->d_list, (size_t)c.L * c.M * c.P));

@@ -9,6 +9,7 @@
 
 #define PN_F 8            // conv output channels per module (feature_num, game_ac_network.py:132)
 #define PN_ALIGN 32       // slab alignment of every tensor, in floats
+#define PN_HEAD_CHUNK 16  // transitions per partial of the head weight gradient
 #define PN_RMS_CHUNK 2048 // floats per RMSProp work chunk (never straddles a tensor)
 
 struct PnNetDesc {        // passed by value to kernels

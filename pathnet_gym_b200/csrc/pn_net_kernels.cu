@@ -265,13 +265,13 @@ __global__ void path_loss_kernel(const float* __restrict__ loss_t, int P, int B,
     loss[p] = s;
 }
 
-// head weight gradients, stage 1: per chunk of 64 transitions
+// head weight gradients, stage 1: per chunk of PN_HEAD_CHUNK transitions
 __global__ void head_wgrad_partial_kernel(const float* __restrict__ Hin, const float* __restrict__ dzv, PnNetDesc nd,
                                           int T, float* __restrict__ part) {
-    __shared__ float dz[64][32];
+    __shared__ float dz[PN_HEAD_CHUNK][32];
     const int Hd = nd.hidden, A1 = nd.A + 1;
-    const int t0 = blockIdx.x * 64, nt = min(64, T - t0);
-    for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) {
+    const int t0 = blockIdx.x * PN_HEAD_CHUNK, nt = min(PN_HEAD_CHUNK, T - t0);
+    for (int i = threadIdx.x; i < PN_HEAD_CHUNK * 32; i += blockDim.x) {
         const int tt = i >> 5;
         dz[tt][i & 31] = tt < nt ? dzv[(size_t)(t0 + tt) * 32 + (i & 31)] : 0.f;
     }
@@ -298,15 +298,25 @@ __global__ void head_wgrad_partial_kernel(const float* __restrict__ Hin, const f
     }
 }
 
-// stage 2: fixed-order sum over chunks, scatter into W_fc2/b_fc2/W_fc3/b_fc3
-__global__ void head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc nd,
-                                         float* __restrict__ grads) {
+// stage 2: fixed-order sum over chunks, scatter into W_fc2/b_fc2/W_fc3/b_fc3.
+// block = 32 elements x 8 chunk groups; group g adds chunks g, g+8, ... in order, then the 8 group sums are
+// added in group order (deterministic, 8x more loads in flight than one thread per element)
+__global__ void __launch_bounds__(256)
+head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc nd, float* __restrict__ grads) {
+    __shared__ float red[8][33];
     const int Hd = nd.hidden, A = nd.A, A1 = A + 1;
     const int n = Hd * A1 + A1;
-    const int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= n) return;
+    const int el = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    const int e = blockIdx.x * 32 + el;
     float s = 0.f;
-    for (int c = 0; c < nchunks; ++c) s += part[(size_t)c * n + e];
+    if (e < n)
+        for (int c = grp; c < nchunks; c += 8) s += part[(size_t)c * n + e];
+    red[grp][el] = s;
+    __syncthreads();
+    if (grp != 0 || e >= n) return;
+    s = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s += red[q][el];
     if (e < Hd * A1) {
         const int i = e / A1, kx = e % A1;
         if (kx < A) grads[nd.fc2W + (long long)i * A + kx] = s;
@@ -570,21 +580,33 @@ conv_wgrad_kernel(const TIn* __restrict__ X, float in_scale, const float* __rest
     }
 }
 
-// fixed-order reduction of the partials over the paths that use module (l, j)
-__global__ void conv_wgrad_reduce_kernel(const float* __restrict__ part, PnNetDesc nd, int l,
-                                         const int* __restrict__ list, const int* __restrict__ list_count, int P,
-                                         int nch_alloc, int nch_active, float* __restrict__ grads) {
+// fixed-order reduction of the partials over the paths that use module (l, j).
+// block = 32 elements x 8 term groups (term = (path in the module's list, chunk)); group g adds terms
+// g, g+8, ... in order, then the 8 group sums are added in group order.
+__global__ void __launch_bounds__(256)
+conv_wgrad_reduce_kernel(const float* __restrict__ part, PnNetDesc nd, int l, const int* __restrict__ list,
+                         const int* __restrict__ list_count, int P, int nch_alloc, int nch_active,
+                         float* __restrict__ grads) {
+    __shared__ float red[8][33];
     const int j = blockIdx.x, KK = nd.KK[l];
     const int n = KK * PN_F + PN_F;
-    const int e = blockIdx.y * blockDim.x + threadIdx.x;
-    if (e >= n) return;
+    const int el = threadIdx.x & 31, grp = threadIdx.x >> 5;
+    const int e = blockIdx.y * 32 + el;
     const int lm = l * nd.M + j, cnt = list_count[lm];
     const int* lst = list + (size_t)lm * P;
+    const int nterms = cnt * nch_active;
     float s = 0.f;
-    for (int i = 0; i < cnt; ++i) {
-        const int p = lst[i];
-        for (int c = 0; c < nch_active; ++c) s += part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
-    }
+    if (e < n)
+        for (int i = grp; i < nterms; i += 8) {
+            const int p = lst[i / nch_active], c = i - (i / nch_active) * nch_active;
+            s += part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
+        }
+    red[grp][el] = s;
+    __syncthreads();
+    if (grp != 0 || e >= n) return;
+    s = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s += red[q][el];
     const long long wb = nd.convW_base[l] + (long long)j * nd.conv_stride[l];
     if (e < KK * PN_F) grads[wb + e] = s;
     else grads[wb + nd.convb_off[l] + (e - KK * PN_F)] = s;
@@ -673,13 +695,13 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     const int T = h->P * B, P = h->P;
     // heads
     {
-        const int nchunks = (T + 63) / 64;
+        const int nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
         const int threads = max(32, (max(nd.hidden, nd.A + 1) + 31) / 32 * 32);
         PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
         head_wgrad_partial_kernel<<<nchunks, threads, 0, st>>>(h->hbuf, h->dzv, nd, T, h->head_part);
         PN_LAUNCH_CHECK(h, "head_wgrad_partial_kernel");
         const int n = nd.hidden * (nd.A + 1) + nd.A + 1;
-        head_wgrad_reduce_kernel<<<(n + 255) / 256, 256, 0, st>>>(h->head_part, nchunks, nd, h->grads);
+        head_wgrad_reduce_kernel<<<(n + 31) / 32, 256, 0, st>>>(h->head_part, nchunks, nd, h->grads);
         PN_LAUNCH_CHECK(h, "head_wgrad_reduce_kernel");
     }
     // linear modules
@@ -711,7 +733,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
             int nch_used = 1;
             if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used)) return rc;
             const int n1 = nd.KK[l] * PN_F + PN_F;
-            dim3 gr1(nd.M, (n1 + 255) / 256);
+            dim3 gr1(nd.M, (n1 + 31) / 32);
             {
                 PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
                 conv_wgrad_reduce_kernel<<<gr1, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
@@ -723,7 +745,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         if (l == 0 && is_u8 && h->tc_conv0) {
             if (int rc = pn_launch_conv0_wgrad_tc(h, (const uint8_t*)frames, B, st)) return rc;
             const int n0 = nd.KK[l] * PN_F + PN_F;
-            dim3 gr0(nd.M, (n0 + 255) / 256);
+            dim3 gr0(nd.M, (n0 + 31) / 32);
             {
                 PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
                 conv_wgrad_reduce_kernel<<<gr0, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
@@ -751,7 +773,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         }
         PN_LAUNCH_CHECK(h, "conv_wgrad_kernel");
         const int n = nd.KK[l] * PN_F + PN_F;
-        dim3 gr(nd.M, (n + 255) / 256);
+        dim3 gr(nd.M, (n + 31) / 32);
         {
             PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
             conv_wgrad_reduce_kernel<<<gr, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
