@@ -7,7 +7,7 @@ using namespace pntc;
 
 // cfg: M, N, a_off (bytes added to the A start), a_lbo, a_sbo, b_lbo, b_sbo, a_mn, b_mn, reps
 // cfg[11]: number of extra warps that hammer TMEM loads (tcgen05.ld) while the MMAs run; cfg[12]: extra warps doing LDS
-__global__ void __launch_bounds__(384) timing(const int* cfg, long long* out) {
+__global__ void __launch_bounds__(416) timing(const int* cfg, long long* out, const uint8_t* gsrc) {
     extern __shared__ __align__(1024) uint8_t sm[];
     __shared__ uint64_t bar;
     __shared__ uint32_t tbase;
@@ -74,6 +74,18 @@ __global__ void __launch_bounds__(384) timing(const int* cfg, long long* out) {
         }
         if (acc == 0x12345) out[2] = acc;
     }
+    if (threadIdx.x == 384 && cfg[13]) {
+        // stream 28 KB "frames" into the upper part of shared memory, like the conv kernels' TMA producer
+        __shared__ uint64_t pbar;
+        mbar_init(&pbar, 1); fence_mbar_init();
+        uint32_t ph = 0; long long n = 0;
+        while (!done) {
+            mbar_expect_tx(&pbar, 28224);
+            bulk_g2s(sm + 120 * 1024, gsrc + (n % 64) * 28224, 28224, &pbar);
+            mbar_wait(&pbar, ph); ph ^= 1; ++n;
+        }
+        out[3] = n;
+    }
     __syncthreads();
     tc_fence_before(); __syncthreads();
     if (threadIdx.x < 32) tmem_dealloc(td, 512);
@@ -81,18 +93,20 @@ __global__ void __launch_bounds__(384) timing(const int* cfg, long long* out) {
 
 int main() {
     int* cfg_d; long long* out_d;
-    CK(cudaMalloc(&cfg_d, 64)); CK(cudaMalloc(&out_d, 32));
+    CK(cudaMalloc(&cfg_d, 64)); CK(cudaMalloc(&out_d, 32)); uint8_t* gsrc; CK(cudaMalloc(&gsrc, 64 * 28224)); CK(cudaMemset(gsrc, 1, 64 * 28224));
     CK(cudaFuncSetAttribute(timing, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    struct C { const char* name; int v[13]; };
+    struct C { const char* name; int v[14]; };
     const int R = 7056;
     C cases[] = {
-        {"M128 N80 back to back, one commit         ", {128, 80, 0, R, 128, 128, 2048, 0, 0, 2000, 4, 0, 0}},
-        {"M128 N80 commit+fence every 8, varying desc", {128, 80, 0, R, 128, 128, 2048, 0, 0, 2001, 4, 0, 0}},
-        {"M128 N80 commit AND WAIT every 8           ", {128, 80, 0, R, 128, 128, 2048, 0, 0, 2002, 4, 0, 0}},
+        {"M128 N80 A K-major SBO128 LBO7168 off 0  ", {128, 80, 0, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
+        {"M128 N80 A K-major SBO128 LBO7168 off 16 ", {128, 80, 16, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
+        {"M128 N80 A K-major SBO128 LBO7168 off 80 ", {128, 80, 80, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
+        {"M128 N80 A K-major SBO128 LBO7168 off 64 ", {128, 80, 64, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
+        {"M128 N80 A off 80 + 8 warps LDTM         ", {128, 80, 80, 7168, 128, 128, 2048, 0, 0, 4000, 4, 8, 0, 0}},
     };
     for (auto& c : cases) {
         CK(cudaMemcpy(cfg_d, c.v, sizeof(c.v), cudaMemcpyHostToDevice));
-        timing<<<1, 384, 160 * 1024>>>(cfg_d, out_d);
+        timing<<<1, 416, 160 * 1024>>>(cfg_d, out_d, gsrc);
         CK(cudaDeviceSynchronize());
         long long o[2];
         CK(cudaMemcpy(o, out_d, 16, cudaMemcpyDeviceToHost));

@@ -745,6 +745,11 @@ size_t pn_conv0_tc_scratch_bytes(const pn_handle* h) {
     return (((size_t)h->nd.M * (kSlotBytes + 8 * sizeof(float)) + 15) & ~(size_t)15) + 16;
 }
 
+unsigned* pn_conv0_absmax_slot(const pn_handle* h) {
+    if (!h->tc_conv0 || !h->tc_w8) return nullptr;
+    return reinterpret_cast<unsigned*>(h->tc_w8 + pn_conv0_tc_scratch_bytes(h) - 16);
+}
+
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st) {
     TcGeom g;
     size_t smem_bytes = 0;
@@ -778,13 +783,14 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     const PnNetDesc& nd = h->nd;
     const int P = h->P, T = P * B;
     const int npix = g.OH * g.OW;
-    unsigned* absmax = reinterpret_cast<unsigned*>(h->tc_w8 + pn_conv0_tc_scratch_bytes(h) - 16);
-    PN_CUDA(h, cudaMemsetAsync(absmax, 0, sizeof(unsigned), st));
-    {
+    unsigned* absmax = pn_conv0_absmax_slot(h);
+    if (!h->absmax_fused) {          // the layer-1 data-gradient kernel normally leaves the abs-max behind
+        PN_CUDA(h, cudaMemsetAsync(absmax, 0, sizeof(unsigned), st));
         PnProfScope prof(h, PN_PROF_CONV0_DQUANT, st);
         absmax_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->dact[0], (size_t)T * npix * PN_F / 4, absmax);
+        PN_LAUNCH_CHECK(h, "absmax_kernel");
     }
-    PN_LAUNCH_CHECK(h, "absmax_kernel");
+    h->absmax_fused = false;
     // chunks per path: balance P*nch items over the SMs, at most 32 transitions per chunk (int32 accumulators)
     int best_nch = 1;
     double best_eff = -1.0;

@@ -186,12 +186,14 @@ __device__ __forceinline__ void stage_dpre(float4* __restrict__ Ds, const float*
 // ---------------------------------------------------------------------------------------------------
 // data gradient: CTA = (path, 4 transitions); thread = (input pixel in phase-plane order, pair of transitions)
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(512, 2)
 conv_mid_dgrad_kernel(const float* __restrict__ dY, const uint8_t* __restrict__ R, const float* __restrict__ params,
-                      PnNetDesc nd, int l, MidGeom g, const uint32_t* __restrict__ masks, int B, float* __restrict__ dX) {
+                      PnNetDesc nd, int l, MidGeom g, const uint32_t* __restrict__ masks, int B, float* __restrict__ dX,
+                      unsigned* __restrict__ absmax_out) {
     extern __shared__ __align__(16) float4 sm4[];
     float4* Ds = sm4;                                            // [kG][kPass][2][npix]
     float4* Ws = Ds + (size_t)kG * kPass * 2 * g.npix;           // [kPass][KK*2]
+    float amax = 0.f;                                            // max |dX| written by this thread (first conv layer's quantiser scale)
     const int p = blockIdx.x, b0 = blockIdx.y * kG;
     const int ntg = min(kG, B - b0);
     const uint32_t mask = masks[p * nd.L + l];
@@ -258,13 +260,27 @@ conv_mid_dgrad_kernel(const float* __restrict__ dY, const uint8_t* __restrict__ 
                 float4* o = reinterpret_cast<float4*>(dX + (((size_t)p * B + ba) * g.npix_in + ipix) * 8);
                 o[0] = make_float4(acc0[0].x + acc0[0].y, acc0[1].x + acc0[1].y, acc0[2].x + acc0[2].y, acc0[3].x + acc0[3].y);
                 o[1] = make_float4(acc0[4].x + acc0[4].y, acc0[5].x + acc0[5].y, acc0[6].x + acc0[6].y, acc0[7].x + acc0[7].y);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) amax = fmaxf(amax, fabsf(acc0[c].x + acc0[c].y));
             }
             if (bb < B) {
                 float4* o = reinterpret_cast<float4*>(dX + (((size_t)p * B + bb) * g.npix_in + ipix) * 8);
                 o[0] = make_float4(acc1[0].x + acc1[0].y, acc1[1].x + acc1[1].y, acc1[2].x + acc1[2].y, acc1[3].x + acc1[3].y);
                 o[1] = make_float4(acc1[4].x + acc1[4].y, acc1[5].x + acc1[5].y, acc1[6].x + acc1[6].y, acc1[7].x + acc1[7].y);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) amax = fmaxf(amax, fabsf(acc1[c].x + acc1[c].y));
             }
         }
+    }
+    if (absmax_out) {                    // warp -> block -> one global atomic per CTA (non-negative floats order like uints)
+        __shared__ unsigned blk_amax;
+        if (threadIdx.x == 0) blk_amax = 0u;
+        __syncthreads();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        if ((threadIdx.x & 31) == 0) atomicMax(&blk_amax, __float_as_uint(amax));
+        __syncthreads();
+        if (threadIdx.x == 0 && blk_amax) atomicMax(absmax_out, blk_amax);
     }
 }
 
@@ -431,9 +447,13 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
         const int units = g.s * g.s * g.PS * (kG / 2);
         const int threads = std::min(512, (units + 31) / 32 * 32);
         dim3 grid(P, (B + kG - 1) / kG);
+        // layer 1 writes the first conv layer's output gradient: fold the abs-max its quantiser needs into this pass
+        unsigned* amax = l == 1 ? pn_conv0_absmax_slot(h) : nullptr;
+        if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, sizeof(unsigned), st));
         PnProfScope prof(h, PN_PROF_CONV_DGRAD + l, st);
         conv_mid_dgrad_kernel<<<grid, threads, smem, st>>>(h->dact[l], h->rmask[l], h->params, nd, l, g, h->d_masks, B,
-                                                          h->dact[l - 1]);
+                                                          h->dact[l - 1], amax);
+        h->absmax_fused = amax != nullptr;
     }
     PN_LAUNCH_CHECK(h, "conv_mid_dgrad_kernel");
     return PN_OK;

@@ -78,6 +78,7 @@ struct pn_handle {
     float* loss_t = nullptr;            // [T]
     float* wpart[PN_MAX_LAYERS] = {};   // conv wgrad partials [P*nch][M][KK*F+F]
     int nch = 1;                        // transition chunks per path in conv wgrad
+    float* pending_loss = nullptr;      // per-path loss output of the step in flight (written by the head reduce launch)
     float* head_part = nullptr;         // [head_chunks][hidden*(A+1) + (A+1)]
     int head_chunks = 0;
     // rmsprop
@@ -87,6 +88,7 @@ struct pn_handle {
     int* d_tensor_nchunks = nullptr;
     float* d_chunk_ss = nullptr;        // [n_chunks] partial sums of squares
     // tensor-core conv0 (pn_conv0_tc.cu)
+    bool absmax_fused = false;          // the layer-1 data-gradient launch of this step already wrote max |dY0|
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
     int num_sms = 148;
     uint8_t* tc_w8 = nullptr;           // [M][6144] int8 weight digits + [M][8] fp32 scales + batch max|dY|
@@ -151,6 +153,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
 // pn_conv0_tc.cu
 bool pn_conv0_tc_supported(const pn_handle* h);
 size_t pn_conv0_tc_scratch_bytes(const pn_handle* h);
+unsigned* pn_conv0_absmax_slot(const pn_handle* h);   // nullptr when the tensor-core conv0 path is off
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 // pn_conv_mid.cu

@@ -58,65 +58,68 @@ __device__ __forceinline__ void split_row8(const float* v, uint4& hi, uint4& lo)
     lo = *reinterpret_cast<uint4*>(l);
 }
 
-// ---- prep: W_lin -> Wp (every step: RMSProp changed the weights) ------------------------------------------
-__global__ void __launch_bounds__(256)
-lin_wsplit_kernel(const float* __restrict__ params, PnNetDesc nd, LinGeom g, uint8_t* __restrict__ wp) {
-    // one thread per (module, kb, c-block of 8): reads 8 rows x 8 floats, writes a hi and a lo block
-    const int ncb = g.Hd / 8;
-    const long long total = (long long)g.M * g.KB * ncb;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int cb = (int)(i % ncb), kb = (int)((i / ncb) % g.KB), j = (int)(i / ((long long)ncb * g.KB));
-        const float* W = params + nd.linW_base + (long long)j * nd.lin_stride;
-        const int h = cb / 16, cb16 = cb % 16;
-        uint8_t* dst = wp + (size_t)j * g.wp_module + ((size_t)h * g.KB + kb) * 16 * kBlk + (size_t)cb16 * kBlk;
-        const size_t hl_stride = (size_t)2 * g.KB * 16 * kBlk;
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const int k = kb * 8 + r;
-            float v[8];
-            if (k < g.K) {
-                const float4 a = *reinterpret_cast<const float4*>(W + (size_t)k * g.Hd + cb * 8);
-                const float4 b = *reinterpret_cast<const float4*>(W + (size_t)k * g.Hd + cb * 8 + 4);
-                v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
-            } else {
-#pragma unroll
-                for (int q = 0; q < 8; ++q) v[q] = 0.f;
-            }
-            uint4 hi, lo;
-            split_row8(v, hi, lo);
-            *reinterpret_cast<uint4*>(dst + r * 16) = hi;
-            *reinterpret_cast<uint4*>(dst + hl_stride + r * 16) = lo;
-        }
-    }
-}
-
-// ---- prep: flat activations -> Xp ------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-lin_xsplit_kernel(const float* __restrict__ X, LinGeom g, int P, int B, uint8_t* __restrict__ xp) {
-    // one thread per (path, chunk, kb, row b of the chunk): 8 floats -> one hi row + one lo row
-    const long long total = (long long)P * g.nbc * g.KB * kNB;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int br = (int)(i % kNB), kb = (int)((i / kNB) % g.KB);
-        const int bc = (int)((i / ((long long)kNB * g.KB)) % g.nbc), p = (int)(i / ((long long)kNB * g.KB * g.nbc));
-        const int b = bc * kNB + br;
-        float v[8];
+// ---- prep: W_lin -> Wp (every step: RMSProp changed the weights) and flat activations -> Xp, one launch ----
+// One thread per 16-byte output row.  Lane mapping: 8 consecutive lanes fill the 8 rows of one 128-byte block
+// and groups of 4 lanes read 4 x 32 = 128 contiguous source bytes, so both sides move whole 128-byte lines.
+__device__ __forceinline__ void wsplit_item(long long i, const float* __restrict__ params, const PnNetDesc& nd,
+                                            const LinGeom& g, uint8_t* __restrict__ wp) {
+    const int ncb4 = g.Hd / 32;
+    const int r = (int)(i & 7), cbq = (int)((i >> 3) & 3);
+    long long rest = i >> 5;
+    const int cb4 = (int)(rest % ncb4); rest /= ncb4;
+    const int kb = (int)(rest % g.KB), j = (int)(rest / g.KB);
+    if (j >= g.M) return;
+    const int cb = cb4 * 4 + cbq, h = cb / 16, cb16 = cb % 16, k = kb * 8 + r;
+    float v[8];
+    if (k < g.K) {
+        const float* W = params + nd.linW_base + (long long)j * nd.lin_stride + (size_t)k * g.Hd + cb * 8;
+        const float4 a = *reinterpret_cast<const float4*>(W), b = *reinterpret_cast<const float4*>(W + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
 #pragma unroll
         for (int q = 0; q < 8; ++q) v[q] = 0.f;
-        if (b < B) {
-            if (kb * 8 < g.K) {
-                const float* src = X + ((size_t)p * B + b) * g.K + kb * 8;
-                const float4 a = *reinterpret_cast<const float4*>(src), c = *reinterpret_cast<const float4*>(src + 4);
-                v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
-            } else {
-                v[0] = 1.0f;          // the "ones" k-row: the weight-gradient GEMM turns it into the bias gradient
-            }
-        }
-        uint4 hi, lo;
-        split_row8(v, hi, lo);
-        uint8_t* dst = xp + (size_t)p * g.xp_path + (size_t)bc * g.xp_chunk + ((size_t)kb * 4 + br / 8) * kBlk + (br % 8) * 16;
-        *reinterpret_cast<uint4*>(dst) = hi;
-        *reinterpret_cast<uint4*>(dst + g.xp_chunk / 2) = lo;
     }
+    uint4 hi, lo;
+    split_row8(v, hi, lo);
+    uint8_t* dst = wp + (size_t)j * g.wp_module + ((size_t)h * g.KB + kb) * 16 * kBlk + (size_t)cb16 * kBlk + r * 16;
+    *reinterpret_cast<uint4*>(dst) = hi;
+    *reinterpret_cast<uint4*>(dst + (size_t)2 * g.KB * 16 * kBlk) = lo;
+}
+
+__device__ __forceinline__ void xsplit_item(long long i, const float* __restrict__ X, const LinGeom& g, int P, int B,
+                                            uint8_t* __restrict__ xp) {
+    const int nkb4 = (g.KB + 3) / 4;
+    const int kbq = (int)(i & 3), r8 = (int)((i >> 2) & 7), bb = (int)((i >> 5) & 3);
+    long long rest = i >> 7;
+    const int kb4 = (int)(rest % nkb4); rest /= nkb4;
+    const int bc = (int)(rest % g.nbc), p = (int)(rest / g.nbc);
+    const int kb = kb4 * 4 + kbq;
+    if (p >= P || kb >= g.KB) return;
+    const int b = bc * kNB + bb * 8 + r8;
+    float v[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = 0.f;
+    if (b < B) {
+        if (kb * 8 < g.K) {
+            const float* src = X + ((size_t)p * B + b) * g.K + kb * 8;
+            const float4 a = *reinterpret_cast<const float4*>(src), c = *reinterpret_cast<const float4*>(src + 4);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+        } else {
+            v[0] = 1.0f;          // the "ones" k-row: the weight-gradient GEMM turns it into the bias gradient
+        }
+    }
+    uint4 hi, lo;
+    split_row8(v, hi, lo);
+    uint8_t* dst = xp + (size_t)p * g.xp_path + (size_t)bc * g.xp_chunk + ((size_t)kb * 4 + bb) * kBlk + r8 * 16;
+    *reinterpret_cast<uint4*>(dst) = hi;
+    *reinterpret_cast<uint4*>(dst + g.xp_chunk / 2) = lo;
+}
+
+__global__ void __launch_bounds__(256)
+lin_prep_kernel(const float* __restrict__ params, PnNetDesc nd, LinGeom g, uint8_t* __restrict__ wp, int wblocks,
+                const float* __restrict__ X, int P, int B, uint8_t* __restrict__ xp) {
+    if ((int)blockIdx.x < wblocks) wsplit_item((long long)blockIdx.x * 256 + threadIdx.x, params, nd, g, wp);
+    else xsplit_item((long long)(blockIdx.x - wblocks) * 256 + threadIdx.x, X, g, P, B, xp);
 }
 
 // ---- forward GEMM ----------------------------------------------------------------------------------------------------
@@ -279,39 +282,39 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
 
 
 // ---- prep: dh * relu-mask -> Dp --------------------------------------------------------------------------------
+// grid = (row groups, slot, path); blocks of inactive slots leave at once.  Same lane mapping as above.
 __global__ void __launch_bounds__(256)
 lin_dsplit_kernel(const float* __restrict__ dh, const uint8_t* __restrict__ Rl, LinGeom g, const uint32_t* __restrict__ masks,
                   int P, int B, uint8_t* __restrict__ dp) {
-    // one thread per (path, chunk, slot, cb, row b of the chunk)
-    const int ncb = g.Hd / 8;
-    const long long total = (long long)P * g.nbc * g.M * ncb * kNB;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int br = (int)(i % kNB), cb = (int)((i / kNB) % ncb), slot = (int)((i / ((long long)kNB * ncb)) % g.M);
-        const int bc = (int)((i / ((long long)kNB * ncb * g.M)) % g.nbc), p = (int)(i / ((long long)kNB * ncb * g.M * g.nbc));
-        const uint32_t mask = masks[p * g.L + g.L - 1];
-        if (slot >= __popc(mask)) continue;
-        const int j = __fns(mask, 0, slot + 1);
-        const int b = bc * kNB + br;
-        float v[8];
+    const int p = blockIdx.z, slot = blockIdx.y;
+    const uint32_t mask = masks[p * g.L + g.L - 1];
+    if (slot >= __popc(mask)) return;
+    const int j = __fns(mask, 0, slot + 1);
+    const int ncb4 = g.Hd / 32;
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    const int cbq = i & 3, r8 = (i >> 2) & 7, bb = (i >> 5) & 3;
+    const int cb4 = (i >> 7) % ncb4, bc = (i >> 7) / ncb4;
+    if (bc >= g.nbc) return;
+    const int cb = cb4 * 4 + cbq, b = bc * kNB + bb * 8 + r8;
+    float v[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) v[q] = 0.f;
-        if (b < B) {
-            const size_t t = (size_t)p * B + b;
-            const float* src = dh + t * g.Hd + cb * 8;
-            const float4 a = *reinterpret_cast<const float4*>(src), c = *reinterpret_cast<const float4*>(src + 4);
-            const uint2 mk = *reinterpret_cast<const uint2*>(Rl + (t * g.M + j) * g.Hd + cb * 8);
-            v[0] = (mk.x & 0xFFu) ? a.x : 0.f;       v[1] = (mk.x & 0xFF00u) ? a.y : 0.f;
-            v[2] = (mk.x & 0xFF0000u) ? a.z : 0.f;   v[3] = (mk.x & 0xFF000000u) ? a.w : 0.f;
-            v[4] = (mk.y & 0xFFu) ? c.x : 0.f;       v[5] = (mk.y & 0xFF00u) ? c.y : 0.f;
-            v[6] = (mk.y & 0xFF0000u) ? c.z : 0.f;   v[7] = (mk.y & 0xFF000000u) ? c.w : 0.f;
-        }
-        uint4 hi, lo;
-        split_row8(v, hi, lo);
-        uint8_t* dst = dp + (size_t)p * g.dp_path + (size_t)bc * g.dp_chunk + (size_t)slot * g.dp_slot +
-                       ((size_t)cb * 4 + br / 8) * kBlk + (br % 8) * 16;
-        *reinterpret_cast<uint4*>(dst) = hi;
-        *reinterpret_cast<uint4*>(dst + g.dp_slot / 2) = lo;
+    for (int q = 0; q < 8; ++q) v[q] = 0.f;
+    if (b < B) {
+        const size_t t = (size_t)p * B + b;
+        const float* src = dh + t * g.Hd + cb * 8;
+        const float4 a = *reinterpret_cast<const float4*>(src), c = *reinterpret_cast<const float4*>(src + 4);
+        const uint2 mk = *reinterpret_cast<const uint2*>(Rl + (t * g.M + j) * g.Hd + cb * 8);
+        v[0] = (mk.x & 0xFFu) ? a.x : 0.f;       v[1] = (mk.x & 0xFF00u) ? a.y : 0.f;
+        v[2] = (mk.x & 0xFF0000u) ? a.z : 0.f;   v[3] = (mk.x & 0xFF000000u) ? a.w : 0.f;
+        v[4] = (mk.y & 0xFFu) ? c.x : 0.f;       v[5] = (mk.y & 0xFF00u) ? c.y : 0.f;
+        v[6] = (mk.y & 0xFF0000u) ? c.z : 0.f;   v[7] = (mk.y & 0xFF000000u) ? c.w : 0.f;
     }
+    uint4 hi, lo;
+    split_row8(v, hi, lo);
+    uint8_t* dst = dp + (size_t)p * g.dp_path + (size_t)bc * g.dp_chunk + (size_t)slot * g.dp_slot +
+                   ((size_t)cb * 4 + bb) * kBlk + r8 * 16;
+    *reinterpret_cast<uint4*>(dst) = hi;
+    *reinterpret_cast<uint4*>(dst + g.dp_slot / 2) = lo;
 }
 
 // ---- data gradient: d(flat)[b, k] = sum_j sum_c dpre_j[b, c] W_j[k, c] ------------------------------------------
@@ -658,11 +661,12 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     uint8_t* xp = wp + gmax.wp_module * g.M;
     {
         PnProfScope prof(h, PN_PROF_LIN_PREP, st);
-        lin_wsplit_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->params, nd, g, wp);
-        lin_xsplit_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->act[nd.nconv - 1], g, h->P, B, xp);
+        const long long wthreads = (long long)g.M * g.KB * (g.Hd / 32) * 32;
+        const long long xthreads = (long long)h->P * g.nbc * ((g.KB + 3) / 4) * 128;
+        const int wblocks = (int)((wthreads + 255) / 256), xblocks = (int)((xthreads + 255) / 256);
+        lin_prep_kernel<<<wblocks + xblocks, 256, 0, st>>>(h->params, nd, g, wp, wblocks, h->act[nd.nconv - 1], h->P, B, xp);
     }
-    PN_LAUNCH_CHECK(h, "lin_wsplit_kernel");
-    PN_LAUNCH_CHECK(h, "lin_xsplit_kernel");
+    PN_LAUNCH_CHECK(h, "lin_prep_kernel");
     const size_t smem = (size_t)kWStages * 2 * kWChunkKb * 16 * kBlk + g.xp_chunk + 256;
     PN_CUDA(h, cudaFuncSetAttribute(lin_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int items = h->P * g.nbc * 2;
@@ -684,7 +688,8 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
     uint8_t* dp = xp + gmax.xp_path * h->P;
     {
         PnProfScope prof(h, PN_PROF_LIN_PREP, st);
-        lin_dsplit_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->dh, h->lmask, g, h->d_masks, h->P, B, dp);
+        dim3 dgrid((g.nbc * (g.Hd / 32) * 128 + 255) / 256, g.M, h->P);
+        lin_dsplit_kernel<<<dgrid, 256, 0, st>>>(h->dh, h->lmask, g, h->d_masks, h->P, B, dp);
     }
     PN_LAUNCH_CHECK(h, "lin_dsplit_kernel");
     const int KT = (g.K / 8 + 1 + 15) / 16;          // tiles of 16 k-blocks covering the K rows plus the ones row

@@ -12,6 +12,7 @@
 //   hbuf     [T][hidden]     fp32  (sum of relu(linear))/M
 //   lmask    [T][M][hidden]  u8    0/1
 #include "pn_internal.cuh"
+#include "pn_tc.cuh"
 
 #include <algorithm>
 
@@ -184,36 +185,107 @@ lin_fwd_kernel(const float* __restrict__ X, const float* __restrict__ params, Pn
 // heads + A3C loss + closed-form dL/dlogits, dL/dv, dL/dh : one warp per transition
 // (game_ac_network.py:198-201 heads, :38-59 loss)
 // ---------------------------------------------------------------------------
+// One block = one chunk of PN_HEAD_CHUNK (16) transitions, 256 threads.  The chunk's hidden activations, logits
+// and dL/dz stay in shared memory, so the block runs its small dense phases back to back:
+//   1. z[tt][k]  = sum_i h[tt][i] Wc[i][k]     thread = (transition tt, 1/16 slice of i), 16-lane shuffle reduce
+//   2. softmax / loss / dL/dz                  one warp per transition
+//   3. dh[tt][i] = sum_k dz[tt][k] Wc[i][k]  and the chunk's partial head-weight gradient
+//      d Wc[i][k] = sum_tt h[tt][i] dz[tt][k] (fixed order)       thread = hidden unit i
+// Wc[i][0..A-1] = W_fc2[i][:], Wc[i][A] = W_fc3[i], zero up to NP (a multiple of 4): every inner loop is
+// float4 shared loads feeding packed fp32x2 FMAs with no per-column predicate.
+template <int NP>
 __global__ void __launch_bounds__(256)
 head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnNetDesc nd, int T, int training,
             const int32_t* __restrict__ actions, const float* __restrict__ td, const float* __restrict__ r,
             float beta, float* __restrict__ pi_out, float* __restrict__ v_out, float* __restrict__ dzv,
-            float* __restrict__ dh, float* __restrict__ loss_t) {
+            float* __restrict__ dh, float* __restrict__ loss_t, float* __restrict__ part) {
+    static_assert(PN_HEAD_CHUNK == 16 && NP % 4 == 0 && NP <= 32, "phase 1 maps 16 transitions x 16 slices onto 256 threads");
     extern __shared__ __align__(16) float hsm[];
-    const int Hd = nd.hidden, A = nd.A;
-    float* W2s = hsm;                 // [Hd*A]
-    float* W3s = W2s + Hd * A;        // [Hd]
-    float* b2s = W3s + Hd;            // [32] (b3 at index A)
-    float* hs = b2s + 32;             // [8][Hd]
-    float* dzs = hs + 8 * Hd;         // [8][32]
-    for (int i = threadIdx.x; i < Hd * A; i += blockDim.x) W2s[i] = params[nd.fc2W + i];
-    for (int i = threadIdx.x; i < Hd; i += blockDim.x) W3s[i] = params[nd.fc3W + i];
-    if (threadIdx.x < 32) b2s[threadIdx.x] = threadIdx.x < A ? params[nd.fc2b + threadIdx.x]
-                                                              : (threadIdx.x == A ? params[nd.fc3b] : 0.f);
+    const int Hd = nd.hidden, A = nd.A, A1 = A + 1;
+    const int hpitch = ((Hd + 3) & ~3) + 16;   // +16 floats: the two transitions of a warp hit different banks
+    float* Wc = hsm;                           // [Hd][NP]
+    float* b2s = Wc + (size_t)Hd * NP;         // [32] (b3 at index A)
+    float* hs = b2s + 32;                      // [16][hpitch]
+    float* zs = hs + PN_HEAD_CHUNK * hpitch;   // [16][32] logits (k < A), value (k == A)
+    float* dzs = zs + PN_HEAD_CHUNK * 32;      // [16][32]
+    const int t0 = blockIdx.x * PN_HEAD_CHUNK, nt = min(PN_HEAD_CHUNK, T - t0);
+    {
+        const int m4 = Hd >> 2;
+        if ((Hd & 3) == 0) {
+            for (int i = threadIdx.x; i < nt * m4; i += blockDim.x) {
+                const int tt = i / m4, c = i - tt * m4;
+                pntc::cp_async16(hs + tt * hpitch + 4 * c, Hin + (size_t)(t0 + tt) * Hd + 4 * c);
+            }
+        } else {
+            for (int i = threadIdx.x; i < nt * Hd; i += blockDim.x) {
+                const int tt = i / Hd, c = i - tt * Hd;
+                hs[tt * hpitch + c] = Hin[(size_t)(t0 + tt) * Hd + c];
+            }
+        }
+        for (int i = threadIdx.x; i < Hd; i += blockDim.x) {       // one weight row per thread, loads issued together
+            float wr[NP];
+            const float* src = params + nd.fc2W + (size_t)i * A;
+            if ((A & 1) == 0) {
+#pragma unroll
+                for (int k = 0; k < NP; k += 2) {
+                    const float2 v = k < A ? *reinterpret_cast<const float2*>(src + k) : make_float2(0.f, 0.f);
+                    wr[k] = v.x; wr[k + 1] = v.y;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) wr[k] = k < A ? src[k] : 0.f;
+            }
+            const float w3 = params[nd.fc3W + i];
+#pragma unroll
+            for (int k = 0; k < NP; ++k) wr[k] = k == A ? w3 : wr[k];
+#pragma unroll
+            for (int q = 0; q < NP / 4; ++q)
+                reinterpret_cast<float4*>(Wc + (size_t)i * NP)[q] = make_float4(wr[4 * q], wr[4 * q + 1], wr[4 * q + 2], wr[4 * q + 3]);
+        }
+        if (threadIdx.x < 32) b2s[threadIdx.x] = threadIdx.x < A ? params[nd.fc2b + threadIdx.x]
+                                                                  : (threadIdx.x == A ? params[nd.fc3b] : 0.f);
+        for (int i = threadIdx.x; i < PN_HEAD_CHUNK * 32; i += blockDim.x) dzs[i] = 0.f;
+        pntc::cp_async_wait_all();
+    }
     __syncthreads();
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float* hw = hs + w * Hd;
-    float* dzw = dzs + w * 32;
-    const int nwarps = gridDim.x * 8;
-    for (int t = blockIdx.x * 8 + w; t < T; t += nwarps) {
-        for (int i = lane; i < Hd; i += 32) hw[i] = Hin[(size_t)t * Hd + i];
-        __syncwarp();
-        float acc = b2s[lane];
-        if (lane < A) {
-            for (int i = 0; i < Hd; ++i) acc = fmaf(hw[i], W2s[i * A + lane], acc);
-        } else if (lane == A) {
-            for (int i = 0; i < Hd; ++i) acc = fmaf(hw[i], W3s[i], acc);
+    {   // phase 1
+        const int tt = threadIdx.x >> 4, ks = threadIdx.x & 15;
+        float2 acc[NP / 2];
+#pragma unroll
+        for (int k = 0; k < NP / 2; ++k) acc[k] = make_float2(0.f, 0.f);
+        if (tt < nt) {
+            const float* hrow = hs + tt * hpitch;
+            for (int i = ks; i < Hd; i += 16) {
+                const float hv = hrow[i];
+                const float2 h2 = make_float2(hv, hv);
+                const float4* wrow = reinterpret_cast<const float4*>(Wc + (size_t)i * NP);
+#pragma unroll
+                for (int q = 0; q < NP / 4; ++q) {
+                    const float4 wv = wrow[q];
+                    acc[2 * q] = __ffma2_rn(h2, make_float2(wv.x, wv.y), acc[2 * q]);
+                    acc[2 * q + 1] = __ffma2_rn(h2, make_float2(wv.z, wv.w), acc[2 * q + 1]);
+                }
+            }
         }
+#pragma unroll
+        for (int k = 0; k < NP / 2; ++k) {
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                acc[k].x += __shfl_xor_sync(0xffffffffu, acc[k].x, o);
+                acc[k].y += __shfl_xor_sync(0xffffffffu, acc[k].y, o);
+            }
+        }
+        if (ks == 0) {
+#pragma unroll
+            for (int q = 0; q < NP / 4; ++q)
+                reinterpret_cast<float4*>(zs + tt * 32)[q] = make_float4(acc[2 * q].x, acc[2 * q].y, acc[2 * q + 1].x, acc[2 * q + 1].y);
+        }
+    }
+    __syncthreads();
+    for (int tt = w; tt < nt; tt += 8) {       // phase 2
+        const int t = t0 + tt;
+        const float acc = lane < A1 ? zs[tt * 32 + lane] + b2s[lane] : 0.f;
         const float v = __shfl_sync(0xffffffffu, acc, A);
         const float zk = lane < A ? acc : -INFINITY;
         const float m = warp_max(zk);
@@ -243,58 +315,50 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
             const float dv = -0.5f * diff;
             const float val = lane < A ? dz : (lane == A ? dv : 0.f);
             dzv[(size_t)t * 32 + lane] = val;
-            dzw[lane] = val;
-            __syncwarp();
-            const float Mf = (float)nd.M;
-            for (int i = lane; i < Hd; i += 32) {
-                float g = dzw[A] * W3s[i];
-                for (int kx = 0; kx < A; ++kx) g = fmaf(dzw[kx], W2s[i * A + kx], g);
-                dh[(size_t)t * Hd + i] = g / Mf;
-            }
+            dzs[tt * 32 + lane] = val;
             if (lane == 0) loss_t[t] = loss;
         }
-        __syncwarp();
     }
-}
-
-__global__ void path_loss_kernel(const float* __restrict__ loss_t, int P, int B, float* __restrict__ loss) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= P) return;
-    float s = 0.f;
-    for (int b = 0; b < B; ++b) s += loss_t[(size_t)p * B + b];
-    loss[p] = s;
-}
-
-// head weight gradients, stage 1: per chunk of PN_HEAD_CHUNK transitions
-__global__ void head_wgrad_partial_kernel(const float* __restrict__ Hin, const float* __restrict__ dzv, PnNetDesc nd,
-                                          int T, float* __restrict__ part) {
-    __shared__ float dz[PN_HEAD_CHUNK][32];
-    const int Hd = nd.hidden, A1 = nd.A + 1;
-    const int t0 = blockIdx.x * PN_HEAD_CHUNK, nt = min(PN_HEAD_CHUNK, T - t0);
-    for (int i = threadIdx.x; i < PN_HEAD_CHUNK * 32; i += blockDim.x) {
-        const int tt = i >> 5;
-        dz[tt][i & 31] = tt < nt ? dzv[(size_t)(t0 + tt) * 32 + (i & 31)] : 0.f;
-    }
+    if (!training) return;
     __syncthreads();
-    float* out = part + (size_t)blockIdx.x * ((size_t)Hd * A1 + A1);
-    const int i = threadIdx.x;
-    if (i < Hd) {
-        float acc[32];
+    const float rM = 1.0f / (float)nd.M;
+    float* out = part ? part + (size_t)blockIdx.x * ((size_t)Hd * A1 + A1) : nullptr;
+    for (int i = threadIdx.x; i < Hd; i += blockDim.x) {       // phase 3
+        float2 wr[NP / 2], acc[NP / 2];
 #pragma unroll
-        for (int kx = 0; kx < 32; ++kx) acc[kx] = 0.f;
-        for (int tt = 0; tt < nt; ++tt) {
-            const float hv = Hin[(size_t)(t0 + tt) * Hd + i];
-#pragma unroll
-            for (int kx = 0; kx < 32; ++kx) acc[kx] = fmaf(hv, dz[tt][kx], acc[kx]);
+        for (int q = 0; q < NP / 4; ++q) {
+            const float4 wv = reinterpret_cast<const float4*>(Wc + (size_t)i * NP)[q];
+            wr[2 * q] = make_float2(wv.x, wv.y); wr[2 * q + 1] = make_float2(wv.z, wv.w);
+            acc[2 * q] = acc[2 * q + 1] = make_float2(0.f, 0.f);
         }
+        for (int tt = 0; tt < nt; ++tt) {
+            const float hv = hs[tt * hpitch + i];
+            const float2 h2 = make_float2(hv, hv);
+            const float4* dz4 = reinterpret_cast<const float4*>(dzs + tt * 32);
+            float2 g = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int kx = 0; kx < 32; ++kx)
-            if (kx < A1) out[(size_t)i * A1 + kx] = acc[kx];
+            for (int q = 0; q < NP / 4; ++q) {
+                const float4 d = dz4[q];
+                const float2 d0 = make_float2(d.x, d.y), d1 = make_float2(d.z, d.w);
+                g = __ffma2_rn(d0, wr[2 * q], g);
+                g = __ffma2_rn(d1, wr[2 * q + 1], g);
+                acc[2 * q] = __ffma2_rn(h2, d0, acc[2 * q]);
+                acc[2 * q + 1] = __ffma2_rn(h2, d1, acc[2 * q + 1]);
+            }
+            dh[(size_t)(t0 + tt) * Hd + i] = (g.x + g.y) * rM;
+        }
+        if (out) {
+#pragma unroll
+            for (int k = 0; k < NP / 2; ++k) {
+                if (2 * k < A1) out[(size_t)i * A1 + 2 * k] = acc[k].x;
+                if (2 * k + 1 < A1) out[(size_t)i * A1 + 2 * k + 1] = acc[k].y;
+            }
+        }
     }
-    if (i < A1) {
+    if (out && threadIdx.x < A1) {
         float s = 0.f;
-        for (int tt = 0; tt < nt; ++tt) s += dz[tt][i];
-        out[(size_t)Hd * A1 + i] = s;
+        for (int tt = 0; tt < nt; ++tt) s += dzs[tt * 32 + threadIdx.x];
+        out[(size_t)Hd * A1 + threadIdx.x] = s;
     }
 }
 
@@ -302,10 +366,20 @@ __global__ void head_wgrad_partial_kernel(const float* __restrict__ Hin, const f
 // block = 32 elements x 8 chunk groups; group g adds chunks g, g+8, ... in order, then the 8 group sums are
 // added in group order (deterministic, 8x more loads in flight than one thread per element)
 __global__ void __launch_bounds__(256)
-head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc nd, float* __restrict__ grads) {
+head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc nd, float* __restrict__ grads,
+                         int nred_blocks, const float* __restrict__ loss_t, int P, int B, float* __restrict__ loss) {
     __shared__ float red[8][33];
     const int Hd = nd.hidden, A = nd.A, A1 = A + 1;
     const int n = Hd * A1 + A1;
+    if ((int)blockIdx.x >= nred_blocks) {            // trailing blocks: per-path loss = sum over its B transitions
+        const int p = ((int)blockIdx.x - nred_blocks) * blockDim.x + threadIdx.x;
+        if (p < P) {
+            float s = 0.f;
+            for (int b = 0; b < B; ++b) s += loss_t[(size_t)p * B + b];
+            loss[p] = s;
+        }
+        return;
+    }
     const int el = threadIdx.x & 31, grp = threadIdx.x >> 5;
     const int e = blockIdx.x * 32 + el;
     float s = 0.f;
@@ -673,20 +747,19 @@ int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, 
                     float beta, float* pi, float* v, float* loss, cudaStream_t st) {
     const PnNetDesc& nd = h->nd;
     const int T = h->P * B;
-    const size_t sm = ((size_t)nd.hidden * nd.A + nd.hidden + 32 + 8 * (size_t)nd.hidden + 8 * 32) * sizeof(float);
-    if (int rc = set_smem(h, head_kernel, sm)) return rc;
-    const int blocks = max(1, min((T + 7) / 8, 148 * 2));
+    const size_t hpitch = (((size_t)nd.hidden + 3) & ~(size_t)3) + 16;
+    const int np = nd.A + 1 <= 8 ? 8 : (nd.A + 1 <= 20 ? 20 : 32);
+    const size_t sm = ((size_t)nd.hidden * np + 32 + PN_HEAD_CHUNK * hpitch + 2 * PN_HEAD_CHUNK * 32) * sizeof(float);
+    const int nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
+    auto kern = np == 8 ? head_kernel<8> : (np == 20 ? head_kernel<20> : head_kernel<32>);
+    if (int rc = set_smem(h, kern, sm)) return rc;
     {
         PnProfScope prof(h, PN_PROF_HEAD, st);
-        head_kernel<<<blocks, 256, sm, st>>>(h->hbuf, h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v,
-                                             h->dzv, h->dh, h->loss_t);
+        kern<<<nchunks, 256, sm, st>>>(h->hbuf, h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v, h->dzv,
+                                       h->dh, h->loss_t, h->head_part);
     }
     PN_LAUNCH_CHECK(h, "head_kernel");
-    if (training && loss) {
-        PnProfScope prof(h, PN_PROF_HEAD, st);
-        path_loss_kernel<<<(h->P + 127) / 128, 128, 0, st>>>(h->loss_t, h->P, B, loss);
-        PN_LAUNCH_CHECK(h, "path_loss_kernel");
-    }
+    h->pending_loss = training ? loss : nullptr;     // summed per path by the head-gradient reduce launch
     return PN_OK;
 }
 
@@ -696,12 +769,12 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     // heads
     {
         const int nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
-        const int threads = max(32, (max(nd.hidden, nd.A + 1) + 31) / 32 * 32);
         PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
-        head_wgrad_partial_kernel<<<nchunks, threads, 0, st>>>(h->hbuf, h->dzv, nd, T, h->head_part);
-        PN_LAUNCH_CHECK(h, "head_wgrad_partial_kernel");
         const int n = nd.hidden * (nd.A + 1) + nd.A + 1;
-        head_wgrad_reduce_kernel<<<(n + 31) / 32, 256, 0, st>>>(h->head_part, nchunks, nd, h->grads);
+        const int nred = (n + 31) / 32, nloss = h->pending_loss ? (P + 255) / 256 : 0;
+        head_wgrad_reduce_kernel<<<nred + nloss, 256, 0, st>>>(h->head_part, nchunks, nd, h->grads, nred, h->loss_t, P,
+                                                               B, h->pending_loss);
+        h->pending_loss = nullptr;
         PN_LAUNCH_CHECK(h, "head_wgrad_reduce_kernel");
     }
     // linear modules
