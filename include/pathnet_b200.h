@@ -67,7 +67,8 @@ typedef struct pn_config {
     int32_t B_max;          /* max transitions per path per call                   */
     int32_t device;         /* CUDA device ordinal                                 */
     int32_t flags;          /* debug: bit 0 / bit 1 force the fp32 CUDA-core kernels for layer 0 / the linear modules,
-                             * bit 2 the simple (untiled) kernels for the middle conv layers */
+                             * bit 2 the simple (untiled) kernels for the middle conv layers,
+                             * bit 3 the tiled CUDA-core kernels (instead of tcgen05) for the middle conv layers */
 } pn_config;
 
 /* One row per trainable tensor, in get_vars() order with nothing frozen

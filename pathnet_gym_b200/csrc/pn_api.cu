@@ -183,6 +183,10 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
         if (h->tc_conv0) PN_TRY(dev_alloc(h, &h->tc_w8, pn_conv0_tc_scratch_bytes(h)));
         h->tc_lin = !(c.flags & 2) && prop.major == 10 && pn_lin_tc_supported(h);
         if (h->tc_lin) PN_TRY(dev_alloc(h, &h->tc_lin_buf, pn_lin_tc_scratch_bytes(h)));
+        for (int l = 1; l < nd.nconv; ++l) {
+            h->tc_mid[l] = !(c.flags & 8) && !(c.flags & 4) && prop.major == 10 && pn_conv_mid_tc_supported(h, l);
+            if (h->tc_mid[l]) PN_TRY(dev_alloc(h, &h->tc_mid_buf[l], pn_conv_mid_tc_scratch_bytes(h, l)));
+        }
         if (h->tc_conv0 && getenv("PN_TC_DEBUG")) {
             PN_TRY(dev_alloc(h, &h->tc_dbg, (size_t)h->num_sms * 8 + 8));
             PN_TRYC(cudaMemset(h->tc_dbg, 0, ((size_t)h->num_sms * 8 + 8) * sizeof(long long)));
@@ -212,6 +216,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     cudaFree(h->head_part); cudaFree(h->d_masks); cudaFree(h->d_list); cudaFree(h->d_list_count);
     cudaFree(h->d_frozen); cudaFree(h->d_chunks); cudaFree(h->d_tensor_chunk0); cudaFree(h->d_tensor_nchunks);
     cudaFree(h->tc_w8); cudaFree(h->tc_dbg); cudaFree(h->tc_lin_buf);
+    for (int l = 0; l < PN_MAX_LAYERS; ++l) cudaFree(h->tc_mid_buf[l]);
     cudaFree(h->d_chunk_ss); cudaFree(h->st_frames); cudaFree(h->st_actions); cudaFree(h->st_td);
     cudaFree(h->st_r); cudaFree(h->st_loss);
     for (auto& sl : h->slot) {
@@ -276,7 +281,8 @@ extern "C" PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int c
         else if (slot < PN_PROF_LIN_FWD) { base = "conv_dgrad"; layer = slot - PN_PROF_CONV_DGRAD; }
         else {
             static const char* names[] = {"lin_fwd", "head_loss", "head_wgrad", "lin_dgrad", "lin_wgrad",
-                                          "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant", "lin_prep"};
+                                          "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant", "lin_prep",
+                                          "conv_mid_prep"};
             base = names[slot - PN_PROF_LIN_FWD];
         }
         if (layer >= 0) snprintf(out[n].name, sizeof(out[n].name), "%s_l%d", base, layer);
@@ -312,6 +318,11 @@ extern "C" PN_API int pn_set_genotypes(pn_handle* h, const uint32_t* masks_host,
     for (int i = 0; i < P * L; ++i)
         if (masks_host[i] & ~valid) return pn_fail(h, PN_ERR_INVALID, "mask[%d] = 0x%x has bits >= M = %d", i, masks_host[i], M);
     h->h_masks.assign(masks_host, masks_host + (size_t)P * L);
+    for (int l = 0; l < L; ++l) {
+        int mx = 0;
+        for (int p = 0; p < P; ++p) mx = std::max(mx, __builtin_popcount(masks_host[p * L + l]));
+        h->max_active[l] = mx;
+    }
     std::vector<int> list((size_t)L * M * P, 0), cnt((size_t)L * M, 0);
     for (int p = 0; p < P; ++p)
         for (int l = 0; l < L; ++l)

@@ -1,0 +1,350 @@
+// Module convolutions of the middle layers (k = 4, stride 2, 8 -> 8 channels per module) on the tensor
+// cores: tcgen05 kind::f16 with bf16 hi/lo operands (three MMAs per product, as in pn_lin_tc.cu) and fp32
+// accumulation in TMEM.
+//
+// Reference semantics: relu(conv2d(net, W_conv[l,j], stride, VALID) + b_conv[l,j]) * gate_j summed over the
+// active modules in ascending j (game_ac_network.py:186-193); gradients = tf.gradients
+// (a3c_training_thread.py:55-60).
+//
+// Formulation.  Space-to-depth by the stride turns the 4x4/s2 convolution into a 2x2/s1 convolution over
+// "blocks" of 2x2 pixels x 8 channels = 32 values; a path's whole batch is one raster of blocks
+//     row R = b * RB + Y * Xp + X        (RB = Yp * Xp blocks per transition, e.g. 10 x 10)
+// and the output pixel (b, oy, ox) sits on raster row m = b * RB + oy * Xp + ox, so that
+//     out[m][slot, co] = sum over taps (dy, dx) and the 32 block values of  Xs2d[m + dy * Xp + dx][.] * W[tap][.][slot, co]
+// i.e. four GEMMs whose A operands are the SAME staged rows shifted by dy * Xp + dx rows.  Rows with
+// oy = Yp - 1 or ox = Xp - 1 are junk and never stored (19 % for 10 x 10: the tensor pipe has time to spare).
+//
+// Shared-memory operand ("chunk-major"): a chunk = the 8 channels of one (py, px) pixel of a block = 16 bytes of
+// bf16; chunk q of row r lives at q * chunk_bytes + r * 16, so 8 consecutive rows of one chunk are one
+// 128-byte tcgen05 core matrix (K-major: SBO = 128, LBO = chunk_bytes) and a tap shift is a plain
+// start-address offset of 16 * (dy * Xp + dx) bytes.  Converter warps read the fp32 NHWC activations straight
+// from global memory (64 contiguous bytes per (block, py)), split them into bf16 hi/lo and store the chunks;
+// there is no im2col and no separate conversion pass.
+#include "pn_internal.cuh"
+#include "pn_tc.cuh"
+
+#include <cuda_bf16.h>
+
+#include <algorithm>
+
+using namespace pntc;
+
+namespace {
+
+constexpr int kTileM = 128;
+constexpr int kXStages = 3;
+constexpr int kFwdThreads = 320;      // warps 0-3 epilogue, 4-8 operand converters, 9 MMA issue + weight loads
+constexpr int kConvWarps = 5;
+constexpr int kConvThreads = kConvWarps * 32;
+constexpr int kModBytes = 2048;       // one module's bf16 weights (hi or lo): 128 k x 8 co x 2 bytes
+
+struct MidTcGeom {
+    int IH, IW, Yp, Xp, RB, OH, OW, npix, npix_in;
+    int xrows;            // staged raster rows per tile: 128 + Xp + 1 rounded up to a multiple of 8
+    int chunk_bytes;      // xrows * 16
+    int hl_bytes;         // 4 chunks
+    int stage_bytes;      // hi + lo
+};
+
+bool make_mid_tc_geom(const PnNetDesc& nd, int l, MidTcGeom& g) {
+    if (l < 1 || l >= nd.nconv) return false;
+    if (nd.Cin[l] != 8 || nd.k[l] != 4 || nd.s[l] != 2 || (nd.IH[l] & 1) || (nd.IW[l] & 1)) return false;
+    g.IH = nd.IH[l]; g.IW = nd.IW[l]; g.Yp = g.IH / 2; g.Xp = g.IW / 2; g.RB = g.Yp * g.Xp;
+    g.OH = nd.OH[l]; g.OW = nd.OW[l]; g.npix = g.OH * g.OW; g.npix_in = g.IH * g.IW;
+    if (g.OH != g.Yp - 1 || g.OW != g.Xp - 1 || g.Xp > 62) return false;
+    g.xrows = (kTileM + g.Xp + 1 + 7) & ~7;
+    g.chunk_bytes = g.xrows * 16;
+    g.hl_bytes = 4 * g.chunk_bytes;
+    g.stage_bytes = 2 * g.hl_bytes;
+    return true;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+// 8 consecutive floats -> one 16-byte chunk of bf16 hi and one of bf16 lo (x ~ hi + lo to ~2^-17 relative)
+__device__ __forceinline__ void split8(const float4& a, const float4& b, uint4& hi, uint4& lo) {
+    const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    float h[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) h[i] = __bfloat162float(__float2bfloat16_rn(v[i]));
+    hi = make_uint4(pack_bf16x2(h[0], h[1]), pack_bf16x2(h[2], h[3]), pack_bf16x2(h[4], h[5]), pack_bf16x2(h[6], h[7]));
+    lo = make_uint4(pack_bf16x2(v[0] - h[0], v[1] - h[1]), pack_bf16x2(v[2] - h[2], v[3] - h[3]),
+                    pack_bf16x2(v[4] - h[4], v[5] - h[5]), pack_bf16x2(v[6] - h[6], v[7] - h[7]));
+}
+
+// ---- weights -> bf16 hi/lo operand blocks, every step (RMSProp changed them) ------------------------------------
+// wf [M][hl][kc 16][co 8][ci 8]   forward B operand (K-major over k = kc * 8 + ci;  kc = tap * 4 + py * 2 + px)
+// wd [M][hl][kc 16][ci 8][co 8]   data-gradient B operand (K-major over co)
+// with (kh, kw) = (2 dy + py, 2 dx + px), tap = dy * 2 + dx; source W[(kh * 4 + kw) * 8 + ci][co].
+__global__ void __launch_bounds__(256)
+conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, uint8_t* __restrict__ wf, uint8_t* __restrict__ wd) {
+    const int j = blockIdx.x;
+    const float* W = params + nd.convW_base[l] + (long long)j * nd.conv_stride[l];
+    const int t = threadIdx.x & 127, kc = t >> 3, e = t & 7;
+    const int tap = kc >> 2, pq = kc & 3;
+    const int kh = (tap >> 1) * 2 + (pq >> 1), kw = (tap & 1) * 2 + (pq & 1);
+    const float* src = W + (size_t)(kh * 4 + kw) * 64;
+    float v[8];
+    if (threadIdx.x < 128) {
+#pragma unroll
+        for (int ci = 0; ci < 8; ++ci) v[ci] = src[ci * 8 + e];          // e = co
+    } else {
+#pragma unroll
+        for (int co = 0; co < 8; ++co) v[co] = src[e * 8 + co];          // e = ci
+    }
+    uint4 hi, lo;
+    split8(make_float4(v[0], v[1], v[2], v[3]), make_float4(v[4], v[5], v[6], v[7]), hi, lo);
+    uint8_t* dst = (threadIdx.x < 128 ? wf : wd) + (size_t)j * 2 * kModBytes + kc * 128 + e * 16;
+    *reinterpret_cast<uint4*>(dst) = hi;
+    *reinterpret_cast<uint4*>(dst + kModBytes) = lo;
+}
+
+// =====================================================================================================
+// forward.  Work list = (path, tile of 128 raster rows), path-major; CTA c owns a contiguous range.
+// =====================================================================================================
+__global__ void __launch_bounds__(kFwdThreads, 3)
+conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ wf, const float* __restrict__ params,
+                       PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int P, int B, int ntile,
+                       int w_slots, uint32_t tmem_cols, float* __restrict__ Y, uint8_t* __restrict__ R) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kXStages]
+    uint64_t* x_empty = x_full + kXStages;                     // [kXStages]
+    uint64_t* acc_full = x_empty + kXStages;                   // [2]
+    uint64_t* acc_empty = acc_full + 2;                        // [2]
+    uint64_t* w_full = acc_empty + 2;
+    uint64_t* w_free = w_full + 1;
+    uint8_t* w_s = smem + 128;                                 // [hl][w_slots][kModBytes]
+    uint8_t* x_s = w_s + (size_t)2 * w_slots * kModBytes;      // [kXStages][stage_bytes]
+    __shared__ uint32_t tmem_base_s;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const long long NT = (long long)P * ntile;
+    const int g0 = (int)(NT * blockIdx.x / gridDim.x), g1 = (int)(NT * (blockIdx.x + 1) / gridDim.x);
+    const int NR = B * g.RB;
+    const uint32_t acc_stride = 8u * (uint32_t)w_slots;        // TMEM columns per accumulator stage
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kXStages; ++i) { mbar_init(&x_full[i], kConvWarps); mbar_init(&x_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+        mbar_init(w_full, 1); mbar_init(w_free, 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) tmem_alloc(&tmem_base_s, tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t td = tmem_base_s;
+
+    if (warp >= 4 && warp < 4 + kConvWarps) {
+        // ================= operand converters: global fp32 NHWC -> bf16 hi/lo chunks =================
+        const int cidx = threadIdx.x - 128;
+        int it = 0;
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile, tile = gt - p * ntile;
+            float4 v[2][4];
+            int rr[2], pyy[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int item = cidx + u * kConvThreads;
+                const int py = item >= g.xrows ? 1 : 0, r = item - py * g.xrows;
+                rr[u] = item < 2 * g.xrows ? r : -1;
+                pyy[u] = py;
+                const int Rr = tile * kTileM + r;
+                if (rr[u] >= 0 && Rr < NR) {
+                    const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+                    const float4* src = reinterpret_cast<const float4*>(
+                        X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[u][q] = __ldg(src + q);
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[u][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            const int stage = it % kXStages;
+            mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
+            uint8_t* xs = x_s + (size_t)stage * g.stage_bytes;
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (rr[u] >= 0) {
+#pragma unroll
+                    for (int px = 0; px < 2; ++px) {
+                        uint4 hi, lo;
+                        split8(v[u][2 * px], v[u][2 * px + 1], hi, lo);
+                        uint8_t* dst = xs + (size_t)(pyy[u] * 2 + px) * g.chunk_bytes + rr[u] * 16;
+                        *reinterpret_cast<uint4*>(dst) = hi;
+                        *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
+                    }
+                }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&x_full[stage]);
+        }
+    } else if (warp == 9) {
+        // ================= weight loads + MMA issue (whole warp, uniform values, elected instructions) =================
+        int cur_p = -1, ns = 0, it = 0;
+        uint32_t wphase = 0, fphase = 0, idesc = 0;
+        const uint32_t ws = smem_u32(w_s);
+        const uint32_t w_hl = (uint32_t)w_slots * kModBytes;
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile;
+            if (p != cur_p) {
+                const uint32_t mask = __reduce_or_sync(0xffffffffu, masks[p * nd.L + l]);
+                ns = __popc(mask);
+                if (it > 0) {                       // the previous path's MMAs still read the weight buffer
+                    if (elect_one()) umma_commit(w_free);
+                    __syncwarp();
+                    mbar_wait(w_free, fphase);
+                    fphase ^= 1;
+                }
+                if (ns > 0) {
+                    if (elect_one()) {
+                        mbar_expect_tx(w_full, (uint32_t)(ns * 2 * kModBytes));
+                        for (int slot = 0; slot < ns; ++slot) {
+                            const int j = __fns(mask, 0, slot + 1);
+                            bulk_g2s(w_s + (size_t)slot * kModBytes, wf + (size_t)j * 2 * kModBytes, kModBytes, w_full);
+                            bulk_g2s(w_s + w_hl + (size_t)slot * kModBytes, wf + (size_t)j * 2 * kModBytes + kModBytes,
+                                     kModBytes, w_full);
+                        }
+                    }
+                    __syncwarp();
+                    mbar_wait(w_full, wphase);
+                    wphase ^= 1;
+                }
+                idesc = make_idesc_f16(kTileM, 8 * ((ns + 1) & ~1), 1, 1, 0, 0);   // bf16 x bf16, both K-major
+                cur_p = p;
+            }
+            const int stage = it % kXStages, as = it & 1;
+            mbar_wait(&acc_empty[as], ((it >> 1) & 1) ^ 1);
+            mbar_wait(&x_full[stage], (it / kXStages) & 1);
+            tc_fence_after();
+            if (ns > 0) {
+                const uint32_t xs = smem_u32(x_s + (size_t)stage * g.stage_bytes);
+                const uint32_t dcol = td + as * acc_stride;
+#pragma unroll
+                for (int tap = 0; tap < 4; ++tap) {
+                    const uint32_t shift = (uint32_t)(((tap >> 1) * g.Xp + (tap & 1)) * 16);
+#pragma unroll
+                    for (int kk = 0; kk < 2; ++kk) {
+                        const uint32_t a_addr = xs + (uint32_t)(2 * kk) * g.chunk_bytes + shift;
+                        const uint32_t b_addr = ws + (uint32_t)((tap * 4 + 2 * kk) * 128);
+                        const uint64_t a_hi = make_smem_desc(a_addr, g.chunk_bytes, 128);
+                        const uint64_t a_lo = make_smem_desc(a_addr + g.hl_bytes, g.chunk_bytes, 128);
+                        const uint64_t b_hi = make_smem_desc(b_addr, 128, kModBytes);
+                        const uint64_t b_lo = make_smem_desc(b_addr + w_hl, 128, kModBytes);
+                        if (elect_one()) {
+                            umma_f16(dcol, a_hi, b_hi, idesc, (tap | kk) ? 1u : 0u);
+                            umma_f16(dcol, a_hi, b_lo, idesc, 1u);
+                            umma_f16(dcol, a_lo, b_hi, idesc, 1u);
+                        }
+                    }
+                }
+                if (elect_one()) { umma_commit(&x_empty[stage]); umma_commit(&acc_full[as]); }
+            } else {
+                if (elect_one()) { mbar_arrive(&x_empty[stage]); mbar_arrive(&acc_full[as]); }
+            }
+            __syncwarp();
+        }
+    } else if (warp < 4) {
+        // ================= epilogue: thread = raster row of the tile =================
+        int it = 0;
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile, tile = gt - p * ntile;
+            const uint32_t mask = masks[p * nd.L + l];
+            const int ns = __popc(mask);
+            const int Rr = tile * kTileM + warp * 32 + lane;
+            const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+            const bool valid = Rr < NR && Yb < g.OH && Xb < g.OW;
+            const size_t t = (size_t)p * B + b;
+            const int pix = Yb * g.OW + Xb;
+            const int as = it & 1;
+            float sum[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) sum[c] = 0.f;
+            mbar_wait(&acc_full[as], (it >> 1) & 1);
+            tc_fence_after();
+            for (int s0 = 0; s0 < ns; s0 += 2) {
+                uint32_t d[16];
+                tmem_ld16(td + ((uint32_t)(warp * 32) << 16) + as * acc_stride + s0 * 8, d);
+                tmem_ld_wait();
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    if (s0 + u < ns) {
+                        const int j = __fns(mask, 0, s0 + u + 1);
+                        const float4* bp = reinterpret_cast<const float4*>(
+                            params + nd.convW_base[l] + (long long)j * nd.conv_stride[l] + nd.convb_off[l]);
+                        const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1);
+                        const float bias[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+                        unsigned bits = 0;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const float pre = __uint_as_float(d[u * 8 + c]) + bias[c];
+                            if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
+                        }
+                        if (valid) R[(t * nd.M + j) * g.npix + pix] = (uint8_t)bits;
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&acc_empty[as]);
+            if (valid) {
+                float4* yo = reinterpret_cast<float4*>(Y + (t * g.npix + pix) * 8);
+                yo[0] = make_float4(sum[0], sum[1], sum[2], sum[3]);
+                yo[1] = make_float4(sum[4], sum[5], sum[6], sum[7]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(td, tmem_cols);
+}
+
+uint32_t pow2_cols(uint32_t n) {
+    uint32_t c = 32;
+    while (c < n) c <<= 1;
+    return c;
+}
+
+}  // namespace
+
+bool pn_conv_mid_tc_supported(const pn_handle* h, int l) {
+    MidTcGeom g;
+    if (!make_mid_tc_geom(h->nd, l, g)) return false;
+    const int w_slots = (h->nd.M + 1) & ~1;
+    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * g.stage_bytes;
+    return smem <= 200 * 1024 && 16 * w_slots <= 512 && h->nd.convb_off[l] % 4 == 0;
+}
+
+size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l) {
+    (void)l;
+    return (size_t)h->nd.M * 2 * kModBytes * 2;       // wf | wd
+}
+
+int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    MidTcGeom g;
+    if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+    uint8_t* wf = h->tc_mid_buf[l];
+    uint8_t* wd = wf + (size_t)nd.M * 2 * kModBytes;
+    {
+        PnProfScope prof(h, PN_PROF_CONV_MID_PREP, st);
+        conv_mid_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, l, wf, wd);
+    }
+    PN_LAUNCH_CHECK(h, "conv_mid_wprep_kernel");
+    const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
+    const uint32_t tmem_cols = pow2_cols(16u * w_slots);
+    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * g.stage_bytes;
+    PN_CUDA(h, cudaFuncSetAttribute(conv_mid_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int ntile = (B * g.RB + kTileM - 1) / kTileM;
+    const long long NT = (long long)h->P * ntile;
+    const int grid = (int)std::min<long long>(NT, 3ll * h->num_sms);
+    {
+        PnProfScope prof(h, PN_PROF_CONV_FWD + l, st);
+        conv_mid_fwd_tc_kernel<<<grid, kFwdThreads, smem, st>>>(h->act[l - 1], wf, h->params, nd, l, g, h->d_masks, h->P, B,
+                                                                ntile, w_slots, tmem_cols, h->act[l], h->rmask[l]);
+    }
+    PN_LAUNCH_CHECK(h, "conv_mid_fwd_tc_kernel");
+    return PN_OK;
+}

@@ -41,6 +41,7 @@ enum PnProfSlot {
     PN_PROF_CONV0_WPREP,
     PN_PROF_CONV0_DQUANT,
     PN_PROF_LIN_PREP,
+    PN_PROF_CONV_MID_PREP,
     PN_PROF_NSLOTS
 };
 #define PN_PROF_RING 64
@@ -88,6 +89,9 @@ struct pn_handle {
     int* d_tensor_nchunks = nullptr;
     float* d_chunk_ss = nullptr;        // [n_chunks] partial sums of squares
     // tensor-core conv0 (pn_conv0_tc.cu)
+    bool tc_mid[PN_MAX_LAYERS] = {};    // middle conv layer l runs on the tensor cores (cfg.flags bit 3 clear)
+    uint8_t* tc_mid_buf[PN_MAX_LAYERS] = {};   // bf16 hi/lo weight operand blocks of that layer
+    int max_active[PN_MAX_LAYERS] = {}; // largest number of active modules of any path, per layer (from pn_set_genotypes)
     bool absmax_fused = false;          // the layer-1 data-gradient launch of this step already wrote max |dY0|
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
     int num_sms = 148;
@@ -156,6 +160,10 @@ size_t pn_conv0_tc_scratch_bytes(const pn_handle* h);
 unsigned* pn_conv0_absmax_slot(const pn_handle* h);   // nullptr when the tensor-core conv0 path is off
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
+// pn_conv_mid_tc.cu
+bool pn_conv_mid_tc_supported(const pn_handle* h, int l);
+size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l);
+int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st);
 // pn_conv_mid.cu
 bool pn_conv_mid_supported(const pn_handle* h, int l);
 int pn_launch_conv_mid_fwd(pn_handle* h, int l, int B, cudaStream_t st);

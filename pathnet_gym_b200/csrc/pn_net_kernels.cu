@@ -708,6 +708,10 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
             if (int rc = pn_launch_conv0_fwd_tc(h, (const uint8_t*)frames, B, st)) return rc;
             continue;
         }
+        if (l >= 1 && h->tc_mid[l]) {
+            if (int rc = pn_launch_conv_mid_fwd_tc(h, l, B, st)) return rc;
+            continue;
+        }
         if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
             if (int rc = pn_launch_conv_mid_fwd(h, l, B, st)) return rc;
             continue;

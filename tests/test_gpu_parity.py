@@ -212,18 +212,23 @@ def test_tensor_core_layer0_matches_cuda_core_path(eng_mod):
     masks[1, 0] = (1 << cfg.M) - 1
     fd, ad, tdd, rd = dev(frames), dev(actions), dev(td), dev(r)
     out = []
-    for flags in (0, 3):
+    for flags in (0, 11):
         pop = make_pop(eng_mod, cfg, P, B, params, masks, flags=flags)
         loss, pi, v = pop.train_step(fd, ad, tdd, rd, 0.01, want_outputs=True)
         out.append((pi.clone(), v.clone(), loss.clone(), pop.grads.clone()))
         pop.close()
     (pi0, v0, l0, g0), (pi1, v1, l1, g1) = out
-    assert hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()) < 1e-5
-    assert hp.rel_err(v0.cpu().numpy(), v1.cpu().numpy()) < 1e-5
-    assert hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()) < 1e-5
-    assert hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()) < 1e-4
     _note("tc_vs_simt.pi", hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()))
+    _note("tc_vs_simt.v", hp.rel_err(v0.cpu().numpy(), v1.cpu().numpy()))
+    _note("tc_vs_simt.loss", hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()))
     _note("tc_vs_simt.grads", hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()))
+    # the bf16 hi/lo split of the middle conv layers and the linear modules leaves ~2^-17 per product: forward
+    # values agree to ~1e-5; a handful of pre-activations within that distance of zero get the other ReLU
+    # mask bit, which moves the gradient of the affected module by ~1/sqrt(units) -- same budget as the oracle
+    assert hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()) < 1e-4
+    assert hp.rel_err(v0.cpu().numpy(), v1.cpu().numpy()) < 1e-4
+    assert hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()) < 1e-4
+    assert hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()) < REL_TOL
 
 
 def test_pi_underflow_case(eng_mod):
