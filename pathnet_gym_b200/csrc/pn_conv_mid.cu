@@ -422,7 +422,7 @@ int pn_launch_conv_mid_fwd(pn_handle* h, int l, int B, cudaStream_t st) {
     return PN_OK;
 }
 
-int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used) {
+int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used, bool do_wgrad, bool do_dgrad) {
     const PnNetDesc& nd = h->nd;
     const MidGeom g = make_mid_geom(nd, l);
     const int P = h->P;
@@ -430,7 +430,7 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
     int nch = std::max(1, std::min(h->nch, (2 * h->num_sms + P - 1) / P));
     int cs = ((B + nch - 1) / nch + kG - 1) / kG * kG;
     nch = (B + cs - 1) / cs;
-    {
+    if (do_wgrad) {
         const size_t smem = std::max(((size_t)kG * g.in_f4 + (size_t)kG * kPass * 2 * g.npix) * 16,
                                      (size_t)kG * (g.KK / 2) * (2 * kPass * 8 + 1) * 4);
         if (int rc = set_smem_mid(h, conv_mid_wgrad_kernel, smem)) return rc;
@@ -441,7 +441,7 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
     }
     PN_LAUNCH_CHECK(h, "conv_mid_wgrad_kernel");
     *nch_used = nch;
-    {
+    if (do_dgrad) {
         const size_t smem = ((size_t)kG * kPass * 2 * g.npix + (size_t)kPass * g.KK * 2) * 16;
         if (int rc = set_smem_mid(h, conv_mid_dgrad_kernel, smem)) return rc;
         const int units = g.s * g.s * g.PS * (kG / 2);

@@ -301,6 +301,229 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
     if (warp == 9) tmem_dealloc(td, tmem_cols);
 }
 
+// =====================================================================================================
+// data gradient.  In raster form
+//     dX[R][(py, px, ci)] = sum over taps (dy, dx), slots, co of  dpre_slot[R - (dy * Xp + dx)][co] * W_slot[2dy+py, 2dx+px][ci][co]
+// with dpre = dY * relu-mask on the output raster (junk rows, rows before the path's first transition and rows
+// past its last are zero), i.e. the forward structure again: A = dpre chunks (chunk = slot, 8 co), shifted
+// BACK by the tap offset; B = wd; N = 32 = one block of the input raster; K = 8 * slots per tap.
+// The staged A rows start kLead = Xp + 1 rows before the tile so that every shift stays inside the stage.
+// =====================================================================================================
+__global__ void __launch_bounds__(kFwdThreads, 3)
+conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict__ R, const uint8_t* __restrict__ wd,
+                         PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int P, int B, int ntile,
+                         int w_slots, float* __restrict__ dX, unsigned* __restrict__ absmax_out) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kXStages]
+    uint64_t* x_empty = x_full + kXStages;                     // [kXStages]
+    uint64_t* acc_full = x_empty + kXStages;                   // [2]
+    uint64_t* acc_empty = acc_full + 2;                        // [2]
+    uint64_t* w_full = acc_empty + 2;
+    uint64_t* w_free = w_full + 1;
+    uint8_t* w_s = smem + 128;                                 // [hl][w_slots][kModBytes]
+    const int d_hl = w_slots * g.chunk_bytes;                  // bytes of the hi (or lo) chunks of one stage
+    uint8_t* d_s = w_s + (size_t)2 * w_slots * kModBytes;      // [kXStages][hl][w_slots][xrows] 16-byte rows
+    __shared__ uint32_t tmem_base_s;
+    __shared__ unsigned blk_amax;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const long long NT = (long long)P * ntile;
+    const int g0 = (int)(NT * blockIdx.x / gridDim.x), g1 = (int)(NT * (blockIdx.x + 1) / gridDim.x);
+    const int NR = B * g.RB;
+    const int lead = g.Xp + 1;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kXStages; ++i) { mbar_init(&x_full[i], kConvWarps); mbar_init(&x_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+        mbar_init(w_full, 1); mbar_init(w_free, 1);
+        fence_mbar_init();
+        blk_amax = 0u;
+    }
+    if (warp == 9) tmem_alloc(&tmem_base_s, 64);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t td = tmem_base_s;
+
+    if (warp >= 4 && warp < 4 + kConvWarps) {
+        // ================= converters: masked output gradient -> bf16 hi/lo chunks, one raster row per thread =================
+        const int r = threadIdx.x - 128;
+        int it = 0, cur_p = -1, ns = 0, ns_pad = 0;
+        uint32_t mask = 0;
+        int jq[4] = {0, 0, 0, 0};
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile, tile = gt - p * ntile;
+            if (p != cur_p) {
+                mask = masks[p * nd.L + l];
+                ns = __popc(mask); ns_pad = (ns + 1) & ~1;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) jq[q] = q < ns ? __fns(mask, 0, q + 1) : 0;
+                cur_p = p;
+            }
+            const int m = tile * kTileM - lead + r;
+            bool valid = r < g.xrows && m >= 0 && m < NR;
+            int b = 0, pix = 0;
+            if (valid) {
+                b = m / g.RB;
+                const int rem = m - b * g.RB, oy = rem / g.Xp, ox = rem - oy * g.Xp;
+                valid = oy < g.OH && ox < g.OW;
+                pix = oy * g.OW + ox;
+            }
+            const size_t t = (size_t)p * B + b;
+            float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+            unsigned mk[4] = {0, 0, 0, 0};
+            if (valid) {
+                const float4* src = reinterpret_cast<const float4*>(dY + (t * g.npix + pix) * 8);
+                v0 = __ldg(src); v1 = __ldg(src + 1);
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (q < ns) mk[q] = R[(t * nd.M + jq[q]) * g.npix + pix];
+            }
+            const int stage = it % kXStages;
+            mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
+            if (r < g.xrows) {
+                uint8_t* dst = d_s + (size_t)stage * 2 * d_hl + r * 16;
+                for (int slot = 0; slot < ns_pad; ++slot) {
+                    unsigned bits = 0;
+                    if (slot < 4) bits = slot == 0 ? mk[0] : (slot == 1 ? mk[1] : (slot == 2 ? mk[2] : mk[3]));
+                    else if (valid && slot < ns) bits = R[(t * nd.M + __fns(mask, 0, slot + 1)) * g.npix + pix];
+                    const float4 a = make_float4((bits & 1u) ? v0.x : 0.f, (bits & 2u) ? v0.y : 0.f, (bits & 4u) ? v0.z : 0.f,
+                                                 (bits & 8u) ? v0.w : 0.f);
+                    const float4 c = make_float4((bits & 16u) ? v1.x : 0.f, (bits & 32u) ? v1.y : 0.f, (bits & 64u) ? v1.z : 0.f,
+                                                 (bits & 128u) ? v1.w : 0.f);
+                    uint4 hi, lo;
+                    split8(a, c, hi, lo);
+                    *reinterpret_cast<uint4*>(dst + (size_t)slot * g.chunk_bytes) = hi;
+                    *reinterpret_cast<uint4*>(dst + d_hl + (size_t)slot * g.chunk_bytes) = lo;
+                }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&x_full[stage]);
+        }
+    } else if (warp == 9) {
+        // ================= weight loads + MMA issue =================
+        int cur_p = -1, ns = 0, it = 0;
+        uint32_t wphase = 0, fphase = 0;
+        const uint32_t ws = smem_u32(w_s);
+        const uint32_t w_hl = (uint32_t)w_slots * kModBytes;
+        const uint32_t idesc = make_idesc_f16(kTileM, 32, 1, 1, 0, 0);
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile;
+            if (p != cur_p) {
+                const uint32_t mask = __reduce_or_sync(0xffffffffu, masks[p * nd.L + l]);
+                ns = __popc(mask);
+                if (it > 0) {
+                    if (elect_one()) umma_commit(w_free);
+                    __syncwarp();
+                    mbar_wait(w_free, fphase);
+                    fphase ^= 1;
+                }
+                if (ns > 0) {
+                    if (ns & 1) {                   // zero the pad slot (its A chunk is zero too; stale bits could be NaN)
+                        uint4* z0 = reinterpret_cast<uint4*>(w_s + (size_t)ns * kModBytes);
+                        uint4* z1 = reinterpret_cast<uint4*>(w_s + w_hl + (size_t)ns * kModBytes);
+                        for (int i = lane; i < kModBytes / 16; i += 32) { z0[i] = make_uint4(0, 0, 0, 0); z1[i] = make_uint4(0, 0, 0, 0); }
+                        fence_proxy_async();
+                        __syncwarp();
+                    }
+                    if (elect_one()) {
+                        mbar_expect_tx(w_full, (uint32_t)(ns * 2 * kModBytes));
+                        for (int slot = 0; slot < ns; ++slot) {
+                            const int j = __fns(mask, 0, slot + 1);
+                            bulk_g2s(w_s + (size_t)slot * kModBytes, wd + (size_t)j * 2 * kModBytes, kModBytes, w_full);
+                            bulk_g2s(w_s + w_hl + (size_t)slot * kModBytes, wd + (size_t)j * 2 * kModBytes + kModBytes,
+                                     kModBytes, w_full);
+                        }
+                    }
+                    __syncwarp();
+                    mbar_wait(w_full, wphase);
+                    wphase ^= 1;
+                }
+                cur_p = p;
+            }
+            const int stage = it % kXStages, as = it & 1;
+            mbar_wait(&acc_empty[as], ((it >> 1) & 1) ^ 1);
+            mbar_wait(&x_full[stage], (it / kXStages) & 1);
+            tc_fence_after();
+            if (ns > 0) {
+                const uint32_t ds = smem_u32(d_s + (size_t)stage * 2 * d_hl);
+                const uint32_t dcol = td + as * 32;
+                const int nk = (ns + 1) >> 1;
+#pragma unroll
+                for (int tap = 0; tap < 4; ++tap) {
+                    const uint32_t shift = (uint32_t)((lead - ((tap >> 1) * g.Xp + (tap & 1))) * 16);
+                    for (int kk = 0; kk < nk; ++kk) {
+                        const uint32_t a_addr = ds + (uint32_t)(2 * kk) * g.chunk_bytes + shift;
+                        const uint32_t b_addr = ws + (uint32_t)(tap * 512) + (uint32_t)(2 * kk) * kModBytes;
+                        const uint64_t a_hi = make_smem_desc(a_addr, g.chunk_bytes, 128);
+                        const uint64_t a_lo = make_smem_desc(a_addr + d_hl, g.chunk_bytes, 128);
+                        const uint64_t b_hi = make_smem_desc(b_addr, kModBytes, 128);
+                        const uint64_t b_lo = make_smem_desc(b_addr + w_hl, kModBytes, 128);
+                        if (elect_one()) {
+                            umma_f16(dcol, a_hi, b_hi, idesc, (tap | kk) ? 1u : 0u);
+                            umma_f16(dcol, a_hi, b_lo, idesc, 1u);
+                            umma_f16(dcol, a_lo, b_hi, idesc, 1u);
+                        }
+                    }
+                }
+                if (elect_one()) { umma_commit(&x_empty[stage]); umma_commit(&acc_full[as]); }
+            } else {
+                if (elect_one()) { mbar_arrive(&x_empty[stage]); mbar_arrive(&acc_full[as]); }
+            }
+            __syncwarp();
+        }
+    } else if (warp < 4) {
+        // ================= epilogue: thread = input raster row; 32 columns = (py, px, ci) =================
+        int it = 0;
+        float amax = 0.f;
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile, tile = gt - p * ntile;
+            const int ns = __popc(masks[p * nd.L + l]);
+            const int Rr = tile * kTileM + warp * 32 + lane;
+            const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+            const bool valid = Rr < NR;
+            const int as = it & 1;
+            mbar_wait(&acc_full[as], (it >> 1) & 1);
+            tc_fence_after();
+            uint32_t d[32];
+            if (ns > 0) {
+                const uint32_t ta = td + ((uint32_t)(warp * 32) << 16) + as * 32;
+                tmem_ld16(ta, *reinterpret_cast<uint32_t(*)[16]>(&d[0]));
+                tmem_ld16(ta + 16, *reinterpret_cast<uint32_t(*)[16]>(&d[16]));
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int c = 0; c < 32; ++c) d[c] = 0u;
+            }
+            tc_fence_before();
+            mbar_arrive(&acc_empty[as]);
+            if (valid) {
+#pragma unroll
+                for (int py = 0; py < 2; ++py) {
+                    float4* o = reinterpret_cast<float4*>(
+                        dX + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 v = make_float4(__uint_as_float(d[py * 16 + q * 4]), __uint_as_float(d[py * 16 + q * 4 + 1]),
+                                                     __uint_as_float(d[py * 16 + q * 4 + 2]), __uint_as_float(d[py * 16 + q * 4 + 3]));
+                        o[q] = v;
+                        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+                    }
+                }
+            }
+        }
+        if (absmax_out) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+            if (lane == 0) atomicMax(&blk_amax, __float_as_uint(amax));   // non-negative floats order like uints
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(td, 64);
+    if (threadIdx.x == 0 && absmax_out && blk_amax) atomicMax(absmax_out, blk_amax);
+}
+
 uint32_t pow2_cols(uint32_t n) {
     uint32_t c = 32;
     while (c < n) c <<= 1;
@@ -346,5 +569,29 @@ int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
                                                                 ntile, w_slots, tmem_cols, h->act[l], h->rmask[l]);
     }
     PN_LAUNCH_CHECK(h, "conv_mid_fwd_tc_kernel");
+    return PN_OK;
+}
+
+int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    MidTcGeom g;
+    if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+    const uint8_t* wd = h->tc_mid_buf[l] + (size_t)nd.M * 2 * kModBytes;     // written by this step's forward launch
+    const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
+    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * 2 * w_slots * g.chunk_bytes;
+    PN_CUDA(h, cudaFuncSetAttribute(conv_mid_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int ntile = (B * g.RB + kTileM - 1) / kTileM;
+    const long long NT = (long long)h->P * ntile;
+    const int grid = (int)std::min<long long>(NT, 3ll * h->num_sms);
+    // layer 1 writes the first conv layer's output gradient: fold the abs-max its quantiser needs into this pass
+    unsigned* amax = l == 1 ? pn_conv0_absmax_slot(h) : nullptr;
+    if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, sizeof(unsigned), st));
+    {
+        PnProfScope prof(h, PN_PROF_CONV_DGRAD + l, st);
+        conv_mid_dgrad_tc_kernel<<<grid, kFwdThreads, smem, st>>>(h->dact[l], h->rmask[l], wd, nd, l, g, h->d_masks, h->P, B,
+                                                                  ntile, w_slots, h->dact[l - 1], amax);
+    }
+    h->absmax_fused = amax != nullptr;
+    PN_LAUNCH_CHECK(h, "conv_mid_dgrad_tc_kernel");
     return PN_OK;
 }

@@ -164,10 +164,11 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
 bool pn_conv_mid_tc_supported(const pn_handle* h, int l);
 size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l);
 int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st);
+int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st);
 // pn_conv_mid.cu
 bool pn_conv_mid_supported(const pn_handle* h, int l);
 int pn_launch_conv_mid_fwd(pn_handle* h, int l, int B, cudaStream_t st);
-int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used);
+int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used, bool do_wgrad, bool do_dgrad);
 // pn_lin_tc.cu
 bool pn_lin_tc_supported(const pn_handle* h);
 size_t pn_lin_tc_scratch_bytes(const pn_handle* h);

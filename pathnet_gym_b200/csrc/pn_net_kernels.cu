@@ -808,7 +808,9 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         const int npix = nd.OH[l] * nd.OW[l];
         if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
             int nch_used = 1;
-            if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used)) return rc;
+            if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, true, !h->tc_mid[l])) return rc;
+            if (h->tc_mid[l])
+                if (int rc = pn_launch_conv_mid_dgrad_tc(h, l, B, st)) return rc;
             const int n1 = nd.KK[l] * PN_F + PN_F;
             dim3 gr1(nd.M, (n1 + 31) / 32);
             {
