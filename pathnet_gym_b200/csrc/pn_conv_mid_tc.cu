@@ -524,6 +524,225 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
     if (threadIdx.x == 0 && absmax_out && blk_amax) atomicMax(absmax_out, blk_amax);
 }
 
+// =====================================================================================================
+// weight gradient.  d W_slot[(2dy+py, 2dx+px)][ci][co] = sum over raster rows m of  dpre_slot[m][co] * Xs2d[m + dy*Xp + dx][(py,px,ci)]
+// as D[(hl, slot, co) = 64 rows][tap * 32 + (py, px, ci) = 128 columns], accumulated in TMEM over all tiles of
+// one (path, chunk) item: A = dpre chunks (MN-major, chunk = hi slot 0..3 | lo slot 0..3), B = the forward's X
+// chunks (MN-major, N = 32 per tap, the tap being a start-address shift), K = 16 raster rows per MMA.
+//   D rows 0..31  = dpre_hi * (X_hi + X_lo),  rows 32..63 = dpre_lo * (X_hi + X_lo); the flush adds the halves.
+// The bias gradient (plain row sums of dpre) is accumulated in fp32 registers by the dpre converter threads
+// (a fixed row per thread) and reduced in a fixed order.  At most 4 active modules per path (else the
+// CUDA-core kernel runs).
+// Warps 0-3: dpre converters, then flush; warps 4-8: X converters; warp 9: MMA issue.
+// =====================================================================================================
+constexpr int kWgStages = 2;
+constexpr int kDChunk = kTileM * 16;          // bytes of one dpre chunk of a tile
+
+__global__ void __launch_bounds__(kFwdThreads, 3)
+conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ dY, const uint8_t* __restrict__ R,
+                         PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int B, int ntile, int nch,
+                         int nch_alloc, float* __restrict__ part) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kWgStages]
+    uint64_t* x_empty = x_full + kWgStages;                    // [kWgStages]
+    uint64_t* acc_full = x_empty + kWgStages;
+    uint8_t* st_s = smem + 128;                                // [kWgStages][ X hi/lo chunks | dpre 8 chunks ]
+    const int stage_bytes = g.stage_bytes + 8 * kDChunk;
+    __shared__ uint32_t tmem_base_s;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const int p = blockIdx.x / nch, ch = blockIdx.x - p * nch;
+    const int t_lo = (int)((long long)ntile * ch / nch), t_hi = (int)((long long)ntile * (ch + 1) / nch);
+    const uint32_t mask = masks[p * nd.L + l];
+    const int ns = __popc(mask);
+    if (ns == 0 || t_lo >= t_hi) return;                       // the path is in no module's list: its partials are never read
+    const int NR = B * g.RB;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kWgStages; ++i) { mbar_init(&x_full[i], 9); mbar_init(&x_empty[i], 1); }
+        mbar_init(acc_full, 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) tmem_alloc(&tmem_base_s, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t td = tmem_base_s;
+
+    if (warp < 4) {
+        // ================= dpre converters (one raster row per thread), then flush =================
+        const int r = threadIdx.x;
+        int jq[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) jq[q] = q < ns ? __fns(mask, 0, q + 1) : 0;
+        float bacc[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) bacc[q][c] = 0.f;
+        int it = 0;
+        for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+            const int m = tile * kTileM + r;
+            bool valid = m < NR;
+            int b = 0, pix = 0;
+            if (valid) {
+                b = m / g.RB;
+                const int rem = m - b * g.RB, oy = rem / g.Xp, ox = rem - oy * g.Xp;
+                valid = oy < g.OH && ox < g.OW;
+                pix = oy * g.OW + ox;
+            }
+            const size_t t = (size_t)p * B + b;
+            float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+            unsigned mk[4] = {0, 0, 0, 0};
+            if (valid) {
+                const float4* src = reinterpret_cast<const float4*>(dY + (t * g.npix + pix) * 8);
+                v0 = __ldg(src); v1 = __ldg(src + 1);
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (q < ns) mk[q] = R[(t * nd.M + jq[q]) * g.npix + pix];
+            }
+            const int stage = it % kWgStages;
+            mbar_wait(&x_empty[stage], ((it / kWgStages) & 1) ^ 1);
+            uint8_t* dst = st_s + (size_t)stage * stage_bytes + g.stage_bytes + r * 16;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const unsigned bits = mk[q];
+                const float4 a = make_float4((bits & 1u) ? v0.x : 0.f, (bits & 2u) ? v0.y : 0.f, (bits & 4u) ? v0.z : 0.f,
+                                             (bits & 8u) ? v0.w : 0.f);
+                const float4 c = make_float4((bits & 16u) ? v1.x : 0.f, (bits & 32u) ? v1.y : 0.f, (bits & 64u) ? v1.z : 0.f,
+                                             (bits & 128u) ? v1.w : 0.f);
+                bacc[q][0] += a.x; bacc[q][1] += a.y; bacc[q][2] += a.z; bacc[q][3] += a.w;
+                bacc[q][4] += c.x; bacc[q][5] += c.y; bacc[q][6] += c.z; bacc[q][7] += c.w;
+                uint4 hi, lo;
+                split8(a, c, hi, lo);
+                *reinterpret_cast<uint4*>(dst + (size_t)q * kDChunk) = hi;
+                *reinterpret_cast<uint4*>(dst + (size_t)(4 + q) * kDChunk) = lo;
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&x_full[stage]);
+        }
+        // ---- flush: TMEM -> shared (fp32 [64 rows][129]) -> hi + lo -> partial buffer ----
+        mbar_wait(acc_full, 0);
+        tc_fence_after();
+        float* fs = reinterpret_cast<float*>(st_s);            // the stages are free: every MMA has completed
+        constexpr int kPitch = 129;
+        {
+            // M = 64: accumulator row q sits in TMEM lane (q / 16) * 32 + q % 16 -> lanes 0..15 of each warp's quadrant
+            const int row = warp * 16 + lane;
+#pragma unroll
+            for (int c0 = 0; c0 < 128; c0 += 16) {
+                uint32_t d[16];
+                tmem_ld16(td + ((uint32_t)(warp * 32) << 16) + c0, d);
+                tmem_ld_wait();
+                if (lane < 16) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) fs[row * kPitch + c0 + c] = __uint_as_float(d[c]);
+                }
+            }
+        }
+        float* bs = fs + 64 * kPitch;                          // [128 threads][33] bias partials
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) bs[r * 33 + q * 8 + c] = bacc[q][c];
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int stride_part = 128 * 8 + 8;
+        for (int slot = 0; slot < ns; ++slot) {
+            float* out = part + ((size_t)(p * nch_alloc + ch) * nd.M + __fns(mask, 0, slot + 1)) * stride_part;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const int idx = i * 128 + r;                   // = ((kh * 4 + kw) * 8 + ci) * 8 + co
+                const int co = idx & 7, ci = (idx >> 3) & 7, khkw = idx >> 6, kh = khkw >> 2, kw = khkw & 3;
+                const int n = ((kh >> 1) * 2 + (kw >> 1)) * 32 + ((kh & 1) * 2 + (kw & 1)) * 8 + ci;
+                const int row = slot * 8 + co;
+                out[idx] = fs[row * kPitch + n] + fs[(32 + row) * kPitch + n];
+            }
+            if (r < 8) {
+                float sacc = 0.f;
+                for (int k = 0; k < 128; ++k) sacc += bs[k * 33 + slot * 8 + r];
+                out[128 * 8 + r] = sacc;
+            }
+        }
+    } else if (warp < 4 + kConvWarps) {
+        // ================= X converters (as in the forward kernel) =================
+        const int cidx = threadIdx.x - 128;
+        int it = 0;
+        for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+            float4 v[2][4];
+            int rr[2], pyy[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const int item = cidx + u * kConvThreads;
+                const int py = item >= g.xrows ? 1 : 0, r = item - py * g.xrows;
+                rr[u] = item < 2 * g.xrows ? r : -1;
+                pyy[u] = py;
+                const int Rr = tile * kTileM + r;
+                if (rr[u] >= 0 && Rr < NR) {
+                    const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+                    const float4* src = reinterpret_cast<const float4*>(
+                        X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[u][q] = __ldg(src + q);
+                } else {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) v[u][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            const int stage = it % kWgStages;
+            mbar_wait(&x_empty[stage], ((it / kWgStages) & 1) ^ 1);
+            uint8_t* xs = st_s + (size_t)stage * stage_bytes;
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (rr[u] >= 0) {
+#pragma unroll
+                    for (int px = 0; px < 2; ++px) {
+                        uint4 hi, lo;
+                        split8(v[u][2 * px], v[u][2 * px + 1], hi, lo);
+                        uint8_t* dst = xs + (size_t)(pyy[u] * 2 + px) * g.chunk_bytes + rr[u] * 16;
+                        *reinterpret_cast<uint4*>(dst) = hi;
+                        *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
+                    }
+                }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&x_full[stage]);
+        }
+    } else {
+        // ================= MMA issue =================
+        const uint32_t idesc = make_idesc_f16(64, 32, 1, 1, 1, 1);         // bf16, A and B MN-major
+        int it = 0;
+        for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+            const int stage = it % kWgStages;
+            mbar_wait(&x_full[stage], (it / kWgStages) & 1);
+            tc_fence_after();
+            const uint32_t xs = smem_u32(st_s + (size_t)stage * stage_bytes);
+            const uint32_t ds = xs + (uint32_t)g.stage_bytes;
+#pragma unroll 2
+            for (int ks = 0; ks < kTileM / 16; ++ks) {
+                const uint64_t a_d = make_smem_desc(ds + (uint32_t)(ks * 256), 128, kDChunk);
+#pragma unroll
+                for (int tap = 0; tap < 4; ++tap) {
+                    const uint32_t b_addr = xs + (uint32_t)(((tap >> 1) * g.Xp + (tap & 1)) * 16 + ks * 256);
+                    const uint64_t b_hi = make_smem_desc(b_addr, 128, g.chunk_bytes);
+                    const uint64_t b_lo = make_smem_desc(b_addr + g.hl_bytes, 128, g.chunk_bytes);
+                    if (elect_one()) {
+                        umma_f16(td + tap * 32, a_d, b_hi, idesc, (it | ks) ? 1u : 0u);
+                        umma_f16(td + tap * 32, a_d, b_lo, idesc, 1u);
+                    }
+                }
+            }
+            if (elect_one()) umma_commit(&x_empty[stage]);
+            __syncwarp();
+        }
+        if (elect_one()) umma_commit(acc_full);
+        __syncwarp();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(td, 128);
+}
+
 uint32_t pow2_cols(uint32_t n) {
     uint32_t c = 32;
     while (c < n) c <<= 1;
@@ -593,5 +812,25 @@ int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     }
     h->absmax_fused = amax != nullptr;
     PN_LAUNCH_CHECK(h, "conv_mid_dgrad_tc_kernel");
+    return PN_OK;
+}
+
+bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) { return h->tc_mid[l] && h->max_active[l] <= 4; }
+
+int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used) {
+    const PnNetDesc& nd = h->nd;
+    MidTcGeom g;
+    if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+    const int ntile = (B * g.RB + kTileM - 1) / kTileM;
+    const int nch = std::max(1, std::min(std::min(h->nch, ntile), 3 * h->num_sms / std::max(1, h->P)));
+    const size_t smem = 128 + (size_t)kWgStages * (g.stage_bytes + 8 * kDChunk);
+    PN_CUDA(h, cudaFuncSetAttribute(conv_mid_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        PnProfScope prof(h, PN_PROF_CONV_WGRAD + l, st);
+        conv_mid_wgrad_tc_kernel<<<h->P * nch, kFwdThreads, smem, st>>>(h->act[l - 1], h->dact[l], h->rmask[l], nd, l, g,
+                                                                       h->d_masks, B, ntile, nch, h->nch, h->wpart[l]);
+    }
+    PN_LAUNCH_CHECK(h, "conv_mid_wgrad_tc_kernel");
+    *nch_used = nch;
     return PN_OK;
 }

@@ -165,6 +165,8 @@ bool pn_conv_mid_tc_supported(const pn_handle* h, int l);
 size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l);
 int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st);
 int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st);
+bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l);
+int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used);
 // pn_conv_mid.cu
 bool pn_conv_mid_supported(const pn_handle* h, int l);
 int pn_launch_conv_mid_fwd(pn_handle* h, int l, int B, cudaStream_t st);

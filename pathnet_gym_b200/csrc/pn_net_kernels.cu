@@ -808,7 +808,11 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         const int npix = nd.OH[l] * nd.OW[l];
         if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
             int nch_used = 1;
-            if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, true, !h->tc_mid[l])) return rc;
+            const bool wg_tc = pn_conv_mid_wgrad_tc_usable(h, l);
+            if (wg_tc)
+                if (int rc = pn_launch_conv_mid_wgrad_tc(h, l, B, st, &nch_used)) return rc;
+            if (!wg_tc || !h->tc_mid[l])
+                if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, !wg_tc, !h->tc_mid[l])) return rc;
             if (h->tc_mid[l])
                 if (int rc = pn_launch_conv_mid_dgrad_tc(h, l, B, st)) return rc;
             const int n1 = nd.KK[l] * PN_F + PN_F;
