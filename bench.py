@@ -116,10 +116,8 @@ def kernel_work(name, pop, B):
         return "tensor", 2.0 * dims[l][0] * dims[l][1] * cfg.F * pc(l) * B
     if name in ("lin_fwd", "lin_dgrad", "lin_wgrad"):
         return "tensor", 2.0 * pop.last_lin * cfg.hidden * pc(cfg.L - 1) * B
-    if name == "head_loss":
-        return "tensor", 2.0 * cfg.hidden * (cfg.A + 1) * 2 * T
-    if name == "head_wgrad":
-        return "tensor", 2.0 * cfg.hidden * (cfg.A + 1) * T
+    if name == "head_loss":          # logits + dh + chunk partials of the head weight gradient in one kernel
+        return "tensor", 2.0 * cfg.hidden * (cfg.A + 1) * 3 * T
     nonfrozen = float(sum(t["length"] for t, f in zip(pop.tensors, pop.frozen) if not f))
     if name == "rms_update":
         return "hbm", 20.0 * nonfrozen          # read g, var, ms; write var, ms (momentum slot elided)

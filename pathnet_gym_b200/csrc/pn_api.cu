@@ -194,6 +194,9 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
             PN_TRYC(cudaMemcpy(h->tc_dbg + (size_t)h->num_sms * 8, &mode, sizeof(mode), cudaMemcpyHostToDevice));
         }
     }
+    PN_TRYC(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
+    PN_TRYC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+    PN_TRYC(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     // staging for the host-pointer entry point
     PN_TRY(dev_alloc(h, &h->st_actions, T));
     PN_TRY(dev_alloc(h, &h->st_td, T));
@@ -224,6 +227,9 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
         if (sl.copied) cudaEventDestroy(sl.copied);
         if (sl.consumed) cudaEventDestroy(sl.consumed);
     }
+    if (h->side) cudaStreamDestroy(h->side);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
     delete h;
 }
@@ -280,9 +286,9 @@ extern "C" PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int c
         else if (slot < PN_PROF_CONV_DGRAD) { base = "conv_wgrad_reduce"; layer = slot - PN_PROF_CONV_WGRAD_REDUCE; }
         else if (slot < PN_PROF_LIN_FWD) { base = "conv_dgrad"; layer = slot - PN_PROF_CONV_DGRAD; }
         else {
-            static const char* names[] = {"lin_fwd", "head_loss", "head_wgrad", "lin_dgrad", "lin_wgrad",
+            static const char* names[] = {"lin_fwd", "head_loss", "grad_reduce", "lin_dgrad", "lin_wgrad",
                                           "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant", "lin_prep",
-                                          "conv_mid_prep"};
+                                          "conv_mid_prep", "lin_wprep"};
             base = names[slot - PN_PROF_LIN_FWD];
         }
         if (layer >= 0) snprintf(out[n].name, sizeof(out[n].name), "%s_l%d", base, layer);

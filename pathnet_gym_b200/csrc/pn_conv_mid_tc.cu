@@ -764,10 +764,8 @@ size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l) {
     return (size_t)h->nd.M * 2 * kModBytes * 2;       // wf | wd
 }
 
-int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
+int pn_launch_conv_mid_wprep(pn_handle* h, int l, cudaStream_t st) {
     const PnNetDesc& nd = h->nd;
-    MidTcGeom g;
-    if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
     uint8_t* wf = h->tc_mid_buf[l];
     uint8_t* wd = wf + (size_t)nd.M * 2 * kModBytes;
     {
@@ -775,6 +773,14 @@ int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
         conv_mid_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, l, wf, wd);
     }
     PN_LAUNCH_CHECK(h, "conv_mid_wprep_kernel");
+    return PN_OK;
+}
+
+int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    MidTcGeom g;
+    if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+    const uint8_t* wf = h->tc_mid_buf[l];
     const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
     const uint32_t tmem_cols = pow2_cols(16u * w_slots);
     const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * g.stage_bytes;

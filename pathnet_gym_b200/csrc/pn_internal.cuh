@@ -42,6 +42,7 @@ enum PnProfSlot {
     PN_PROF_CONV0_DQUANT,
     PN_PROF_LIN_PREP,
     PN_PROF_CONV_MID_PREP,
+    PN_PROF_LIN_WPREP,
     PN_PROF_NSLOTS
 };
 #define PN_PROF_RING 64
@@ -92,6 +93,8 @@ struct pn_handle {
     bool tc_mid[PN_MAX_LAYERS] = {};    // middle conv layer l runs on the tensor cores (cfg.flags bit 3 clear)
     uint8_t* tc_mid_buf[PN_MAX_LAYERS] = {};   // bf16 hi/lo weight operand blocks of that layer
     int max_active[PN_MAX_LAYERS] = {}; // largest number of active modules of any path, per layer (from pn_set_genotypes)
+    cudaStream_t side = nullptr;        // weight-operand preparation runs here, beside the first conv layer
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool absmax_fused = false;          // the layer-1 data-gradient launch of this step already wrote max |dY0|
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
     int num_sms = 148;
@@ -163,6 +166,7 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
 // pn_conv_mid_tc.cu
 bool pn_conv_mid_tc_supported(const pn_handle* h, int l);
 size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l);
+int pn_launch_conv_mid_wprep(pn_handle* h, int l, cudaStream_t st);
 int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st);
 int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st);
 bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l);
@@ -174,6 +178,7 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
 // pn_lin_tc.cu
 bool pn_lin_tc_supported(const pn_handle* h);
 size_t pn_lin_tc_scratch_bytes(const pn_handle* h);
+int pn_launch_lin_wsplit(pn_handle* h, cudaStream_t st);
 int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st);
 int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st);
 // pn_rmsprop.cu

@@ -651,6 +651,20 @@ size_t pn_lin_tc_scratch_bytes(const pn_handle* h) {
     return g.wp_module * g.M + g.xp_path * h->P + g.dp_path * h->P;
 }
 
+// W_lin -> Wp: depends on the parameters only, so the forward launcher runs it on the side stream
+int pn_launch_lin_wsplit(pn_handle* h, cudaStream_t st) {
+    LinGeom g;
+    if (!lin_geom(h, h->Bmax, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core linear path not supported");
+    {
+        PnProfScope prof(h, PN_PROF_LIN_WPREP, st);
+        const long long wthreads = (long long)g.M * g.KB * (g.Hd / 32) * 32;
+        const int wblocks = (int)((wthreads + 255) / 256);
+        lin_prep_kernel<<<wblocks, 256, 0, st>>>(h->params, h->nd, g, h->tc_lin_buf, wblocks, nullptr, h->P, 1, nullptr);
+    }
+    PN_LAUNCH_CHECK(h, "lin_prep_kernel");
+    return PN_OK;
+}
+
 int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     LinGeom g;
     if (!lin_geom(h, B, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core linear path not supported");
@@ -661,10 +675,9 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     uint8_t* xp = wp + gmax.wp_module * g.M;
     {
         PnProfScope prof(h, PN_PROF_LIN_PREP, st);
-        const long long wthreads = (long long)g.M * g.KB * (g.Hd / 32) * 32;
         const long long xthreads = (long long)h->P * g.nbc * ((g.KB + 3) / 4) * 128;
-        const int wblocks = (int)((wthreads + 255) / 256), xblocks = (int)((xthreads + 255) / 256);
-        lin_prep_kernel<<<wblocks + xblocks, 256, 0, st>>>(h->params, nd, g, wp, wblocks, h->act[nd.nconv - 1], h->P, B, xp);
+        const int xblocks = (int)((xthreads + 255) / 256);
+        lin_prep_kernel<<<xblocks, 256, 0, st>>>(h->params, nd, g, wp, 0, h->act[nd.nconv - 1], h->P, B, xp);
     }
     PN_LAUNCH_CHECK(h, "lin_prep_kernel");
     const size_t smem = (size_t)kWStages * 2 * kWChunkKb * 16 * kBlk + g.xp_chunk + 256;

@@ -365,14 +365,13 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
 // stage 2: fixed-order sum over chunks, scatter into W_fc2/b_fc2/W_fc3/b_fc3.
 // block = 32 elements x 8 chunk groups; group g adds chunks g, g+8, ... in order, then the 8 group sums are
 // added in group order (deterministic, 8x more loads in flight than one thread per element)
-__global__ void __launch_bounds__(256)
-head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc nd, float* __restrict__ grads,
-                         int nred_blocks, const float* __restrict__ loss_t, int P, int B, float* __restrict__ loss) {
-    __shared__ float red[8][33];
+__device__ __forceinline__ void head_reduce_body(int bid, const float* __restrict__ part, int nchunks, const PnNetDesc& nd,
+                                                 float* __restrict__ grads, int nred_blocks, const float* __restrict__ loss_t,
+                                                 int P, int B, float* __restrict__ loss, float (*red)[33]) {
     const int Hd = nd.hidden, A = nd.A, A1 = A + 1;
     const int n = Hd * A1 + A1;
-    if ((int)blockIdx.x >= nred_blocks) {            // trailing blocks: per-path loss = sum over its B transitions
-        const int p = ((int)blockIdx.x - nred_blocks) * blockDim.x + threadIdx.x;
+    if (bid >= nred_blocks) {                        // trailing blocks: per-path loss = sum over its B transitions
+        const int p = (bid - nred_blocks) * blockDim.x + threadIdx.x;
         if (p < P) {
             float s = 0.f;
             for (int b = 0; b < B; ++b) s += loss_t[(size_t)p * B + b];
@@ -381,7 +380,7 @@ head_wgrad_reduce_kernel(const float* __restrict__ part, int nchunks, PnNetDesc 
         return;
     }
     const int el = threadIdx.x & 31, grp = threadIdx.x >> 5;
-    const int e = blockIdx.x * 32 + el;
+    const int e = bid * 32 + el;
     float s = 0.f;
     if (e < n)
         for (int c = grp; c < nchunks; c += 8) s += part[(size_t)c * n + e];
@@ -657,15 +656,13 @@ conv_wgrad_kernel(const TIn* __restrict__ X, float in_scale, const float* __rest
 // fixed-order reduction of the partials over the paths that use module (l, j).
 // block = 32 elements x 8 term groups (term = (path in the module's list, chunk)); group g adds terms
 // g, g+8, ... in order, then the 8 group sums are added in group order.
-__global__ void __launch_bounds__(256)
-conv_wgrad_reduce_kernel(const float* __restrict__ part, PnNetDesc nd, int l, const int* __restrict__ list,
-                         const int* __restrict__ list_count, int P, int nch_alloc, int nch_active,
-                         float* __restrict__ grads) {
-    __shared__ float red[8][33];
-    const int j = blockIdx.x, KK = nd.KK[l];
+__device__ __forceinline__ void conv_reduce_body(int j, int by, const float* __restrict__ part, const PnNetDesc& nd, int l,
+                                                 const int* __restrict__ list, const int* __restrict__ list_count, int P,
+                                                 int nch_alloc, int nch_active, float* __restrict__ grads, float (*red)[33]) {
+    const int KK = nd.KK[l];
     const int n = KK * PN_F + PN_F;
     const int el = threadIdx.x & 31, grp = threadIdx.x >> 5;
-    const int e = blockIdx.y * 32 + el;
+    const int e = by * 32 + el;
     const int lm = l * nd.M + j, cnt = list_count[lm];
     const int* lst = list + (size_t)lm * P;
     const int nterms = cnt * nch_active;
@@ -686,6 +683,33 @@ conv_wgrad_reduce_kernel(const float* __restrict__ part, PnNetDesc nd, int l, co
     else grads[wb + nd.convb_off[l] + (e - KK * PN_F)] = s;
 }
 
+// One launch finishes every gradient that is accumulated through partial buffers: the conv layers' weight
+// gradients (sum over the paths of each module's list and their chunks), the head weights (sum over chunks) and
+// the per-path loss.  All sums run in a fixed order.
+struct PnReduceJobs {
+    int nconv;                                   // conv jobs in use
+    int l[PN_MAX_LAYERS], nch_active[PN_MAX_LAYERS], nby[PN_MAX_LAYERS], blk0[PN_MAX_LAYERS];
+    const float* part[PN_MAX_LAYERS];
+    int head_blk0, head_nred, head_nchunks;
+};
+
+__global__ void __launch_bounds__(256)
+grad_reduce_kernel(PnReduceJobs jobs, PnNetDesc nd, const int* __restrict__ list, const int* __restrict__ list_count, int P,
+                   int B, int nch_alloc, const float* __restrict__ head_part, const float* __restrict__ loss_t,
+                   float* __restrict__ loss, float* __restrict__ grads) {
+    __shared__ float red[8][33];
+    const int bid = blockIdx.x;
+    if (bid >= jobs.head_blk0) {
+        head_reduce_body(bid - jobs.head_blk0, head_part, jobs.head_nchunks, nd, grads, jobs.head_nred, loss_t, P, B, loss, red);
+        return;
+    }
+    int q = 0;
+    while (q + 1 < jobs.nconv && bid >= jobs.blk0[q + 1]) ++q;
+    const int local = bid - jobs.blk0[q];
+    conv_reduce_body(local / jobs.nby[q], local % jobs.nby[q], jobs.part[q], nd, jobs.l[q], list, list_count, P, nch_alloc,
+                     jobs.nch_active[q], grads, red);
+}
+
 template <typename K>
 int set_smem(pn_handle* h, K kern, size_t bytes) {
     if (bytes > 48 * 1024) {
@@ -703,7 +727,26 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
     const PnNetDesc& nd = h->nd;
     const int T = h->P * B;
     (void)training;
+    // operand preparation that depends on the parameters only (bf16 hi/lo weight blocks of the middle conv layers and
+    // the linear modules) runs on the side stream, next to the first conv layer
+    bool forked = false;
+    {
+        bool any = h->tc_lin;
+        for (int l = 1; l < nd.nconv; ++l) any = any || h->tc_mid[l];
+        if (any) {
+            PN_CUDA(h, cudaEventRecord(h->ev_fork, st));
+            PN_CUDA(h, cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+            for (int l = 1; l < nd.nconv; ++l)
+                if (h->tc_mid[l])
+                    if (int rc = pn_launch_conv_mid_wprep(h, l, h->side)) return rc;
+            if (h->tc_lin)
+                if (int rc = pn_launch_lin_wsplit(h, h->side)) return rc;
+            PN_CUDA(h, cudaEventRecord(h->ev_join, h->side));
+            forked = true;
+        }
+    }
     for (int l = 0; l < nd.nconv; ++l) {
+        if (l == 1 && forked) { PN_CUDA(h, cudaStreamWaitEvent(st, h->ev_join, 0)); forked = false; }
         if (l == 0 && is_u8 && h->tc_conv0) {
             if (int rc = pn_launch_conv0_fwd_tc(h, (const uint8_t*)frames, B, st)) return rc;
             continue;
@@ -736,6 +779,7 @@ int pn_launch_forward(pn_handle* h, const void* frames, int is_u8, int B, bool t
         }
         PN_LAUNCH_CHECK(h, "conv_fwd_kernel");
     }
+    if (forked) { PN_CUDA(h, cudaStreamWaitEvent(st, h->ev_join, 0)); forked = false; }
     if (h->tc_lin) return pn_launch_lin_fwd_tc(h, B, st);
     dim3 grid(h->P, (nd.hidden + 63) / 64, (B + 31) / 32);
     {
@@ -770,17 +814,13 @@ int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, 
 int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaStream_t st) {
     const PnNetDesc& nd = h->nd;
     const int T = h->P * B, P = h->P;
-    // heads
-    {
-        const int nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
-        PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
-        const int n = nd.hidden * (nd.A + 1) + nd.A + 1;
-        const int nred = (n + 31) / 32, nloss = h->pending_loss ? (P + 255) / 256 : 0;
-        head_wgrad_reduce_kernel<<<nred + nloss, 256, 0, st>>>(h->head_part, nchunks, nd, h->grads, nred, h->loss_t, P,
-                                                               B, h->pending_loss);
-        h->pending_loss = nullptr;
-        PN_LAUNCH_CHECK(h, "head_wgrad_reduce_kernel");
-    }
+    PnReduceJobs jobs;
+    jobs.nconv = 0;
+    auto add_job = [&](int l, int nch_active) {
+        const int q = jobs.nconv++;
+        jobs.l[q] = l; jobs.nch_active[q] = nch_active; jobs.part[q] = h->wpart[l];
+        jobs.nby[q] = (nd.KK[l] * PN_F + PN_F + 31) / 32;
+    };
     // linear modules
     if (h->tc_lin) {
         if (int rc = pn_launch_lin_bwd_tc(h, B, st)) return rc;
@@ -815,26 +855,12 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
                 if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, !wg_tc, !h->tc_mid[l])) return rc;
             if (h->tc_mid[l])
                 if (int rc = pn_launch_conv_mid_dgrad_tc(h, l, B, st)) return rc;
-            const int n1 = nd.KK[l] * PN_F + PN_F;
-            dim3 gr1(nd.M, (n1 + 31) / 32);
-            {
-                PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
-                conv_wgrad_reduce_kernel<<<gr1, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
-                                                              nch_used, h->grads);
-            }
-            PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
+            add_job(l, nch_used);
             continue;
         }
         if (l == 0 && is_u8 && h->tc_conv0) {
             if (int rc = pn_launch_conv0_wgrad_tc(h, (const uint8_t*)frames, B, st)) return rc;
-            const int n0 = nd.KK[l] * PN_F + PN_F;
-            dim3 gr0(nd.M, (n0 + 31) / 32);
-            {
-                PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
-                conv_wgrad_reduce_kernel<<<gr0, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
-                                                              h->last_wgrad_nch, h->grads);
-            }
-            PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
+            add_job(l, h->last_wgrad_nch);
             continue;
         }
         const int threads = (nd.KK[l] + 31) / 32 * 32;
@@ -855,14 +881,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         }
         }
         PN_LAUNCH_CHECK(h, "conv_wgrad_kernel");
-        const int n = nd.KK[l] * PN_F + PN_F;
-        dim3 gr(nd.M, (n + 31) / 32);
-        {
-            PnProfScope prof(h, PN_PROF_CONV_WGRAD_REDUCE + l, st);
-            conv_wgrad_reduce_kernel<<<gr, 256, 0, st>>>(h->wpart[l], nd, l, h->d_list, h->d_list_count, P, h->nch,
-                                                         nch_active, h->grads);
-        }
-        PN_LAUNCH_CHECK(h, "conv_wgrad_reduce_kernel");
+        add_job(l, nch_active);
         if (l > 0) {
             const size_t smd = (((size_t)npix * PN_F + 3) & ~(size_t)3) * sizeof(float) +
                                (size_t)nd.M * nd.KK[l] * PN_F * sizeof(float) + (size_t)nd.M * npix;
@@ -872,6 +891,20 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
                                                    h->dact[l - 1]);
             PN_LAUNCH_CHECK(h, "conv_dgrad_kernel");
         }
+    }
+    {
+        int blk = 0;
+        for (int q = 0; q < jobs.nconv; ++q) { jobs.blk0[q] = blk; blk += nd.M * jobs.nby[q]; }
+        const int nh = nd.hidden * (nd.A + 1) + nd.A + 1;
+        jobs.head_blk0 = blk;
+        jobs.head_nred = (nh + 31) / 32;
+        jobs.head_nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
+        const int nloss = h->pending_loss ? (P + 255) / 256 : 0;
+        PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
+        grad_reduce_kernel<<<blk + jobs.head_nred + nloss, 256, 0, st>>>(jobs, nd, h->d_list, h->d_list_count, P, B, h->nch,
+                                                                         h->head_part, h->loss_t, h->pending_loss, h->grads);
+        h->pending_loss = nullptr;
+        PN_LAUNCH_CHECK(h, "grad_reduce_kernel");
     }
     return PN_OK;
 }
