@@ -45,6 +45,13 @@ __global__ void __launch_bounds__(416) timing(const int* cfg, long long* out, co
                 mbar_wait(&bar2, ph); ph ^= 1;
                 tc_fence_after();
             }
+        } else if (cfg[9] >= 3000 && cfg[9] < 3004) {   // distinct operand data per MMA: A and/or B start address cycles through its region
+            const uint64_t am = (cfg[9] & 1) ? 1 : 0, bm = (cfg[9] & 2) ? 1 : 0;
+            for (int i = 0; i < 4000; i += 20) {
+#pragma unroll
+                for (int j = 0; j < 20; ++j)
+                    umma_i8(td + (j & 3) * 128, ad + am * (uint64_t)((j * 4096) >> 4), bd + bm * (uint64_t)(((j % 5) * 256) >> 4), idesc, (i | j) >= 4);
+            }
         } else
         if (nacc == 4) { for (int i = 0; i < reps; ++i) umma_i8(td + (i & 3) * 128, ad, bd, idesc, i >= 4); }
         else if (nacc == 2) { for (int i = 0; i < reps; ++i) umma_i8(td + (i & 1) * 128, ad, bd, idesc, i >= 2); }
@@ -53,7 +60,7 @@ __global__ void __launch_bounds__(416) timing(const int* cfg, long long* out, co
         umma_commit(&bar);
         mbar_wait(&bar, 0);
         const long long t2 = clock64();
-        out[0] = t1 - t0; out[1] = t2 - t0;
+        out[0] = t1 - t0; out[1] = t2 - t0; if (cfg[9] >= 3000) { out[0] = out[0] * cfg[9] / 4000; out[1] = out[1] * cfg[9] / 4000; }
         done = 1;
     } else if (threadIdx.x >= 128) {
         const int w = (threadIdx.x >> 5) - 4;            // 0..7
@@ -98,19 +105,21 @@ int main() {
     struct C { const char* name; int v[14]; };
     const int R = 7056;
     C cases[] = {
-        {"M128 N80 A K-major SBO128 LBO7168 off 0  ", {128, 80, 0, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
-        {"M128 N80 A K-major SBO128 LBO7168 off 16 ", {128, 80, 16, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
-        {"M128 N80 A K-major SBO128 LBO7168 off 80 ", {128, 80, 80, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
-        {"M128 N80 A K-major SBO128 LBO7168 off 64 ", {128, 80, 64, 7168, 128, 128, 2048, 0, 0, 4000, 4, 0, 0, 0}},
-        {"M128 N80 A off 80 + 8 warps LDTM         ", {128, 80, 80, 7168, 128, 128, 2048, 0, 0, 4000, 4, 8, 0, 0}},
+        {"M128 N80 same A, same B        ", {128, 80, 0, 128, 128, 128, 2048, 0, 0, 3000, 4, 0, 0, 0}},
+        {"M128 N80 distinct A (80 KB)    ", {128, 80, 0, 128, 128, 128, 2048, 0, 0, 3001, 4, 0, 0, 0}},
+        {"M128 N80 distinct B            ", {128, 80, 0, 128, 128, 128, 2048, 0, 0, 3002, 4, 0, 0, 0}},
+        {"M128 N80 distinct A and B      ", {128, 80, 0, 128, 128, 128, 2048, 0, 0, 3003, 4, 0, 0, 0}},
+        {"M128 N80 distinct A, LBO 7168  ", {128, 80, 0, 7168, 128, 128, 2048, 0, 0, 3001, 4, 0, 0, 0}},
     };
     for (auto& c : cases) {
         CK(cudaMemcpy(cfg_d, c.v, sizeof(c.v), cudaMemcpyHostToDevice));
-        timing<<<1, 416, 160 * 1024>>>(cfg_d, out_d, gsrc);
-        CK(cudaDeviceSynchronize());
-        long long o[2];
-        CK(cudaMemcpy(o, out_d, 16, cudaMemcpyDeviceToHost));
-        printf("%s issue %.1f cyc/mma, complete %.1f cyc/mma\n", c.name, (double)o[0] / c.v[9], (double)o[1] / c.v[9]);
+        for (int grid : {1, 148}) {
+            timing<<<grid, 416, 160 * 1024>>>(cfg_d, out_d, gsrc);
+            CK(cudaDeviceSynchronize());
+            long long o[2];
+            CK(cudaMemcpy(o, out_d, 16, cudaMemcpyDeviceToHost));
+            printf("%s grid %3d: issue %.1f cyc/mma, complete %.1f cyc/mma\n", c.name, grid, (double)o[0] / c.v[9], (double)o[1] / c.v[9]);
+        }
     }
     return 0;
 }

@@ -153,6 +153,8 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
     const int t_lo = (int)((long long)T * blockIdx.x / gridDim.x);
     const int t_hi = (int)((long long)T * (blockIdx.x + 1) / gridDim.x);
     const int npix = gm.OH * gm.OW;
+    const bool dbg_detail = dbg && dbg[gridDim.x * 8] == 1;
+    const long long t_entry = dbg ? clock64() : 0;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < gm.nst; ++i) { mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1); }
@@ -187,7 +189,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             __syncwarp();
             if (++stage == gm.nst) { stage = 0; phase ^= 1; }
         }
-        if (dbg && lane == 0) { dbg[blockIdx.x * 8 + 0] = w_empty; dbg[blockIdx.x * 8 + 1] = clock64() - t_begin; }
+        if (dbg && lane == 0 && dbg[gridDim.x * 8] == 4) { dbg[blockIdx.x * 8 + 0] = w_empty; dbg[blockIdx.x * 8 + 1] = clock64() - t_begin; }
     } else if (warp == 4 * kEpiGroups + 1) {
         // ================= B gather + MMA issue =================
         // Everything here is executed by the whole (converged) warp on warp-uniform values; only the
@@ -196,9 +198,12 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         uint32_t fphase = 0, drain_phase = 0, b_phase = 0, idle_phase = 0;
         uint32_t tilec = 0, fill_par = 0;            // tiles issued; bit a = parity of the fills of accumulator stage a
         const long long t_begin = clock64();
-        long long w_frame = 0, w_acc = 0;
+        long long w_frame = 0, w_acc = 0, w_path = 0, w_issue = 0, w_fence = 0, w_commit = 0, w_desc = 0, w_fend = 0;
+        const bool dbg_nomma = dbg && __reduce_or_sync(0xffffffffu, (unsigned)(dbg[gridDim.x * 8] == 6));   // experiment: no MMAs at all
+        const bool dbg_twice = dbg && __reduce_or_sync(0xffffffffu, (unsigned)(dbg[gridDim.x * 8] == 3));   // experiment: every MMA twice
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
+            const long long cp0 = dbg_detail ? clock64() : 0;
             if (p != cur_path) {
                 if (cur_path >= 0) {
                     // every MMA that reads the old B has completed, every accumulator has been drained
@@ -230,9 +235,11 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                 if (elect_one()) mbar_arrive(path_ready);
                 cur_path = p;
             }
-            const long long cf0 = dbg ? clock64() : 0;
+            if (dbg_detail) w_path += clock64() - cp0;
+            const long long cf0 = dbg_detail ? clock64() : 0;
             mbar_wait(&frame_full[stage], fphase);
-            if (dbg) w_frame += clock64() - cf0;
+            if (dbg_detail) w_frame += clock64() - cf0;
+            const long long cd0 = dbg_detail ? clock64() : 0;
             tc_fence_after();
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
@@ -249,37 +256,82 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             }
             const uint32_t ahi = desc_hi(128), bhi = desc_hi(2048);
             const int nmma = 4 * gm.ksteps;
+            if (dbg_detail) w_desc += clock64() - cd0;
+            if (npass == 1 && gm.tiles == kAccStages && nmma == 8) {
+                // Common case (84x84x4 frames, at most 4 active modules): a frame is exactly one tile per
+                // accumulator stage.  This warp's scalar instruction stream is the critical path of the whole
+                // kernel (one warp, dependent uniform-datapath ops at ~7 cycles each: 120 instructions per tile were
+                // measured at ~870 cycles against 424 cycles of tensor time), so everything is hoisted: the 16
+                // descriptors are built once per frame as 64-bit values and a tile costs one add per MMA.
+                const int N = (24 * ns + 15) & ~15;
+                const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
+                uint64_t a64[8], b64[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { a64[i] = desc_join(alo[i], ahi); b64[i] = desc_join(blo[i], bhi); }
+#pragma unroll
+                for (int tile = 0; tile < kAccStages; ++tile) {
+                    mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
+                    tc_fence_after();
+                    const uint32_t dcol = td + tile * kAccCols;
+                    if (!dbg_nomma && elect_one()) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) umma_i8(dcol, a64[i] + (uint64_t)(tile * 128), b64[i], idesc, i ? 1u : 0u);
+                        umma_commit(&acc_full[tile]);
+                    } else if (dbg_nomma && elect_one()) {
+                        umma_commit(&acc_full[tile]);
+                    }
+                    __syncwarp();
+                }
+                fill_par ^= (1u << kAccStages) - 1u;
+                tilec += kAccStages;
+            } else
             for (int tile = 0; tile < gm.tiles && npass > 0; ++tile, ++tilec) {
                 const uint32_t acc = tilec & (kAccStages - 1);
                 for (int pass = 0; pass < npass; ++pass) {
-                    const long long ca0 = dbg ? clock64() : 0;
+                    const long long ca0 = dbg_detail ? clock64() : 0;
                     mbar_wait(&acc_empty[acc], ((fill_par >> acc) & 1u) ^ 1u);
-                    if (dbg) w_acc += clock64() - ca0;
+                    if (dbg_detail) w_acc += clock64() - ca0;
+                    const long long cq0 = dbg_detail ? clock64() : 0;
                     tc_fence_after();
+                    if (dbg_detail) w_fence += clock64() - cq0;
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const int N = (24 * nsl + 15) & ~15;
                     const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
                     const uint32_t dcol = td + acc * kAccCols;
                     const uint32_t a_adv = (uint32_t)(tile * 128), b_adv = (uint32_t)((pass * kPassSlots * kSlotBytes) >> 4);
+                    const long long ci0 = dbg_detail ? clock64() : 0;
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
-                        if (i < nmma && elect_one())
+                        if (i < nmma && !dbg_nomma && elect_one())
                             umma_i8(dcol, desc_join(alo[i] + a_adv, ahi), desc_join(blo[i] + b_adv, bhi), idesc, i ? 1u : 0u);
+                    if (dbg_detail) w_issue += clock64() - ci0;
+                    if (dbg_twice) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (i < nmma && elect_one())
+                                umma_i8(dcol, desc_join(alo[i] + a_adv, ahi), desc_join(blo[i] + b_adv, bhi), idesc, 1u);
+                    }
+                    const long long cc0 = dbg_detail ? clock64() : 0;
                     if (elect_one()) umma_commit(&acc_full[acc]);
                     __syncwarp();
+                    if (dbg_detail) w_commit += clock64() - cc0;
                     fill_par ^= 1u << acc;
                 }
             }
             // the frame stage is free once every MMA issued so far has completed
+            const long long ce0 = dbg_detail ? clock64() : 0;
             if (elect_one()) {
                 if (npass > 0) umma_commit(&frame_empty[stage]);
                 else mbar_arrive(&frame_empty[stage]);
             }
             __syncwarp();
+            if (dbg_detail) w_fend += clock64() - ce0;
             if (++stage == gm.nst) { stage = 0; fphase ^= 1; }
         }
         if (dbg && lane == 0) {
-            dbg[blockIdx.x * 8 + 2] = w_frame; dbg[blockIdx.x * 8 + 3] = w_acc; dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
+            dbg[blockIdx.x * 8 + 2] = w_desc; dbg[blockIdx.x * 8 + 3] = w_fend; dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
+            dbg[blockIdx.x * 8 + 4] = w_path; dbg[blockIdx.x * 8 + 0] = dbg_detail ? w_issue : t_begin - t_entry;
+            dbg[blockIdx.x * 8 + 1] = w_fence; dbg[blockIdx.x * 8 + 6] = dbg_detail ? w_commit : clock64();
         }
     } else {
         // ================= epilogue: thread = TMEM lane = output pixel of the tile =================
@@ -364,11 +416,15 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                 }
             }
         }
-        if (dbg && threadIdx.x == 0) { dbg[blockIdx.x * 8 + 6] = w_full; dbg[blockIdx.x * 8 + 7] = clock64() - t_begin; }
+        if (dbg && threadIdx.x == 0) { if (dbg[gridDim.x * 8] == 4) dbg[blockIdx.x * 8 + 6] = w_full; dbg[blockIdx.x * 8 + 7] = clock64() - t_begin; }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 4 * kEpiGroups + 1) tmem_dealloc(td, kAccStages * kAccCols);
+    if (dbg && !dbg_detail && threadIdx.x == 0) {        // timeline: MMA-loop end -> kernel exit, entry -> exit
+        dbg[blockIdx.x * 8 + 6] = clock64() - dbg[blockIdx.x * 8 + 6];
+        dbg[blockIdx.x * 8 + 7] = clock64() - t_entry;
+    }
 }
 
 
