@@ -170,6 +170,16 @@ PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* frames_host,
                                 void* copy_stream);
 PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, float* loss_host, void* stream);
 
+/* Multi-GPU overlap (the reference has one process and no exchange).  The gradient slab is
+ * ordered like the parameters: conv tensors, linear-module tensors, head tensors.  The linear modules hold
+ * ~97 % of the gradient bytes and their weight-gradient kernel runs BEFORE the conv layers' backward pass, so
+ * the host can start summing that region over the GPUs while the rest of the step still runs:
+ *   pn_lin_grads_region    -> offset / length (in floats) of the W_lin, b_lin region inside the gradient slab
+ *   pn_stream_wait_lin_grads -> `stream` waits until the most recent pn_train_step* has written that region
+ * The other two regions are complete when the step's stream work is. */
+PN_API int pn_lin_grads_region(const pn_handle* h, int64_t* offset_floats, int64_t* count_floats);
+PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
+
 /* Replaces RMSPropApplier.apply_gradients for the non-frozen tensors
  * (rmsprop_applier.py:79-106): per tensor g' = clip_by_norm(g, clip_norm);
  * ms += (g'^2 - ms)(1-decay); mom = momentum*mom + lr*g'/sqrt(ms+eps);

@@ -197,6 +197,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
     PN_TRYC(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    PN_TRYC(cudaEventCreateWithFlags(&h->ev_lin_grads, cudaEventDisableTiming));
     // staging for the host-pointer entry point
     PN_TRY(dev_alloc(h, &h->st_actions, T));
     PN_TRY(dev_alloc(h, &h->st_td, T));
@@ -230,6 +231,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     if (h->side) cudaStreamDestroy(h->side);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->ev_lin_grads) cudaEventDestroy(h->ev_lin_grads);
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
     delete h;
 }
@@ -341,6 +343,20 @@ extern "C" PN_API int pn_set_genotypes(pn_handle* h, const uint32_t* masks_host,
     PN_CUDA(h, cudaMemcpyAsync(h->d_list_count, cnt.data(), cnt.size() * sizeof(int), cudaMemcpyHostToDevice, st));
     PN_CUDA(h, cudaStreamSynchronize(st));   // the host vectors above go out of scope
     h->have_masks = true;
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_lin_grads_region(const pn_handle* h, int64_t* offset_floats, int64_t* count_floats) {
+    if (!h || !offset_floats || !count_floats) return pn_fail_global(PN_ERR_INVALID, "pn_lin_grads_region: null argument");
+    *offset_floats = h->nd.linW_base;
+    *count_floats = h->nd.fc2W - h->nd.linW_base;      // the head tensors follow the linear modules in the slab
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "pn_stream_wait_lin_grads: null handle");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    PN_CUDA(h, cudaStreamWaitEvent((cudaStream_t)stream, h->ev_lin_grads, 0));
     return PN_OK;
 }
 

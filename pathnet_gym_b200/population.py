@@ -236,6 +236,18 @@ class PathNetPopulation:
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
             dist.all_reduce(self.grads, op=dist.ReduceOp.SUM)
 
+    def lin_grads_region(self):
+        """(offset, count) in floats of the W_lin/b_lin gradients inside the gradient slab."""
+        import ctypes as C
+        off, cnt = C.c_int64(0), C.c_int64(0)
+        nat.check(self.lib.pn_lin_grads_region(self._h, C.byref(off), C.byref(cnt)), self._h)
+        return int(off.value), int(cnt.value)
+
+    def stream_wait_lin_grads(self, stream: "torch.cuda.Stream"):
+        """`stream` waits until the latest train_step has written the W_lin/b_lin gradients."""
+        import ctypes as C
+        nat.check(self.lib.pn_stream_wait_lin_grads(self._h, C.c_void_p(stream.cuda_stream)), self._h)
+
     def apply_gradients(self, lr, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0):
         """Per-tensor clip_by_norm + RMSProp on the non-frozen tensors (rmsprop_applier.py:79-106)."""
         nat.check(self.lib.pn_rmsprop_apply(self._h, float(lr), float(decay), float(momentum), float(epsilon),

@@ -1,0 +1,50 @@
+"""torchrun --nproc-per-node N tools/multigpu_check.py : the overlapped gradient sum (trainer.OverlappedGradSum)
+against one plain all-reduce of the whole slab, on N GPUs with different paths per rank.  Bit-exact expected:
+both are NCCL sums of the same per-rank values in the same dtype (ring order may differ -> allow 1e-6 rel)."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from pathnet_gym_b200.population import PathNetConfig, PathNetPopulation, geopath_init
+from pathnet_gym_b200.trainer import OverlappedGradSum
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cfg, P, B = PathNetConfig(), 16, 32
+    pop = PathNetPopulation(cfg, P, B, device=local)
+    pop.init_params(1)
+    masks = geopath_init(P * world, cfg.L, cfg.M, 3, 7, 0, device=local)[rank * P:(rank + 1) * P]
+    pop.set_genotypes(masks.cpu().numpy().view("uint32"))
+    gen = torch.Generator(device=pop.device).manual_seed(100 + rank)
+    frames = torch.randint(0, 256, (P, B, cfg.H, cfg.W, cfg.C), dtype=torch.uint8, device=pop.device, generator=gen)
+    actions = torch.randint(0, cfg.A, (P, B), dtype=torch.int32, device=pop.device, generator=gen)
+    td = torch.randn(P, B, device=pop.device, generator=gen)
+    r = torch.randn(P, B, device=pop.device, generator=gen)
+    gs = OverlappedGradSum(pop)
+    worst = 0.0
+    for it in range(5):
+        pop.train_step(frames, actions, td, r, 0.01)
+        ref = pop.grads.clone()
+        dist.all_reduce(ref)
+        pop.train_step(frames, actions, td, r, 0.01)      # same inputs -> same local gradients (deterministic kernels)
+        gs()
+        torch.cuda.synchronize()
+        err = float((pop.grads - ref).norm() / ref.norm())
+        worst = max(worst, err)
+    if rank == 0:
+        print(json.dumps({"world": world, "overlapped_vs_plain_allreduce_rel_err": worst}))
+    assert worst < 1e-6, worst
+    pop.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
