@@ -260,7 +260,7 @@ def run_b200(args):
                 "frac": round(ach / peak, 5), "traffic": traffic, "peak_source": peak_src,
                 "work_per_launch": work, "avg_launch_ms": round(prof[dom][0], 5)}
         tensor_rows = []
-        for kn in ("conv_fwd_l0", "conv_wgrad_l0", "lin_fwd", "lin_dgrad", "lin_wgrad"):
+        for kn in ("conv_fwd_l0", "conv_wgrad_l0", "conv_fwd_l1", "conv_dgrad_l1", "conv_wgrad_l1", "lin_fwd", "lin_dgrad", "lin_wgrad"):
             if kn in prof:
                 _, wk = kernel_work(kn, pop, B)
                 a = wk / (prof[kn][0] * 1e-3) / 1e12

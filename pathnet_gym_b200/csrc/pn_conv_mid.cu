@@ -1,11 +1,9 @@
 // Module convolutions of the middle layers (layers 1 .. L-2: 8 input channels, 8 output channels per module)
 // as register-tiled fp32 CUDA-core kernels.
 //
-// Why not tcgen05 here: a path enables ~3 modules, i.e. 24 output columns.  A tcgen05.mma with N <= 96 costs
-// ~50 cycles whatever N is (operand fetch from shared memory; measured in csrc/dev/umma_timing.cu), and fp32
-// activations need a bf16 hi/lo split (3 MMAs per product), so for these 1 GFLOP layers the tensor pipe would
-// not beat well-fed FFMA.  Layer 0 (68 % of the flops, exact u8 operand) and the linear modules (256 columns
-// per module) are the tensor-core kernels (pn_conv0_tc.cu, pn_lin_tc.cu).
+// The k = 4 / stride 2 layers normally run on the tensor cores (pn_conv_mid_tc.cu).  These kernels cover what that
+// path does not take -- other kernel/stride geometries (3x3/s1 in the L = 4 configuration), weight gradients of paths
+// with more than 4 active modules -- and are the comparison arm of the tests (cfg.flags bit 3).
 //
 // Reference semantics: relu(conv2d(net, W_conv[l,j], stride, VALID) + b_conv[l,j]) * gate_j summed over the
 // active modules in ascending j (game_ac_network.py:186-193); gradients = tf.gradients
