@@ -188,6 +188,14 @@ PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
 PN_API int pn_rmsprop_apply(pn_handle* h, float lr, float decay, float momentum, float epsilon,
                      float clip_norm, void* stream);
 
+/* The same update for the tensors [first_tensor, first_tensor + n_tensors) of the table only, or (complement != 0)
+ * for every tensor outside that range (the update of one tensor never depends on another: rmsprop_applier.py:92-106
+ * loops over (grad, var) pairs).  Lets the host update the linear modules -- whose summed gradients are ready first,
+ * see pn_stream_wait_lin_grads -- on a second stream while the conv layers' backward pass still runs, and the rest
+ * afterwards.  Over one step the calls must cover every tensor exactly once. */
+PN_API int pn_rmsprop_apply_range(pn_handle* h, int first_tensor, int n_tensors, int complement, float lr, float decay,
+                           float momentum, float epsilon, float clip_norm, void* stream);
+
 /* Replaces the re-initialisation loop at task switch (doom_pathnet.py:289-293):
  * every non-frozen tensor <- backup_params_dev (same slab layout).  RMSProp
  * slots are not reset (as in the reference). */

@@ -67,6 +67,7 @@ SIGNATURES = {
     "pn_stage_inputs_host": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp]),
     "pn_train_step_staged": (_i, [_vp, _i, _f, _vp, _vp]),
     "pn_rmsprop_apply": (_i, [_vp, _f, _f, _f, _f, _f, _vp]),
+    "pn_rmsprop_apply_range": (_i, [_vp, _i, _i, _i, _f, _f, _f, _f, _f, _vp]),
     "pn_rmsprop_apply_noalloc": (_i, [_vp, _vp, _vp, _vp, C.POINTER(PnTensorDesc), _vp, _i, _f, _f, _f, _f, _f, _vp]),
     "pn_reinit_unfrozen": (_i, [_vp, _vp, _vp]),
     "pn_geopath_init": (_i, [_vp, _i, _i, _i, _i, _i, C.c_uint64, C.c_uint32, _vp]),

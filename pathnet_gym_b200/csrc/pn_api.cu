@@ -2,6 +2,8 @@
 // slab layout, genotype / freeze tables and the entry points of the hot path.
 #include "pn_internal.cuh"
 
+#include <map>
+#include <mutex>
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
@@ -103,6 +105,18 @@ int check_B(pn_handle* h, int B) {
 
 }  // namespace
 
+int pn_set_smem_cached(pn_handle* h, const void* kern, int bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, int> have;       // (device, kernel) -> largest size set so far
+    std::lock_guard<std::mutex> lock(mu);
+    int& cur = have[std::make_pair(h->cfg.device, kern)];
+    if (bytes > cur) {
+        PN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+        cur = bytes;
+    }
+    return PN_OK;
+}
+
 extern "C" PN_API int pn_abi_version(void) { return PN_ABI_VERSION; }
 
 extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
@@ -173,6 +187,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
     PN_TRY(dev_alloc(h, &h->d_chunk_ss, h->h_chunks.size()));
     PN_TRYC(cudaMemcpy(h->d_chunks, h->h_chunks.data(), h->h_chunks.size() * sizeof(PnRmsChunk), cudaMemcpyHostToDevice));
     PN_TRYC(cudaMemcpy(h->d_tensor_chunk0, chunk0.data(), nt * sizeof(int), cudaMemcpyHostToDevice));
+    h->h_tensor_chunk0 = chunk0;
     PN_TRYC(cudaMemcpy(h->d_tensor_nchunks, nchunks.data(), nt * sizeof(int), cudaMemcpyHostToDevice));
     // tensor-core path for layer 0 (u8 frames); cfg.flags bit 0 forces the CUDA-core kernels
     {
@@ -487,7 +502,20 @@ extern "C" PN_API int pn_rmsprop_apply(pn_handle* h, float lr, float decay, floa
     if (!h->params || !h->ms || !h->grads) return pn_fail(h, PN_ERR_STATE, "params / rms / grads slabs must be bound");
     if (momentum != 0.0f && !h->mom) return pn_fail(h, PN_ERR_STATE, "momentum != 0 needs a momentum slab");
     if (!(clip_norm > 0.0f)) return pn_fail(h, PN_ERR_INVALID, "clip_norm must be > 0");
-    return pn_launch_rmsprop(h, lr, decay, momentum, epsilon, clip_norm, (cudaStream_t)stream);
+    return pn_launch_rmsprop(h, 0, (int)h->tensors.size(), false, lr, decay, momentum, epsilon, clip_norm, (cudaStream_t)stream);
+}
+
+extern "C" PN_API int pn_rmsprop_apply_range(pn_handle* h, int first_tensor, int n_tensors, int complement, float lr, float decay,
+                                             float momentum, float epsilon, float clip_norm, void* stream) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "null handle");
+    if (!h->params || !h->ms || !h->grads) return pn_fail(h, PN_ERR_STATE, "params / rms / grads slabs must be bound");
+    if (momentum != 0.0f && !h->mom) return pn_fail(h, PN_ERR_STATE, "momentum != 0 needs a momentum slab");
+    if (!(clip_norm > 0.0f)) return pn_fail(h, PN_ERR_INVALID, "clip_norm must be > 0");
+    const int nt = (int)h->tensors.size();
+    if (first_tensor < 0 || n_tensors < 0 || first_tensor + n_tensors > nt)
+        return pn_fail(h, PN_ERR_INVALID, "tensor range [%d, %d) outside 0..%d", first_tensor, first_tensor + n_tensors, nt);
+    return pn_launch_rmsprop(h, first_tensor, n_tensors, complement != 0, lr, decay, momentum, epsilon, clip_norm,
+                             (cudaStream_t)stream);
 }
 
 extern "C" PN_API int pn_reinit_unfrozen(pn_handle* h, const float* backup_params_dev, void* stream) {

@@ -819,7 +819,7 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
         conv0_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, g.s, w8, wscale);
     }
     PN_LAUNCH_CHECK(h, "conv0_wprep_kernel");
-    PN_CUDA(h, cudaFuncSetAttribute(conv0_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    PN_SET_SMEM(h, conv0_fwd_tc_kernel, smem_bytes);
     const int grid = T < h->num_sms ? T : h->num_sms;
     CUtensorMap tmap;
     if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
@@ -862,7 +862,7 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     const int nch = best_nch, cs = (B + nch - 1) / nch;
     const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), 256 * 32 * sizeof(float));
     const size_t smem_bytes = 2 * (size_t)g.stage_bytes + dq_total + 16 * sizeof(uint64_t);
-    PN_CUDA(h, cudaFuncSetAttribute(conv0_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    PN_SET_SMEM(h, conv0_wgrad_tc_kernel, smem_bytes);
     const int items = P * nch;
     const int grid = items < h->num_sms ? items : h->num_sms;
     CUtensorMap tmap;

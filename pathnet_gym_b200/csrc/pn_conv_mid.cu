@@ -388,7 +388,7 @@ conv_mid_wgrad_kernel(const float* __restrict__ X, const float* __restrict__ dY,
 
 template <typename K>
 int set_smem_mid(pn_handle* h, K kern, size_t bytes) {
-    PN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    PN_SET_SMEM(h, kern, bytes);
     return PN_OK;
 }
 

@@ -784,7 +784,7 @@ int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
     const uint32_t tmem_cols = pow2_cols(16u * w_slots);
     const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * g.stage_bytes;
-    PN_CUDA(h, cudaFuncSetAttribute(conv_mid_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PN_SET_SMEM(h, conv_mid_fwd_tc_kernel, smem);
     const int ntile = (B * g.RB + kTileM - 1) / kTileM;
     const long long NT = (long long)h->P * ntile;
     const int grid = (int)std::min<long long>(NT, 3ll * h->num_sms);
@@ -804,7 +804,7 @@ int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     const uint8_t* wd = h->tc_mid_buf[l] + (size_t)nd.M * 2 * kModBytes;     // written by this step's forward launch
     const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
     const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * 2 * w_slots * g.chunk_bytes;
-    PN_CUDA(h, cudaFuncSetAttribute(conv_mid_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PN_SET_SMEM(h, conv_mid_dgrad_tc_kernel, smem);
     const int ntile = (B * g.RB + kTileM - 1) / kTileM;
     const long long NT = (long long)h->P * ntile;
     const int grid = (int)std::min<long long>(NT, 3ll * h->num_sms);
@@ -830,7 +830,7 @@ int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int
     const int ntile = (B * g.RB + kTileM - 1) / kTileM;
     const int nch = std::max(1, std::min(std::min(h->nch, ntile), 3 * h->num_sms / std::max(1, h->P)));
     const size_t smem = 128 + (size_t)kWgStages * (g.stage_bytes + 8 * kDChunk);
-    PN_CUDA(h, cudaFuncSetAttribute(conv_mid_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PN_SET_SMEM(h, conv_mid_wgrad_tc_kernel, smem);
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + l, st);
         conv_mid_wgrad_tc_kernel<<<h->P * nch, kFwdThreads, smem, st>>>(h->act[l - 1], h->dact[l], h->rmask[l], nd, l, g,

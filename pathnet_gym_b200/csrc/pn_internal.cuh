@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "pathnet_b200.h"
@@ -85,6 +86,7 @@ struct pn_handle {
     int head_chunks = 0;
     // rmsprop
     std::vector<PnRmsChunk> h_chunks;
+    std::vector<int> h_tensor_chunk0;   // host copy of d_tensor_chunk0
     PnRmsChunk* d_chunks = nullptr;
     int* d_tensor_chunk0 = nullptr;     // first chunk of each tensor
     int* d_tensor_nchunks = nullptr;
@@ -144,6 +146,14 @@ int pn_fail_global(int code, const char* fmt, ...);
                            cudaGetErrorString(e__), __FILE__, __LINE__);                      \
     } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) only when this process has not yet set at least `bytes` for the kernel
+// on the handle's device (the call costs several microseconds of host time; a training step used to make twelve)
+int pn_set_smem_cached(pn_handle* h, const void* kern, int bytes);
+#define PN_SET_SMEM(h, kern, bytes)                                                        \
+    do {                                                                                   \
+        if (int rc__ = pn_set_smem_cached((h), (const void*)(kern), (int)(bytes))) return rc__; \
+    } while (0)
+
 #define PN_LAUNCH_CHECK(h, name)                                                              \
     do {                                                                                      \
         ++(h)->launches;                                                                      \
@@ -183,7 +193,8 @@ int pn_launch_lin_wsplit(pn_handle* h, cudaStream_t st);
 int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st);
 int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st);
 // pn_rmsprop.cu
-int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st);
+int pn_launch_rmsprop(pn_handle* h, int first_tensor, int n_tensors, bool complement, float lr, float decay,
+                      float momentum, float eps, float clip, cudaStream_t st);
 int pn_launch_reinit(pn_handle* h, const float* backup, cudaStream_t st);
 
 // ---------------------------------------------------------------------------

@@ -681,7 +681,7 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     }
     PN_LAUNCH_CHECK(h, "lin_prep_kernel");
     const size_t smem = (size_t)kWStages * 2 * kWChunkKb * 16 * kBlk + g.xp_chunk + 256;
-    PN_CUDA(h, cudaFuncSetAttribute(lin_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PN_SET_SMEM(h, lin_fwd_tc_kernel, smem);
     const int items = h->P * g.nbc * 2;
     const int grid = items < h->num_sms ? items : h->num_sms;
     {
@@ -708,7 +708,7 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
     const int KT = (g.K / 8 + 1 + 15) / 16;          // tiles of 16 k-blocks covering the K rows plus the ones row
     {
         const size_t smem = 2 * (size_t)(2 * 16 * 16 * kBlk) + 2 * g.dp_slot + 256;
-        PN_CUDA(h, cudaFuncSetAttribute(lin_dgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PN_SET_SMEM(h, lin_dgrad_tc_kernel, smem);
         const int items = h->P * g.nbc * KT;
         const int grid = items < h->num_sms ? items : h->num_sms;
         PnProfScope prof(h, PN_PROF_LIN_DGRAD, st);
@@ -717,7 +717,7 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
     PN_LAUNCH_CHECK(h, "lin_dgrad_tc_kernel");
     {
         const size_t smem = 4 * (size_t)(4 * 16 * 4 * kBlk) + 256;
-        PN_CUDA(h, cudaFuncSetAttribute(lin_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        PN_SET_SMEM(h, lin_wgrad_tc_kernel, smem);
         const int items = g.M * KT * 2;
         const int grid = items < h->num_sms ? items : h->num_sms;
         PnProfScope prof(h, PN_PROF_LIN_WGRAD, st);

@@ -713,7 +713,7 @@ grad_reduce_kernel(PnReduceJobs jobs, PnNetDesc nd, const int* __restrict__ list
 template <typename K>
 int set_smem(pn_handle* h, K kern, size_t bytes) {
     if (bytes > 48 * 1024) {
-        PN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        PN_SET_SMEM(h, kern, bytes);
     }
     return PN_OK;
 }

@@ -38,9 +38,11 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 
 __global__ void __launch_bounds__(kThreads)
 rms_sumsq_kernel(const float* __restrict__ grads, const PnRmsChunk* __restrict__ chunks,
-                 const uint8_t* __restrict__ frozen, float* __restrict__ chunk_ss) {
+                 const uint8_t* __restrict__ frozen, float* __restrict__ chunk_ss, int c0, int n0, int c1) {
     __shared__ float red[32];
-    const PnRmsChunk ck = chunks[blockIdx.x];
+    // two chunk segments in one launch: [c0, c0 + n0) then [c1, ...)
+    const int cid = (int)blockIdx.x < n0 ? c0 + (int)blockIdx.x : c1 + ((int)blockIdx.x - n0);
+    const PnRmsChunk ck = chunks[cid];
     if (frozen[ck.tensor]) return;
     const float* g = grads + ck.off;
     const int n4 = ck.len >> 2;
@@ -51,7 +53,7 @@ rms_sumsq_kernel(const float* __restrict__ grads, const PnRmsChunk* __restrict__
     }
     for (int i = (n4 << 2) + threadIdx.x; i < ck.len; i += kThreads) s = fmaf(g[i], g[i], s);
     s = block_sum(s, red);
-    if (threadIdx.x == 0) chunk_ss[blockIdx.x] = s;
+    if (threadIdx.x == 0) chunk_ss[cid] = s;
 }
 
 template <bool HAS_MOM>
@@ -70,9 +72,9 @@ rms_update_kernel(float* __restrict__ params, float* __restrict__ msl, float* __
                   const float* __restrict__ grads, const PnRmsChunk* __restrict__ chunks,
                   const uint8_t* __restrict__ frozen, const int* __restrict__ tchunk0,
                   const int* __restrict__ tnchunks, const float* __restrict__ chunk_ss, float lr, float decay,
-                  float momentum, float eps, float clip) {
+                  float momentum, float eps, float clip, int c0, int n0, int c1) {
     __shared__ float s_scale;
-    const PnRmsChunk ck = chunks[blockIdx.x];
+    const PnRmsChunk ck = chunks[(int)blockIdx.x < n0 ? c0 + (int)blockIdx.x : c1 + ((int)blockIdx.x - n0)];
     if (frozen[ck.tensor]) return;
     if (threadIdx.x == 0) {
         const int c0 = tchunk0[ck.tensor], nc = tnchunks[ck.tensor];
@@ -122,22 +124,31 @@ reinit_kernel(float* __restrict__ params, const float* __restrict__ backup, cons
 
 }  // namespace
 
-int pn_launch_rmsprop(pn_handle* h, float lr, float decay, float momentum, float eps, float clip, cudaStream_t st) {
-    const int nchunks = (int)h->h_chunks.size();
+int pn_launch_rmsprop(pn_handle* h, int first_tensor, int n_tensors, bool complement, float lr, float decay,
+                      float momentum, float eps, float clip, cudaStream_t st) {
+    // chunks are stored in tensor order: a contiguous range of tensors is a contiguous range of chunks
+    const int nt = (int)h->tensors.size(), nall = (int)h->h_chunks.size();
+    const int ca = first_tensor < nt ? h->h_tensor_chunk0[first_tensor] : nall;
+    const int cb = first_tensor + n_tensors < nt ? h->h_tensor_chunk0[first_tensor + n_tensors] : nall;
+    // segment 0 = [c0, c0 + n0), segment 1 = [c1, c1 + n1)
+    const int c0 = complement ? 0 : ca, n0 = complement ? ca : cb - ca;
+    const int c1 = cb, n1 = complement ? nall - cb : 0;
+    const int nchunks = n0 + n1;
+    if (nchunks <= 0) return PN_OK;
     {
         PnProfScope prof(h, PN_PROF_RMS_SUMSQ, st);
-        rms_sumsq_kernel<<<nchunks, kThreads, 0, st>>>(h->grads, h->d_chunks, h->d_frozen, h->d_chunk_ss);
+        rms_sumsq_kernel<<<nchunks, kThreads, 0, st>>>(h->grads, h->d_chunks, h->d_frozen, h->d_chunk_ss, c0, n0, c1);
     }
     PN_LAUNCH_CHECK(h, "rms_sumsq_kernel");
     PnProfScope prof(h, PN_PROF_RMS_UPDATE, st);
     if (momentum != 0.0f) {
         rms_update_kernel<true><<<nchunks, kThreads, 0, st>>>(h->params, h->ms, h->mom, h->grads, h->d_chunks,
                                                               h->d_frozen, h->d_tensor_chunk0, h->d_tensor_nchunks,
-                                                              h->d_chunk_ss, lr, decay, momentum, eps, clip);
+                                                              h->d_chunk_ss, lr, decay, momentum, eps, clip, c0, n0, c1);
     } else {
         rms_update_kernel<false><<<nchunks, kThreads, 0, st>>>(h->params, h->ms, nullptr, h->grads, h->d_chunks,
                                                                h->d_frozen, h->d_tensor_chunk0, h->d_tensor_nchunks,
-                                                               h->d_chunk_ss, lr, decay, momentum, eps, clip);
+                                                               h->d_chunk_ss, lr, decay, momentum, eps, clip, c0, n0, c1);
     }
     PN_LAUNCH_CHECK(h, "rms_update_kernel");
     return PN_OK;

@@ -253,6 +253,19 @@ class PathNetPopulation:
         nat.check(self.lib.pn_rmsprop_apply(self._h, float(lr), float(decay), float(momentum), float(epsilon),
                                             float(clip_norm), self._stream()), self._h)
 
+    def apply_gradients_range(self, first_tensor, n_tensors, lr, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0,
+                              complement=False):
+        """apply_gradients for a contiguous range of the tensor table (or for everything outside it)."""
+        nat.check(self.lib.pn_rmsprop_apply_range(self._h, int(first_tensor), int(n_tensors), 1 if complement else 0,
+                                                  float(lr), float(decay), float(momentum), float(epsilon),
+                                                  float(clip_norm), self._stream()), self._h)
+
+    def lin_tensor_range(self):
+        """(first, count) of the W_lin / b_lin rows of the tensor table."""
+        off, cnt = self.lin_grads_region()
+        idx = [i for i, t in enumerate(self.tensors) if off <= t["offset"] < off + cnt]
+        return idx[0], len(idx)
+
     def reinit_unfrozen(self, backup: torch.Tensor):
         """Every non-frozen tensor <- backup (doom_pathnet.py:289-293)."""
         assert backup.dtype == torch.float32 and backup.numel() == self.slab_floats and backup.is_cuda

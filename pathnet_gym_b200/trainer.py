@@ -13,21 +13,22 @@ class OverlappedGradSum(object):
         import torch
         self.pop = pop
         self.active = parallel.world()[1] > 1
-        if self.active:
-            off, cnt = pop.lin_grads_region()
-            g = pop.grads
-            self.lin, self.head, self.conv = g[off:off + cnt], g[off + cnt:], g[:off]
-            self.comm = torch.cuda.Stream(device=pop.device)
+        off, cnt = pop.lin_grads_region()
+        g = pop.grads
+        self.lin, self.head, self.conv = g[off:off + cnt], g[off + cnt:], g[:off]
+        self.comm = torch.cuda.Stream(device=pop.device)
 
-    def __call__(self):
+    def sum_lin(self):
+        """On the side stream (already waiting for the linear gradients): all-reduce them."""
+        if self.active:
+            import torch.distributed as dist
+            dist.all_reduce(self.lin, op=dist.ReduceOp.SUM)
+
+    def sum_rest(self):
+        """On the compute stream, after the step's last kernel: one grouped NCCL launch for the two small regions."""
         if not self.active:
             return
-        import torch
         import torch.distributed as dist
-        self.pop.stream_wait_lin_grads(self.comm)
-        with torch.cuda.stream(self.comm):
-            dist.all_reduce(self.lin, op=dist.ReduceOp.SUM)
-        # the two small regions are complete only when the step's last kernel is: one grouped NCCL launch for both
         try:
             with dist._coalescing_manager(device=self.pop.device):
                 dist.all_reduce(self.conv, op=dist.ReduceOp.SUM)
@@ -35,27 +36,60 @@ class OverlappedGradSum(object):
         except (AttributeError, TypeError, RuntimeError):
             dist.all_reduce(self.conv, op=dist.ReduceOp.SUM)
             dist.all_reduce(self.head, op=dist.ReduceOp.SUM)
+
+    def __call__(self):
+        """Gradient sum only (no update): the slab holds the global sum when the compute stream gets there."""
+        if not self.active:
+            return
+        import torch
+        self.pop.stream_wait_lin_grads(self.comm)
+        with torch.cuda.stream(self.comm):
+            self.sum_lin()
+        self.sum_rest()
         torch.cuda.current_stream(self.pop.device).wait_stream(self.comm)
+
+
+class StepTail(object):
+    """Everything between the backward pass and the next step: gradient sum over the GPUs + clipped RMSProp
+    (a3c_training_thread.py:205-216 apply_gradients).  The linear modules' tensors -- gradients final right after their
+    weight-gradient kernel -- are summed AND updated on a side stream while the conv layers' backward pass runs; the
+    conv and head tensors follow on the compute stream.  Per-tensor results are the same as one apply_gradients call
+    (tensors are independent in rmsprop_applier.py:92-106)."""
+
+    def __init__(self, pop, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0):
+        self.pop = pop
+        self.hp = (decay, momentum, epsilon, clip_norm)
+        self.gradsum = OverlappedGradSum(pop)
+        self.lin_first, self.lin_count = pop.lin_tensor_range()
+
+    def __call__(self, lr):
+        import torch
+        pop, gs = self.pop, self.gradsum
+        pop.stream_wait_lin_grads(gs.comm)
+        with torch.cuda.stream(gs.comm):
+            gs.sum_lin()
+            pop.apply_gradients_range(self.lin_first, self.lin_count, lr, *self.hp)
+        gs.sum_rest()
+        pop.apply_gradients_range(self.lin_first, self.lin_count, lr, *self.hp, complement=True)
+        torch.cuda.current_stream(pop.device).wait_stream(gs.comm)
 
 
 class PopulationTrainer(object):
     def __init__(self, pop, entropy_beta=0.01, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0):
         self.pop, self.beta = pop, entropy_beta
         self.decay, self.momentum, self.epsilon, self.clip_norm = decay, momentum, epsilon, clip_norm
-        self.gradsum = OverlappedGradSum(pop)
+        self.tail = StepTail(pop, decay, momentum, epsilon, clip_norm)
 
     def step(self, frames, actions, td, r, lr):
         """Device tensors [P,B,...]; returns the per-path losses (device tensor)."""
         loss = self.pop.train_step(frames, actions, td, r, self.beta)
-        self.gradsum()
-        self.pop.apply_gradients(lr, self.decay, self.momentum, self.epsilon, self.clip_norm)
+        self.tail(lr)
         return loss
 
     def step_host(self, frames, actions, td, r, lr, loss_out=None):
         """Host (pinned) tensors: copies happen inside the C ABI call."""
         loss = self.pop.train_step_host(frames, actions, td, r, self.beta, loss_out=loss_out)
-        self.gradsum()
-        self.pop.apply_gradients(lr, self.decay, self.momentum, self.epsilon, self.clip_norm)
+        self.tail(lr)
         return loss
 
 
@@ -68,7 +102,7 @@ class PipelinedHostTrainer(object):
         self.pop, self.beta = pop, entropy_beta
         self.decay, self.momentum, self.epsilon, self.clip_norm = decay, momentum, epsilon, clip_norm
         self.copy_stream = torch.cuda.Stream(device=pop.device)
-        self.gradsum = OverlappedGradSum(pop)
+        self.tail = StepTail(pop, decay, momentum, epsilon, clip_norm)
         self.i = 0
         self.primed = False
 
@@ -84,8 +118,7 @@ class PipelinedHostTrainer(object):
         if next_batch is not None:
             self.pop.stage_host(cur ^ 1, *next_batch, copy_stream=self.copy_stream)
         self.pop.train_step_staged(cur, self.beta, loss_out)
-        self.gradsum()
-        self.pop.apply_gradients(lr, self.decay, self.momentum, self.epsilon, self.clip_norm)
+        self.tail(lr)
         self.i += 1
         self.primed = next_batch is not None
         return loss_out
