@@ -125,6 +125,13 @@ __device__ __forceinline__ void stage_frame_tma(uint8_t* dst, const CUtensorMap*
 }
 
 // ---- the convolution -----------------------------------------------------------------------------------
+// clock read that the compiler cannot move across memory operations / other volatile asm (debug brackets)
+__device__ __forceinline__ long long pinned_clock() {
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory");
+    return t;
+}
+
 __global__ void __launch_bounds__(kFwdThreads, 1)
 conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __restrict__ w8,
                     const float* __restrict__ wscale, const float* __restrict__ params, PnNetDesc nd,
@@ -340,12 +347,15 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         const int L = quad * 32 + lane;
         int cur_path = -1, ns = 0;
         uint32_t path_phase = 0, mask = 0, tilec = 0, gi = 0;   // gi: items this group has consumed from its stage
-        long long w_full = 0, t_begin = clock64();
+        long long w_full = 0, t_begin = clock64(), e_ld = 0, e_math = 0, e_t0 = 0, e_path = 0, e_ystore = 0;
+        const bool dbg_epi = dbg && dbg[gridDim.x * 8] == 7;
         for (int t = t_lo; t < t_hi; ++t) {
             const int p = t / B;
             if (p != cur_path) {
                 if (cur_path >= 0) mbar_arrive(epi_idle);
+                const long long cpw = dbg_epi ? pinned_clock() : 0;
                 mbar_wait(path_ready, path_phase);
+                if (dbg_epi) e_path += pinned_clock() - cpw;
                 path_phase ^= 1;
                 cur_path = p;
                 mask = masks[p * nd.L];
@@ -368,13 +378,16 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                 for (int c = 0; c < 8; ++c) sum[c] = 0.f;
                 for (int pass = 0; pass < npass; ++pass, ++gi) {
                     const uint32_t acc = (uint32_t)group;
-                    const long long ce0 = clock64();
+                    const long long ce0 = dbg_epi ? pinned_clock() : 0;
                     mbar_wait(&acc_full[acc], gi & 1u);
-                    w_full += clock64() - ce0;
+                    if (dbg_epi) { const long long c = pinned_clock(); w_full += c - ce0; e_t0 = c; }
                     tc_fence_after();
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const uint32_t tbase = td + ((uint32_t)(quad * 32) << 16) + acc * kAccCols;
-                    if (dbg && dbg[gridDim.x * 8] == 2) {          // experiment: handshake only
+                    // The TMEM read-out is this kernel's bottleneck (64 B/clk): a warp whose 32 raster rows all lie past the
+                    // end of the frame's raster (the last tile covers 36 useful rows of 128) skips it.
+                    const bool warp_all_junk = tile * 128 + quad * 32 >= gm.OH * gm.Ws;
+                    if (warp_all_junk || (dbg && dbg[gridDim.x * 8] == 2)) {          // (debug mode 2: handshake only)
                         tc_fence_before();
                         mbar_arrive(&acc_empty[acc]);
                         continue;
@@ -393,6 +406,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                         *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
                         *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
                         tmem_ld_wait();
+                        if (dbg_epi) { const long long c = pinned_clock(); e_ld += c - e_t0; e_t0 = c; }
                         if (sl == nsl - 1) {        // last read of this accumulator stage: hand it back to the MMA warp
                             tc_fence_before();
                             mbar_arrive(&acc_empty[acc]);
@@ -407,16 +421,24 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                             if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
                         }
                         if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
+                        if (dbg_epi) { const long long c = pinned_clock(); e_math += c - e_t0; e_t0 = c; }
                     }
                 }
+                const long long cys = dbg_epi ? pinned_clock() : 0;
                 if (valid) {
                     float4* yo = reinterpret_cast<float4*>(Y + ((size_t)t * npix + pix) * PN_F);
                     yo[0] = make_float4(sum[0], sum[1], sum[2], sum[3]);
                     yo[1] = make_float4(sum[4], sum[5], sum[6], sum[7]);
                 }
+                if (dbg_epi) e_ystore += pinned_clock() - cys;
             }
         }
         if (dbg && threadIdx.x == 0) { if (dbg[gridDim.x * 8] == 4) dbg[blockIdx.x * 8 + 6] = w_full; dbg[blockIdx.x * 8 + 7] = clock64() - t_begin; }
+        if (dbg_epi && threadIdx.x == 0) {      // epilogue group 0, warp 0: where its time goes
+            dbg[blockIdx.x * 8 + 1] = w_full; dbg[blockIdx.x * 8 + 2] = e_ld; dbg[blockIdx.x * 8 + 3] = e_math;
+            dbg[blockIdx.x * 8 + 4] = clock64() - t_begin;
+            dbg[blockIdx.x * 8 + 0] = e_path; dbg[blockIdx.x * 8 + 5] = e_ystore;
+        }
     }
     tc_fence_before();
     __syncthreads();
