@@ -142,7 +142,8 @@ PN_API int pn_forward(pn_handle* h, const void* frames_dev, int frames_are_u8, i
  * ops: forward, prepare_loss (game_ac_network.py:20-59), tf.gradients
  * (a3c_training_thread.py:55-60,205-216) for every path, summed over the P
  * local paths into the bound gradient slab (overwritten, not accumulated).
- * actions_dev [P,B] int32 (the one-hot `a` feed), td_dev [P,B], r_dev [P,B].
+ * actions_dev [P,B] int32 (the one-hot `a` feed; a NEGATIVE action marks a padded transition that contributes
+ * nothing to the loss or the gradients -- see pn_nstep_returns), td_dev [P,B], r_dev [P,B].
  * loss_dev [P] (total_loss per path) may be NULL; pi_dev / v_dev may be NULL. */
 PN_API int pn_train_step(pn_handle* h, const void* frames_dev, int frames_are_u8,
                   const int32_t* actions_dev, const float* td_dev, const float* r_dev, int B,
@@ -263,6 +264,22 @@ PN_API int pn_mutate(uint32_t* masks_dev, int n_paths, int path_id0, int L, int 
 PN_API int pn_tournament(uint32_t* genotypes_dev, float* scores_dev, const uint32_t* fixed_dev,
                   uint32_t* effective_dev, int32_t* winners_dev, int P_total, int L, int M, int N,
                   int Bcand, int n_groups, uint64_t seed, uint32_t epoch, void* stream);
+
+/* ---- rollout bookkeeping (the host code between two network calls of a rollout) ---- */
+
+/* Replaces A3CTrainingThread.choose_action (a3c_training_thread.py:89-90), np.random.choice(range(A), p=pi), for n
+ * probability rows at once: numpy's algorithm (fp64 cumsum, normalise by the last entry, searchsorted side='right')
+ * on ONE uniform per row from the Philox stream, counter (epoch, id0 + row, 0, 3<<24), key = seed. */
+PN_API int pn_sample_actions(const float* pi_dev, int n, int A, uint64_t seed, uint32_t epoch, uint32_t id0,
+                      int32_t* actions_dev, void* stream);
+
+/* Replaces the batch assembly of A3CTrainingThread.process (a3c_training_thread.py:136,155-180) for P paths: rewards
+ * clipped to [-1,1]; R <- r_i + gamma*R backwards from bootstrap[p] (V(s_T), or 0 after a terminal step); td = R - V_i;
+ * fp64 scan like the Python floats, rounded once to fp32.  rewards/values/R/td are [P,B] in rollout order;
+ * lengths_dev[p] <= B (NULL: all B) is the number of transitions path p really has -- the rest are padding and get
+ * R = td = 0; give them action = -1 in pn_train_step*, which then contribute nothing to loss or gradients. */
+PN_API int pn_nstep_returns(const float* rewards_dev, const float* values_dev, const float* bootstrap_dev,
+                     const int32_t* lengths_dev, int P, int B, double gamma, float* R_dev, float* td_dev, void* stream);
 
 #ifdef __cplusplus
 }

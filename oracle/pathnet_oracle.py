@@ -368,6 +368,38 @@ def nstep_returns(rewards, values, bootstrap, gamma=GAMMA):
     return Rs, tds
 
 
+def nstep_returns_batch(rewards, values, bootstrap, lengths=None, gamma=GAMMA):
+    """nstep_returns for [P, B] arrays with padding (rows past lengths[p] -> 0), rounded to fp32 like the feed."""
+    rewards, values = np.asarray(rewards), np.asarray(values)
+    P, B = rewards.shape
+    R = np.zeros((P, B), np.float32)
+    td = np.zeros((P, B), np.float32)
+    for p in range(P):
+        n = B if lengths is None else int(lengths[p])
+        Rs, tds = nstep_returns(rewards[p, :n].astype(np.float64), values[p, :n].astype(np.float64), float(bootstrap[p]), gamma)
+        R[p, :n], td[p, :n] = Rs.astype(np.float32), tds.astype(np.float32)
+    return R, td
+
+
+DOMAIN_ACTION = 3
+
+
+def choice_from_uniform(p, u) -> int:
+    """np.random.choice(range(A), p=p) as numpy's legacy RandomState implements it, with the uniform draw u made
+    explicit: cdf = cumsum(float64(p)); cdf /= cdf[-1]; index = searchsorted(cdf, u, side='right')
+    (a3c_training_thread.py:89-90).  Pinned against RandomState.choice itself in tests/test_oracle.py."""
+    cdf = np.cumsum(np.asarray(p, dtype=np.float64))
+    cdf = cdf / cdf[-1]
+    return int(min(np.searchsorted(cdf, u, side="right"), len(cdf) - 1))
+
+
+def sample_actions(pi, seed, epoch, id0=0) -> np.ndarray:
+    """choose_action for every row of pi [n, A] with u = Philox(seed; epoch, id0 + row, 0, DOMAIN_ACTION)."""
+    pi = np.asarray(pi, dtype=np.float32)
+    return np.asarray([choice_from_uniform(pi[t], philox_uniform(seed, epoch, id0 + t, 0, DOMAIN_ACTION, 0))
+                       for t in range(pi.shape[0])], dtype=np.int32)
+
+
 # ----------------------------------------------------------------------------
 # Population step = the unit the CUDA library implements
 # ----------------------------------------------------------------------------

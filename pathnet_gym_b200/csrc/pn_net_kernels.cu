@@ -313,10 +313,11 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
             const float dot = warp_sum(dpi * pik);
             const float dz = pik * (dpi - dot);
             const float dv = -0.5f * diff;
-            const float val = lane < A ? dz : (lane == A ? dv : 0.f);
+            // action < 0 marks a padded transition (a path whose rollout ended before B steps): no loss, no gradient
+            const float val = a < 0 ? 0.f : (lane < A ? dz : (lane == A ? dv : 0.f));
             dzv[(size_t)t * 32 + lane] = val;
             dzs[tt * 32 + lane] = val;
-            if (lane == 0) loss_t[t] = loss;
+            if (lane == 0) loss_t[t] = a < 0 ? 0.f : loss;
         }
     }
     if (!training) return;

@@ -302,6 +302,36 @@ def geopath_init(n_paths, L, M, N, seed, epoch, path_id0=0, device=0) -> torch.T
     return masks
 
 
+def sample_actions(pi: torch.Tensor, seed, epoch, id0=0) -> torch.Tensor:
+    """choose_action (a3c_training_thread.py:89-90) for every row of pi [..., A]: int32 actions, one Philox draw per row."""
+    lib = nat.load()
+    assert pi.is_cuda and pi.dtype == torch.float32 and pi.is_contiguous()
+    A = pi.shape[-1]
+    n = pi.numel() // A
+    out = torch.empty(pi.shape[:-1], dtype=torch.int32, device=pi.device)
+    st = C.c_void_p(torch.cuda.current_stream(pi.device).cuda_stream)
+    nat.check(lib.pn_sample_actions(_ptr(pi), n, A, int(seed), int(epoch), int(id0), _ptr(out), st))
+    return out
+
+
+def nstep_returns(rewards: torch.Tensor, values: torch.Tensor, bootstrap: torch.Tensor, lengths=None, gamma=0.99):
+    """Batch assembly of A3CTrainingThread.process (a3c_training_thread.py:136,155-180) for [P, B] rollouts:
+    returns (R, td) fp32 [P, B]; entries at or beyond lengths[p] are padding (0)."""
+    lib = nat.load()
+    P, B = rewards.shape
+    for t in (rewards, values, bootstrap):
+        assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+    assert values.shape == (P, B) and bootstrap.shape == (P,)
+    if lengths is not None:
+        assert lengths.is_cuda and lengths.dtype == torch.int32 and lengths.shape == (P,)
+    R = torch.empty(P, B, dtype=torch.float32, device=rewards.device)
+    td = torch.empty_like(R)
+    st = C.c_void_p(torch.cuda.current_stream(rewards.device).cuda_stream)
+    nat.check(lib.pn_nstep_returns(_ptr(rewards), _ptr(values), _ptr(bootstrap), _ptr(lengths), P, B, float(gamma),
+                                   _ptr(R), _ptr(td), st))
+    return R, td
+
+
 def mutate_(masks: torch.Tensor, M, N, seed, epoch, path_id0=0) -> torch.Tensor:
     lib = nat.load()
     assert masks.is_cuda and masks.dtype == torch.int32 and masks.is_contiguous()

@@ -122,3 +122,53 @@ class PipelinedHostTrainer(object):
         self.i += 1
         self.primed = next_batch is not None
         return loss_out
+
+
+class PopulationRollout(object):
+    """The rollout loop of A3CTrainingThread.process (a3c_training_thread.py:118-180) for all paths of a population at
+    once, with the bookkeeping on the device: one batched acting forward per environment step (run_policy_and_value),
+    choose_action by `pn_sample_actions` (Philox stream instead of the global numpy RNG), reward clip + n-step returns +
+    td by `pn_nstep_returns`.  Paths whose episode ends early stop collecting; their remaining slots are padding
+    (action = -1).  `env_step(actions) -> (next_frames [P,H,W,C] u8 device tensor, rewards [P] float tensor,
+    terminal [P] bool tensor)` is the caller's environment."""
+
+    def __init__(self, pop, t_max, seed=0):
+        import torch
+        self.pop, self.t_max, self.seed = pop, int(t_max), int(seed)
+        assert 1 <= self.t_max <= pop.B_max
+        P, cfg, dev = pop.P, pop.cfg, pop.device
+        self.frames = torch.zeros(P, self.t_max, cfg.H, cfg.W, cfg.C, dtype=torch.uint8, device=dev)
+        self.actions = torch.full((P, self.t_max), -1, dtype=torch.int32, device=dev)
+        self.values = torch.zeros(P, self.t_max, dtype=torch.float32, device=dev)
+        self.rewards = torch.zeros(P, self.t_max, dtype=torch.float32, device=dev)
+        self.epoch = 0
+
+    def collect(self, state, env_step):
+        """Runs up to t_max steps from `state` [P,H,W,C] u8; returns (frames, actions, td, R, lengths, last_state)."""
+        import torch
+        from .population import nstep_returns, sample_actions
+        pop, P = self.pop, self.pop.P
+        alive = torch.ones(P, dtype=torch.bool, device=pop.device)
+        lengths = torch.zeros(P, dtype=torch.int32, device=pop.device)
+        self.actions.fill_(-1)
+        self.rewards.zero_()
+        self.values.zero_()
+        for i in range(self.t_max):
+            pi, v = pop.forward(state.unsqueeze(1).contiguous())            # [P,1,A], [P,1]
+            a = sample_actions(pi.reshape(P, -1).contiguous(), self.seed, self.epoch, id0=0)
+            self.epoch += 1
+            self.frames[:, i] = state
+            self.actions[:, i] = torch.where(alive, a, torch.full_like(a, -1))
+            self.values[:, i] = v.reshape(P)
+            nxt, rew, term = env_step(a)
+            self.rewards[:, i] = torch.where(alive, rew.to(torch.float32), torch.zeros_like(self.rewards[:, i]))
+            lengths += alive.to(torch.int32)
+            state = torch.where(alive.view(P, 1, 1, 1), nxt, state)
+            alive = alive & ~term
+            if not bool(alive.any()):
+                break
+        # bootstrap: V(s_T) for the paths still running, 0 after a terminal step (a3c_training_thread.py:151-153)
+        _, vT = pop.forward(state.unsqueeze(1).contiguous())
+        boot = torch.where(alive, vT.reshape(P), torch.zeros(P, device=pop.device)).contiguous()
+        R, td = nstep_returns(self.rewards, self.values, boot, lengths)
+        return self.frames, self.actions, td, R, lengths, state

@@ -111,3 +111,73 @@ def test_controller_tournament_freeze_reinit(native_lib):
     ctl.start_task()                                           # task 2: new genotypes OR the fixed path
     assert np.all((pop.masks & g_ref[ctl.winner_idx][None, :]) == g_ref[ctl.winner_idx][None, :])
     pop.close()
+
+
+def test_population_rollout_matches_host_bookkeeping(native_lib):
+    """PopulationRollout (device bookkeeping) against the reference's host loop restated with the oracle functions,
+    on a deterministic synthetic environment: same actions (same Philox draws on the same pi), same R / td, padding
+    after terminal steps (a3c_training_thread.py:118-180)."""
+    from pathnet_gym_b200.population import PathNetPopulation
+    from pathnet_gym_b200.trainer import PopulationRollout
+    cfg, P, T = hp.TINY, 4, 6
+    pop = PathNetPopulation(hp.to_engine_cfg(cfg), P, T)
+    pop.load(pop.params, po.init_params(cfg, 2))
+    masks = np.stack([po.get_geopath_masks(cfg.L, cfg.M, cfg.N, 7, 0, p) for p in range(P)])
+    pop.set_genotypes(masks)
+    dev = pop.device
+    gen = torch.Generator(device="cpu").manual_seed(3)
+    states = torch.randint(0, 256, (T + 1, P, cfg.H, cfg.W, cfg.C), dtype=torch.uint8, generator=gen).to(dev)
+    rewards = (torch.randn(T, P, generator=gen) * 2).to(dev)
+    term_at = [T + 5, 2, 4, 0]                                   # path p's episode ends with step term_at[p]
+    clock = {"i": 0}
+
+    def env_step(a):
+        i = clock["i"]
+        clock["i"] += 1
+        term = torch.tensor([i >= term_at[q] for q in range(P)], device=dev)
+        return states[i + 1], rewards[i], term
+
+    ro = PopulationRollout(pop, T, seed=5)
+    frames, actions, td, R, lengths, last = ro.collect(states[0], env_step)
+    lengths = lengths.cpu().numpy()
+    assert list(lengths) == [min(T, t + 1) for t in term_at]
+    acts = actions.cpu().numpy()
+    for i in range(T):
+        pi, _ = pop.forward(states[i].unsqueeze(1).contiguous())
+        want = po.sample_actions(pi.reshape(P, -1).cpu().numpy(), 5, i, id0=0)
+        for q in range(P):
+            assert acts[q, i] == (want[q] if i < lengths[q] else -1)
+    _, vT = pop.forward(last.unsqueeze(1).contiguous())
+    boot = np.asarray([float(vT[q, 0]) if term_at[q] >= T else 0.0 for q in range(P)], np.float32)
+    Rw, tdw = po.nstep_returns_batch(rewards.t().cpu().numpy(), ro.values.cpu().numpy(), boot, lengths)
+    assert np.array_equal(R.cpu().numpy(), Rw) and np.array_equal(td.cpu().numpy(), tdw)
+    # and the assembled batch trains: padded transitions carry no loss
+    loss = pop.train_step(frames, actions, td, R, 0.01)
+    assert torch.isfinite(loss).all()
+    pop.close()
+
+
+def test_population_checkpoint_roundtrip(native_lib, tmp_path):
+    from pathnet_gym_b200 import checkpoint as ck
+    from pathnet_gym_b200.population import PathNetPopulation
+    cfg, P, B = hp.TINY, 2, 3
+    pop = PathNetPopulation(hp.to_engine_cfg(cfg), P, B)
+    pop.load(pop.params, po.init_params(cfg, 8))
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, P, B, 9)
+    pop.set_genotypes(masks)
+    d = lambda x: torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    pop.train_step(d(frames), d(actions), d(td), d(r), 0.01)
+    pop.apply_gradients(1e-3)
+    path = str(tmp_path / "pop.npz")
+    ck.save_population(path, pop, global_t=7)
+    want_p, want_s = pop.dump(pop.params), pop.dump(pop.ms)
+    pop2 = PathNetPopulation(hp.to_engine_cfg(cfg), P, B)
+    got = ck.load_population(path, pop2)
+    assert got["global_t"] == 7 and np.array_equal(pop2.masks, masks)
+    assert all(np.array_equal(a, b) for a, b in zip(pop2.dump(pop2.params), want_p))
+    assert all(np.array_equal(a, b) for a, b in zip(pop2.dump(pop2.ms), want_s))
+    # the restored population continues identically
+    l1 = pop.train_step(d(frames), d(actions), d(td), d(r), 0.01).cpu().numpy()
+    l2 = pop2.train_step(d(frames), d(actions), d(td), d(r), 0.01).cpu().numpy()
+    assert np.array_equal(l1, l2)
+    pop.close(); pop2.close()

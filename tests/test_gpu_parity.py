@@ -433,3 +433,57 @@ def test_c2_full_size_properties(eng_mod):
             assert not torch.equal(pop.params[sl], p0[sl])
     for q in (pop, one, sub):
         q.close()
+
+
+# ---------------------------------------------------------------------------
+# rollout bookkeeping
+# ---------------------------------------------------------------------------
+def test_sample_actions_bit_exact(eng_mod):
+    rng = np.random.default_rng(11)
+    for A in (3, 18, 31):
+        z = rng.normal(size=(257, A)) * 3
+        pi = np.exp(z - z.max(1, keepdims=True)); pi = (pi / pi.sum(1, keepdims=True)).astype(np.float32)
+        pi[5] = 0; pi[5, A - 1] = 1.0                     # deterministic row
+        pi[6] = 0; pi[6, 0] = 1.0
+        got = eng_mod.sample_actions(dev(pi), 99, 4, id0=1000).cpu().numpy()
+        want = po.sample_actions(pi, 99, 4, id0=1000)
+        assert np.array_equal(got, want)
+        assert got[5] == A - 1 and got[6] == 0
+
+
+def test_nstep_returns_bit_exact(eng_mod):
+    rng = np.random.default_rng(12)
+    P, B = 37, 20
+    rew = (rng.normal(size=(P, B)) * 2).astype(np.float32)
+    val = rng.normal(size=(P, B)).astype(np.float32)
+    boot = rng.normal(size=P).astype(np.float32)
+    boot[::3] = 0.0                                       # terminal rollouts bootstrap from 0
+    lengths = rng.integers(0, B + 1, size=P).astype(np.int32)
+    for ln in (None, lengths):
+        R, td = eng_mod.nstep_returns(dev(rew), dev(val), dev(boot), None if ln is None else dev(ln))
+        Rw, tdw = po.nstep_returns_batch(rew, val, boot, ln)
+        assert np.array_equal(R.cpu().numpy(), Rw) and np.array_equal(td.cpu().numpy(), tdw)
+
+
+def test_padded_transitions_contribute_nothing(eng_mod):
+    """action = -1 marks padding: loss and gradients equal those of the batch without the padded transitions."""
+    cfg = hp.TINY
+    params = po.init_params(cfg, 4)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, 2, 5, 21)
+    n_real = [3, 5]
+    act_pad = actions.copy()
+    act_pad[0, 3:] = -1
+    pop = make_pop(eng_mod, cfg, 2, 5, params, masks)
+    loss = pop.train_step(dev(frames), dev(act_pad), dev(td), dev(r), 0.01).cpu().numpy()
+    got = pop.dump(pop.grads)
+    pop.close()
+    # oracle: each path on its own real transitions, gradients summed over paths
+    G = None
+    for p in range(2):
+        n = n_real[p]
+        _, _, loss_r, Gp = po.population_step(cfg, params, frames[p:p + 1, :n], masks[p:p + 1], actions[p:p + 1, :n],
+                                              td[p:p + 1, :n], r[p:p + 1, :n])
+        assert hp.rel_err(loss[p:p + 1], loss_r) < REL_TOL
+        G = Gp if G is None else [a + b for a, b in zip(G, Gp)]
+    for a, b, t in zip(got, G, po.tensor_table(cfg)):
+        assert hp.rel_err(a, b) < REL_TOL, t["name"]

@@ -147,3 +147,35 @@ def test_param_counts_match_survey():
     n = lambda cfg: sum(int(np.prod(t["shape"])) for t in po.tensor_table(cfg))
     assert n(hp.C1) == 1697203 and n(hp.C3) == 1047683
     assert hp.C1.last_lin == 648 and hp.C3.last_lin == 392
+
+
+def test_choice_restatement_matches_numpy_randomstate():
+    """choice_from_uniform is numpy's legacy RandomState.choice with the uniform made explicit: feed it the uniform
+    the RandomState is about to draw and compare with what RandomState.choice returns (a3c_training_thread.py:89-90)."""
+    rng = np.random.default_rng(5)
+    for case in range(400):
+        A = int(rng.integers(2, 19))
+        z = rng.normal(size=A) * rng.choice([0.1, 1.0, 8.0])
+        p = np.exp(z - z.max()); p = (p / p.sum()).astype(np.float32)
+        rs = np.random.RandomState(1000 + case)
+        st = rs.get_state()
+        u = rs.random_sample()
+        rs.set_state(st)
+        want = rs.choice(range(A), p=p.astype(np.float64) / p.astype(np.float64).sum())
+        got = po.choice_from_uniform(p, u)
+        assert got == want, (case, A, u)
+
+
+def test_nstep_returns_batch_padding():
+    rng = np.random.default_rng(6)
+    P, B = 5, 7
+    rew = rng.normal(size=(P, B)).astype(np.float32) * 2
+    val = rng.normal(size=(P, B)).astype(np.float32)
+    boot = rng.normal(size=P).astype(np.float32)
+    lengths = np.asarray([7, 3, 1, 0, 5], np.int32)
+    R, td = po.nstep_returns_batch(rew, val, boot, lengths)
+    for p in range(P):
+        n = int(lengths[p])
+        Rs, tds = po.nstep_returns(rew[p, :n], val[p, :n], boot[p])
+        assert np.array_equal(R[p, :n], Rs.astype(np.float32)) and np.array_equal(td[p, :n], tds.astype(np.float32))
+        assert not R[p, n:].any() and not td[p, n:].any()

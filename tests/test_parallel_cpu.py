@@ -55,3 +55,36 @@ def test_gloo_world_size_2():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_checkpoint_roundtrip_and_tf_names(tmp_path):
+    """tensors in get_vars() order, slots, genotypes, frozen path; TF-Saver name mapping
+    (game_ac_network.py:125-148: variables are created in get_vars() order inside scope net_<i>)."""
+    import numpy as np
+    from oracle import pathnet_oracle as po
+    from pathnet_gym_b200 import checkpoint as ck
+    from tests import helpers as hp
+    cfg = hp.TINY
+    tt = po.tensor_table(cfg)
+    assert ck.tensor_names(cfg) == [t["name"] for t in tt]
+    names = ck.tf_saver_names(cfg)
+    assert names[0] == "net_0/Variable" and names[1] == "net_0/Variable_1" and len(names) == len(tt)
+    params = po.init_params(cfg, 3)
+    rms = [np.full(t["shape"], 1.0 + i, np.float32) for i, t in enumerate(tt)]
+    geno = np.asarray([[3, 5, 6], [9, 10, 12]], np.uint32)
+    fixed = np.zeros((cfg.L, cfg.M), np.float32); fixed[0, 1] = 1
+    path = str(tmp_path / "ck.npz")
+    ck.save_checkpoint(path, cfg, params, rms, None, geno, fixed, global_t=1234, extra={"scores": np.arange(2.0)})
+    got = ck.load_checkpoint(path, cfg)
+    assert got["global_t"] == 1234 and got["momentum"] is None
+    assert all(np.array_equal(a, b) for a, b in zip(got["params"], params))
+    assert all(np.array_equal(a, b) for a, b in zip(got["rms"], rms))
+    assert np.array_equal(got["genotypes"], geno) and np.array_equal(got["fixed_path"], fixed)
+    assert np.array_equal(got["extra"]["scores"], np.arange(2.0))
+    # a reference Saver dump maps back onto the slab order through its variable names
+    tfvars = {nm: p for nm, p in zip(names, params)}
+    back = ck.from_tf_variables(cfg, tfvars)
+    assert all(np.array_equal(a, b) for a, b in zip(back, params))
+    import pytest
+    with pytest.raises(ValueError):
+        ck.load_checkpoint(path, hp.TINY4)
