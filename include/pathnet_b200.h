@@ -281,6 +281,14 @@ PN_API int pn_sample_actions(const float* pi_dev, int n, int A, uint64_t seed, u
 PN_API int pn_nstep_returns(const float* rewards_dev, const float* values_dev, const float* bootstrap_dev,
                      const int32_t* lengths_dev, int P, int B, double gamma, float* R_dev, float* td_dev, void* stream);
 
+/* Replaces GameState._process_frame + the stack update (game_state.py:37-51,62-66,75-81) for n environments:
+ * obs_dev [n,Hin,Win,3] u8 -> cv2.cvtColor(COLOR_BGR2GRAY) -> cv2.resize(.., (W,H)) (INTER_LINEAR), both bit-exact
+ * restatements of OpenCV's 8-bit fixed-point paths -> pushed into frames_dev [n,H,W,C] u8 in place
+ * (channels shift down by one, the new frame becomes channel C-1; where reset_dev[e] != 0 all C channels are set to
+ * the new frame, as GameState.reset does).  The u8 value k stands for k/255, the reference's fp32 scaling. */
+PN_API int pn_preprocess_frames(const uint8_t* obs_dev, int n, int Hin, int Win, uint8_t* frames_dev, int H, int W,
+                         int C, const uint8_t* reset_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -381,6 +381,62 @@ def nstep_returns_batch(rewards, values, bootstrap, lengths=None, gamma=GAMMA):
     return R, td
 
 
+# ----------------------------------------------------------------------------
+# Frame preprocessing (game_state.py:37-51,62-66,75-81): OpenCV's 8-bit paths restated
+# ----------------------------------------------------------------------------
+def bgr2gray_u8(img) -> np.ndarray:
+    """cv2.cvtColor(img, cv2.COLOR_BGR2GRAY) for u8: 15-bit fixed point, round half up (pinned against cv2)."""
+    img = np.asarray(img)
+    b, g, r = (img[..., k].astype(np.int32) for k in range(3))
+    return ((3735 * b + 19235 * g + 9798 * r + (1 << 14)) >> 15).astype(np.uint8)
+
+
+def _resize_taps(dn, sn):
+    idx = np.zeros((dn, 2), np.int32)
+    a = np.zeros((dn, 2), np.int32)
+    scale = float(sn) / float(dn)
+    for d in range(dn):
+        f = np.float32((d + 0.5) * scale - 0.5)
+        s = int(np.floor(f))
+        f = np.float32(f - np.float32(s))
+        if s < 0:
+            s, f = 0, np.float32(0)
+        if s >= sn - 1:
+            s, f = sn - 1, np.float32(0)
+        idx[d] = (s, min(s + 1, sn - 1))
+        a[d, 0] = int(np.rint(np.float32((np.float32(1) - f) * np.float32(2048))))
+        a[d, 1] = int(np.rint(np.float32(f * np.float32(2048))))
+    return idx, a
+
+
+def resize_linear_u8(src, dw, dh) -> np.ndarray:
+    """cv2.resize(src, (dw, dh)) with the default INTER_LINEAR on a u8 image: 11-bit coefficients, the fixed-point
+    horizontal pass then `(((b0*(r0>>4))>>16) + ((b1*(r1>>4))>>16) + 2) >> 2` vertically (pinned against cv2)."""
+    S = np.asarray(src).astype(np.int32)
+    sh, sw = S.shape
+    xi, xa = _resize_taps(dw, sw)
+    yi, ya = _resize_taps(dh, sh)
+    rows = S[:, xi[:, 0]] * xa[:, 0] + S[:, xi[:, 1]] * xa[:, 1]
+    r0, r1 = rows[yi[:, 0]], rows[yi[:, 1]]
+    out = (((ya[:, 0:1] * (r0 >> 4)) >> 16) + ((ya[:, 1:2] * (r1 >> 4)) >> 16) + 2) >> 2
+    return np.clip(out, 0, 255).astype(np.uint8)
+
+
+def preprocess_frames(obs, frames, reset=None) -> np.ndarray:
+    """GameState._process_frame + stack update for n environments: obs [n,Hin,Win,3] u8, frames [n,H,W,C] u8 (copy
+    returned): new frame appended as the last channel, or all channels on reset."""
+    out = np.array(frames, dtype=np.uint8).copy()
+    n, H, W, C = out.shape
+    for e in range(n):
+        x = resize_linear_u8(bgr2gray_u8(obs[e]), W, H)
+        if reset is not None and reset[e]:
+            out[e] = x[..., None]
+        else:
+            out[e, :, :, :-1] = out[e, :, :, 1:]
+            out[e, :, :, -1] = x
+    return out
+
+
 DOMAIN_ACTION = 3
 
 

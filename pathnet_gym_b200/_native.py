@@ -75,6 +75,7 @@ SIGNATURES = {
     "pn_tournament": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, C.c_uint64, C.c_uint32, _vp]),
     "pn_sample_actions": (_i, [_vp, _i, _i, C.c_uint64, C.c_uint32, C.c_uint32, _vp, _vp]),
     "pn_nstep_returns": (_i, [_vp, _vp, _vp, _vp, _i, _i, C.c_double, _vp, _vp, _vp]),
+    "pn_preprocess_frames": (_i, [_vp, _i, _i, _i, _vp, _i, _i, _i, _vp, _vp]),
 }
 
 _lib = None

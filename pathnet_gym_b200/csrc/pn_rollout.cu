@@ -75,3 +75,71 @@ extern "C" PN_API int pn_nstep_returns(const float* rewards_dev, const float* va
     if (e != cudaSuccess) return pn_fail_global(PN_ERR_CUDA, "nstep_returns_kernel: %s", cudaGetErrorString(e));
     return PN_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Frame preprocessing (game_state.py:37-51,62-66,75-81): the step right before the hot path.
+//   observation [n, Hin, Win, 3] u8  --cv2.cvtColor(COLOR_BGR2GRAY)-->  gray u8  --cv2.resize(INTER_LINEAR)-->  [H, W] u8
+//   --> pushed into the 4-frame stack [n, H, W, C] u8 (s_t1 = append(s_t[:, :, 1:], x_t1); on reset all C channels = x_t).
+// The reference then multiplies by 1/255 into fp32; the product's u8 frame k IS k/255 (pathnet_b200.h), so nothing is lost.
+// Bit-exact restatement of OpenCV's 8-bit paths (checked against cv2 itself in tests/test_oracle.py):
+//   gray = (3735 B + 19235 G + 9798 R + 2^14) >> 15
+//   resize: fx = float((dx + 0.5) * (Win / W) - 0.5); sx = floor(fx); fx -= sx; clamp to the image (weights (1, 0));
+//           ia = round_half_even((1 - fx) * 2048), ib = round_half_even(fx * 2048); same in y;
+//           row value r = S[sx] * ia + S[sx + 1] * ib;  out = (((by0 * (r0 >> 4)) >> 16) + ((by1 * (r1 >> 4)) >> 16) + 2) >> 2
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+__device__ __forceinline__ void resize_tap(int d, int dn, int sn, int& s0, int& s1, int& a0, int& a1) {
+    const double scale = (double)sn / (double)dn;
+    float f = (float)__dsub_rn(__dmul_rn((double)d + 0.5, scale), 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    if (s < 0) { s = 0; f = 0.f; }
+    if (s >= sn - 1) { s = sn - 1; f = 0.f; }
+    s0 = s; s1 = min(s + 1, sn - 1);
+    a0 = __float2int_rn((1.f - f) * 2048.f);
+    a1 = __float2int_rn(f * 2048.f);
+}
+
+__device__ __forceinline__ int gray_at(const uint8_t* __restrict__ img, int Win, int y, int x) {
+    const uint8_t* px = img + ((size_t)y * Win + x) * 3;
+    return (3735 * (int)px[0] + 19235 * (int)px[1] + 9798 * (int)px[2] + (1 << 14)) >> 15;
+}
+
+__global__ void preprocess_frames_kernel(const uint8_t* __restrict__ obs, int n, int Hin, int Win, uint8_t* __restrict__ frames,
+                                         int H, int W, int C, const uint8_t* __restrict__ reset) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n * H * W) return;
+    const int x = (int)(i % W), y = (int)((i / W) % H), e = (int)(i / ((long long)W * H));
+    int x0, x1, ax0, ax1, y0, y1, ay0, ay1;
+    resize_tap(x, W, Win, x0, x1, ax0, ax1);
+    resize_tap(y, H, Hin, y0, y1, ay0, ay1);
+    const uint8_t* img = obs + (size_t)e * Hin * Win * 3;
+    const int r0 = gray_at(img, Win, y0, x0) * ax0 + gray_at(img, Win, y0, x1) * ax1;
+    const int r1 = gray_at(img, Win, y1, x0) * ax0 + gray_at(img, Win, y1, x1) * ax1;
+    int v = (((ay0 * (r0 >> 4)) >> 16) + ((ay1 * (r1 >> 4)) >> 16) + 2) >> 2;
+    v = v < 0 ? 0 : (v > 255 ? 255 : v);
+    uint8_t* px = frames + (size_t)i * C;
+    if (reset && reset[e]) {
+        for (int c = 0; c < C; ++c) px[c] = (uint8_t)v;
+    } else {
+        for (int c = 0; c + 1 < C; ++c) px[c] = px[c + 1];
+        px[C - 1] = (uint8_t)v;
+    }
+}
+
+}  // namespace
+
+extern "C" PN_API int pn_preprocess_frames(const uint8_t* obs_dev, int n, int Hin, int Win, uint8_t* frames_dev, int H, int W,
+                                           int C, const uint8_t* reset_dev, void* stream) {
+    if (!obs_dev || !frames_dev) return pn_fail_global(PN_ERR_INVALID, "pn_preprocess_frames: null argument");
+    if (n < 0 || Hin < 1 || Win < 1 || H < 1 || W < 1 || C < 1 || C > 16)
+        return pn_fail_global(PN_ERR_INVALID, "pn_preprocess_frames: n = %d, %dx%d -> %dx%dx%d", n, Hin, Win, H, W, C);
+    const long long total = (long long)n * H * W;
+    if (total == 0) return PN_OK;
+    preprocess_frames_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(obs_dev, n, Hin, Win, frames_dev,
+                                                                                             H, W, C, reset_dev);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return pn_fail_global(PN_ERR_CUDA, "preprocess_frames_kernel: %s", cudaGetErrorString(e));
+    return PN_OK;
+}

@@ -332,6 +332,25 @@ def nstep_returns(rewards: torch.Tensor, values: torch.Tensor, bootstrap: torch.
     return R, td
 
 
+def preprocess_frames_(obs: torch.Tensor, frames: torch.Tensor, reset: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """GameState._process_frame + stack update (game_state.py:37-51,75-81) for n environments, in place on `frames`:
+    obs [n, Hin, Win, 3] u8 (BGR order as cv2 sees it) -> gray -> bilinear resize -> newest channel of the u8 stack
+    frames [n, H, W, C]; reset [n] u8/bool: fill all C channels (GameState.reset)."""
+    lib = nat.load()
+    assert obs.is_cuda and obs.dtype == torch.uint8 and obs.is_contiguous() and obs.dim() == 4 and obs.shape[3] == 3
+    assert frames.is_cuda and frames.dtype == torch.uint8 and frames.is_contiguous() and frames.dim() == 4
+    n, Hin, Win, _ = obs.shape
+    assert frames.shape[0] == n
+    rs = None
+    if reset is not None:
+        rs = reset.to(torch.uint8).contiguous()
+        assert rs.is_cuda and rs.shape == (n,)
+    st = C.c_void_p(torch.cuda.current_stream(obs.device).cuda_stream)
+    nat.check(lib.pn_preprocess_frames(_ptr(obs), n, Hin, Win, _ptr(frames), frames.shape[1], frames.shape[2],
+                                       frames.shape[3], _ptr(rs), st))
+    return frames
+
+
 def mutate_(masks: torch.Tensor, M, N, seed, epoch, path_id0=0) -> torch.Tensor:
     lib = nat.load()
     assert masks.is_cuda and masks.dtype == torch.int32 and masks.is_contiguous()

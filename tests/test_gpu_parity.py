@@ -487,3 +487,16 @@ def test_padded_transitions_contribute_nothing(eng_mod):
         G = Gp if G is None else [a + b for a, b in zip(G, Gp)]
     for a, b, t in zip(got, G, po.tensor_table(cfg)):
         assert hp.rel_err(a, b) < REL_TOL, t["name"]
+
+
+def test_preprocess_frames_bit_exact(eng_mod):
+    """pn_preprocess_frames against the oracle restatement (itself pinned against cv2): gray, resize, stack push, reset."""
+    rng = np.random.default_rng(13)
+    for (hin, win), (H, W, C) in [((210, 160), (84, 84, 4)), ((480, 640), (160, 120, 4)), ((50, 40), (21, 33, 3))]:
+        n = 3
+        obs = rng.integers(0, 256, (n, hin, win, 3), dtype=np.uint8)
+        fr = rng.integers(0, 256, (n, H, W, C), dtype=np.uint8)
+        reset = np.asarray([0, 1, 0], np.uint8)
+        for rs in (None, reset):
+            got = eng_mod.preprocess_frames_(dev(obs), dev(fr.copy()), None if rs is None else dev(rs)).cpu().numpy()
+            assert np.array_equal(got, po.preprocess_frames(obs, fr, rs))

@@ -179,3 +179,26 @@ def test_nstep_returns_batch_padding():
         Rs, tds = po.nstep_returns(rew[p, :n], val[p, :n], boot[p])
         assert np.array_equal(R[p, :n], Rs.astype(np.float32)) and np.array_equal(td[p, :n], tds.astype(np.float32))
         assert not R[p, n:].any() and not td[p, n:].any()
+
+
+def test_frame_preprocessing_restatement_matches_cv2():
+    """bgr2gray_u8 / resize_linear_u8 are OpenCV's 8-bit fixed-point paths restated (game_state.py:41-45): compare
+    with cv2 itself, bit for bit, on the geometries the reference sees."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(0)
+    for (h, w), (dw, dh) in [((210, 160), (84, 84)), ((210, 160), (120, 160)), ((480, 640), (120, 160)), ((84, 84), (84, 84)),
+                             ((100, 37), (84, 84))]:
+        for k in range(3):
+            img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+            if k == 1:
+                img[:] = rng.integers(0, 256, (1, 1, 3))                 # flat colour
+            g = cv2.cvtColor(img, cv2.COLOR_BGR2GRAY)
+            assert np.array_equal(po.bgr2gray_u8(img), g)
+            assert np.array_equal(po.resize_linear_u8(g, dw, dh), cv2.resize(g, (dw, dh)))
+    obs = rng.integers(0, 256, (2, 50, 40, 3), dtype=np.uint8)
+    fr = rng.integers(0, 256, (2, 21, 21, 4), dtype=np.uint8)
+    out = po.preprocess_frames(obs, fr, reset=[0, 1])
+    x0 = cv2.resize(cv2.cvtColor(obs[0], cv2.COLOR_BGR2GRAY), (21, 21))
+    assert np.array_equal(out[0, :, :, :3], fr[0, :, :, 1:]) and np.array_equal(out[0, :, :, 3], x0)
+    x1 = cv2.resize(cv2.cvtColor(obs[1], cv2.COLOR_BGR2GRAY), (21, 21))
+    assert all(np.array_equal(out[1, :, :, c], x1) for c in range(4))
