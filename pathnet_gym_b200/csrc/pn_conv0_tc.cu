@@ -633,46 +633,38 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 for (int sl = 0; sl < kPassSlots; ++sl)
 #pragma unroll
                     for (int c = 0; c < 8; ++c) bsum[sl][c] = 0.f;
-                // the loads of a transition's rows (dY, mask bytes) are issued one transition ahead, so that their
-                // latency (~2 K cycles) runs underneath the quantisation of the previous transition
-                struct QLoad { int mm[2], pixv[2]; bool val[2]; float4 ga[2], gb[2]; uint32_t rb[2]; };
-                auto qload = [&](QLoad& L, size_t t, int base) {
-#pragma unroll
-                    for (int u = 0; u < 2; ++u) {
-                        const int m = base + u * 256 + tid;
-                        L.mm[u] = m;
-                        const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
-                        L.val[u] = m < gm.mq && ox < gm.OW && oy < gm.OH;
-                        L.pixv[u] = oy * gm.OW + ox;
-                        L.ga[u] = L.gb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        L.rb[u] = 0;
-                        if (L.val[u]) {
-                            const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + L.pixv[u]) * PN_F);
-                            L.ga[u] = g4[0]; L.gb[u] = g4[1];
-#pragma unroll
-                            for (int sl = 0; sl < kPassSlots; ++sl)
-                                if (sl < nsl) L.rb[u] |= (uint32_t)R[(t * nd.M + jl[sl]) * npix + L.pixv[u]] << (8 * sl);
-                        }
-                    }
-                };
-                const bool ahead = gm.mq <= 512;                 // one group of rows per transition: prefetch across transitions
-                QLoad nxt;
-                if (ahead) qload(nxt, (size_t)p * B + b_lo, 0);
                 for (int b = b_lo; b < b_hi; ++b) {
                     const size_t t = (size_t)p * B + b;
-                    QLoad cur0 = nxt;
-                    if (ahead && b + 1 < b_hi) qload(nxt, t + 1, 0);
                     mbar_wait(&dq_empty[stage], phase ^ 1);
                     uint8_t* dq = dq_s + (size_t)stage * dq_stage_bytes;
                     for (int base = 0; base < gm.mq; base += 512) {
-                        QLoad cur = cur0;
-                        if (!ahead) qload(cur, t, base);
+                        // two raster rows per thread; all global loads are issued before either is processed
+                        int mm[2], pixv[2];
+                        bool val[2];
+                        float4 ga[2], gb[2];
+                        uint32_t rb[2];
 #pragma unroll
                         for (int u = 0; u < 2; ++u) {
-                            const int m = cur.mm[u];
+                            const int m = base + u * 256 + tid;
+                            mm[u] = m;
+                            const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
+                            val[u] = m < gm.mq && ox < gm.OW && oy < gm.OH;
+                            pixv[u] = oy * gm.OW + ox;
+                            ga[u] = gb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            rb[u] = 0;
+                            if (val[u]) {
+                                const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pixv[u]) * PN_F);
+                                ga[u] = g4[0]; gb[u] = g4[1];
+#pragma unroll
+                                for (int sl = 0; sl < kPassSlots; ++sl)
+                                    if (sl < nsl) rb[u] |= (uint32_t)R[(t * nd.M + jl[sl]) * npix + pixv[u]] << (8 * sl);
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            const int m = mm[u];
                             if (m >= gm.mq) continue;
-                            const float dv[8] = {cur.ga[u].x, cur.ga[u].y, cur.ga[u].z, cur.ga[u].w,
-                                                 cur.gb[u].x, cur.gb[u].y, cur.gb[u].z, cur.gb[u].w};
+                            const float dv[8] = {ga[u].x, ga[u].y, ga[u].z, ga[u].w, gb[u].x, gb[u].y, gb[u].z, gb[u].w};
                             uint32_t w[4][2];                    // [digit][channels 0-3 / 4-7]
                             int dg[4][8];
 #pragma unroll
@@ -691,7 +683,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
 #pragma unroll
                             for (int sl = 0; sl < kPassSlots; ++sl) {
                                 if (sl >= nsl) break;
-                                const unsigned bits = (cur.rb[u] >> (8 * sl)) & 255u;     // 0 for rows outside the output grid
+                                const unsigned bits = (rb[u] >> (8 * sl)) & 255u;     // 0 for rows outside the output grid
                                 const uint32_t mlo = nib_to_bytemask(bits & 15u), mhi = nib_to_bytemask(bits >> 4);
                                 const uint4 g0 = make_uint4(w[0][0] & mlo, w[0][1] & mhi, w[1][0] & mlo, w[1][1] & mhi);
                                 const uint4 g1 = make_uint4(w[2][0] & mlo, w[2][1] & mhi, w[3][0] & mlo, w[3][1] & mhi);
