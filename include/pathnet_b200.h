@@ -181,6 +181,16 @@ PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, floa
 PN_API int pn_lin_grads_region(const pn_handle* h, int64_t* offset_floats, int64_t* count_floats);
 PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
 
+/* Sum of the two small gradient regions (everything but the linear modules: conv layers + heads, ~140 KB) over the
+ * GPUs of one node in ONE kernel over NVLink peer memory, instead of an all-reduce that would sit exposed at the end of
+ * the step: every rank publishes its values in an exchange buffer that all ranks have mapped (symmetric memory of
+ * pn_peer_buffer_bytes() bytes, zero-initialised, allocated and exchanged by the host, e.g.
+ * torch.distributed._symmetric_memory), raises a flag on every peer, waits for the peers and adds the copies in rank
+ * order (bit-identical on all ranks).  peer_bufs_host[r] = address of rank r's buffer in THIS process; step = 0, 1, 2, ...
+ * identical on all ranks.  No counterpart in the reference (single process per parameter server). */
+PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h);
+PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, void* stream);
+
 /* Replaces RMSPropApplier.apply_gradients for the non-frozen tensors
  * (rmsprop_applier.py:79-106): per tensor g' = clip_by_norm(g, clip_norm);
  * ms += (g'^2 - ms)(1-decay); mom = momentum*mom + lr*g'/sqrt(ms+eps);

@@ -56,6 +56,8 @@ SIGNATURES = {
     "pn_launch_count": (C.c_int64, [_vp]),
     "pn_lin_grads_region": (_i, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "pn_stream_wait_lin_grads": (_i, [_vp, _vp]),
+    "pn_peer_buffer_bytes": (C.c_int64, [_vp]),
+    "pn_peer_sum_small": (_i, [_vp, _vp, _i, _i, C.c_uint32, _vp]),
     "pn_profile_enable": (_i, [_vp, _i]),
     "pn_profile_read": (_i, [_vp, C.POINTER(PnProfileEntry), _i]),
     "pn_bind_slabs": (_i, [_vp, _vp, _vp, _vp, _vp]),

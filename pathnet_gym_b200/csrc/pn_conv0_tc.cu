@@ -493,7 +493,9 @@ __device__ __forceinline__ uint32_t nib_to_bytemask(unsigned nib) {
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ dY, const uint8_t* __restrict__ R,
                       const unsigned* __restrict__ absmax, PnNetDesc nd, const uint32_t* __restrict__ masks, int B,
-                      int P, int cs, int nch, int nch_alloc, TcGeom gm, float* __restrict__ part) {
+                      int P, int cs, int nch, int nch_alloc, TcGeom gm, float* __restrict__ part, long long* __restrict__ dbg) {
+    const bool dbg8 = dbg && dbg[148 * 8] == 8;                 // PN_TC_DEBUG=8: where the weight-gradient kernel's roles wait
+    const long long t_entry = dbg8 ? pinned_clock() : 0;
     extern __shared__ __align__(1024) uint8_t smem[];
     const int region_q = gm.mq * 16;                       // bytes of one 16-column group of dq
     const int dq_stage_bytes = 2 * kPassSlots * region_q;  // up to 4 modules x 2 groups
@@ -557,6 +559,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
         // whole-warp, warp-uniform code; only the tcgen05 instructions are elected to one lane
         int stage = 0;
         uint32_t phase = 0, nflush = 0;
+        long long m_wframe = 0, m_wdq = 0, m_wacc = 0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int p = item / nch, ch = item % nch;
             const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
@@ -567,12 +570,17 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                 const int N = kWgSlotCols * nsl;
                 const uint32_t idesc = make_idesc_i8(64, N, 0, 1, 1, 1);
+                const long long ca = dbg8 ? pinned_clock() : 0;
                 mbar_wait(acc_empty, (nflush & 1) ^ 1);       // previous flush has drained the accumulators
+                if (dbg8) m_wacc += pinned_clock() - ca;
                 tc_fence_after();
                 uint32_t accum = 0;
                 for (int b = b_lo; b < b_hi; ++b) {
+                    const long long c0 = dbg8 ? pinned_clock() : 0;
                     mbar_wait(&frame_full[stage], phase);
+                    const long long c1 = dbg8 ? pinned_clock() : 0;
                     mbar_wait(&dq_full[stage], phase);
+                    if (dbg8) { const long long c2 = pinned_clock(); m_wframe += c1 - c0; m_wdq += c2 - c1; }
                     tc_fence_after();
                     const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
                     const uint32_t qbase = smem_u32(dq_s + (size_t)stage * dq_stage_bytes);
@@ -604,6 +612,10 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 ++nflush;
             }
         }
+        if (dbg8 && lane == 0) {
+            dbg[blockIdx.x * 8 + 0] = m_wframe; dbg[blockIdx.x * 8 + 1] = m_wdq; dbg[blockIdx.x * 8 + 2] = m_wacc;
+            dbg[blockIdx.x * 8 + 3] = pinned_clock() - t_entry;
+        }
     } else {
         // ================= quantise dq per transition, flush the accumulators per (item, pass) =================
         const int quad = warp & 3, fgroup = warp >> 2;         // TMEM lane quadrant; flush group (taps 2*fgroup, +1)
@@ -616,6 +628,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
         const float qscale = am ? ldexpf(1.0f, 30 - e) : 0.f;
         const double dscale = am ? ldexp(1.0, e - 30) / 255.0 : 0.0;
         const int stride_part = nd.KK[0] * PN_F + PN_F;
+        long long q_wempty = 0, q_wfull = 0, q_flush = 0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int p = item / nch, ch = item % nch;
             const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
@@ -635,7 +648,9 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     for (int c = 0; c < 8; ++c) bsum[sl][c] = 0.f;
                 for (int b = b_lo; b < b_hi; ++b) {
                     const size_t t = (size_t)p * B + b;
+                    const long long cq = dbg8 ? pinned_clock() : 0;
                     mbar_wait(&dq_empty[stage], phase ^ 1);
+                    if (dbg8) q_wempty += pinned_clock() - cq;
                     uint8_t* dq = dq_s + (size_t)stage * dq_stage_bytes;
                     for (int base = 0; base < gm.mq; base += 512) {
                         // two raster rows per thread; all global loads are issued before either is processed
@@ -700,7 +715,10 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
                 // ---- flush ----
+                const long long cf = dbg8 ? pinned_clock() : 0;
                 mbar_wait(acc_full, nflush & 1);
+                const long long cf1 = dbg8 ? pinned_clock() : 0;
+                if (dbg8) q_wfull += cf1 - cf;
                 tc_fence_after();
                 const bool rowvalid = lane < 16;
                 const int r = quad * 16 + lane;                   // accumulator row = (g, byte) of the tap
@@ -741,8 +759,13 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 tc_fence_before();
                 mbar_arrive(acc_empty);
+                if (dbg8) q_flush += pinned_clock() - cf1;
                 ++nflush;
             }
+        }
+        if (dbg8 && tid == 0) {
+            dbg[blockIdx.x * 8 + 4] = q_wempty; dbg[blockIdx.x * 8 + 5] = q_wfull; dbg[blockIdx.x * 8 + 6] = q_flush;
+            dbg[blockIdx.x * 8 + 7] = pinned_clock() - t_entry;
         }
     }
     tc_fence_before();
@@ -892,7 +915,7 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + 0, st);
         conv0_wgrad_tc_kernel<<<grid, kTcThreads, smem_bytes, st>>>(tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
-                                                                   B, P, cs, nch, h->nch, g, h->wpart[0]);
+                                                                   B, P, cs, nch, h->nch, g, h->wpart[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_wgrad_tc_kernel");
     h->last_wgrad_nch = nch;

@@ -1,0 +1,111 @@
+// Cross-GPU sum of the small gradient regions (conv layers + heads, ~140 KB) over NVLink peer memory, in ONE kernel.
+//
+// Why: in a sharded population the linear modules' gradients (97 % of the bytes) are all-reduced by NCCL
+// underneath the conv layers' backward pass, but the conv and head gradients only exist when the step's last kernel has
+// run, so their all-reduce sits exposed at the end of every step and is pure latency (two dependent NCCL kernels'
+// worth of launch + handshake for 140 KB).  Here every GPU publishes its values in a buffer its peers can read
+// (symmetric memory: the same allocation mapped into every process of the node), raises a flag on every peer, waits
+// for the peers' flags, and adds up all copies itself in rank order -- one launch, and bit-identical on every rank.
+//
+//   exchange buffer of a rank: [flags: 64 x u32][slot 0: n floats][slot 1: n floats]
+//   flags[r] = number of steps rank r has published (monotonic).  Step s uses slot s & 1: a rank publishes step s + 1 only
+//   after it has finished reading every peer's step-s slot, and nobody can overwrite slot s & 1 (step s + 2) before all
+//   ranks have published s + 1, so two slots are enough.
+// The grid must be co-resident (the CTAs spin): it is capped at one CTA per SM, far below that in practice.
+#include "pn_internal.cuh"
+
+#include <algorithm>
+
+namespace {
+
+constexpr int kPeerFlagWords = 64;
+constexpr int kPeerMaxWorld = 16;
+
+struct PeerPtrs {
+    uint64_t buf[kPeerMaxWorld];
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ float ld_peer(const float* p) {       // never from a stale L1 line
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// slab index of element e of the small set: the conv region [0, lin_off) followed by the head region after the linear one
+__device__ __forceinline__ long long small_index(int e, long long lin_off, long long lin_cnt) {
+    return e < lin_off ? (long long)e : (long long)e + lin_cnt;
+}
+
+__global__ void __launch_bounds__(256)
+peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long lin_cnt, int n, PeerPtrs peers, int rank, int world,
+                      unsigned step, unsigned* __restrict__ cta_counter) {
+    const int slot = step & 1u;
+    float* mine = reinterpret_cast<float*>(peers.buf[rank]) + kPeerFlagWords + (size_t)slot * n;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+    // A: publish my values
+    for (int e = tid; e < n; e += nthreads) mine[e] = grads[small_index(e, lin_off, lin_cnt)];
+    __threadfence_system();
+    __syncthreads();
+    __shared__ unsigned last;
+    if (threadIdx.x == 0) last = atomicAdd(cta_counter, 1u) == step * gridDim.x + gridDim.x - 1 ? 1u : 0u;   // counter is monotonic
+    __syncthreads();
+    if (last) __threadfence_system();     // every CTA's values (fenced before its atomicAdd) are ordered before the flag
+    if (last && threadIdx.x < world) {
+        // the last CTA to finish writing raises my flag on every rank (including myself)
+        unsigned* f = reinterpret_cast<unsigned*>(peers.buf[threadIdx.x]) + rank;
+        st_release_sys(f, step + 1u);
+    }
+    // B: wait until every rank has published this step
+    if (threadIdx.x < world) {
+        const unsigned* f = reinterpret_cast<const unsigned*>(peers.buf[rank]) + threadIdx.x;
+        while ((int)(ld_acquire_sys(f) - (step + 1u)) < 0) { }
+    }
+    __syncthreads();
+    // C: fixed-order sum over the ranks
+    for (int e = tid; e < n; e += nthreads) {
+        float s = 0.f;
+        for (int r = 0; r < world; ++r)
+            s += ld_peer(reinterpret_cast<const float*>(peers.buf[r]) + kPeerFlagWords + (size_t)slot * n + e);
+        grads[small_index(e, lin_off, lin_cnt)] = s;
+    }
+}
+
+}  // namespace
+
+extern "C" PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h) {
+    if (!h) return -1;
+    const long long n = h->slab_floats - (h->nd.fc2W - h->nd.linW_base);
+    return (int64_t)(kPeerFlagWords * 4 + 2 * n * 4);
+}
+
+extern "C" PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step,
+                                        void* stream) {
+    if (!h || !peer_bufs_host) return pn_fail_global(PN_ERR_INVALID, "pn_peer_sum_small: null argument");
+    if (world < 1 || world > kPeerMaxWorld || rank < 0 || rank >= world)
+        return pn_fail(h, PN_ERR_INVALID, "pn_peer_sum_small: rank %d of %d (at most %d ranks)", rank, world, kPeerMaxWorld);
+    if (!h->grads) return pn_fail(h, PN_ERR_STATE, "gradient slab not bound");
+    const long long lin_off = h->nd.linW_base, lin_cnt = h->nd.fc2W - h->nd.linW_base;
+    const int n = (int)(h->slab_floats - lin_cnt);
+    PeerPtrs pp;
+    for (int r = 0; r < kPeerMaxWorld; ++r) pp.buf[r] = r < world ? peer_bufs_host[r] : 0;
+    if (!h->peer_counter) {
+        PN_CUDA(h, cudaMalloc(&h->peer_counter, sizeof(unsigned)));
+        PN_CUDA(h, cudaMemsetAsync(h->peer_counter, 0, sizeof(unsigned), (cudaStream_t)stream));
+        h->peer_step0 = step;
+    }
+    const int grid = std::max(1, std::min(h->num_sms / 4, (n + 1023) / 1024));
+    if (h->peer_grid && h->peer_grid != grid) return pn_fail(h, PN_ERR_STATE, "pn_peer_sum_small: grid changed between steps");
+    h->peer_grid = grid;
+    peer_sum_small_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h->grads, lin_off, lin_cnt, n, pp, rank, world, step - h->peer_step0,
+                                                                 h->peer_counter);
+    PN_LAUNCH_CHECK(h, "peer_sum_small_kernel");
+    return PN_OK;
+}

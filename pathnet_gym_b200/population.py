@@ -243,6 +243,15 @@ class PathNetPopulation:
         nat.check(self.lib.pn_lin_grads_region(self._h, C.byref(off), C.byref(cnt)), self._h)
         return int(off.value), int(cnt.value)
 
+    def peer_buffer_bytes(self) -> int:
+        return int(self.lib.pn_peer_buffer_bytes(self._h))
+
+    def peer_sum_small(self, peer_ptrs, rank, world, step):
+        """Conv + head gradient regions <- sum over the node's GPUs through peer memory (pn_peer_sum_small)."""
+        import ctypes as C
+        arr = (C.c_uint64 * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
+        nat.check(self.lib.pn_peer_sum_small(self._h, arr, int(rank), int(world), int(step), self._stream()), self._h)
+
     def stream_wait_lin_grads(self, stream: "torch.cuda.Stream"):
         """`stream` waits until the latest train_step has written the W_lin/b_lin gradients."""
         import ctypes as C

@@ -17,6 +17,34 @@ class OverlappedGradSum(object):
         g = pop.grads
         self.lin, self.head, self.conv = g[off:off + cnt], g[off + cnt:], g[:off]
         self.comm = torch.cuda.Stream(device=pop.device)
+        self.peer = None
+        self.step = 0
+        if self.active:
+            self._setup_peer_exchange()
+
+    def _setup_peer_exchange(self):
+        """Symmetric (peer-mapped) exchange buffers for the small regions; any failure leaves the NCCL path in place."""
+        import os
+        import torch
+        import torch.distributed as dist
+        if os.environ.get("PN_NO_PEER_SUM"):
+            return
+        ok = torch.zeros(1, device=self.pop.device)
+        try:
+            import torch.distributed._symmetric_memory as symm
+            nfloat = (self.pop.peer_buffer_bytes() + 3) // 4
+            self._peer_buf = symm.empty(nfloat, dtype=torch.float32, device=self.pop.device)
+            self._peer_buf.zero_()
+            self._peer_hdl = symm.rendezvous(self._peer_buf, dist.group.WORLD)
+            self.peer = [int(p) for p in self._peer_hdl.buffer_ptrs]
+            ok.fill_(1)
+        except Exception as e:      # noqa: BLE001  (old torch, no P2P, restricted container, ...)
+            self.peer = None
+            self.peer_error = repr(e)
+        torch.cuda.synchronize(self.pop.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)       # all ranks take the same path; also orders the zero-fill
+        if float(ok.item()) < 1:
+            self.peer = None
 
     def sum_lin(self):
         """On the side stream (already waiting for the linear gradients): all-reduce them."""
@@ -27,6 +55,11 @@ class OverlappedGradSum(object):
     def sum_rest(self):
         """On the compute stream, after the step's last kernel: one grouped NCCL launch for the two small regions."""
         if not self.active:
+            return
+        if self.peer is not None:
+            rank, world = parallel.world()
+            self.pop.peer_sum_small(self.peer, rank, world, self.step)
+            self.step += 1
             return
         import torch.distributed as dist
         try:

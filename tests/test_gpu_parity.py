@@ -500,3 +500,34 @@ def test_preprocess_frames_bit_exact(eng_mod):
         for rs in (None, reset):
             got = eng_mod.preprocess_frames_(dev(obs), dev(fr.copy()), None if rs is None else dev(rs)).cpu().numpy()
             assert np.array_equal(got, po.preprocess_frames(obs, fr, rs))
+
+
+def test_rmsprop_range_plus_complement_equals_full(eng_mod):
+    """pn_rmsprop_apply_range over the linear modules' rows + its complement == one pn_rmsprop_apply (per-tensor updates are
+    independent, rmsprop_applier.py:92-106); also checks pn_lin_grads_region against the tensor table."""
+    cfg = hp.TINY
+    tt = po.tensor_table(cfg)
+    rng = np.random.default_rng(3)
+    params = po.init_params(cfg, 5)
+    grads = [rng.normal(size=t["shape"]).astype(np.float32) * (30.0 if i % 4 == 0 else 0.05) for i, t in enumerate(tt)]
+    frozen = np.zeros(len(tt), np.uint8); frozen[3] = 1
+    pops = []
+    for k in range(2):
+        pop = make_pop(eng_mod, cfg, 1, 1, params, np.zeros((1, cfg.L), np.uint32))
+        pop.load(pop.grads, grads)
+        pop.set_frozen(frozen)
+        pops.append(pop)
+    first, count = pops[1].lin_tensor_range()
+    names = [t["name"] for t in tt]
+    assert names[first] == "W_lin[0]" and names[first + count - 1] == "b_lin[%d]" % (cfg.M - 1) and count == 2 * cfg.M
+    off, cnt = pops[1].lin_grads_region()
+    assert off == pops[1].tensors[first]["offset"] and off + cnt == pops[1].tensors[first + count]["offset"]
+    for step in range(2):
+        pops[0].apply_gradients(1e-2, 0.99, 0.0, 0.1, 40.0)
+        pops[1].apply_gradients_range(first, count, 1e-2, 0.99, 0.0, 0.1, 40.0)
+        pops[1].apply_gradients_range(first, count, 1e-2, 0.99, 0.0, 0.1, 40.0, complement=True)
+    for slab in ("params", "ms"):
+        a, b = pops[0].dump(getattr(pops[0], slab)), pops[1].dump(getattr(pops[1], slab))
+        assert all(np.array_equal(x, y) for x, y in zip(a, b)), slab
+    for pop in pops:
+        pop.close()

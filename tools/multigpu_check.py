@@ -30,7 +30,7 @@ def main():
     r = torch.randn(P, B, device=pop.device, generator=gen)
     gs = OverlappedGradSum(pop)
     worst = 0.0
-    for it in range(5):
+    for it in range(25):
         pop.train_step(frames, actions, td, r, 0.01)
         ref = pop.grads.clone()
         dist.all_reduce(ref)
@@ -40,7 +40,9 @@ def main():
         err = float((pop.grads - ref).norm() / ref.norm())
         worst = max(worst, err)
     if rank == 0:
-        print(json.dumps({"world": world, "overlapped_vs_plain_allreduce_rel_err": worst}))
+        print(json.dumps({"world": world, "overlapped_vs_plain_allreduce_rel_err": worst,
+                          "small_regions_via_peer_memory": gs.peer is not None,
+                          "peer_setup_error": getattr(gs, "peer_error", None)}))
     assert worst < 1e-6, worst
     pop.close()
     dist.destroy_process_group()
