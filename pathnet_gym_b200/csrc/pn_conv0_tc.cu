@@ -502,7 +502,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     uint8_t* frame_s = smem;
     uint8_t* dq_s = smem + 2 * (size_t)gm.stage_bytes;
     // the dq ring doubles as the 16 KB scratch of the bias-gradient reduction at flush time
-    const int dq_total = max(2 * dq_stage_bytes, 256 * 32 * (int)sizeof(float));
+    const int dq_total = max(2 * dq_stage_bytes, (256 + 8) * 32 * (int)sizeof(float));
     uint64_t* bars = reinterpret_cast<uint64_t*>(dq_s + dq_total);
     uint64_t* frame_full = bars;          // [2]
     uint64_t* frame_empty = bars + 2;     // [2]
@@ -751,9 +751,19 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
 #pragma unroll
                     for (int c = 0; c < 8; ++c) bred[tid * 32 + sl * 8 + c] = bsum[sl][c];
                 asm volatile("bar.sync 1, 256;" ::: "memory");
+                {   // two levels, both in a fixed order: 8 groups of 32 thread-partials, then the 8 group sums
+                    float* red2 = bred + 256 * 32;
+                    const int grp = tid >> 5, o = tid & 31;
+                    float s8 = 0.f;
+#pragma unroll 8
+                    for (int i = 0; i < 32; ++i) s8 += bred[(grp * 32 + i) * 32 + o];
+                    red2[grp * 32 + o] = s8;
+                }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (tid < nsl * 8) {
                     float sacc = 0.f;
-                    for (int i = 0; i < 256; ++i) sacc += bred[i * 32 + tid];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) sacc += bred[256 * 32 + q * 32 + tid];
                     part[((size_t)(p * nch_alloc + ch) * nd.M + jl[tid >> 3]) * stride_part + (size_t)nd.KK[0] * PN_F + (tid & 7)] = sacc;
                 }
                 asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -905,7 +915,7 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     }
     if (best_eff < 0) return pn_fail(h, PN_ERR_STATE, "no valid chunking for the conv0 weight-gradient kernel");
     const int nch = best_nch, cs = (B + nch - 1) / nch;
-    const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), 256 * 32 * sizeof(float));
+    const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), (256 + 8) * 32 * sizeof(float));
     const size_t smem_bytes = 2 * (size_t)g.stage_bytes + dq_total + 16 * sizeof(uint64_t);
     PN_SET_SMEM(h, conv0_wgrad_tc_kernel, smem_bytes);
     const int items = P * nch;
