@@ -187,7 +187,7 @@ PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
  * pn_peer_buffer_bytes() bytes, zero-initialised, allocated and exchanged by the host, e.g.
  * torch.distributed._symmetric_memory), raises a flag on every peer, waits for the peers and adds the copies in rank
  * order (bit-identical on all ranks).  peer_bufs_host[r] = address of rank r's buffer in THIS process; step = 0, 1, 2, ...
- * identical on all ranks.  No counterpart in the reference (single process per parameter server). */
+ * counted PER SET OF BUFFERS (a fresh zeroed set starts again at 0), identical on all ranks.  No counterpart in the reference (single process per parameter server). */
 PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h);
 PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, void* stream);
 

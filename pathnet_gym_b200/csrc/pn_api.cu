@@ -247,7 +247,6 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->ev_lin_grads) cudaEventDestroy(h->ev_lin_grads);
-    cudaFree(h->peer_counter);
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
     delete h;
 }

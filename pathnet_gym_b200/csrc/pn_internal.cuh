@@ -97,9 +97,6 @@ struct pn_handle {
     int max_active[PN_MAX_LAYERS] = {}; // largest number of active modules of any path, per layer (from pn_set_genotypes)
     cudaStream_t side = nullptr;        // weight-operand preparation runs here, beside the first conv layer
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
-    unsigned* peer_counter = nullptr;   // pn_peer_sum_small: CTAs that have published, monotonic over steps
-    uint32_t peer_step0 = 0;
-    int peer_grid = 0;
     cudaEvent_t ev_lin_grads = nullptr; // recorded after the linear weight-gradient launch of every training step
     bool absmax_fused = false;          // the layer-1 data-gradient launch of this step already wrote max |dY0|
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0

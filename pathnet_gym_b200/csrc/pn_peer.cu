@@ -7,7 +7,7 @@
 // (symmetric memory: the same allocation mapped into every process of the node), raises a flag on every peer, waits
 // for the peers' flags, and adds up all copies itself in rank order -- one launch, and bit-identical on every rank.
 //
-//   exchange buffer of a rank: [flags: 64 x u32][slot 0: n floats][slot 1: n floats]
+//   exchange buffer of a rank: [64 x u32: flags[0..31], CTA counter at word 32][slot 0: n floats][slot 1: n floats]
 //   flags[r] = number of steps rank r has published (monotonic).  Step s uses slot s & 1: a rank publishes step s + 1 only
 //   after it has finished reading every peer's step-s slot, and nobody can overwrite slot s & 1 (step s + 2) before all
 //   ranks have published s + 1, so two slots are enough.
@@ -46,8 +46,9 @@ __device__ __forceinline__ long long small_index(int e, long long lin_off, long 
 
 __global__ void __launch_bounds__(256)
 peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long lin_cnt, int n, PeerPtrs peers, int rank, int world,
-                      unsigned step, unsigned* __restrict__ cta_counter) {
+                      unsigned step) {
     const int slot = step & 1u;
+    unsigned* cta_counter = reinterpret_cast<unsigned*>(peers.buf[rank]) + 32;   // lives in the buffer: one count per buffer
     float* mine = reinterpret_cast<float*>(peers.buf[rank]) + kPeerFlagWords + (size_t)slot * n;
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
     // A: publish my values
@@ -96,16 +97,9 @@ extern "C" PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_
     const int n = (int)(h->slab_floats - lin_cnt);
     PeerPtrs pp;
     for (int r = 0; r < kPeerMaxWorld; ++r) pp.buf[r] = r < world ? peer_bufs_host[r] : 0;
-    if (!h->peer_counter) {
-        PN_CUDA(h, cudaMalloc(&h->peer_counter, sizeof(unsigned)));
-        PN_CUDA(h, cudaMemsetAsync(h->peer_counter, 0, sizeof(unsigned), (cudaStream_t)stream));
-        h->peer_step0 = step;
-    }
-    const int grid = std::max(1, std::min(h->num_sms / 4, (n + 1023) / 1024));
-    if (h->peer_grid && h->peer_grid != grid) return pn_fail(h, PN_ERR_STATE, "pn_peer_sum_small: grid changed between steps");
-    h->peer_grid = grid;
-    peer_sum_small_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h->grads, lin_off, lin_cnt, n, pp, rank, world, step - h->peer_step0,
-                                                                 h->peer_counter);
+    if (world > 32) return pn_fail(h, PN_ERR_INVALID, "pn_peer_sum_small: at most 32 ranks");
+    const int grid = std::max(1, std::min(h->num_sms / 4, (n + 1023) / 1024));      // a function of the handle only: the same every step
+    peer_sum_small_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h->grads, lin_off, lin_cnt, n, pp, rank, world, step);
     PN_LAUNCH_CHECK(h, "peer_sum_small_kernel");
     return PN_OK;
 }
