@@ -48,13 +48,15 @@ class OverlappedGradSum(object):
 
     def sum_lin(self):
         """On the side stream (already waiting for the linear gradients): all-reduce them."""
-        if self.active:
+        import os
+        if self.active and "lin" not in os.environ.get("PN_DEBUG_SKIP_SUM", ""):     # (timing experiments only)
             import torch.distributed as dist
             dist.all_reduce(self.lin, op=dist.ReduceOp.SUM)
 
     def sum_rest(self):
         """On the compute stream, after the step's last kernel: one grouped NCCL launch for the two small regions."""
-        if not self.active:
+        import os
+        if not self.active or "small" in os.environ.get("PN_DEBUG_SKIP_SUM", ""):    # (timing experiments only)
             return
         if self.peer is not None:
             rank, world = parallel.world()

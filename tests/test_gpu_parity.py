@@ -531,3 +531,27 @@ def test_rmsprop_range_plus_complement_equals_full(eng_mod):
         assert all(np.array_equal(x, y) for x, y in zip(a, b)), slab
     for pop in pops:
         pop.close()
+
+
+def test_peer_sum_small_single_rank(eng_mod):
+    """pn_peer_sum_small with world = 1 (the exchange buffer is ordinary device memory): the kernel's publish / flag /
+    wait / sum sequence must leave the conv + head regions equal to their input, the linear region untouched, for
+    several steps in a row (slot alternation, monotonic flags).  The multi-GPU behaviour is checked by
+    tools/multigpu_check.py under torchrun."""
+    cfg = hp.TINY
+    pop = make_pop(eng_mod, cfg, 1, 1, po.init_params(cfg, 1), np.zeros((1, cfg.L), np.uint32))
+    rng = np.random.default_rng(8)
+    nbytes = pop.peer_buffer_bytes()
+    buf = torch.zeros((nbytes + 3) // 4, dtype=torch.float32, device="cuda")
+    off, cnt = pop.lin_grads_region()
+    for step in range(5):
+        g0 = torch.from_numpy(rng.normal(size=pop.slab_floats).astype(np.float32)).cuda()
+        pop.grads.copy_(g0)
+        pop.peer_sum_small([buf.data_ptr()], 0, 1, step)
+        torch.cuda.synchronize()
+        assert torch.equal(pop.grads, g0)
+        slot = buf[64 + (step & 1) * (pop.slab_floats - cnt):][:pop.slab_floats - cnt]
+        assert torch.equal(slot[:off], g0[:off]) and torch.equal(slot[off:], g0[off + cnt:])
+    flags = buf[:64].view(torch.int32)
+    assert int(flags[0]) == 5
+    pop.close()
