@@ -706,15 +706,8 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
     }
     PN_LAUNCH_CHECK(h, "lin_dsplit_kernel");
     const int KT = (g.K / 8 + 1 + 15) / 16;          // tiles of 16 k-blocks covering the K rows plus the ones row
-    {
-        const size_t smem = 2 * (size_t)(2 * 16 * 16 * kBlk) + 2 * g.dp_slot + 256;
-        PN_SET_SMEM(h, lin_dgrad_tc_kernel, smem);
-        const int items = h->P * g.nbc * KT;
-        const int grid = items < h->num_sms ? items : h->num_sms;
-        PnProfScope prof(h, PN_PROF_LIN_DGRAD, st);
-        lin_dgrad_tc_kernel<<<grid, 192, smem, st>>>(wp, dp, g, h->d_masks, h->P, B, KT, h->dact[nd.nconv - 1]);
-    }
-    PN_LAUNCH_CHECK(h, "lin_dgrad_tc_kernel");
+    // weight gradient first: its result (97 % of the gradient bytes) is what a multi-GPU host wants to start summing,
+    // and the data-gradient GEMM that follows gives that all-reduce SMs to share (one 192-thread CTA per SM)
     {
         const size_t smem = 4 * (size_t)(4 * 16 * 4 * kBlk) + 256;
         PN_SET_SMEM(h, lin_wgrad_tc_kernel, smem);
@@ -724,5 +717,15 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
         lin_wgrad_tc_kernel<<<grid, 192, smem, st>>>(xp, dp, nd, g, h->d_masks, h->d_list, h->d_list_count, h->P, KT, h->grads);
     }
     PN_LAUNCH_CHECK(h, "lin_wgrad_tc_kernel");
+    PN_CUDA(h, cudaEventRecord(h->ev_lin_grads, st));     // W_lin / b_lin gradients are final from here on
+    {
+        const size_t smem = 2 * (size_t)(2 * 16 * 16 * kBlk) + 2 * g.dp_slot + 256;
+        PN_SET_SMEM(h, lin_dgrad_tc_kernel, smem);
+        const int items = h->P * g.nbc * KT;
+        const int grid = items < h->num_sms ? items : h->num_sms;
+        PnProfScope prof(h, PN_PROF_LIN_DGRAD, st);
+        lin_dgrad_tc_kernel<<<grid, 192, smem, st>>>(wp, dp, g, h->d_masks, h->P, B, KT, h->dact[nd.nconv - 1]);
+    }
+    PN_LAUNCH_CHECK(h, "lin_dgrad_tc_kernel");
     return PN_OK;
 }

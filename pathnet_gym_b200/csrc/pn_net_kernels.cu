@@ -841,7 +841,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         }
         PN_LAUNCH_CHECK(h, "lin_wgrad_kernel");
     }
-    PN_CUDA(h, cudaEventRecord(h->ev_lin_grads, st));     // W_lin / b_lin gradients are final from here on
+    if (!h->tc_lin) PN_CUDA(h, cudaEventRecord(h->ev_lin_grads, st));     // (the tensor-core launcher records it itself)
     // conv layers, last to first
     const int nch_simt = std::min(h->nch, std::max(1, (296 + P - 1) / P));
     const int cs = (B + nch_simt - 1) / nch_simt;
