@@ -125,10 +125,18 @@ lin_prep_kernel(const float* __restrict__ params, PnNetDesc nd, LinGeom g, uint8
 // ---- forward GEMM ----------------------------------------------------------------------------------------------------
 // item = (path, batch chunk, half h of the hidden units); D[c = h*128 + lane, b] per active slot in TMEM columns
 // slot*32.  Warps 0-3 epilogue, warp 4 bulk-copy producer, warp 5 MMA issue (warp-uniform code).
+__device__ __forceinline__ long long lin_clock() {      // clock read that stays where it is written (debug brackets)
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory");
+    return t;
+}
+
 __global__ void __launch_bounds__(192, 1)
 lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp, const float* __restrict__ params,
                   PnNetDesc nd, LinGeom g, const uint32_t* __restrict__ masks, int P, int B, float* __restrict__ Hout,
-                  uint8_t* __restrict__ Rl) {
+                  uint8_t* __restrict__ Rl, long long* __restrict__ dbg) {
+    const bool dbg9 = dbg && dbg[148 * 8] == 9;              // PN_TC_DEBUG=9: where the forward GEMM's roles wait
+    const long long t_entry = dbg9 ? lin_clock() : 0;
     extern __shared__ __align__(1024) uint8_t smem[];
     const int w_stage_bytes = 2 * kWChunkKb * 16 * kBlk;             // hi + lo, 8 k-blocks x 16 c-blocks
     uint8_t* w_s = smem;
@@ -138,8 +146,9 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
     uint64_t* w_empty = bars + kWStages;      // [kWStages]
     uint64_t* x_full = bars + 2 * kWStages;
     uint64_t* x_empty = x_full + 1;
-    uint64_t* acc_full = x_full + 2;
+    uint64_t* acc_full = x_full + 2;          // (kept for the no-module case)
     uint64_t* acc_empty = x_full + 3;
+    uint64_t* slot_full = x_full + 4;         // [16] (M <= 16 here): slot s of the item is complete -> its epilogue runs under slot s+1's MMAs
     __shared__ uint32_t tmem_base_s;
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int nitems = P * g.nbc * 2;
@@ -149,6 +158,7 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
     if (threadIdx.x == 0) {
         for (int i = 0; i < kWStages; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); }
         mbar_init(x_full, 1); mbar_init(x_empty, 1); mbar_init(acc_full, 1); mbar_init(acc_empty, 128);
+        for (int i = 0; i < 16; ++i) mbar_init(&slot_full[i], 1);
         fence_mbar_init();
     }
     if (warp == 5) tmem_alloc(&tmem_base_s, 512);
@@ -194,18 +204,23 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
         // ================= MMA issue (whole warp, uniform values, elected instructions) =================
         int stage = 0;
         uint32_t wphase = 0, it = 0;
+        long long d_wx = 0, d_ww = 0;
         const uint32_t idesc = make_idesc_f16(128, kNB, 1, 1, 1, 0);      // bf16 x bf16, A MN-major, B K-major
         const uint32_t xs = smem_u32(x_s);
         for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
             const int p = (item >> 1) / g.nbc;
             const int ns = __popc(__reduce_or_sync(0xffffffffu, masks[p * g.L + g.L - 1]));
             mbar_wait(acc_empty, (it & 1) ^ 1);
+            const long long cx = dbg9 ? lin_clock() : 0;
             mbar_wait(x_full, it & 1);
+            if (dbg9) d_wx += lin_clock() - cx;
             tc_fence_after();
             for (int slot = 0; slot < ns; ++slot) {
                 const uint32_t dcol = td + slot * kNB;
                 for (int c = 0; c < nchunk; ++c) {
+                    const long long cw = dbg9 ? lin_clock() : 0;
                     mbar_wait(&w_full[stage], wphase);
+                    if (dbg9) d_ww += lin_clock() - cw;
                     tc_fence_after();
                     const uint32_t ws = smem_u32(w_s + (size_t)stage * w_stage_bytes);
 #pragma unroll
@@ -227,12 +242,17 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
                     __syncwarp();
                     if (++stage == kWStages) { stage = 0; wphase ^= 1; }
                 }
+                if (elect_one()) umma_commit(&slot_full[slot]);
+                __syncwarp();
             }
             if (elect_one()) {
-                if (ns > 0) { umma_commit(x_empty); umma_commit(acc_full); }
-                else { mbar_arrive(x_empty); mbar_arrive(acc_full); }
+                if (ns > 0) umma_commit(x_empty);
+                else mbar_arrive(x_empty);
             }
             __syncwarp();
+        }
+        if (dbg9 && lane == 0) {
+            dbg[blockIdx.x * 8 + 0] = d_wx; dbg[blockIdx.x * 8 + 1] = d_ww; dbg[blockIdx.x * 8 + 2] = lin_clock() - t_entry;
         }
     } else {
         // ================= epilogue: thread = hidden unit c, registers = the 32 batch rows =================
@@ -246,9 +266,11 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
             float sum[kNB];
 #pragma unroll
             for (int b = 0; b < kNB; ++b) sum[b] = 0.f;
-            mbar_wait(acc_full, it & 1);
-            tc_fence_after();
             for (int slot = 0; slot < ns; ++slot) {
+                const long long ce = dbg9 ? lin_clock() : 0;
+                mbar_wait(&slot_full[slot], it & 1);
+                if (dbg9 && threadIdx.x == 0 && slot == ns - 1) { dbg[blockIdx.x * 8 + 3] = lin_clock() - ce; dbg[blockIdx.x * 8 + 4] = lin_clock() - t_entry; }
+                tc_fence_after();
                 const int j = __fns(mask, 0, slot + 1);
                 const float bias = params[nd.linW_base + (long long)j * nd.lin_stride + nd.linb_off + c];
                 uint32_t d[kNB];
@@ -271,8 +293,9 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
 #pragma unroll
             for (int b = 0; b < kNB; ++b) {
                 const int bg = bc * kNB + b;
-                if (bg < B) Hout[((size_t)p * B + bg) * g.Hd + c] = sum[b] / Mf;   // net / FLAGS.M (game_ac_network.py:194)
+                if (bg < B) Hout[((size_t)p * B + bg) * g.Hd + c] = __fdividef(sum[b], Mf);   // net / FLAGS.M (game_ac_network.py:194)
             }
+            if (dbg9 && threadIdx.x == 0) dbg[blockIdx.x * 8 + 5] = lin_clock() - t_entry;
         }
     }
     tc_fence_before();
@@ -686,7 +709,7 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     const int grid = items < h->num_sms ? items : h->num_sms;
     {
         PnProfScope prof(h, PN_PROF_LIN_FWD, st);
-        lin_fwd_tc_kernel<<<grid, 192, smem, st>>>(wp, xp, h->params, nd, g, h->d_masks, h->P, B, h->hbuf, h->lmask);
+        lin_fwd_tc_kernel<<<grid, 192, smem, st>>>(wp, xp, h->params, nd, g, h->d_masks, h->P, B, h->hbuf, h->lmask, h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "lin_fwd_tc_kernel");
     return PN_OK;
