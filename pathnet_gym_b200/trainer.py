@@ -27,7 +27,7 @@ class OverlappedGradSum(object):
         import os
         import torch
         import torch.distributed as dist
-        if os.environ.get("PN_PEER_SUM", "0") != "1":     # opt-in until it has run on this node type (the kernel spins on peers)
+        if os.environ.get("PN_PEER_SUM", "1") == "0":     # PN_PEER_SUM=0: keep the grouped NCCL all-reduce
             return
         ok = torch.zeros(1, device=self.pop.device)
         try:
