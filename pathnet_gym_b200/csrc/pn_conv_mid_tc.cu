@@ -44,6 +44,7 @@ struct MidTcGeom {
     int chunk_bytes;      // xrows * 16
     int hl_bytes;         // 4 chunks
     int stage_bytes;      // hi + lo
+    uint32_t rcp_RB, rcp_Xp;   // ceil(2^32 / d): m / d == __umulhi(m, rcp) for every m with m * d < 2^32 (raster rows here < 2^24)
 };
 
 bool make_mid_tc_geom(const PnNetDesc& nd, int l, MidTcGeom& g) {
@@ -56,7 +57,18 @@ bool make_mid_tc_geom(const PnNetDesc& nd, int l, MidTcGeom& g) {
     g.chunk_bytes = g.xrows * 16;
     g.hl_bytes = 4 * g.chunk_bytes;
     g.stage_bytes = 2 * g.hl_bytes;
+    g.rcp_RB = (uint32_t)(((1ull << 32) + g.RB - 1) / g.RB);
+    g.rcp_Xp = (uint32_t)(((1ull << 32) + g.Xp - 1) / g.Xp);
     return true;
+}
+
+// raster row -> (transition b, block row Y, block column X) without integer division (two multiply-high instead of ~40
+// instructions: these decompositions were a fifth of the kernels' issued instructions)
+__device__ __forceinline__ void raster_split(int R, const MidTcGeom& g, int& b, int& Y, int& X) {
+    b = (int)__umulhi((uint32_t)R, g.rcp_RB);
+    const int rem = R - b * g.RB;
+    Y = (int)__umulhi((uint32_t)rem, g.rcp_Xp);
+    X = rem - Y * g.Xp;
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
@@ -152,7 +164,8 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                 pyy[u] = py;
                 const int Rr = tile * kTileM + r;
                 if (rr[u] >= 0 && Rr < NR) {
-                    const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+                    int b, Yb, Xb;
+            raster_split(Rr, g, b, Yb, Xb);
                     const float4* src = reinterpret_cast<const float4*>(
                         X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
 #pragma unroll
@@ -255,7 +268,8 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
             const uint32_t mask = masks[p * nd.L + l];
             const int ns = __popc(mask);
             const int Rr = tile * kTileM + warp * 32 + lane;
-            const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+            int b, Yb, Xb;
+            raster_split(Rr, g, b, Yb, Xb);
             const bool valid = Rr < NR && Yb < g.OH && Xb < g.OW;
             const size_t t = (size_t)p * B + b;
             const int pix = Yb * g.OW + Xb;
@@ -363,8 +377,8 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
             bool valid = r < g.xrows && m >= 0 && m < NR;
             int b = 0, pix = 0;
             if (valid) {
-                b = m / g.RB;
-                const int rem = m - b * g.RB, oy = rem / g.Xp, ox = rem - oy * g.Xp;
+                int oy, ox;
+                raster_split(m, g, b, oy, ox);
                 valid = oy < g.OH && ox < g.OW;
                 pix = oy * g.OW + ox;
             }
@@ -480,7 +494,8 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
             const int p = gt / ntile, tile = gt - p * ntile;
             const int ns = __popc(masks[p * nd.L + l]);
             const int Rr = tile * kTileM + warp * 32 + lane;
-            const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+            int b, Yb, Xb;
+            raster_split(Rr, g, b, Yb, Xb);
             const bool valid = Rr < NR;
             const int as = it & 1;
             mbar_wait(&acc_full[as], (it >> 1) & 1);
@@ -585,8 +600,8 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
             bool valid = m < NR;
             int b = 0, pix = 0;
             if (valid) {
-                b = m / g.RB;
-                const int rem = m - b * g.RB, oy = rem / g.Xp, ox = rem - oy * g.Xp;
+                int oy, ox;
+                raster_split(m, g, b, oy, ox);
                 valid = oy < g.OH && ox < g.OW;
                 pix = oy * g.OW + ox;
             }
@@ -678,7 +693,8 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
                 pyy[u] = py;
                 const int Rr = tile * kTileM + r;
                 if (rr[u] >= 0 && Rr < NR) {
-                    const int b = Rr / g.RB, rem = Rr - b * g.RB, Yb = rem / g.Xp, Xb = rem - Yb * g.Xp;
+                    int b, Yb, Xb;
+            raster_split(Rr, g, b, Yb, Xb);
                     const float4* src = reinterpret_cast<const float4*>(
                         X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
 #pragma unroll
