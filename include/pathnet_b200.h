@@ -191,6 +191,16 @@ PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
 PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h);
 PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, void* stream);
 
+/* All-reduce of the linear modules' gradient region (pn_lin_grads_region) in place over NVLink peer memory, for hosts
+ * whose GRADIENT SLABS are themselves symmetric memory (peer_slabs_host[r] = rank r's slab base in this process,
+ * peer_slabs_host[rank] must be the slab bound with pn_bind_slabs; peer_bufs_host = the exchange buffers of
+ * pn_peer_sum_small, whose control words carry the flags).  Rank r adds shard r of all slabs in rank order and writes the
+ * sum into shard r of every slab, between a "gradients ready" and a "sums written" barrier; bit-identical results on all
+ * ranks.  Enqueue it where the gradients are final (after pn_stream_wait_lin_grads); step = 0, 1, 2, ... per set of
+ * exchange buffers.  No counterpart in the reference. */
+PN_API int pn_peer_allreduce_lin(pn_handle* h, const uint64_t* peer_slabs_host, const uint64_t* peer_bufs_host, int rank,
+                          int world, uint32_t step, void* stream);
+
 /* Replaces RMSPropApplier.apply_gradients for the non-frozen tensors
  * (rmsprop_applier.py:79-106): per tensor g' = clip_by_norm(g, clip_norm);
  * ms += (g'^2 - ms)(1-decay); mom = momentum*mom + lr*g'/sqrt(ms+eps);

@@ -58,6 +58,7 @@ SIGNATURES = {
     "pn_stream_wait_lin_grads": (_i, [_vp, _vp]),
     "pn_peer_buffer_bytes": (C.c_int64, [_vp]),
     "pn_peer_sum_small": (_i, [_vp, _vp, _i, _i, C.c_uint32, _vp]),
+    "pn_peer_allreduce_lin": (_i, [_vp, _vp, _vp, _i, _i, C.c_uint32, _vp]),
     "pn_profile_enable": (_i, [_vp, _i]),
     "pn_profile_read": (_i, [_vp, C.POINTER(PnProfileEntry), _i]),
     "pn_bind_slabs": (_i, [_vp, _vp, _vp, _vp, _vp]),

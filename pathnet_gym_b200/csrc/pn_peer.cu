@@ -7,7 +7,9 @@
 // (symmetric memory: the same allocation mapped into every process of the node), raises a flag on every peer, waits
 // for the peers' flags, and adds up all copies itself in rank order -- one launch, and bit-identical on every rank.
 //
-//   exchange buffer of a rank: [64 x u32: flags[0..31], CTA counter at word 32][slot 0: n floats][slot 1: n floats]
+//   exchange buffer of a rank: [256 x u32 control words][slot 0: n floats][slot 1: n floats]
+//   control words: [0..31] flags of the small-region sum, [32] its CTA counter;
+//                  [64..95] / [96..127] "gradients ready" / "sums written" flags of the linear-region all-reduce, [128] its CTA counter
 //   flags[r] = number of steps rank r has published (monotonic).  Step s uses slot s & 1: a rank publishes step s + 1 only
 //   after it has finished reading every peer's step-s slot, and nobody can overwrite slot s & 1 (step s + 2) before all
 //   ranks have published s + 1, so two slots are enough.
@@ -18,7 +20,7 @@
 
 namespace {
 
-constexpr int kPeerFlagWords = 64;
+constexpr int kPeerFlagWords = 256;    // control words in front of the data slots (see the layout above)
 constexpr int kPeerMaxWorld = 16;
 
 struct PeerPtrs {
@@ -79,7 +81,85 @@ peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long li
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// All-reduce of the linear modules' gradient region (97 % of the slab) in place, over peer memory.  The gradient slabs
+// themselves are symmetric memory here, so nothing is staged:
+//   1. rank r tells every peer "my linear gradients are final" (stream order guarantees it at kernel start)
+//   2. waits for all peers, then owns shard r of the region: reads shard r of every rank's slab over NVLink, adds the
+//      copies in rank order and writes the sum into shard r of EVERY rank's slab (reduce-scatter and all-gather in one pass)
+//   3. tells every peer "my shard is written everywhere" and waits for all peers before the kernel ends, so the update
+//      kernel that follows in the stream reads complete sums and nobody overwrites a slab a peer still reads.
+// Only rank r reads or writes shard r between the two barriers, so there is no write/read overlap; the sums are
+// bit-identical on all ranks.  The CTAs spin: the grid is kept far below one CTA per SM.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+peer_allreduce_lin_kernel(PeerPtrs slabs, PeerPtrs ctrl, long long lin_off, long long lin_cnt, int rank, int world, unsigned step) {
+    unsigned* my_ctrl = reinterpret_cast<unsigned*>(ctrl.buf[rank]);
+    // 1. gradients ready
+    if (blockIdx.x == 0 && threadIdx.x < world) {
+        __threadfence_system();
+        st_release_sys(reinterpret_cast<unsigned*>(ctrl.buf[threadIdx.x]) + 64 + rank, step + 1u);
+    }
+    if (threadIdx.x < world) {
+        const unsigned* f = my_ctrl + 64 + threadIdx.x;
+        while ((int)(ld_acquire_sys(f) - (step + 1u)) < 0) { }
+    }
+    __syncthreads();
+    // 2. my shard: float4 granularity
+    const long long n4 = lin_cnt >> 2;
+    const long long lo4 = n4 * rank / world, hi4 = n4 * (rank + 1) / world;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (long long)gridDim.x * blockDim.x;
+    for (long long e = lo4 + tid; e < hi4; e += nthreads) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < world; ++r) {
+            const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(slabs.buf[r]) + lin_off) + e;
+            float4 v;
+            asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src) : "memory");
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        for (int r = 0; r < world; ++r)
+            *(reinterpret_cast<float4*>(reinterpret_cast<float*>(slabs.buf[r]) + lin_off) + e) = s;
+    }
+    if (rank == world - 1 && blockIdx.x == 0)             // tail that is not a multiple of 4 floats (never with 32-float aligned tensors)
+        for (long long e = (n4 << 2) + threadIdx.x; e < lin_cnt; e += blockDim.x) {
+            float s = 0.f;
+            for (int r = 0; r < world; ++r) s += ld_peer(reinterpret_cast<const float*>(slabs.buf[r]) + lin_off + e);
+            for (int r = 0; r < world; ++r) (reinterpret_cast<float*>(slabs.buf[r]) + lin_off)[e] = s;
+        }
+    // 3. sums written everywhere
+    __threadfence_system();
+    __syncthreads();
+    __shared__ unsigned last;
+    if (threadIdx.x == 0) last = atomicAdd(my_ctrl + 128, 1u) == step * gridDim.x + gridDim.x - 1 ? 1u : 0u;
+    __syncthreads();
+    if (last) __threadfence_system();
+    if (last && threadIdx.x < world) st_release_sys(reinterpret_cast<unsigned*>(ctrl.buf[threadIdx.x]) + 96 + rank, step + 1u);
+    if (threadIdx.x < world) {
+        const unsigned* f = my_ctrl + 96 + threadIdx.x;
+        while ((int)(ld_acquire_sys(f) - (step + 1u)) < 0) { }
+    }
+    __syncthreads();
+}
+
 }  // namespace
+
+extern "C" PN_API int pn_peer_allreduce_lin(pn_handle* h, const uint64_t* peer_slabs_host, const uint64_t* peer_bufs_host, int rank,
+                                            int world, uint32_t step, void* stream) {
+    if (!h || !peer_slabs_host || !peer_bufs_host) return pn_fail_global(PN_ERR_INVALID, "pn_peer_allreduce_lin: null argument");
+    if (world < 1 || world > kPeerMaxWorld || rank < 0 || rank >= world)
+        return pn_fail(h, PN_ERR_INVALID, "pn_peer_allreduce_lin: rank %d of %d (at most %d ranks)", rank, world, kPeerMaxWorld);
+    if (!h->grads) return pn_fail(h, PN_ERR_STATE, "gradient slab not bound");
+    if ((uint64_t)(uintptr_t)h->grads != peer_slabs_host[rank])
+        return pn_fail(h, PN_ERR_STATE, "pn_peer_allreduce_lin: peer_slabs[rank] is not the bound gradient slab");
+    const long long lin_off = h->nd.linW_base, lin_cnt = h->nd.fc2W - h->nd.linW_base;
+    if (lin_off & 3) return pn_fail(h, PN_ERR_STATE, "linear region not 16-byte aligned");
+    PeerPtrs ps, pc;
+    for (int r = 0; r < kPeerMaxWorld; ++r) { ps.buf[r] = r < world ? peer_slabs_host[r] : 0; pc.buf[r] = r < world ? peer_bufs_host[r] : 0; }
+    const int grid = std::max(1, std::min(h->num_sms / 4, (int)((lin_cnt / world + 4095) / 4096)));
+    peer_allreduce_lin_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(ps, pc, lin_off, lin_cnt, rank, world, step);
+    PN_LAUNCH_CHECK(h, "peer_allreduce_lin_kernel");
+    return PN_OK;
+}
 
 extern "C" PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h) {
     if (!h) return -1;

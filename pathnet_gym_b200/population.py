@@ -252,6 +252,19 @@ class PathNetPopulation:
         arr = (C.c_uint64 * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
         nat.check(self.lib.pn_peer_sum_small(self._h, arr, int(rank), int(world), int(step), self._stream()), self._h)
 
+    def peer_allreduce_lin(self, peer_slabs, peer_ptrs, rank, world, step):
+        """Linear-module gradient region <- sum over the node's GPUs, in place through peer memory (pn_peer_allreduce_lin)."""
+        import ctypes as C
+        a = (C.c_uint64 * len(peer_slabs))(*[int(p) for p in peer_slabs])
+        b = (C.c_uint64 * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
+        nat.check(self.lib.pn_peer_allreduce_lin(self._h, a, b, int(rank), int(world), int(step), self._stream()), self._h)
+
+    def rebind_grads(self, grads: torch.Tensor):
+        """Use `grads` (fp32, slab_floats, same device; e.g. symmetric memory) as the gradient slab from now on."""
+        assert grads.is_cuda and grads.dtype == torch.float32 and grads.numel() == self.slab_floats and grads.is_contiguous()
+        nat.check(self.lib.pn_bind_slabs(self._h, _ptr(self.params), _ptr(self.ms), _ptr(self.mom), _ptr(grads)), self._h)
+        self.grads = grads
+
     def stream_wait_lin_grads(self, stream: "torch.cuda.Stream"):
         """`stream` waits until the latest train_step has written the W_lin/b_lin gradients."""
         import ctypes as C

@@ -18,7 +18,9 @@ class OverlappedGradSum(object):
         self.lin, self.head, self.conv = g[off:off + cnt], g[off + cnt:], g[:off]
         self.comm = torch.cuda.Stream(device=pop.device)
         self.peer = None
+        self.peer_slabs = None
         self.step = 0
+        self.lin_step = 0
         if self.active:
             self._setup_peer_exchange()
 
@@ -37,19 +39,36 @@ class OverlappedGradSum(object):
             self._peer_buf.zero_()
             self._peer_hdl = symm.rendezvous(self._peer_buf, dist.group.WORLD)
             self.peer = [int(p) for p in self._peer_hdl.buffer_ptrs]
+            if os.environ.get("PN_PEER_LIN", "0") == "1":
+                # the gradient slab itself becomes symmetric memory: the linear region is then all-reduced in place
+                # by pn_peer_allreduce_lin instead of NCCL
+                g = symm.empty(self.pop.slab_floats, dtype=torch.float32, device=self.pop.device)
+                g.copy_(self.pop.grads)
+                self._slab_hdl = symm.rendezvous(g, dist.group.WORLD)
+                self.peer_slabs = [int(p) for p in self._slab_hdl.buffer_ptrs]
+                self.pop.rebind_grads(g)
+                off, cnt = self.pop.lin_grads_region()
+                self.lin, self.head, self.conv = g[off:off + cnt], g[off + cnt:], g[:off]
             ok.fill_(1)
         except Exception as e:      # noqa: BLE001  (old torch, no P2P, restricted container, ...)
             self.peer = None
+            self.peer_slabs = None
             self.peer_error = repr(e)
         torch.cuda.synchronize(self.pop.device)
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)       # all ranks take the same path; also orders the zero-fill
         if float(ok.item()) < 1:
             self.peer = None
+            self.peer_slabs = None
 
     def sum_lin(self):
         """On the side stream (already waiting for the linear gradients): all-reduce them."""
         import os
         if self.active and "lin" not in os.environ.get("PN_DEBUG_SKIP_SUM", ""):     # (timing experiments only)
+            if self.peer is not None and self.peer_slabs is not None:
+                rank, world = parallel.world()
+                self.pop.peer_allreduce_lin(self.peer_slabs, self.peer, rank, world, self.lin_step)
+                self.lin_step += 1
+                return
             import torch.distributed as dist
             dist.all_reduce(self.lin, op=dist.ReduceOp.SUM)
 

@@ -550,7 +550,7 @@ def test_peer_sum_small_single_rank(eng_mod):
         pop.peer_sum_small([buf.data_ptr()], 0, 1, step)
         torch.cuda.synchronize()
         assert torch.equal(pop.grads, g0)
-        slot = buf[64 + (step & 1) * (pop.slab_floats - cnt):][:pop.slab_floats - cnt]
+        slot = buf[256 + (step & 1) * (pop.slab_floats - cnt):][:pop.slab_floats - cnt]
         assert torch.equal(slot[:off], g0[:off]) and torch.equal(slot[off:], g0[off + cnt:])
     flags = buf[:64].view(torch.int32)
     assert int(flags[0]) == 5

@@ -42,6 +42,7 @@ def main():
     if rank == 0:
         print(json.dumps({"world": world, "overlapped_vs_plain_allreduce_rel_err": worst,
                           "small_regions_via_peer_memory": gs.peer is not None,
+                          "linear_region_via_peer_memory": gs.peer_slabs is not None,
                           "peer_setup_error": getattr(gs, "peer_error", None)}))
     assert worst < 1e-6, worst
     pop.close()
