@@ -109,16 +109,34 @@ peer_allreduce_lin_kernel(PeerPtrs slabs, PeerPtrs ctrl, long long lin_off, long
     const long long n4 = lin_cnt >> 2;
     const long long lo4 = n4 * rank / world, hi4 = n4 * (rank + 1) / world;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (long long)gridDim.x * blockDim.x;
-    for (long long e = lo4 + tid; e < hi4; e += nthreads) {
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    // four float4 per thread and rank in flight (NVLink latency ~2 us: the loop is all about bytes in flight)
+    constexpr int kU = 4;
+    for (long long e0 = lo4 + tid; e0 < hi4; e0 += nthreads * kU) {
+        float4 s[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u) s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int r = 0; r < world; ++r) {
-            const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(slabs.buf[r]) + lin_off) + e;
-            float4 v;
-            asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src) : "memory");
-            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            const float4* base = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(slabs.buf[r]) + lin_off);
+            float4 v[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const long long e = e0 + u * nthreads;
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (e < hi4)
+                    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(base + e) : "memory");
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) { s[u].x += v[u].x; s[u].y += v[u].y; s[u].z += v[u].z; s[u].w += v[u].w; }
         }
-        for (int r = 0; r < world; ++r)
-            *(reinterpret_cast<float4*>(reinterpret_cast<float*>(slabs.buf[r]) + lin_off) + e) = s;
+        for (int r = 0; r < world; ++r) {
+            float4* base = reinterpret_cast<float4*>(reinterpret_cast<float*>(slabs.buf[r]) + lin_off);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const long long e = e0 + u * nthreads;
+                if (e < hi4) base[e] = s[u];
+            }
+        }
     }
     if (rank == world - 1 && blockIdx.x == 0)             // tail that is not a multiple of 4 floats (never with 32-float aligned tensors)
         for (long long e = (n4 << 2) + threadIdx.x; e < lin_cnt; e += blockDim.x) {
