@@ -37,6 +37,7 @@ constexpr int kFwdThreads = 320;      // warps 0-3 epilogue, 4-8 operand convert
 constexpr int kConvWarps = 5;
 constexpr int kConvThreads = kConvWarps * 32;
 constexpr int kModBytes = 2048;       // one module's bf16 weights (hi or lo): 128 k x 8 co x 2 bytes
+constexpr bool kEnableS1 = true;      // 3x3 / stride-1 layers: forward on the tensor cores (backward stays on pn_conv_mid.cu)
 
 struct MidTcGeom {
     int IH, IW, Yp, Xp, RB, OH, OW, npix, npix_in;
@@ -45,18 +46,55 @@ struct MidTcGeom {
     int hl_bytes;         // 4 chunks
     int stage_bytes;      // hi + lo
     uint32_t rcp_RB, rcp_Xp;   // ceil(2^32 / d): m / d == __umulhi(m, rcp) for every m with m * d < 2^32 (raster rows here < 2^24)
+    // forward K steps (16 bf16 = two 16-byte chunks each): A start offset inside a stage, distance between the two
+    // chunks (the descriptor's LBO), offset of the weight block pair inside a module's operand block
+    int s1;               // 1: the 3x3 / stride-1 variant (block = pixel, one chunk per raster row, Xp = IW, Yp = IH)
+    int nk, max_shift;
+    int a_off[8], a_lbo[8], b_off[8];
 };
 
 bool make_mid_tc_geom(const PnNetDesc& nd, int l, MidTcGeom& g) {
     if (l < 1 || l >= nd.nconv) return false;
-    if (nd.Cin[l] != 8 || nd.k[l] != 4 || nd.s[l] != 2 || (nd.IH[l] & 1) || (nd.IW[l] & 1)) return false;
-    g.IH = nd.IH[l]; g.IW = nd.IW[l]; g.Yp = g.IH / 2; g.Xp = g.IW / 2; g.RB = g.Yp * g.Xp;
+    if (nd.Cin[l] != 8) return false;
+    g.IH = nd.IH[l]; g.IW = nd.IW[l];
     g.OH = nd.OH[l]; g.OW = nd.OW[l]; g.npix = g.OH * g.OW; g.npix_in = g.IH * g.IW;
+    if (nd.k[l] == 3 && nd.s[l] == 1 && kEnableS1) {
+        // 3x3 / stride 1: the raster is the image itself; taps t = kh*3 + kw shift by kh*IW + kw rows.  A K step pairs
+        // taps (2i, 2i+1): chunk 0 = rows at shift(2i), chunk 1 = the SAME chunk at shift(2i+1), i.e. the descriptor's
+        // LBO is the difference of the two shifts; the ninth tap is paired with a zero weight block.
+        g.s1 = 1; g.Yp = g.IH; g.Xp = g.IW; g.RB = g.IH * g.IW;
+        if (g.OH != g.IH - 2 || g.OW != g.IW - 2 || g.IW < 3) return false;
+        g.max_shift = 2 * g.IW + 2;
+        g.xrows = (kTileM + g.max_shift + 7) & ~7;
+        if (g.xrows > kConvThreads) return false;             // one converter thread per staged row
+        g.chunk_bytes = g.xrows * 16;
+        g.hl_bytes = g.chunk_bytes;
+        g.stage_bytes = 2 * g.hl_bytes;
+        g.nk = 5;
+        for (int i = 0; i < 5; ++i) {
+            const int t0 = 2 * i, t1 = 2 * i + 1;
+            const int s0 = (t0 / 3) * g.IW + t0 % 3, sh1 = t1 < 9 ? (t1 / 3) * g.IW + t1 % 3 : s0 + 1;
+            g.a_off[i] = s0 * 16; g.a_lbo[i] = (sh1 - s0) * 16; g.b_off[i] = t0 * 128;
+        }
+        g.rcp_RB = (uint32_t)(((1ull << 32) + g.RB - 1) / g.RB);
+        g.rcp_Xp = (uint32_t)(((1ull << 32) + g.Xp - 1) / g.Xp);
+        return true;
+    }
+    if (nd.k[l] != 4 || nd.s[l] != 2 || (nd.IH[l] & 1) || (nd.IW[l] & 1)) return false;
+    g.s1 = 0; g.Yp = g.IH / 2; g.Xp = g.IW / 2; g.RB = g.Yp * g.Xp;
     if (g.OH != g.Yp - 1 || g.OW != g.Xp - 1 || g.Xp > 62) return false;
+    g.max_shift = g.Xp + 1;
     g.xrows = (kTileM + g.Xp + 1 + 7) & ~7;
     g.chunk_bytes = g.xrows * 16;
     g.hl_bytes = 4 * g.chunk_bytes;
     g.stage_bytes = 2 * g.hl_bytes;
+    g.nk = 8;
+    for (int i = 0; i < 8; ++i) {
+        const int tap = i >> 1, kk = i & 1;
+        g.a_off[i] = 2 * kk * g.chunk_bytes + ((tap >> 1) * g.Xp + (tap & 1)) * 16;
+        g.a_lbo[i] = g.chunk_bytes;
+        g.b_off[i] = (tap * 4 + 2 * kk) * 128;
+    }
     g.rcp_RB = (uint32_t)(((1ull << 32) + g.RB - 1) / g.RB);
     g.rcp_Xp = (uint32_t)(((1ull << 32) + g.Xp - 1) / g.Xp);
     return true;
@@ -91,10 +129,24 @@ __device__ __forceinline__ void split8(const float4& a, const float4& b, uint4& 
 // wd [M][hl][kc 16][ci 8][co 8]   data-gradient B operand (K-major over co)
 // with (kh, kw) = (2 dy + py, 2 dx + px), tap = dy * 2 + dx; source W[(kh * 4 + kw) * 8 + ci][co].
 __global__ void __launch_bounds__(256)
-conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, uint8_t* __restrict__ wf, uint8_t* __restrict__ wd) {
+conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, int s1, uint8_t* __restrict__ wf,
+                      uint8_t* __restrict__ wd) {
     const int j = blockIdx.x;
     const float* W = params + nd.convW_base[l] + (long long)j * nd.conv_stride[l];
     const int t = threadIdx.x & 127, kc = t >> 3, e = t & 7;
+    if (s1) {
+        // 3x3 / stride 1: forward block kc = tap kh*3 + kw ([co][ci]), block 9 = zeros (partner of the ninth tap)
+        if (threadIdx.x >= 128 || kc > 9) return;
+        float v1[8];
+#pragma unroll
+        for (int ci = 0; ci < 8; ++ci) v1[ci] = kc < 9 ? W[(size_t)kc * 64 + ci * 8 + e] : 0.f;
+        uint4 h1, l1;
+        split8(make_float4(v1[0], v1[1], v1[2], v1[3]), make_float4(v1[4], v1[5], v1[6], v1[7]), h1, l1);
+        uint8_t* d1 = wf + (size_t)j * 2 * kModBytes + kc * 128 + e * 16;
+        *reinterpret_cast<uint4*>(d1) = h1;
+        *reinterpret_cast<uint4*>(d1 + kModBytes) = l1;
+        return;
+    }
     const int tap = kc >> 2, pq = kc & 3;
     const int kh = (tap >> 1) * 2 + (pq >> 1), kw = (tap & 1) * 2 + (pq & 1);
     const float* src = W + (size_t)(kh * 4 + kw) * 64;
@@ -154,6 +206,28 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
         int it = 0;
         for (int gt = g0; gt < g1; ++gt, ++it) {
             const int p = gt / ntile, tile = gt - p * ntile;
+            if (g.s1) {
+                // stride 1: one raster row = one pixel = one chunk, and the raster IS the NHWC tensor of the path
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+                const int Rr = tile * kTileM + cidx;
+                if (cidx < g.xrows && Rr < NR) {
+                    const float4* src = reinterpret_cast<const float4*>(X + ((size_t)p * NR + Rr) * 8);
+                    a = __ldg(src); c = __ldg(src + 1);
+                }
+                const int stage = it % kXStages;
+                mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
+                if (cidx < g.xrows) {
+                    uint4 hi, lo;
+                    split8(a, c, hi, lo);
+                    uint8_t* dst = x_s + (size_t)stage * g.stage_bytes + cidx * 16;
+                    *reinterpret_cast<uint4*>(dst) = hi;
+                    *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&x_full[stage]);
+                continue;
+            }
             float4 v[2][4];
             int rr[2], pyy[2];
 #pragma unroll
@@ -165,7 +239,7 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                 const int Rr = tile * kTileM + r;
                 if (rr[u] >= 0 && Rr < NR) {
                     int b, Yb, Xb;
-            raster_split(Rr, g, b, Yb, Xb);
+                    raster_split(Rr, g, b, Yb, Xb);
                     const float4* src = reinterpret_cast<const float4*>(
                         X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
 #pragma unroll
@@ -237,18 +311,16 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                 const uint32_t xs = smem_u32(x_s + (size_t)stage * g.stage_bytes);
                 const uint32_t dcol = td + as * acc_stride;
 #pragma unroll
-                for (int tap = 0; tap < 4; ++tap) {
-                    const uint32_t shift = (uint32_t)(((tap >> 1) * g.Xp + (tap & 1)) * 16);
-#pragma unroll
-                    for (int kk = 0; kk < 2; ++kk) {
-                        const uint32_t a_addr = xs + (uint32_t)(2 * kk) * g.chunk_bytes + shift;
-                        const uint32_t b_addr = ws + (uint32_t)((tap * 4 + 2 * kk) * 128);
-                        const uint64_t a_hi = make_smem_desc(a_addr, g.chunk_bytes, 128);
-                        const uint64_t a_lo = make_smem_desc(a_addr + g.hl_bytes, g.chunk_bytes, 128);
+                for (int i = 0; i < 8; ++i) {              // K steps of the layer's geometry (g.nk of them)
+                    if (i < g.nk) {
+                        const uint32_t a_addr = xs + (uint32_t)g.a_off[i];
+                        const uint32_t b_addr = ws + (uint32_t)g.b_off[i];
+                        const uint64_t a_hi = make_smem_desc(a_addr, (uint32_t)g.a_lbo[i], 128);
+                        const uint64_t a_lo = make_smem_desc(a_addr + g.hl_bytes, (uint32_t)g.a_lbo[i], 128);
                         const uint64_t b_hi = make_smem_desc(b_addr, 128, kModBytes);
                         const uint64_t b_lo = make_smem_desc(b_addr + w_hl, 128, kModBytes);
                         if (elect_one()) {
-                            umma_f16(dcol, a_hi, b_hi, idesc, (tap | kk) ? 1u : 0u);
+                            umma_f16(dcol, a_hi, b_hi, idesc, i ? 1u : 0u);
                             umma_f16(dcol, a_hi, b_lo, idesc, 1u);
                             umma_f16(dcol, a_lo, b_hi, idesc, 1u);
                         }
@@ -786,7 +858,9 @@ int pn_launch_conv_mid_wprep(pn_handle* h, int l, cudaStream_t st) {
     uint8_t* wd = wf + (size_t)nd.M * 2 * kModBytes;
     {
         PnProfScope prof(h, PN_PROF_CONV_MID_PREP, st);
-        conv_mid_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, l, wf, wd);
+        MidTcGeom g;
+        if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+        conv_mid_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, l, g.s1, wf, wd);
     }
     PN_LAUNCH_CHECK(h, "conv_mid_wprep_kernel");
     return PN_OK;
@@ -837,7 +911,12 @@ int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     return PN_OK;
 }
 
-bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) { return h->tc_mid[l] && h->max_active[l] <= 4; }
+// the backward kernels exist for the 4x4 / stride-2 geometry only (3x3 / stride-1 layers: forward here, backward on pn_conv_mid.cu)
+bool pn_conv_mid_tc_has_bwd(const pn_handle* h, int l) {
+    MidTcGeom g;
+    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g) && !g.s1;
+}
+bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) { return pn_conv_mid_tc_has_bwd(h, l) && h->max_active[l] <= 4; }
 
 int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used) {
     const PnNetDesc& nd = h->nd;

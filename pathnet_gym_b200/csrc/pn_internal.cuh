@@ -181,6 +181,7 @@ int pn_launch_conv_mid_wprep(pn_handle* h, int l, cudaStream_t st);
 int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st);
 int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st);
 bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l);
+bool pn_conv_mid_tc_has_bwd(const pn_handle* h, int l);
 int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used);
 // pn_conv_mid.cu
 bool pn_conv_mid_supported(const pn_handle* h, int l);

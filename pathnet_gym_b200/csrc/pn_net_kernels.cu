@@ -853,9 +853,10 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
             const bool wg_tc = pn_conv_mid_wgrad_tc_usable(h, l);
             if (wg_tc)
                 if (int rc = pn_launch_conv_mid_wgrad_tc(h, l, B, st, &nch_used)) return rc;
-            if (!wg_tc || !h->tc_mid[l])
-                if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, !wg_tc, !h->tc_mid[l])) return rc;
-            if (h->tc_mid[l])
+            const bool dg_tc = pn_conv_mid_tc_has_bwd(h, l);
+            if (!wg_tc || !dg_tc)
+                if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, !wg_tc, !dg_tc)) return rc;
+            if (dg_tc)
                 if (int rc = pn_launch_conv_mid_dgrad_tc(h, l, B, st)) return rc;
             add_job(l, nch_used);
             continue;
