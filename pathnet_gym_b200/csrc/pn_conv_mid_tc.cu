@@ -37,7 +37,7 @@ constexpr int kFwdThreads = 320;      // warps 0-3 epilogue, 4-8 operand convert
 constexpr int kConvWarps = 5;
 constexpr int kConvThreads = kConvWarps * 32;
 constexpr int kModBytes = 2048;       // one module's bf16 weights (hi or lo): 128 k x 8 co x 2 bytes
-constexpr bool kEnableS1 = true;      // 3x3 / stride-1 layers: forward on the tensor cores (backward stays on pn_conv_mid.cu)
+constexpr bool kEnableS1 = true;      // 3x3 / stride-1 layers: forward and data gradient on the tensor cores (weight gradient on pn_conv_mid.cu)
 
 struct MidTcGeom {
     int IH, IW, Yp, Xp, RB, OH, OW, npix, npix_in;
@@ -136,13 +136,15 @@ conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, int
     const int t = threadIdx.x & 127, kc = t >> 3, e = t & 7;
     if (s1) {
         // 3x3 / stride 1: forward block kc = tap kh*3 + kw ([co][ci]), block 9 = zeros (partner of the ninth tap)
-        if (threadIdx.x >= 128 || kc > 9) return;
+        // data-gradient block kc = tap ([ci][co], the tensor's own order), 9 blocks
+        const bool fwd = threadIdx.x < 128;
+        if (kc > (fwd ? 9 : 8)) return;
         float v1[8];
 #pragma unroll
-        for (int ci = 0; ci < 8; ++ci) v1[ci] = kc < 9 ? W[(size_t)kc * 64 + ci * 8 + e] : 0.f;
+        for (int q = 0; q < 8; ++q) v1[q] = kc < 9 ? (fwd ? W[(size_t)kc * 64 + q * 8 + e] : W[(size_t)kc * 64 + e * 8 + q]) : 0.f;
         uint4 h1, l1;
         split8(make_float4(v1[0], v1[1], v1[2], v1[3]), make_float4(v1[4], v1[5], v1[6], v1[7]), h1, l1);
-        uint8_t* d1 = wf + (size_t)j * 2 * kModBytes + kc * 128 + e * 16;
+        uint8_t* d1 = (fwd ? wf : wd) + (size_t)j * 2 * kModBytes + kc * 128 + e * 16;
         *reinterpret_cast<uint4*>(d1) = h1;
         *reinterpret_cast<uint4*>(d1 + kModBytes) = l1;
         return;
@@ -415,7 +417,7 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
     const long long NT = (long long)P * ntile;
     const int g0 = (int)(NT * blockIdx.x / gridDim.x), g1 = (int)(NT * (blockIdx.x + 1) / gridDim.x);
     const int NR = B * g.RB;
-    const int lead = g.Xp + 1;
+    const int lead = g.max_shift;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kXStages; ++i) { mbar_init(&x_full[i], kConvWarps); mbar_init(&x_empty[i], 1); }
@@ -492,7 +494,11 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
         uint32_t wphase = 0, fphase = 0;
         const uint32_t ws = smem_u32(w_s);
         const uint32_t w_hl = (uint32_t)w_slots * kModBytes;
-        const uint32_t idesc = make_idesc_f16(kTileM, 32, 1, 1, 0, 0);
+        // stride 2: N = 32 = one 2x2x8 block of the input raster, 4 taps of 4 weight blocks each;
+        // stride 1: N = 8 input channels (issued as N = 16 with SBO = 0: columns 8..15 repeat 0..7 and are ignored), 9 taps
+        const uint32_t idesc = make_idesc_f16(kTileM, g.s1 ? 16 : 32, 1, 1, 0, 0);
+        const int ntap = g.s1 ? 9 : 4;
+        const uint32_t b_tap = g.s1 ? 128u : 512u, b_sbo = g.s1 ? 0u : 128u;
         for (int gt = g0; gt < g1; ++gt, ++it) {
             const int p = gt / ntile;
             if (p != cur_p) {
@@ -535,16 +541,16 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
                 const uint32_t ds = smem_u32(d_s + (size_t)stage * 2 * d_hl);
                 const uint32_t dcol = td + as * 32;
                 const int nk = (ns + 1) >> 1;
-#pragma unroll
-                for (int tap = 0; tap < 4; ++tap) {
-                    const uint32_t shift = (uint32_t)((lead - ((tap >> 1) * g.Xp + (tap & 1))) * 16);
+                for (int tap = 0; tap < ntap; ++tap) {
+                    const int tshift = g.s1 ? (tap / 3) * g.Xp + tap % 3 : (tap >> 1) * g.Xp + (tap & 1);
+                    const uint32_t shift = (uint32_t)((lead - tshift) * 16);
                     for (int kk = 0; kk < nk; ++kk) {
                         const uint32_t a_addr = ds + (uint32_t)(2 * kk) * g.chunk_bytes + shift;
-                        const uint32_t b_addr = ws + (uint32_t)(tap * 512) + (uint32_t)(2 * kk) * kModBytes;
+                        const uint32_t b_addr = ws + (uint32_t)tap * b_tap + (uint32_t)(2 * kk) * kModBytes;
                         const uint64_t a_hi = make_smem_desc(a_addr, g.chunk_bytes, 128);
                         const uint64_t a_lo = make_smem_desc(a_addr + d_hl, g.chunk_bytes, 128);
-                        const uint64_t b_hi = make_smem_desc(b_addr, kModBytes, 128);
-                        const uint64_t b_lo = make_smem_desc(b_addr + w_hl, kModBytes, 128);
+                        const uint64_t b_hi = make_smem_desc(b_addr, kModBytes, b_sbo);
+                        const uint64_t b_lo = make_smem_desc(b_addr + w_hl, kModBytes, b_sbo);
                         if (elect_one()) {
                             umma_f16(dcol, a_hi, b_hi, idesc, (tap | kk) ? 1u : 0u);
                             umma_f16(dcol, a_hi, b_lo, idesc, 1u);
@@ -584,7 +590,17 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
             }
             tc_fence_before();
             mbar_arrive(&acc_empty[as]);
-            if (valid) {
+            if (valid && g.s1) {
+                // stride 1: columns 0..7 = the pixel's 8 input channels; the raster is the NHWC tensor itself
+                float4* o = reinterpret_cast<float4*>(dX + ((size_t)p * NR + Rr) * 8);
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const float4 v = make_float4(__uint_as_float(d[q * 4]), __uint_as_float(d[q * 4 + 1]),
+                                                 __uint_as_float(d[q * 4 + 2]), __uint_as_float(d[q * 4 + 3]));
+                    o[q] = v;
+                    amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+                }
+            } else if (valid) {
 #pragma unroll
                 for (int py = 0; py < 2; ++py) {
                     float4* o = reinterpret_cast<float4*>(
@@ -911,12 +927,16 @@ int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     return PN_OK;
 }
 
-// the backward kernels exist for the 4x4 / stride-2 geometry only (3x3 / stride-1 layers: forward here, backward on pn_conv_mid.cu)
+// data gradient on the tensor cores: both geometries
 bool pn_conv_mid_tc_has_bwd(const pn_handle* h, int l) {
     MidTcGeom g;
-    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g) && !g.s1;
+    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g);
 }
-bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) { return pn_conv_mid_tc_has_bwd(h, l) && h->max_active[l] <= 4; }
+// (the weight-gradient kernel exists for the 4x4 / stride-2 geometry only)
+bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) {
+    MidTcGeom g;
+    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g) && !g.s1 && h->max_active[l] <= 4;
+}
 
 int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used) {
     const PnNetDesc& nd = h->nd;

@@ -23,5 +23,11 @@ e0.record()
 for i in range(K): tr.step(frames[i & 1], actions, td, r, 1e-4)
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / K
+if os.environ.get("PN_KERNELS"):
+    pop.profile_enable(True)
+    for i in range(20): tr.step(frames[i & 1], actions, td, r, 1e-4)
+    torch.cuda.synchronize()
+    for n, (a, c) in sorted(pop.profile_read().items(), key=lambda kv: -kv[1][0] * kv[1][1]): print("%-22s %7.1f us x %d" % (n, a * 1e3, c // 20))
+    pop.profile_enable(False)
 print(json.dumps({"L": L, "M": M, "N": N, "P": P, "B": B, "A": A, "ms_per_step": round(ms, 4), "env_steps_per_s": round(P * B / ms * 1e3, 1)}))
 pop.close()
