@@ -37,7 +37,7 @@ constexpr int kFwdThreads = 320;      // warps 0-3 epilogue, 4-8 operand convert
 constexpr int kConvWarps = 5;
 constexpr int kConvThreads = kConvWarps * 32;
 constexpr int kModBytes = 2048;       // one module's bf16 weights (hi or lo): 128 k x 8 co x 2 bytes
-constexpr bool kEnableS1 = true;      // 3x3 / stride-1 layers: forward and data gradient on the tensor cores (weight gradient on pn_conv_mid.cu)
+constexpr bool kEnableS1 = true;      // 3x3 / stride-1 layers on the tensor cores too
 
 struct MidTcGeom {
     int IH, IW, Yp, Xp, RB, OH, OW, npix, npix_in;
@@ -749,21 +749,30 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
 #pragma unroll
             for (int c = 0; c < 8; ++c) bs[r * 33 + q * 8 + c] = bacc[q][c];
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int stride_part = 128 * 8 + 8;
+        const int KK = nd.KK[l];                               // 128 (4x4x8) or 72 (3x3x8)
+        const int stride_part = KK * 8 + 8;
         for (int slot = 0; slot < ns; ++slot) {
             float* out = part + ((size_t)(p * nch_alloc + ch) * nd.M + __fns(mask, 0, slot + 1)) * stride_part;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const int idx = i * 128 + r;                   // = ((kh * 4 + kw) * 8 + ci) * 8 + co
-                const int co = idx & 7, ci = (idx >> 3) & 7, khkw = idx >> 6, kh = khkw >> 2, kw = khkw & 3;
-                const int n = ((kh >> 1) * 2 + (kw >> 1)) * 32 + ((kh & 1) * 2 + (kw & 1)) * 8 + ci;
-                const int row = slot * 8 + co;
-                out[idx] = fs[row * kPitch + n] + fs[(32 + row) * kPitch + n];
+                const int idx = i * 128 + r;                   // = ((kh * k + kw) * 8 + ci) * 8 + co
+                if (idx < KK * 8) {
+                    const int co = idx & 7;
+                    int n;
+                    if (g.s1) {
+                        n = idx >> 3;                          // column kh * 24 + kw * 8 + ci == im2col row (kh * 3 + kw) * 8 + ci
+                    } else {
+                        const int ci = (idx >> 3) & 7, khkw = idx >> 6, kh = khkw >> 2, kw = khkw & 3;
+                        n = ((kh >> 1) * 2 + (kw >> 1)) * 32 + ((kh & 1) * 2 + (kw & 1)) * 8 + ci;
+                    }
+                    const int row = slot * 8 + co;
+                    out[idx] = fs[row * kPitch + n] + fs[(32 + row) * kPitch + n];
+                }
             }
             if (r < 8) {
                 float sacc = 0.f;
                 for (int k = 0; k < 128; ++k) sacc += bs[k * 33 + slot * 8 + r];
-                out[128 * 8 + r] = sacc;
+                out[KK * 8 + r] = sacc;
             }
         }
     } else if (warp < 4 + kConvWarps) {
@@ -771,6 +780,27 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
         const int cidx = threadIdx.x - 128;
         int it = 0;
         for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
+            if (g.s1) {                 // stride 1: one raster row = one pixel = one chunk (as in the forward kernel)
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+                const int Rr = tile * kTileM + cidx;
+                if (cidx < g.xrows && Rr < NR) {
+                    const float4* src = reinterpret_cast<const float4*>(X + ((size_t)p * NR + Rr) * 8);
+                    a = __ldg(src); c = __ldg(src + 1);
+                }
+                const int stage = it % kWgStages;
+                mbar_wait(&x_empty[stage], ((it / kWgStages) & 1) ^ 1);
+                if (cidx < g.xrows) {
+                    uint4 hi, lo;
+                    split8(a, c, hi, lo);
+                    uint8_t* dst = st_s + (size_t)stage * stage_bytes + cidx * 16;
+                    *reinterpret_cast<uint4*>(dst) = hi;
+                    *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&x_full[stage]);
+                continue;
+            }
             float4 v[2][4];
             int rr[2], pyy[2];
 #pragma unroll
@@ -814,7 +844,11 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
         }
     } else {
         // ================= MMA issue =================
-        const uint32_t idesc = make_idesc_f16(64, 32, 1, 1, 1, 1);         // bf16, A and B MN-major
+        // stride 2: four taps of N = 32 (one block); stride 1: three kernel rows of N = 24 = (kw, ci): the three kw taps are one
+        // row apart, i.e. 16 bytes, which is the B operand's SBO (n / 8 = kw)
+        const uint32_t idesc = make_idesc_f16(64, g.s1 ? 24 : 32, 1, 1, 1, 1);         // bf16, A and B MN-major
+        const int ngrp = g.s1 ? 3 : 4;
+        const uint32_t b_sbo = g.s1 ? 16u : (uint32_t)g.chunk_bytes, dstep = g.s1 ? 24u : 32u;
         int it = 0;
         for (int tile = t_lo; tile < t_hi; ++tile, ++it) {
             const int stage = it % kWgStages;
@@ -827,12 +861,15 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
                 const uint64_t a_d = make_smem_desc(ds + (uint32_t)(ks * 256), 128, kDChunk);
 #pragma unroll
                 for (int tap = 0; tap < 4; ++tap) {
-                    const uint32_t b_addr = xs + (uint32_t)(((tap >> 1) * g.Xp + (tap & 1)) * 16 + ks * 256);
-                    const uint64_t b_hi = make_smem_desc(b_addr, 128, g.chunk_bytes);
-                    const uint64_t b_lo = make_smem_desc(b_addr + g.hl_bytes, 128, g.chunk_bytes);
-                    if (elect_one()) {
-                        umma_f16(td + tap * 32, a_d, b_hi, idesc, (it | ks) ? 1u : 0u);
-                        umma_f16(td + tap * 32, a_d, b_lo, idesc, 1u);
+                    if (tap < ngrp) {
+                        const int tshift = g.s1 ? tap * g.Xp : (tap >> 1) * g.Xp + (tap & 1);
+                        const uint32_t b_addr = xs + (uint32_t)(tshift * 16 + ks * 256);
+                        const uint64_t b_hi = make_smem_desc(b_addr, 128, b_sbo);
+                        const uint64_t b_lo = make_smem_desc(b_addr + g.hl_bytes, 128, b_sbo);
+                        if (elect_one()) {
+                            umma_f16(td + tap * dstep, a_d, b_hi, idesc, (it | ks) ? 1u : 0u);
+                            umma_f16(td + tap * dstep, a_d, b_lo, idesc, 1u);
+                        }
                     }
                 }
             }
@@ -932,10 +969,9 @@ bool pn_conv_mid_tc_has_bwd(const pn_handle* h, int l) {
     MidTcGeom g;
     return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g);
 }
-// (the weight-gradient kernel exists for the 4x4 / stride-2 geometry only)
 bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) {
     MidTcGeom g;
-    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g) && !g.s1 && h->max_active[l] <= 4;
+    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g) && h->max_active[l] <= 4;
 }
 
 int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used) {
@@ -944,7 +980,8 @@ int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int
     if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
     const int ntile = (B * g.RB + kTileM - 1) / kTileM;
     const int nch = std::max(1, std::min(std::min(h->nch, ntile), 3 * h->num_sms / std::max(1, h->P)));
-    const size_t smem = 128 + (size_t)kWgStages * (g.stage_bytes + 8 * kDChunk);
+    // the flush reuses the stages as scratch: fp32 [64][129] accumulator copy + [128][33] bias partials
+    const size_t smem = 128 + std::max<size_t>((size_t)kWgStages * (g.stage_bytes + 8 * kDChunk), (64 * 129 + 128 * 33) * sizeof(float));
     PN_SET_SMEM(h, conv_mid_wgrad_tc_kernel, smem);
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + l, st);
