@@ -1,5 +1,5 @@
-// Module convolutions of the middle layers (k = 4, stride 2, 8 -> 8 channels per module) on the tensor
-// cores: tcgen05 kind::f16 with bf16 hi/lo operands (three MMAs per product, as in pn_lin_tc.cu) and fp32
+// Module convolutions of the middle layers (k = 4 / stride 2 and k = 3 / stride 1, 8 -> 8 channels per module) on the
+// tensor cores (the text below describes the stride-2 case; the stride-1 differences are noted at make_mid_tc_geom): tcgen05 kind::f16 with bf16 hi/lo operands (three MMAs per product, as in pn_lin_tc.cu) and fp32
 // accumulation in TMEM.
 //
 // Reference semantics: relu(conv2d(net, W_conv[l,j], stride, VALID) + b_conv[l,j]) * gate_j summed over the
