@@ -541,10 +541,19 @@ lin_wgrad_tc_kernel(const uint8_t* __restrict__ xp, const uint8_t* __restrict__ 
             const int cnt = __reduce_max_sync(0xffffffffu, list_count[lm]);
             const int nkb = min(16, g.KB - kt * 16);
             const uint32_t abytes = (uint32_t)(nkb * 4 * kBlk);
+            // The module's path list and each path's slot of this module are fetched 32 paths at a time (lane i holds path
+            // i0 + i): one list load + one mask load per path, done serially inside the loop, used to cost ~1 us per path and
+            // left the four-stage ring empty -- the producer, not the tensor pipe, set this kernel's pace.
+            int pv = 0, sv = 0;
             for (int i = 0; i < cnt; ++i) {
-                const int p = __reduce_max_sync(0xffffffffu, list[(size_t)lm * P + i]);
-                const uint32_t mask = __reduce_or_sync(0xffffffffu, masks[p * g.L + g.L - 1]);
-                const int slot = __popc(mask & ((1u << j) - 1u));
+                if ((i & 31) == 0) {
+                    const int ii = i + lane;
+                    pv = ii < cnt ? list[(size_t)lm * P + ii] : 0;
+                    const uint32_t mk = ii < cnt ? masks[pv * g.L + g.L - 1] : 0u;
+                    sv = __popc(mk & ((1u << j) - 1u));
+                }
+                const int p = __shfl_sync(0xffffffffu, pv, i & 31);
+                const int slot = __shfl_sync(0xffffffffu, sv, i & 31);
                 for (int bc = 0; bc < g.nbc; ++bc) {
                     const int st = sc % kStages;
                     mbar_wait(&empty[st], ((sc / kStages) & 1) ^ 1);
