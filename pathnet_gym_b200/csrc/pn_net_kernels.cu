@@ -667,10 +667,19 @@ __device__ __forceinline__ void conv_reduce_body(int j, int by, const float* __r
     const int lm = l * nd.M + j, cnt = list_count[lm];
     const int* lst = list + (size_t)lm * P;
     const int nterms = cnt * nch_active;
+    // the module's path list goes through shared memory first: a list load feeding the address of every partial load
+    // would put two dependent global round trips into each term
+    __shared__ int lst_s[1024];
+    const bool staged = cnt <= 1024;
+    if (staged) {
+        for (int i = threadIdx.x; i < cnt; i += blockDim.x) lst_s[i] = lst[i];
+        __syncthreads();
+    }
     float s = 0.f;
     if (e < n)
         for (int i = grp; i < nterms; i += 8) {
-            const int p = lst[i / nch_active], c = i - (i / nch_active) * nch_active;
+            const int pi = i / nch_active, c = i - pi * nch_active;
+            const int p = staged ? lst_s[pi] : lst[pi];
             s += part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
         }
     red[grp][el] = s;
