@@ -734,9 +734,13 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                         if (rowvalid) {
                             float o[8];
 #pragma unroll
-                            for (int c = 0; c < 8; ++c)
-                                o[c] = (float)(((double)(int)d0[c] + 256.0 * (double)(int)d1[c] + 65536.0 * (double)(int)d2[c] +
-                                                16777216.0 * (double)(int)d3[c]) * dscale);
+                            for (int c = 0; c < 8; ++c) {
+                                // digits combined in 64-bit integers (|sum| < 2^48: exact, and the same value the four
+                                // int -> double conversions gave), then ONE conversion: conversions are the slow instructions here
+                                const long long v = (long long)(int)d0[c] + ((long long)(int)d1[c] << 8) + ((long long)(int)d2[c] << 16) +
+                                                    ((long long)(int)d3[c] << 24);
+                                o[c] = (float)((double)v * dscale);
+                            }
                             float4* dst = reinterpret_cast<float4*>(
                                 part + ((size_t)(p * nch_alloc + ch) * nd.M + jl[sl]) * stride_part + (size_t)kk * PN_F);
                             dst[0] = make_float4(o[0], o[1], o[2], o[3]);
