@@ -253,6 +253,15 @@ typedef struct pn_profile_entry {
  * tensor-core layer-0 kernel records per-CTA wait cycles; copies them out. */
 PN_API int pn_debug_read(pn_handle* h, long long* out_host, int capacity);
 
+/* Test aid: the ReLU decisions the LAST pn_train_step / pn_forward call with batch B made in PathNet layer `layer`
+ * (game_ac_network.py:188-192: relu(...) of every active module).  Synchronises the device and copies to host:
+ *   layer < L-1 : [P*B][M][OH*OW] bytes, bit c = output channel c of that pixel was > 0
+ *   layer = L-1 : [P*B][M][hidden] bytes, 1 = the unit was > 0
+ * Rows of modules that are not active for a path are undefined.  Returns the number of bytes written, or a
+ * negative error code (capacity too small, bad layer).  The parity tests use it to separate arithmetic
+ * differences from ReLU decisions that lie below fp32 resolution. */
+PN_API int64_t pn_debug_read_relu_masks(pn_handle* h, int layer, int B, uint8_t* out_host, int64_t capacity_bytes);
+
 /* When on, every kernel launch is bracketed by cudaEventRecord on the launch
  * stream.  Resets the counters. */
 PN_API int pn_profile_enable(pn_handle* h, int on);

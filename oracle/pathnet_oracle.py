@@ -213,11 +213,18 @@ def _im2col(x, k, s):
 
 
 def forward_backward_numpy(cfg, params, frames_f, gates, actions, td, r, beta=ENTROPY_BETA, dtype=np.float64,
-                           want_grads=True):
+                           want_grads=True, relu_override=None, pre_out=None):
     """Closed-form forward + backward for ONE path.
 
     Only gated-on modules are evaluated: adding exact +0.0 terms does not change
-    the sum (game_ac_network.py:186-193).  Returns pi, v, loss, grads."""
+    the sum (game_ac_network.py:186-193).  Returns pi, v, loss, grads.
+
+    Test aids: `pre_out` (a dict) receives every pre-activation, keyed (layer, module): conv layers
+    [B*OH*OW, F], the linear layer [B, hidden].  `relu_override` (same keys, bool arrays of the same
+    shapes) replaces the decision `pre > 0` of that module: the parity tests use it to evaluate the graph
+    with the ReLU decisions another implementation took, which separates arithmetic differences from
+    decisions on pre-activations that lie below fp32 resolution."""
+    relu_override = relu_override or {}
     tt = tensor_table(cfg)
     idx = {t["name"]: i for i, t in enumerate(tt)}
     P = [np.asarray(p, dtype=dtype) for p in params]
@@ -234,8 +241,10 @@ def forward_backward_numpy(cfg, params, frames_f, gates, actions, td, r, beta=EN
             if gates[l, j] != 1.0:
                 continue
             pre = cols @ P[idx[f"W_conv[{l},{j}]"]].reshape(-1, cfg.F) + P[idx[f"b_conv[{l},{j}]"]]
-            masks[j] = pre > 0
-            acc = acc + np.maximum(pre, 0)
+            if pre_out is not None:
+                pre_out[(l, j)] = pre
+            masks[j] = np.asarray(relu_override[(l, j)]).reshape(pre.shape) if (l, j) in relu_override else pre > 0
+            acc = acc + np.where(masks[j], pre, 0)
         saved.append((x.shape, cols, masks))
         x = np.ascontiguousarray(acc.reshape(n, oh, ow, cfg.F))
     flat = x.reshape(n, cfg.last_lin)
@@ -245,8 +254,11 @@ def forward_backward_numpy(cfg, params, frames_f, gates, actions, td, r, beta=EN
         if gates[cfg.L - 1, j] != 1.0:
             continue
         pre = flat @ P[idx[f"W_lin[{j}]"]] + P[idx[f"b_lin[{j}]"]]
-        lmask[j] = pre > 0
-        h = h + np.maximum(pre, 0)
+        if pre_out is not None:
+            pre_out[(cfg.L - 1, j)] = pre
+        key = (cfg.L - 1, j)
+        lmask[j] = np.asarray(relu_override[key]).reshape(pre.shape) if key in relu_override else pre > 0
+        h = h + np.where(lmask[j], pre, 0)
     h = h / cfg.M
     z = h @ P[idx["W_fc2"]] + P[idx["b_fc2"]]
     zs = z - z.max(axis=1, keepdims=True)
@@ -474,9 +486,10 @@ def masks_from_gates(g) -> np.ndarray:
 
 
 def population_step(cfg, params, frames_u8, masks, actions, td, r, beta=ENTROPY_BETA, dtype="float64",
-                    impl="torch"):
+                    impl="torch", relu_override=None, pre_out=None):
     """Synchronous population gradient: per-path tf.gradients, summed over paths
-    (the shared-module gradient the B200 design all-reduces).  frames_u8 [P,B,H,W,C]."""
+    (the shared-module gradient the B200 design all-reduces).  frames_u8 [P,B,H,W,C].
+    relu_override / pre_out (impl="numpy" only): lists with one dict per path, see forward_backward_numpy."""
     P = frames_u8.shape[0]
     pis, vs, losses = [], [], []
     G = [np.zeros(p.shape, dtype=dtype) for p in params]
@@ -487,7 +500,9 @@ def population_step(cfg, params, frames_u8, masks, actions, td, r, beta=ENTROPY_
             pi, v, ls, g = path_grads_torch(cfg, params, xf, gates, actions[p], td[p], r[p], beta, dtype)
         else:
             pi, v, ls, g = forward_backward_numpy(cfg, params, xf, gates, actions[p], td[p], r[p], beta,
-                                                  np.dtype(dtype).type)
+                                                  np.dtype(dtype).type,
+                                                  relu_override=relu_override[p] if relu_override is not None else None,
+                                                  pre_out=pre_out[p] if pre_out is not None else None)
         pis.append(pi); vs.append(v); losses.append(ls)
         for a, b in zip(G, g):
             a += b

@@ -53,6 +53,7 @@ SIGNATURES = {
     "pn_last_lin": (_i, [_vp]),
     "pn_workspace_bytes": (C.c_int64, [_vp]),
     "pn_debug_read": (_i, [_vp, _vp, _i]),
+    "pn_debug_read_relu_masks": (C.c_int64, [_vp, _i, _i, _vp, C.c_int64]),
     "pn_launch_count": (C.c_int64, [_vp]),
     "pn_lin_grads_region": (_i, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "pn_stream_wait_lin_grads": (_i, [_vp, _vp]),

@@ -266,6 +266,21 @@ extern "C" PN_API int pn_debug_read(pn_handle* h, long long* out_host, int capac
     return n;
 }
 
+extern "C" PN_API int64_t pn_debug_read_relu_masks(pn_handle* h, int layer, int B, uint8_t* out_host, int64_t capacity_bytes) {
+    if (!h || !out_host) return pn_fail_global(PN_ERR_INVALID, "pn_debug_read_relu_masks: null argument");
+    if (layer < 0 || layer >= h->cfg.L) return pn_fail(h, PN_ERR_INVALID, "layer %d outside 0..%d", layer, h->cfg.L - 1);
+    if (int rc = check_B(h, B)) return rc;
+    const PnNetDesc& nd = h->nd;
+    const bool lin = layer == nd.nconv;
+    const size_t per = lin ? (size_t)nd.hidden : (size_t)nd.OH[layer] * nd.OW[layer];
+    const size_t bytes = (size_t)h->P * B * nd.M * per;
+    if ((int64_t)bytes > capacity_bytes) return pn_fail(h, PN_ERR_INVALID, "capacity %lld < %zu bytes", (long long)capacity_bytes, bytes);
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    PN_CUDA(h, cudaDeviceSynchronize());
+    PN_CUDA(h, cudaMemcpy(out_host, lin ? h->lmask : h->rmask[layer], bytes, cudaMemcpyDeviceToHost));
+    return (int64_t)bytes;
+}
+
 extern "C" PN_API int64_t pn_launch_count(const pn_handle* h) { return h ? h->launches : 0; }
 
 extern "C" PN_API int pn_profile_enable(pn_handle* h, int on) {

@@ -24,6 +24,7 @@
 #include "pn_tc.cuh"
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <algorithm>
 
@@ -124,7 +125,27 @@ __device__ __forceinline__ void split8(const float4& a, const float4& b, uint4& 
                     pack_bf16x2(v[4] - h[4], v[5] - h[5]), pack_bf16x2(v[6] - h[6], v[7] - h[7]));
 }
 
-// ---- weights -> bf16 hi/lo operand blocks, every step (RMSProp changed them) ------------------------------------
+// Forward operands are fp16 hi/lo instead (x * scale ~ hi + lo to ~2^-22 relative: 11 + 11 mantissa bits), because the
+// forward pass decides the ReLU masks: with bf16 hi/lo (2^-16) a few pre-activations per million land on the other side of
+// zero than in fp32 arithmetic, and one flipped unit moves a small tensor's gradient by more than the 1e-3 budget.  The
+// power-of-two scales keep the lo parts out of fp16's subnormal range (activations x 2^4, weights x 2^8; the epilogue
+// multiplies by 2^-12, all exact); activations must stay below 65504 / 16.
+constexpr float kActScale = 16.0f, kWgtScale = 256.0f, kFwdUnscale = 1.0f / (16.0f * 256.0f);
+__device__ __forceinline__ uint32_t pack_f16x2(float a, float b) {
+    const __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&v);
+}
+__device__ __forceinline__ void split8_f16(const float4& a, const float4& b, float scale, uint4& hi, uint4& lo) {
+    const float v[8] = {a.x * scale, a.y * scale, a.z * scale, a.w * scale, b.x * scale, b.y * scale, b.z * scale, b.w * scale};
+    float h[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) h[i] = __half2float(__float2half_rn(v[i]));
+    hi = make_uint4(pack_f16x2(h[0], h[1]), pack_f16x2(h[2], h[3]), pack_f16x2(h[4], h[5]), pack_f16x2(h[6], h[7]));
+    lo = make_uint4(pack_f16x2(v[0] - h[0], v[1] - h[1]), pack_f16x2(v[2] - h[2], v[3] - h[3]),
+                    pack_f16x2(v[4] - h[4], v[5] - h[5]), pack_f16x2(v[6] - h[6], v[7] - h[7]));
+}
+
+// ---- weights -> hi/lo operand blocks (wf fp16 x 2^8 for the forward pass, wd bf16 for the data gradient), every step (RMSProp changed them) ------------------------------------
 // wf [M][hl][kc 16][co 8][ci 8]   forward B operand (K-major over k = kc * 8 + ci;  kc = tap * 4 + py * 2 + px)
 // wd [M][hl][kc 16][ci 8][co 8]   data-gradient B operand (K-major over co)
 // with (kh, kw) = (2 dy + py, 2 dx + px), tap = dy * 2 + dx; source W[(kh * 4 + kw) * 8 + ci][co].
@@ -143,7 +164,8 @@ conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, int
 #pragma unroll
         for (int q = 0; q < 8; ++q) v1[q] = kc < 9 ? (fwd ? W[(size_t)kc * 64 + q * 8 + e] : W[(size_t)kc * 64 + e * 8 + q]) : 0.f;
         uint4 h1, l1;
-        split8(make_float4(v1[0], v1[1], v1[2], v1[3]), make_float4(v1[4], v1[5], v1[6], v1[7]), h1, l1);
+        if (fwd) split8_f16(make_float4(v1[0], v1[1], v1[2], v1[3]), make_float4(v1[4], v1[5], v1[6], v1[7]), kWgtScale, h1, l1);
+        else split8(make_float4(v1[0], v1[1], v1[2], v1[3]), make_float4(v1[4], v1[5], v1[6], v1[7]), h1, l1);
         uint8_t* d1 = (fwd ? wf : wd) + (size_t)j * 2 * kModBytes + kc * 128 + e * 16;
         *reinterpret_cast<uint4*>(d1) = h1;
         *reinterpret_cast<uint4*>(d1 + kModBytes) = l1;
@@ -161,7 +183,8 @@ conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, int
         for (int co = 0; co < 8; ++co) v[co] = src[e * 8 + co];          // e = ci
     }
     uint4 hi, lo;
-    split8(make_float4(v[0], v[1], v[2], v[3]), make_float4(v[4], v[5], v[6], v[7]), hi, lo);
+    if (threadIdx.x < 128) split8_f16(make_float4(v[0], v[1], v[2], v[3]), make_float4(v[4], v[5], v[6], v[7]), kWgtScale, hi, lo);
+    else split8(make_float4(v[0], v[1], v[2], v[3]), make_float4(v[4], v[5], v[6], v[7]), hi, lo);
     uint8_t* dst = (threadIdx.x < 128 ? wf : wd) + (size_t)j * 2 * kModBytes + kc * 128 + e * 16;
     *reinterpret_cast<uint4*>(dst) = hi;
     *reinterpret_cast<uint4*>(dst + kModBytes) = lo;
@@ -220,7 +243,7 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                 mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
                 if (cidx < g.xrows) {
                     uint4 hi, lo;
-                    split8(a, c, hi, lo);
+                    split8_f16(a, c, kActScale, hi, lo);
                     uint8_t* dst = x_s + (size_t)stage * g.stage_bytes + cidx * 16;
                     *reinterpret_cast<uint4*>(dst) = hi;
                     *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
@@ -260,7 +283,7 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
 #pragma unroll
                     for (int px = 0; px < 2; ++px) {
                         uint4 hi, lo;
-                        split8(v[u][2 * px], v[u][2 * px + 1], hi, lo);
+                        split8_f16(v[u][2 * px], v[u][2 * px + 1], kActScale, hi, lo);
                         uint8_t* dst = xs + (size_t)(pyy[u] * 2 + px) * g.chunk_bytes + rr[u] * 16;
                         *reinterpret_cast<uint4*>(dst) = hi;
                         *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
@@ -302,7 +325,7 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                     mbar_wait(w_full, wphase);
                     wphase ^= 1;
                 }
-                idesc = make_idesc_f16(kTileM, 8 * ((ns + 1) & ~1), 1, 1, 0, 0);   // bf16 x bf16, both K-major
+                idesc = make_idesc_f16(kTileM, 8 * ((ns + 1) & ~1), 0, 0, 0, 0);   // fp16 x fp16, both K-major
                 cur_p = p;
             }
             const int stage = it % kXStages, as = it & 1;
@@ -368,7 +391,7 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                         unsigned bits = 0;
 #pragma unroll
                         for (int c = 0; c < 8; ++c) {
-                            const float pre = __uint_as_float(d[u * 8 + c]) + bias[c];
+                            const float pre = fmaf(__uint_as_float(d[u * 8 + c]), kFwdUnscale, bias[c]);
                             if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
                         }
                         if (valid) R[(t * nd.M + j) * g.npix + pix] = (uint8_t)bits;
@@ -634,8 +657,8 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
 // chunks (MN-major, N = 32 per tap, the tap being a start-address shift), K = 16 raster rows per MMA.
 //   D rows 0..31  = dpre_hi * (X_hi + X_lo),  rows 32..63 = dpre_lo * (X_hi + X_lo); the flush adds the halves.
 // The bias gradient (plain row sums of dpre) is accumulated in fp32 registers by the dpre converter threads
-// (a fixed row per thread) and reduced in a fixed order.  At most 4 active modules per path (else the
-// CUDA-core kernel runs).
+// (a fixed row per thread) and reduced in a fixed order.  Four active modules per pass; a path with more owns
+// further blocks (one per pass), so the dispatch is per path, not per population.
 // Warps 0-3: dpre converters, then flush; warps 4-8: X converters; warp 9: MMA issue.
 // =====================================================================================================
 constexpr int kWgStages = 2;
@@ -644,7 +667,7 @@ constexpr int kDChunk = kTileM * 16;          // bytes of one dpre chunk of a ti
 __global__ void __launch_bounds__(kFwdThreads, 3)
 conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ dY, const uint8_t* __restrict__ R,
                          PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int B, int ntile, int nch,
-                         int nch_alloc, float* __restrict__ part) {
+                         int nch_alloc, int npass, float* __restrict__ part) {
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kWgStages]
     uint64_t* x_empty = x_full + kWgStages;                    // [kWgStages]
@@ -653,11 +676,15 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
     const int stage_bytes = g.stage_bytes + 8 * kDChunk;
     __shared__ uint32_t tmem_base_s;
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
-    const int p = blockIdx.x / nch, ch = blockIdx.x - p * nch;
+    // block -> (path, chunk of tiles, pass): a pass covers four of the path's active modules, so a path that a mutation
+    // or the frozen path of an earlier task has given more than four modules in this layer simply owns more blocks
+    const int pass = blockIdx.x % npass, pc = blockIdx.x / npass;
+    const int p = pc / nch, ch = pc - p * nch;
     const int t_lo = (int)((long long)ntile * ch / nch), t_hi = (int)((long long)ntile * (ch + 1) / nch);
     const uint32_t mask = masks[p * nd.L + l];
-    const int ns = __popc(mask);
-    if (ns == 0 || t_lo >= t_hi) return;                       // the path is in no module's list: its partials are never read
+    const int s0 = 4 * pass;
+    const int ns = min(4, __popc(mask) - s0);                  // modules of this pass
+    if (ns <= 0 || t_lo >= t_hi) return;                       // nothing to do: these partials are never read
     const int NR = B * g.RB;
 
     if (threadIdx.x == 0) {
@@ -676,7 +703,7 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
         const int r = threadIdx.x;
         int jq[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) jq[q] = q < ns ? __fns(mask, 0, q + 1) : 0;
+        for (int q = 0; q < 4; ++q) jq[q] = q < ns ? __fns(mask, 0, s0 + q + 1) : 0;
         float bacc[4][8];
 #pragma unroll
         for (int q = 0; q < 4; ++q)
@@ -752,7 +779,7 @@ conv_mid_wgrad_tc_kernel(const float* __restrict__ X, const float* __restrict__ 
         const int KK = nd.KK[l];                               // 128 (4x4x8) or 72 (3x3x8)
         const int stride_part = KK * 8 + 8;
         for (int slot = 0; slot < ns; ++slot) {
-            float* out = part + ((size_t)(p * nch_alloc + ch) * nd.M + __fns(mask, 0, slot + 1)) * stride_part;
+            float* out = part + ((size_t)(p * nch_alloc + ch) * nd.M + __fns(mask, 0, s0 + slot + 1)) * stride_part;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const int idx = i * 128 + r;                   // = ((kh * k + kw) * 8 + ci) * 8 + co
@@ -971,7 +998,7 @@ bool pn_conv_mid_tc_has_bwd(const pn_handle* h, int l) {
 }
 bool pn_conv_mid_wgrad_tc_usable(const pn_handle* h, int l) {
     MidTcGeom g;
-    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g) && h->max_active[l] <= 4;
+    return h->tc_mid[l] && make_mid_tc_geom(h->nd, l, g);
 }
 
 int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int* nch_used) {
@@ -985,8 +1012,10 @@ int pn_launch_conv_mid_wgrad_tc(pn_handle* h, int l, int B, cudaStream_t st, int
     PN_SET_SMEM(h, conv_mid_wgrad_tc_kernel, smem);
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + l, st);
-        conv_mid_wgrad_tc_kernel<<<h->P * nch, kFwdThreads, smem, st>>>(h->act[l - 1], h->dact[l], h->rmask[l], nd, l, g,
-                                                                       h->d_masks, B, ntile, nch, h->nch, h->wpart[l]);
+        const int npass = std::max(1, (h->max_active[l] + 3) / 4);
+        conv_mid_wgrad_tc_kernel<<<h->P * nch * npass, kFwdThreads, smem, st>>>(h->act[l - 1], h->dact[l], h->rmask[l], nd, l, g,
+                                                                               h->d_masks, B, ntile, nch, h->nch, npass,
+                                                                               h->wpart[l]);
     }
     PN_LAUNCH_CHECK(h, "conv_mid_wgrad_tc_kernel");
     *nch_used = nch;

@@ -24,6 +24,7 @@
 #include "pn_tc.cuh"
 
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <algorithm>
 
@@ -49,6 +50,26 @@ __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bflo
     lo = __float2bfloat16_rn(x - __bfloat162float(hi));
 }
 
+// The weights (Wp) and the activations (Xp) are stored as fp16 hi/lo instead: x * scale ~ hi + lo to ~2^-22 relative
+// (11 + 11 mantissa bits).  The forward GEMM decides the ReLU masks, and with bf16 hi/lo (2^-16) a few pre-activations
+// per million fall on the other side of zero than in fp32 arithmetic, which moves small gradient tensors by more than the
+// 1e-3 budget.  Power-of-two scales (exact) keep the lo parts out of fp16's subnormal range: weights x 2^8, activations
+// x 2^4 (so activations must stay below 65504 / 16); the forward epilogue undoes them.  The backward GEMMs keep bf16 copies
+// (Wp, Xp) next to the gradient operand Dp, whose dynamic range needs bf16: one tcgen05.mma cannot mix an fp16 operand with a
+// bf16 one (the GPU reports an illegal instruction), so the prep kernels write both forms from one read.
+constexpr float kWScale = 256.0f, kXScale = 16.0f;
+__device__ __forceinline__ void split_row8_f16(const float* v, float scale, uint4& hi, uint4& lo) {
+    __half h[8], l[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const float x = v[i] * scale;
+        h[i] = __float2half_rn(x);
+        l[i] = __float2half_rn(x - __half2float(h[i]));
+    }
+    hi = *reinterpret_cast<uint4*>(h);
+    lo = *reinterpret_cast<uint4*>(l);
+}
+
 // 8 consecutive floats -> one 16-byte row of the hi block and of the lo block
 __device__ __forceinline__ void split_row8(const float* v, uint4& hi, uint4& lo) {
     __nv_bfloat16 h[8], l[8];
@@ -62,7 +83,7 @@ __device__ __forceinline__ void split_row8(const float* v, uint4& hi, uint4& lo)
 // One thread per 16-byte output row.  Lane mapping: 8 consecutive lanes fill the 8 rows of one 128-byte block
 // and groups of 4 lanes read 4 x 32 = 128 contiguous source bytes, so both sides move whole 128-byte lines.
 __device__ __forceinline__ void wsplit_item(long long i, const float* __restrict__ params, const PnNetDesc& nd,
-                                            const LinGeom& g, uint8_t* __restrict__ wp) {
+                                            const LinGeom& g, uint8_t* __restrict__ wp, uint8_t* __restrict__ wph) {
     const int ncb4 = g.Hd / 32;
     const int r = (int)(i & 7), cbq = (int)((i >> 3) & 3);
     long long rest = i >> 5;
@@ -80,14 +101,17 @@ __device__ __forceinline__ void wsplit_item(long long i, const float* __restrict
         for (int q = 0; q < 8; ++q) v[q] = 0.f;
     }
     uint4 hi, lo;
+    const size_t off = (size_t)j * g.wp_module + ((size_t)h * g.KB + kb) * 16 * kBlk + (size_t)cb16 * kBlk + r * 16;
     split_row8(v, hi, lo);
-    uint8_t* dst = wp + (size_t)j * g.wp_module + ((size_t)h * g.KB + kb) * 16 * kBlk + (size_t)cb16 * kBlk + r * 16;
-    *reinterpret_cast<uint4*>(dst) = hi;
-    *reinterpret_cast<uint4*>(dst + (size_t)2 * g.KB * 16 * kBlk) = lo;
+    *reinterpret_cast<uint4*>(wp + off) = hi;
+    *reinterpret_cast<uint4*>(wp + off + (size_t)2 * g.KB * 16 * kBlk) = lo;
+    split_row8_f16(v, kWScale, hi, lo);
+    *reinterpret_cast<uint4*>(wph + off) = hi;
+    *reinterpret_cast<uint4*>(wph + off + (size_t)2 * g.KB * 16 * kBlk) = lo;
 }
 
 __device__ __forceinline__ void xsplit_item(long long i, const float* __restrict__ X, const LinGeom& g, int P, int B,
-                                            uint8_t* __restrict__ xp) {
+                                            uint8_t* __restrict__ xp, uint8_t* __restrict__ xph) {
     const int nkb4 = (g.KB + 3) / 4;
     const int kbq = (int)(i & 3), r8 = (int)((i >> 2) & 7), bb = (int)((i >> 5) & 3);
     long long rest = i >> 7;
@@ -109,17 +133,21 @@ __device__ __forceinline__ void xsplit_item(long long i, const float* __restrict
         }
     }
     uint4 hi, lo;
+    const size_t off = (size_t)p * g.xp_path + (size_t)bc * g.xp_chunk + ((size_t)kb * 4 + bb) * kBlk + r8 * 16;
     split_row8(v, hi, lo);
-    uint8_t* dst = xp + (size_t)p * g.xp_path + (size_t)bc * g.xp_chunk + ((size_t)kb * 4 + bb) * kBlk + r8 * 16;
-    *reinterpret_cast<uint4*>(dst) = hi;
-    *reinterpret_cast<uint4*>(dst + g.xp_chunk / 2) = lo;
+    *reinterpret_cast<uint4*>(xp + off) = hi;
+    *reinterpret_cast<uint4*>(xp + off + g.xp_chunk / 2) = lo;
+    split_row8_f16(v, kXScale, hi, lo);
+    *reinterpret_cast<uint4*>(xph + off) = hi;
+    *reinterpret_cast<uint4*>(xph + off + g.xp_chunk / 2) = lo;
 }
 
 __global__ void __launch_bounds__(256)
-lin_prep_kernel(const float* __restrict__ params, PnNetDesc nd, LinGeom g, uint8_t* __restrict__ wp, int wblocks,
-                const float* __restrict__ X, int P, int B, uint8_t* __restrict__ xp) {
-    if ((int)blockIdx.x < wblocks) wsplit_item((long long)blockIdx.x * 256 + threadIdx.x, params, nd, g, wp);
-    else xsplit_item((long long)(blockIdx.x - wblocks) * 256 + threadIdx.x, X, g, P, B, xp);
+lin_prep_kernel(const float* __restrict__ params, PnNetDesc nd, LinGeom g, uint8_t* __restrict__ wp,
+                uint8_t* __restrict__ wph, int wblocks, const float* __restrict__ X, int P, int B, uint8_t* __restrict__ xp,
+                uint8_t* __restrict__ xph) {
+    if ((int)blockIdx.x < wblocks) wsplit_item((long long)blockIdx.x * 256 + threadIdx.x, params, nd, g, wp, wph);
+    else xsplit_item((long long)(blockIdx.x - wblocks) * 256 + threadIdx.x, X, g, P, B, xp, xph);
 }
 
 // ---- forward GEMM ----------------------------------------------------------------------------------------------------
@@ -130,6 +158,16 @@ __device__ __forceinline__ long long lin_clock() {      // clock read that stays
     asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory");
     return t;
 }
+
+// Accumulators: the tensor core adds into its fp32 accumulator with truncation, so a long chain of accumulations leaves a
+// small one-sided error (measured: ~3e-6 relative over the 75..123 MMAs of one output).  It cancels nowhere downstream --
+// a sum over the batch such as the value head's bias gradient adds it up coherently -- so every slot owns FOUR accumulators of
+// kNB columns: one for the small cross terms (hi*lo + lo*hi, magnitude 2^-11 of the result) and three that take the hi*hi
+// MMAs of the K steps round-robin; the epilogue adds the four in fp32 (round-to-nearest).  Chain length at full magnitude:
+// a third of the K steps instead of three times the K steps.  The slots rotate over a ring of kAccRing TMEM stages.
+constexpr int kAccRing = 4;                // TMEM stages (slots in flight)
+constexpr int kAccPerSlot = 4;             // cross | hh (ks % 3 == 0) | hh (1) | hh (2)
+constexpr int kSlotCols = kAccPerSlot * kNB;
 
 __global__ void __launch_bounds__(192, 1)
 lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp, const float* __restrict__ params,
@@ -146,9 +184,8 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
     uint64_t* w_empty = bars + kWStages;      // [kWStages]
     uint64_t* x_full = bars + 2 * kWStages;
     uint64_t* x_empty = x_full + 1;
-    uint64_t* acc_full = x_full + 2;          // (kept for the no-module case)
-    uint64_t* acc_empty = x_full + 3;
-    uint64_t* slot_full = x_full + 4;         // [16] (M <= 16 here): slot s of the item is complete -> its epilogue runs under slot s+1's MMAs
+    uint64_t* slot_full = x_full + 2;         // [kAccRing] the slot in this TMEM stage is complete -> its epilogue runs under the next slot's MMAs
+    uint64_t* slot_empty = slot_full + kAccRing;   // [kAccRing] the epilogue has read the stage
     __shared__ uint32_t tmem_base_s;
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int nitems = P * g.nbc * 2;
@@ -157,8 +194,8 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kWStages; ++i) { mbar_init(&w_full[i], 1); mbar_init(&w_empty[i], 1); }
-        mbar_init(x_full, 1); mbar_init(x_empty, 1); mbar_init(acc_full, 1); mbar_init(acc_empty, 128);
-        for (int i = 0; i < 16; ++i) mbar_init(&slot_full[i], 1);
+        mbar_init(x_full, 1); mbar_init(x_empty, 1);
+        for (int i = 0; i < kAccRing; ++i) { mbar_init(&slot_full[i], 1); mbar_init(&slot_empty[i], 128); }
         fence_mbar_init();
     }
     if (warp == 5) tmem_alloc(&tmem_base_s, 512);
@@ -203,20 +240,22 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
     } else if (warp == 5) {
         // ================= MMA issue (whole warp, uniform values, elected instructions) =================
         int stage = 0;
-        uint32_t wphase = 0, it = 0;
+        uint32_t wphase = 0, it = 0, sc = 0;                              // sc: slots issued so far (ring position)
         long long d_wx = 0, d_ww = 0;
-        const uint32_t idesc = make_idesc_f16(128, kNB, 1, 1, 1, 0);      // bf16 x bf16, A MN-major, B K-major
+        const uint32_t idesc = make_idesc_f16(128, kNB, 0, 0, 1, 0);      // fp16 x fp16, A MN-major, B K-major
         const uint32_t xs = smem_u32(x_s);
         for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
             const int p = (item >> 1) / g.nbc;
             const int ns = __popc(__reduce_or_sync(0xffffffffu, masks[p * g.L + g.L - 1]));
-            mbar_wait(acc_empty, (it & 1) ^ 1);
             const long long cx = dbg9 ? lin_clock() : 0;
             mbar_wait(x_full, it & 1);
             if (dbg9) d_wx += lin_clock() - cx;
             tc_fence_after();
-            for (int slot = 0; slot < ns; ++slot) {
-                const uint32_t dcol = td + slot * kNB;
+            for (int slot = 0; slot < ns; ++slot, ++sc) {
+                const uint32_t ring = sc % kAccRing;
+                mbar_wait(&slot_empty[ring], ((sc / kAccRing) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t dcol = td + ring * kSlotCols;
                 for (int c = 0; c < nchunk; ++c) {
                     const long long cw = dbg9 ? lin_clock() : 0;
                     mbar_wait(&w_full[stage], wphase);
@@ -232,9 +271,10 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
                         // B: Xp blocks [kb][bb]: b-groups 128 B apart, k-groups 512 B apart
                         const uint64_t b_hi = make_smem_desc(xs + (uint32_t)(ks * 2 * 4 * kBlk), 4 * kBlk, kBlk);
                         const uint64_t b_lo = make_smem_desc(xs + (uint32_t)(g.xp_chunk / 2 + ks * 2 * 4 * kBlk), 4 * kBlk, kBlk);
+                        const uint32_t hh = dcol + (uint32_t)(1 + ks % 3) * kNB;
                         if (ks < nkstep && elect_one()) {
-                            umma_f16(dcol, a_hi, b_hi, idesc, ks ? 1u : 0u);
-                            umma_f16(dcol, a_hi, b_lo, idesc, 1u);
+                            umma_f16(hh, a_hi, b_hi, idesc, ks >= 3 ? 1u : 0u);
+                            umma_f16(dcol, a_hi, b_lo, idesc, ks ? 1u : 0u);
                             umma_f16(dcol, a_lo, b_hi, idesc, 1u);
                         }
                     }
@@ -242,7 +282,7 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
                     __syncwarp();
                     if (++stage == kWStages) { stage = 0; wphase ^= 1; }
                 }
-                if (elect_one()) umma_commit(&slot_full[slot]);
+                if (elect_one()) umma_commit(&slot_full[ring]);
                 __syncwarp();
             }
             if (elect_one()) {
@@ -257,8 +297,8 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
     } else {
         // ================= epilogue: thread = hidden unit c, registers = the 32 batch rows =================
         const int quad = warp & 3;
-        uint32_t it = 0;
-        for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
+        uint32_t sc = 0;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int h = item & 1, bc = (item >> 1) % g.nbc, p = (item >> 1) / g.nbc;
             const uint32_t mask = masks[p * g.L + g.L - 1];
             const int ns = __popc(mask);
@@ -266,29 +306,44 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
             float sum[kNB];
 #pragma unroll
             for (int b = 0; b < kNB; ++b) sum[b] = 0.f;
-            for (int slot = 0; slot < ns; ++slot) {
+            for (int slot = 0; slot < ns; ++slot, ++sc) {
+                const uint32_t ring = sc % kAccRing;
                 const long long ce = dbg9 ? lin_clock() : 0;
-                mbar_wait(&slot_full[slot], it & 1);
+                mbar_wait(&slot_full[ring], (sc / kAccRing) & 1);
                 if (dbg9 && threadIdx.x == 0 && slot == ns - 1) { dbg[blockIdx.x * 8 + 3] = lin_clock() - ce; dbg[blockIdx.x * 8 + 4] = lin_clock() - t_entry; }
                 tc_fence_after();
                 const int j = __fns(mask, 0, slot + 1);
                 const float bias = params[nd.linW_base + (long long)j * nd.lin_stride + nd.linb_off + c];
-                uint32_t d[kNB];
-                const uint32_t ta = td + ((uint32_t)(quad * 32) << 16) + slot * kNB;
-                tmem_ld16(ta, *reinterpret_cast<uint32_t(*)[16]>(&d[0]));
-                tmem_ld16(ta + 16, *reinterpret_cast<uint32_t(*)[16]>(&d[16]));
-                tmem_ld_wait();
+                const uint32_t ta = td + ((uint32_t)(quad * 32) << 16) + ring * kSlotCols;
+                float acc[kNB];
+                {   // ((hh0 + hh1) + hh2) + cross, in fp32 registers
+                    uint32_t d[kNB];
+                    tmem_ld16(ta + kNB, *reinterpret_cast<uint32_t(*)[16]>(&d[0]));
+                    tmem_ld16(ta + kNB + 16, *reinterpret_cast<uint32_t(*)[16]>(&d[16]));
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int b = 0; b < kNB; ++b) acc[b] = __uint_as_float(d[b]);
+#pragma unroll
+                    for (int a = 2; a <= kAccPerSlot; ++a) {
+                        const uint32_t col = ta + (uint32_t)(a % kAccPerSlot) * kNB;      // hh1, hh2, then the cross terms (a = 4 -> 0)
+                        tmem_ld16(col, *reinterpret_cast<uint32_t(*)[16]>(&d[0]));
+                        tmem_ld16(col + 16, *reinterpret_cast<uint32_t(*)[16]>(&d[16]));
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int b = 0; b < kNB; ++b) acc[b] += __uint_as_float(d[b]);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&slot_empty[ring]);
 #pragma unroll
                 for (int b = 0; b < kNB; ++b) {
-                    const float pre = __uint_as_float(d[b]) + bias;
+                    const float pre = fmaf(acc[b], 1.0f / (kWScale * kXScale), bias);
                     const bool on = pre > 0.f;
                     if (on) sum[b] += pre;
                     const int bg = bc * kNB + b;
                     if (bg < B) Rl[(((size_t)p * B + bg) * g.M + j) * g.Hd + c] = on ? 1 : 0;   // 32 consecutive bytes per warp
                 }
             }
-            tc_fence_before();
-            mbar_arrive(acc_empty);
             const float Mf = (float)g.M;
 #pragma unroll
             for (int b = 0; b < kNB; ++b) {
@@ -416,7 +471,7 @@ lin_dgrad_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ 
     } else if (warp == 5) {
         // ================= MMA issue =================
         uint32_t wc = 0, dc = 0, it = 0;
-        const uint32_t idesc = make_idesc_f16(128, kNB, 1, 1, 0, 0);      // A K-major, B K-major
+        const uint32_t idesc = make_idesc_f16(128, kNB, 1, 1, 0, 0);      // bf16 x bf16, A K-major, B K-major
         for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
             const int p = item / (KT * g.nbc);
             const int ns = __popc(__reduce_or_sync(0xffffffffu, masks[p * g.L + g.L - 1]));
@@ -576,7 +631,7 @@ lin_wgrad_tc_kernel(const uint8_t* __restrict__ xp, const uint8_t* __restrict__ 
     } else if (warp == 5) {
         // ================= MMA issue =================
         uint32_t sc = 0, it = 0;
-        const uint32_t idesc = make_idesc_f16(128, 128, 1, 1, 1, 1);      // A MN-major, B MN-major
+        const uint32_t idesc = make_idesc_f16(128, 128, 1, 1, 1, 1);      // bf16 x bf16, A MN-major, B MN-major
         for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
             const int j = (item >> 1) / KT;
             const int cnt = __reduce_max_sync(0xffffffffu, list_count[(g.L - 1) * g.M + j]);
@@ -655,7 +710,7 @@ lin_wgrad_tc_kernel(const uint8_t* __restrict__ xp, const uint8_t* __restrict__ 
 
 bool lin_geom(const pn_handle* h, int B, LinGeom& g) {
     const PnNetDesc& nd = h->nd;
-    if (nd.hidden != 256 || nd.last_lin % 8 || nd.M > 16) return false;
+    if (nd.hidden != 256 || nd.last_lin % 8 || nd.last_lin < 48 || nd.M > 16) return false;   // (>= 3 K steps: every hi*hi accumulator is written)
     g.K = nd.last_lin; g.KB = (g.K / 8 + 2) & ~1; g.Hd = nd.hidden; g.M = nd.M; g.L = nd.L;   // >= K/8 + 1, even
     g.nbc = (B + kNB - 1) / kNB;
     g.wp_module = (size_t)2 * 2 * g.KB * 16 * kBlk;
@@ -679,8 +734,8 @@ bool pn_lin_tc_supported(const pn_handle* h) {
 size_t pn_lin_tc_scratch_bytes(const pn_handle* h) {
     LinGeom g;
     if (!lin_geom(h, h->Bmax, g)) return 0;
-    // Wp | Xp | Dp
-    return g.wp_module * g.M + g.xp_path * h->P + g.dp_path * h->P;
+    // Wp | Xp | Dp (bf16, backward)  |  Wph | Xph (fp16, forward)
+    return 2 * (g.wp_module * g.M + g.xp_path * h->P) + g.dp_path * h->P;
 }
 
 // W_lin -> Wp: depends on the parameters only, so the forward launcher runs it on the side stream
@@ -691,7 +746,8 @@ int pn_launch_lin_wsplit(pn_handle* h, cudaStream_t st) {
         PnProfScope prof(h, PN_PROF_LIN_WPREP, st);
         const long long wthreads = (long long)g.M * g.KB * (g.Hd / 32) * 32;
         const int wblocks = (int)((wthreads + 255) / 256);
-        lin_prep_kernel<<<wblocks, 256, 0, st>>>(h->params, h->nd, g, h->tc_lin_buf, wblocks, nullptr, h->P, 1, nullptr);
+        uint8_t* wph = h->tc_lin_buf + g.wp_module * g.M + g.xp_path * h->P + g.dp_path * h->P;
+        lin_prep_kernel<<<wblocks, 256, 0, st>>>(h->params, h->nd, g, h->tc_lin_buf, wph, wblocks, nullptr, h->P, 1, nullptr, nullptr);
     }
     PN_LAUNCH_CHECK(h, "lin_prep_kernel");
     return PN_OK;
@@ -705,11 +761,13 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     const PnNetDesc& nd = h->nd;
     uint8_t* wp = h->tc_lin_buf;
     uint8_t* xp = wp + gmax.wp_module * g.M;
+    uint8_t* wph = xp + gmax.xp_path * h->P + gmax.dp_path * h->P;
+    uint8_t* xph = wph + gmax.wp_module * g.M;
     {
         PnProfScope prof(h, PN_PROF_LIN_PREP, st);
         const long long xthreads = (long long)h->P * g.nbc * ((g.KB + 3) / 4) * 128;
         const int xblocks = (int)((xthreads + 255) / 256);
-        lin_prep_kernel<<<xblocks, 256, 0, st>>>(h->params, nd, g, wp, 0, h->act[nd.nconv - 1], h->P, B, xp);
+        lin_prep_kernel<<<xblocks, 256, 0, st>>>(h->params, nd, g, wp, wph, 0, h->act[nd.nconv - 1], h->P, B, xp, xph);
     }
     PN_LAUNCH_CHECK(h, "lin_prep_kernel");
     const size_t smem = (size_t)kWStages * 2 * kWChunkKb * 16 * kBlk + g.xp_chunk + 256;
@@ -718,7 +776,7 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     const int grid = items < h->num_sms ? items : h->num_sms;
     {
         PnProfScope prof(h, PN_PROF_LIN_FWD, st);
-        lin_fwd_tc_kernel<<<grid, 192, smem, st>>>(wp, xp, h->params, nd, g, h->d_masks, h->P, B, h->hbuf, h->lmask, h->tc_dbg);
+        lin_fwd_tc_kernel<<<grid, 192, smem, st>>>(wph, xph, h->params, nd, g, h->d_masks, h->P, B, h->hbuf, h->lmask, h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "lin_fwd_tc_kernel");
     return PN_OK;

@@ -293,6 +293,27 @@ class PathNetPopulation:
         assert backup.dtype == torch.float32 and backup.numel() == self.slab_floats and backup.is_cuda
         nat.check(self.lib.pn_reinit_unfrozen(self._h, _ptr(backup), self._stream()), self._h)
 
+    def relu_decisions(self, layer: int, B: int) -> np.ndarray:
+        """Test aid: bool array of the last step's ReLU decisions in `layer`: [P, B, M, OH*OW, F] for a conv layer,
+        [P, B, M, hidden] for the linear layer (rows of inactive modules are undefined)."""
+        cfg = self.cfg
+        lin = layer == cfg.L - 1
+        if lin:
+            per = cfg.hidden
+        else:
+            ih, iw = cfg.H, cfg.W
+            for l in range(layer + 1):
+                ih, iw = (ih - cfg.kernels[l]) // cfg.strides[l] + 1, (iw - cfg.kernels[l]) // cfg.strides[l] + 1
+            per = ih * iw
+        buf = np.empty(self.P * B * cfg.M * per, dtype=np.uint8)
+        n = int(self.lib.pn_debug_read_relu_masks(self._h, int(layer), int(B), buf.ctypes.data_as(C.c_void_p), buf.size))
+        if n < 0:
+            nat.check(n, self._h)
+        buf = buf.reshape(self.P, B, cfg.M, per)
+        if lin:
+            return buf != 0
+        return ((buf[..., None] >> np.arange(cfg.F, dtype=np.uint8)) & 1).astype(bool)
+
     # -- measurement support ---------------------------------------------------
     @property
     def launch_count(self) -> int:

@@ -222,13 +222,17 @@ def test_tensor_core_layer0_matches_cuda_core_path(eng_mod):
     _note("tc_vs_simt.v", hp.rel_err(v0.cpu().numpy(), v1.cpu().numpy()))
     _note("tc_vs_simt.loss", hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()))
     _note("tc_vs_simt.grads", hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()))
-    # the bf16 hi/lo split of the middle conv layers and the linear modules leaves ~2^-17 per product: forward
-    # values agree to ~1e-5; a handful of pre-activations within that distance of zero get the other ReLU
-    # mask bit, which moves the gradient of the affected module by ~1/sqrt(units) -- same budget as the oracle
-    assert hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()) < 1e-4
+    # forward operands are fp16 hi/lo (2^-22 per product), so the ReLU decisions agree with the fp32 kernels' on these
+    # inputs and every tensor is compared on its own
+    assert hp.rel_err(pi0.cpu().numpy(), pi1.cpu().numpy()) < 1e-5
     assert hp.rel_err(v0.cpu().numpy(), v1.cpu().numpy()) < 1e-4
-    assert hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()) < 1e-4
-    assert hp.rel_err(g0.cpu().numpy(), g1.cpu().numpy()) < REL_TOL
+    assert hp.rel_err(l0.cpu().numpy(), l1.cpu().numpy()) < 1e-5
+    tt = po.tensor_table(cfg)
+    pop = make_pop(eng_mod, cfg, 1, 1)
+    for t, d in zip(tt, pop.tensors):
+        sl = slice(d["offset"], d["offset"] + d["length"])
+        assert hp.rel_err(g0[sl].cpu().numpy(), g1[sl].cpu().numpy()) < REL_TOL, t["name"]
+    pop.close()
 
 
 def test_pi_underflow_case(eng_mod):
@@ -575,6 +579,84 @@ def test_tensor_core_matches_cuda_core_path_l4(eng_mod):
     assert hp.rel_err(pi0, pi1) < 1e-4 and hp.rel_err(v0, v1) < 1e-4 and hp.rel_err(l0, l1) < 1e-4
     worst = max((hp.rel_err(a, b), t["name"]) for a, b, t in zip(g0, g1, po.tensor_table(cfg)))
     _note("tc_vs_simt_l4.worst_grad", worst[0])
-    # per tensor: arithmetic differences are ~1e-5; a ReLU-mask flip moves one module's gradient by ~1/sqrt(units)
-    assert worst[0] < 2e-2, worst
-    assert hp.rel_err(np.concatenate([x.ravel() for x in g0]), np.concatenate([x.ravel() for x in g1])) < REL_TOL
+    # per tensor (forward operands are fp16 hi/lo, so the ReLU decisions agree with the fp32 kernels' on these inputs)
+    assert worst[0] < REL_TOL, worst
+
+
+# ---------------------------------------------------------------------------
+# population scale, per tensor, against the fp64 oracle -- with the fp32 oracle beside it
+# ---------------------------------------------------------------------------
+FRAGILE = 1e-5      # a ReLU decision may differ from the fp64 oracle's only where |pre| < FRAGILE * rms(pre of that module)
+
+
+def _per_tensor_vs_fp64(eng_mod, cfg, P, B, seed, tag, masks=None, frozen_path=None, flags=0):
+    """One population step against the fp64 oracle, every output and every gradient tensor on its own.
+
+    A ReLU unit whose pre-activation is within fp32 rounding of zero can fall on either side in ANY fp32-level
+    implementation (the fp32 evaluation of the oracle itself flips a few per million against fp64), and one flipped
+    unit moves a small tensor's gradient by far more than 1e-3.  So the comparison has two parts:
+      1. the CUDA path's ReLU decisions (pn_debug_read_relu_masks) equal the fp64 oracle's except on units with
+         |pre| < FRAGILE * rms(pre) -- counted and recorded;
+      2. against the fp64 oracle evaluated WITH the CUDA path's decisions, every tensor is within REL_TOL.
+    The unconditioned comparison and the fp32 oracle's own distance from fp64 are recorded beside it."""
+    params = po.init_params(cfg, seed)
+    frames, actions, td, r, m0 = hp.synth_inputs(cfg, P, B, seed + 100)
+    masks = m0 if masks is None else masks
+    pre = [{} for _ in range(P)]
+    pi64, v64, l64, G64 = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", dtype="float64",
+                                             pre_out=pre)
+    pi32, v32, l32, G32 = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", dtype="float32")
+    pop = make_pop(eng_mod, cfg, P, B, params, masks, flags=flags)
+    if frozen_path is not None:
+        pop.set_fixed_path(frozen_path)
+    loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
+    G = pop.dump(pop.grads)
+    dec = [pop.relu_decisions(l, B) for l in range(cfg.L)]
+    override, flips, total = [], [], 0
+    for p in range(P):
+        d = {}
+        for (l, j), pr in pre[p].items():
+            mk = dec[l][p, :, j].reshape(pr.shape)
+            d[(l, j)] = mk
+            diff = mk != (pr > 0)
+            total += pr.size
+            if diff.any():
+                flips += [float(x) for x in np.abs(pr[diff]) / np.sqrt(np.mean(pr ** 2))]
+        override.append(d)
+    piF, vF, lF, GF = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", dtype="float64",
+                                         relu_override=override)
+    names = [t["name"] for t in po.tensor_table(cfg)]
+
+    def errs(pi_, v_, l_, G_, ref):
+        e = {"pi": hp.rel_err(pi_, ref[0]), "v": hp.rel_err(v_, ref[1]), "loss": hp.rel_err(l_, ref[2])}
+        e.update({"grad/" + n: hp.rel_err(a, b) for n, a, b in zip(names, G_, ref[3])})
+        return e
+
+    out = (pi.cpu().numpy(), v.cpu().numpy(), loss.cpu().numpy(), G)
+    same = errs(*out, (piF, vF, lF, GF))              # same ReLU decisions: arithmetic only
+    plain = errs(*out, (pi64, v64, l64, G64))         # unconditioned
+    f32 = errs(pi32, v32, l32, G32, (pi64, v64, l64, G64))
+    pop.close()
+    for key, e in (("cuda_same_decisions", same), ("cuda_unconditioned", plain), ("oracle_fp32", f32)):
+        w = max(e, key=e.get)
+        _report["%s.%s.worst" % (tag, key)] = [w, e[w]]
+    _report[tag + ".relu_units"] = total
+    _report[tag + ".relu_decisions_differing"] = len(flips)
+    _report[tag + ".relu_differing_max_abs_pre_over_rms"] = max(flips) if flips else 0.0
+    _note(tag + ".cuda_same_decisions.pi", same["pi"])
+    return same, plain, f32, flips, total
+
+
+def _check_population(same, flips, total):
+    assert all(f < FRAGILE for f in flips), ("a ReLU decision differs on a well-conditioned unit", max(flips))
+    assert len(flips) <= max(8, 1e-5 * total), (len(flips), total)
+    bad = {k: x for k, x in same.items() if not x < REL_TOL}
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("cfgname,P,B", [("C1", 16, 32), ("C3", 6, 32)])
+def test_population_scale_per_tensor_vs_fp64(eng_mod, cfgname, P, B):
+    """north_star's 1e-3, per tensor, at population scale: 16 paths x 32 of the C2 net, 6 x 32 of the C3 net."""
+    cfg = getattr(hp, cfgname)
+    same, plain, f32, flips, total = _per_tensor_vs_fp64(eng_mod, cfg, P, B, 3, "pop_%s_%dx%d" % (cfgname, P, B))
+    _check_population(same, flips, total)
