@@ -169,6 +169,16 @@ PN_API int pn_train_step_host(pn_handle* h, const void* frames_host, int frames_
 PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* frames_host, int frames_are_u8,
                                 const int32_t* actions_host, const float* td_host, const float* r_host, int B,
                                 void* copy_stream);
+
+/* pn_stage_inputs_host for a rollout: consecutive transitions of one rollout share C-1 of the C planes of their frame
+ * stacks (GameState keeps the C most recent frames: game_state.py:62-66 reset, :75-81 step), so the host ships only
+ * the B + C - 1 distinct planes of every path and the stacks are rebuilt on the device:
+ *     planes_host [P][B + C - 1][H][W] u8;  planes[p][0..C-1] = the channels of the rollout's first state (after a
+ *     reset: C copies of the first frame), planes[p][C-1+i] = the frame observed after step i;
+ *     frames[p][b][y][x][c] = planes[p][b + c][y][x].
+ * 3.7x fewer bytes over PCIe at B = 32, C = 4.  Then call pn_train_step_staged as for pn_stage_inputs_host. */
+PN_API int pn_stage_rollout_host(pn_handle* h, int slot, const uint8_t* planes_host, const int32_t* actions_host,
+                                 const float* td_host, const float* r_host, int B, void* copy_stream);
 PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, float* loss_host, void* stream);
 
 /* Multi-GPU overlap (the reference has one process and no exchange).  The gradient slab is
@@ -239,6 +249,11 @@ PN_API int pn_rmsprop_apply_noalloc(float* params_dev, float* ms_dev, float* mom
                                     float clip_norm, void* stream);
 
 /* ---- measurement support (no counterpart in the reference) ------------- */
+
+/* Which engine each layer of this handle runs on ("conv0=tcgen05,conv1=tcgen05,lin=tcgen05"): geometries the
+ * tensor-core kernels do not take (and cfg.flags) fall back to the CUDA-core kernels, and this makes that visible.
+ * Returns the length of the full string. */
+PN_API int pn_engine_paths(const pn_handle* h, char* out, int capacity);
 
 /* Kernels launched through this handle since pn_create. */
 PN_API int64_t pn_launch_count(const pn_handle* h);

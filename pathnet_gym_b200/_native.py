@@ -54,6 +54,7 @@ SIGNATURES = {
     "pn_workspace_bytes": (C.c_int64, [_vp]),
     "pn_debug_read": (_i, [_vp, _vp, _i]),
     "pn_debug_read_relu_masks": (C.c_int64, [_vp, _i, _i, _vp, C.c_int64]),
+    "pn_engine_paths": (_i, [_vp, C.c_char_p, _i]),
     "pn_launch_count": (C.c_int64, [_vp]),
     "pn_lin_grads_region": (_i, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "pn_stream_wait_lin_grads": (_i, [_vp, _vp]),
@@ -69,6 +70,7 @@ SIGNATURES = {
     "pn_train_step": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
     "pn_train_step_host": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _f, _vp, _vp]),
     "pn_stage_inputs_host": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i, _vp]),
+    "pn_stage_rollout_host": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _vp]),
     "pn_train_step_staged": (_i, [_vp, _i, _f, _vp, _vp]),
     "pn_rmsprop_apply": (_i, [_vp, _f, _f, _f, _f, _f, _vp]),
     "pn_rmsprop_apply_range": (_i, [_vp, _i, _i, _i, _f, _f, _f, _f, _f, _vp]),

@@ -9,7 +9,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libpathnet_b200.so")
 SOURCES = ["pn_api.cu", "pn_net_kernels.cu", "pn_rmsprop.cu", "pn_genotype.cu", "pn_noalloc.cu", "pn_conv0_tc.cu", "pn_lin_tc.cu", "pn_conv_mid.cu", "pn_conv_mid_tc.cu", "pn_rollout.cu", "pn_peer.cu"]
-HEADERS = [os.path.join(CSRC, "pn_internal.cuh"), os.path.join(CSRC, "pn_tc.cuh"), os.path.join(ROOT, "include", "pathnet_b200.h")]
+HEADERS = [os.path.join(CSRC, "pn_internal.cuh"), os.path.join(CSRC, "pn_tc.cuh"), os.path.join(CSRC, "pn_rms_core.cuh"), os.path.join(ROOT, "include", "pathnet_b200.h")]
 
 
 def _nvcc():
@@ -20,7 +20,11 @@ def _nvcc():
 
 
 def sources():
-    return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    out = [os.path.join(CSRC, s) for s in SOURCES]
+    missing = [p for p in out if not os.path.exists(p)]
+    if missing:
+        raise RuntimeError("listed CUDA sources are missing: %s" % ", ".join(missing))
+    return out
 
 
 def is_stale():

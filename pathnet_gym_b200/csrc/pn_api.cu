@@ -109,7 +109,9 @@ int pn_set_smem_cached(pn_handle* h, const void* kern, int bytes) {
     static std::mutex mu;
     static std::map<std::pair<int, const void*>, int> have;       // (device, kernel) -> largest size set so far
     std::lock_guard<std::mutex> lock(mu);
-    int& cur = have[std::make_pair(h->cfg.device, kern)];
+    int dev = h->cfg.device;
+    cudaGetDevice(&dev);                                            // the attribute applies to the CURRENT device
+    int& cur = have[std::make_pair(dev, kern)];
     if (bytes > cur) {
         PN_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
         cur = bytes;
@@ -239,7 +241,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     cudaFree(h->d_chunk_ss); cudaFree(h->st_frames); cudaFree(h->st_actions); cudaFree(h->st_td);
     cudaFree(h->st_r); cudaFree(h->st_loss);
     for (auto& sl : h->slot) {
-        cudaFree(sl.frames); cudaFree(sl.actions); cudaFree(sl.td); cudaFree(sl.r); cudaFree(sl.loss);
+        cudaFree(sl.frames); cudaFree(sl.planes); cudaFree(sl.actions); cudaFree(sl.td); cudaFree(sl.r); cudaFree(sl.loss);
         if (sl.copied) cudaEventDestroy(sl.copied);
         if (sl.consumed) cudaEventDestroy(sl.consumed);
     }
@@ -281,6 +283,18 @@ extern "C" PN_API int64_t pn_debug_read_relu_masks(pn_handle* h, int layer, int 
     return (int64_t)bytes;
 }
 
+extern "C" PN_API int pn_engine_paths(const pn_handle* h, char* out, int capacity) {
+    if (!h || !out || capacity < 1) return pn_fail_global(PN_ERR_INVALID, "pn_engine_paths: null argument");
+    std::string s;
+    for (int l = 0; l < h->nd.nconv; ++l) {
+        const bool tc = l == 0 ? h->tc_conv0 : h->tc_mid[l];
+        s += "conv" + std::to_string(l) + (tc ? "=tcgen05" : "=cuda-core") + (l == 0 && tc ? " (u8 frames; fp32 frames take the cuda-core kernel)," : ",");
+    }
+    s += std::string("lin=") + (h->tc_lin ? "tcgen05" : "cuda-core");
+    snprintf(out, (size_t)capacity, "%s", s.c_str());
+    return (int)s.size();
+}
+
 extern "C" PN_API int64_t pn_launch_count(const pn_handle* h) { return h ? h->launches : 0; }
 
 extern "C" PN_API int pn_profile_enable(pn_handle* h, int on) {
@@ -320,7 +334,7 @@ extern "C" PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int c
         else {
             static const char* names[] = {"lin_fwd", "head_loss", "grad_reduce", "lin_dgrad", "lin_wgrad",
                                           "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant", "lin_prep",
-                                          "conv_mid_prep", "lin_wprep"};
+                                          "conv_mid_prep", "lin_wprep", "rms_update_lin", "rms_update_small"};
             base = names[slot - PN_PROF_LIN_FWD];
         }
         if (layer >= 0) snprintf(out[n].name, sizeof(out[n].name), "%s_l%d", base, layer);
@@ -395,6 +409,8 @@ extern "C" PN_API int pn_set_frozen(pn_handle* h, const uint8_t* frozen_host) {
     const int nt = (int)h->tensors.size();
     for (int t = 0; t < nt; ++t) h->h_frozen[t] = frozen_host[t] ? 1 : 0;
     PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    // rare (task switch): wait for every update / re-init kernel in flight on any stream before the table changes
+    PN_CUDA(h, cudaDeviceSynchronize());
     PN_CUDA(h, cudaMemcpy(h->d_frozen, h->h_frozen.data(), nt, cudaMemcpyHostToDevice));
     return PN_OK;
 }
@@ -404,6 +420,7 @@ extern "C" PN_API int pn_forward(pn_handle* h, const void* frames_dev, int frame
     if (int rc = check_ready(h, false)) return rc;
     if (int rc = check_B(h, B)) return rc;
     if (!frames_dev) return pn_fail(h, PN_ERR_INVALID, "frames is null");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
     cudaStream_t st = (cudaStream_t)stream;
     if (int rc = pn_launch_forward(h, frames_dev, frames_are_u8, B, false, st)) return rc;
     return pn_launch_heads(h, B, false, nullptr, nullptr, nullptr, 0.f, pi_dev, v_dev, nullptr, st);
@@ -415,6 +432,7 @@ extern "C" PN_API int pn_train_step(pn_handle* h, const void* frames_dev, int fr
     if (int rc = check_ready(h, true)) return rc;
     if (int rc = check_B(h, B)) return rc;
     if (!frames_dev || !actions_dev || !td_dev || !r_dev) return pn_fail(h, PN_ERR_INVALID, "null input array");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
     cudaStream_t st = (cudaStream_t)stream;
     if (int rc = pn_launch_forward(h, frames_dev, frames_are_u8, B, true, st)) return rc;
     if (int rc = pn_launch_heads(h, B, true, actions_dev, td_dev, r_dev, entropy_beta, pi_dev, v_dev, loss_dev, st))
@@ -455,6 +473,32 @@ extern "C" PN_API int pn_train_step_host(pn_handle* h, const void* frames_host, 
     return PN_OK;
 }
 
+namespace {
+// staging slot set-up shared by the two host-input forms: events, small arrays, frame buffer of the full [P, B_max] size
+int prepare_slot(pn_handle* h, pn_handle::StageSlot& s, size_t want_frames) {
+    const size_t Tmax = (size_t)h->T;
+    if (!s.copied) {
+        PN_CUDA(h, cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
+        PN_CUDA(h, cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
+        PN_CUDA(h, cudaMalloc(&s.actions, Tmax * sizeof(int32_t)));
+        PN_CUDA(h, cudaMalloc(&s.td, Tmax * sizeof(float)));
+        PN_CUDA(h, cudaMalloc(&s.r, Tmax * sizeof(float)));
+        PN_CUDA(h, cudaMalloc(&s.loss, (size_t)h->P * sizeof(float)));
+        h->workspace_bytes += (long long)(Tmax * 12 + (size_t)h->P * 4);
+    }
+    if (s.frames_bytes < want_frames) {
+        PN_CUDA(h, cudaDeviceSynchronize());
+        cudaFree(s.frames);
+        s.frames = nullptr; s.frames_bytes = 0;
+        cudaError_t e = cudaMalloc(&s.frames, want_frames);
+        if (e != cudaSuccess) return pn_fail(h, PN_ERR_NOMEM, "frame staging cudaMalloc(%zu): %s", want_frames, cudaGetErrorString(e));
+        s.frames_bytes = want_frames;
+        h->workspace_bytes += (long long)want_frames;
+    }
+    return PN_OK;
+}
+}  // namespace
+
 extern "C" PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* frames_host, int frames_are_u8,
                                            const int32_t* actions_host, const float* td_host, const float* r_host, int B,
                                            void* copy_stream) {
@@ -468,24 +512,7 @@ extern "C" PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* f
     const size_t Tmax = (size_t)h->T, T = (size_t)h->P * B;
     const size_t esz = frames_are_u8 ? 1 : sizeof(float);
     const size_t want = Tmax * h->cfg.H * h->cfg.W * h->cfg.C * esz, fbytes = T * h->cfg.H * h->cfg.W * h->cfg.C * esz;
-    if (!s.copied) {
-        PN_CUDA(h, cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming));
-        PN_CUDA(h, cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
-        PN_CUDA(h, cudaMalloc(&s.actions, Tmax * sizeof(int32_t)));
-        PN_CUDA(h, cudaMalloc(&s.td, Tmax * sizeof(float)));
-        PN_CUDA(h, cudaMalloc(&s.r, Tmax * sizeof(float)));
-        PN_CUDA(h, cudaMalloc(&s.loss, (size_t)h->P * sizeof(float)));
-        h->workspace_bytes += (long long)(Tmax * 12 + (size_t)h->P * 4);
-    }
-    if (s.frames_bytes < want) {
-        PN_CUDA(h, cudaDeviceSynchronize());
-        cudaFree(s.frames);
-        s.frames = nullptr; s.frames_bytes = 0;
-        cudaError_t e = cudaMalloc(&s.frames, want);
-        if (e != cudaSuccess) return pn_fail(h, PN_ERR_NOMEM, "frame staging cudaMalloc(%zu): %s", want, cudaGetErrorString(e));
-        s.frames_bytes = want;
-        h->workspace_bytes += (long long)want;
-    }
+    if (int rc = prepare_slot(h, s, want)) return rc;
     // do not overwrite the slot while the step that last used it is still reading it
     if (s.used) PN_CUDA(h, cudaStreamWaitEvent(cs, s.consumed, 0));
     PN_CUDA(h, cudaMemcpyAsync(s.frames, frames_host, fbytes, cudaMemcpyHostToDevice, cs));
@@ -494,6 +521,39 @@ extern "C" PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* f
     PN_CUDA(h, cudaMemcpyAsync(s.r, r_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
     PN_CUDA(h, cudaEventRecord(s.copied, cs));
     s.B = B; s.is_u8 = frames_are_u8; s.used = true;
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_stage_rollout_host(pn_handle* h, int slot, const uint8_t* planes_host, const int32_t* actions_host,
+                                            const float* td_host, const float* r_host, int B, void* copy_stream) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "null handle");
+    if (slot < 0 || slot > 1) return pn_fail(h, PN_ERR_INVALID, "slot must be 0 or 1");
+    if (int rc = check_B(h, B)) return rc;
+    if (!planes_host || !actions_host || !td_host || !r_host) return pn_fail(h, PN_ERR_INVALID, "null input array");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    pn_handle::StageSlot& s = h->slot[slot];
+    cudaStream_t cs = (cudaStream_t)copy_stream;
+    const size_t Tmax = (size_t)h->T, T = (size_t)h->P * B;
+    const size_t HW = (size_t)h->cfg.H * h->cfg.W, C = (size_t)h->cfg.C;
+    if (int rc = prepare_slot(h, s, Tmax * HW * C)) return rc;
+    const size_t pwant = (size_t)h->P * (h->Bmax + C - 1) * HW, pbytes = (size_t)h->P * (B + C - 1) * HW;
+    if (s.planes_bytes < pwant) {
+        PN_CUDA(h, cudaDeviceSynchronize());
+        cudaFree(s.planes);
+        s.planes = nullptr; s.planes_bytes = 0;
+        cudaError_t e = cudaMalloc(&s.planes, pwant);
+        if (e != cudaSuccess) return pn_fail(h, PN_ERR_NOMEM, "plane staging cudaMalloc(%zu): %s", pwant, cudaGetErrorString(e));
+        s.planes_bytes = pwant;
+        h->workspace_bytes += (long long)pwant;
+    }
+    if (s.used) PN_CUDA(h, cudaStreamWaitEvent(cs, s.consumed, 0));
+    PN_CUDA(h, cudaMemcpyAsync(s.planes, planes_host, pbytes, cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaMemcpyAsync(s.actions, actions_host, T * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaMemcpyAsync(s.td, td_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
+    PN_CUDA(h, cudaMemcpyAsync(s.r, r_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
+    if (int rc = pn_launch_expand_planes(h, s.planes, B, (uint8_t*)s.frames, cs)) return rc;
+    PN_CUDA(h, cudaEventRecord(s.copied, cs));
+    s.B = B; s.is_u8 = 1; s.used = true;
     return PN_OK;
 }
 
@@ -517,6 +577,7 @@ extern "C" PN_API int pn_rmsprop_apply(pn_handle* h, float lr, float decay, floa
     if (!h->params || !h->ms || !h->grads) return pn_fail(h, PN_ERR_STATE, "params / rms / grads slabs must be bound");
     if (momentum != 0.0f && !h->mom) return pn_fail(h, PN_ERR_STATE, "momentum != 0 needs a momentum slab");
     if (!(clip_norm > 0.0f)) return pn_fail(h, PN_ERR_INVALID, "clip_norm must be > 0");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
     return pn_launch_rmsprop(h, 0, (int)h->tensors.size(), false, lr, decay, momentum, epsilon, clip_norm, (cudaStream_t)stream);
 }
 
@@ -529,6 +590,7 @@ extern "C" PN_API int pn_rmsprop_apply_range(pn_handle* h, int first_tensor, int
     const int nt = (int)h->tensors.size();
     if (first_tensor < 0 || n_tensors < 0 || first_tensor + n_tensors > nt)
         return pn_fail(h, PN_ERR_INVALID, "tensor range [%d, %d) outside 0..%d", first_tensor, first_tensor + n_tensors, nt);
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
     return pn_launch_rmsprop(h, first_tensor, n_tensors, complement != 0, lr, decay, momentum, epsilon, clip_norm,
                              (cudaStream_t)stream);
 }
@@ -536,5 +598,6 @@ extern "C" PN_API int pn_rmsprop_apply_range(pn_handle* h, int first_tensor, int
 extern "C" PN_API int pn_reinit_unfrozen(pn_handle* h, const float* backup_params_dev, void* stream) {
     if (!h) return pn_fail_global(PN_ERR_INVALID, "null handle");
     if (!h->params || !backup_params_dev) return pn_fail(h, PN_ERR_STATE, "params slab and backup must be set");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
     return pn_launch_reinit(h, backup_params_dev, (cudaStream_t)stream);
 }

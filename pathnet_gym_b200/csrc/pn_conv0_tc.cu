@@ -32,6 +32,7 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <vector>
 
 using namespace pntc;
 
@@ -48,6 +49,14 @@ constexpr int kAccCols = 128;            // TMEM columns per accumulator stage (
 constexpr int kSlotBytes = 3 * 2048;     // one module's B rows: 3 digit groups x (8 channels x 256 K bytes)
 constexpr int kPassSlots = 4;            // modules per MMA pass
 constexpr int kQMax = 1 << 22;
+
+// Work split over the CTAs.  A transition's cost depends on how many modules its path has active in layer 0 (and jumps when
+// a second MMA pass is needed), so equal COUNTS per CTA leave the kernel waiting for the CTA that drew the expensive
+// paths: with 10 % of the paths at five modules the forward kernel took 241 us against 130 us for the same work spread
+// evenly.  The host cuts the path-major sequence of work units at equal cumulative cost instead (cost table measured on
+// B200 with uniform populations, tools/layer0_cost.py); CTA c owns units [b[c], b[c+1]).
+struct TcBounds { int b[160]; };
+constexpr int kMaxCtas = 159;
 
 struct TcGeom {
     int H, W, C, s;                  // frame, stride (k = 2s, s*C = 16)
@@ -135,8 +144,8 @@ __device__ __forceinline__ long long pinned_clock() {
 __global__ void __launch_bounds__(kFwdThreads, 1)
 conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __restrict__ w8,
                     const float* __restrict__ wscale, const float* __restrict__ params, PnNetDesc nd,
-                    const uint32_t* __restrict__ masks, int B, int T, TcGeom gm, float* __restrict__ Y,
-                    uint8_t* __restrict__ R, long long* __restrict__ dbg) {
+                    const uint32_t* __restrict__ masks, int B, int T, TcGeom gm, const __grid_constant__ TcBounds bounds,
+                    float* __restrict__ Y, uint8_t* __restrict__ R, long long* __restrict__ dbg) {
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* frame_s = smem;
     uint8_t* Bs = smem + (size_t)gm.nst * gm.stage_bytes;
@@ -157,8 +166,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
     // broadcast through a shuffle so that the compiler knows the warp index is warp-uniform (role branches
     // then count as uniform control flow and the MMA operands can live in uniform registers)
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
-    const int t_lo = (int)((long long)T * blockIdx.x / gridDim.x);
-    const int t_hi = (int)((long long)T * (blockIdx.x + 1) / gridDim.x);
+    const int t_lo = bounds.b[blockIdx.x], t_hi = bounds.b[blockIdx.x + 1];     // equal cumulative cost, not equal counts
     const int npix = gm.OH * gm.OW;
     const bool dbg_detail = dbg && dbg[gridDim.x * 8] == 1;
     const long long t_entry = dbg ? clock64() : 0;
@@ -516,7 +524,8 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     // then count as uniform control flow and the MMA operands can live in uniform registers)
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int npix = gm.OH * gm.OW;
-    const int nitems = P * nch;
+    const int nitems = P * nch;      // round-robin over the CTAs: a path's chunks land on different CTAs, which spreads expensive
+                                     // paths by itself (a contiguous cost-balanced split measured worse here: 237 vs 214 us)
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
@@ -847,6 +856,36 @@ int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T,
     return PN_OK;
 }
 
+// relative cost of one transition by the number of active layer-0 modules of its path (us per 8192 transitions, B200)
+const float kFwdCost[11] = {70.f, 96.f, 107.f, 123.f, 142.f, 338.f, 348.f, 364.f, 381.f, 520.f, 540.f};
+
+// cut `units` work units (unit u belongs to path u / per_path) into `ctas` contiguous ranges of equal cumulative cost
+void balance_units(const pn_handle* h, const float* table, int per_path, int ctas, TcBounds& out) {
+    const int P = h->P, L = h->cfg.L;
+    std::vector<double> cum((size_t)P + 1, 0.0);
+    for (int p = 0; p < P; ++p) {
+        const int ns = std::min(10, __builtin_popcount(h->h_masks[(size_t)p * L]));
+        cum[p + 1] = cum[p] + (double)per_path * (double)table[ns];
+    }
+    const double total = cum[P];
+    const long long units = (long long)P * per_path;
+    out.b[0] = 0;
+    int p = 0;
+    for (int c = 1; c < ctas; ++c) {
+        const double want = total * c / ctas;
+        while (p < P && cum[p + 1] <= want) ++p;
+        long long u;
+        if (p >= P || total <= 0.0) u = units * c / ctas;
+        else {
+            const double per = (cum[p + 1] - cum[p]) / per_path;           // cost of one unit of path p
+            u = (long long)p * per_path + (per > 0.0 ? (long long)((want - cum[p]) / per + 0.5) : 0);
+        }
+        u = std::max<long long>(u, out.b[c - 1]);
+        out.b[c] = (int)std::min(u, units);
+    }
+    out.b[ctas] = (int)units;
+}
+
 }  // namespace
 
 bool pn_conv0_tc_supported(const pn_handle* h) {
@@ -879,12 +918,14 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     }
     PN_LAUNCH_CHECK(h, "conv0_wprep_kernel");
     PN_SET_SMEM(h, conv0_fwd_tc_kernel, smem_bytes);
-    const int grid = T < h->num_sms ? T : h->num_sms;
+    const int grid = std::min(std::min(T, h->num_sms), kMaxCtas);
+    TcBounds bounds;
+    balance_units(h, kFwdCost, B, grid, bounds);
     CUtensorMap tmap;
     if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + 0, st);
-        conv0_fwd_tc_kernel<<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g,
+        conv0_fwd_tc_kernel<<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g, bounds,
                                                                  h->act[0], h->rmask[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_fwd_tc_kernel");
@@ -923,7 +964,7 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     const size_t smem_bytes = 2 * (size_t)g.stage_bytes + dq_total + 16 * sizeof(uint64_t);
     PN_SET_SMEM(h, conv0_wgrad_tc_kernel, smem_bytes);
     const int items = P * nch;
-    const int grid = items < h->num_sms ? items : h->num_sms;
+    const int grid = std::min(std::min(items, h->num_sms), kMaxCtas);
     CUtensorMap tmap;
     if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
     {

@@ -436,8 +436,8 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + l, st);
         conv_mid_wgrad_kernel<<<grid, kG * (g.KK / 2), smem, st>>>(h->act[l - 1], h->dact[l], h->rmask[l], nd, l, g, h->d_masks,
                                                                   B, cs, h->nch, h->wpart[l]);
+        PN_LAUNCH_CHECK(h, "conv_mid_wgrad_kernel");
     }
-    PN_LAUNCH_CHECK(h, "conv_mid_wgrad_kernel");
     *nch_used = nch;
     if (do_dgrad) {
         const size_t smem = ((size_t)kG * kPass * 2 * g.npix + (size_t)kPass * g.KK * 2) * 16;
@@ -452,7 +452,7 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
         conv_mid_dgrad_kernel<<<grid, threads, smem, st>>>(h->dact[l], h->rmask[l], h->params, nd, l, g, h->d_masks, B,
                                                           h->dact[l - 1], amax);
         h->absmax_fused = amax != nullptr;
+        PN_LAUNCH_CHECK(h, "conv_mid_dgrad_kernel");
     }
-    PN_LAUNCH_CHECK(h, "conv_mid_dgrad_kernel");
     return PN_OK;
 }

@@ -44,6 +44,8 @@ enum PnProfSlot {
     PN_PROF_LIN_PREP,
     PN_PROF_CONV_MID_PREP,
     PN_PROF_LIN_WPREP,
+    PN_PROF_RMS_UPDATE_LIN,       // sumsq + update pair over the linear modules' tensors
+    PN_PROF_RMS_UPDATE_SMALL,     // the same pair over everything else (conv + head tensors)
     PN_PROF_NSLOTS
 };
 #define PN_PROF_RING 64
@@ -112,6 +114,7 @@ struct pn_handle {
     // double-buffered staging for the pipelined host path (pn_stage_inputs_host / pn_train_step_staged)
     struct StageSlot {
         void* frames = nullptr; size_t frames_bytes = 0;
+        uint8_t* planes = nullptr; size_t planes_bytes = 0;     // pn_stage_rollout_host: the rollout's unique planes
         int32_t* actions = nullptr; float* td = nullptr; float* r = nullptr; float* loss = nullptr;
         cudaEvent_t copied = nullptr, consumed = nullptr;
         bool used = false; int B = 0; int is_u8 = 1;
@@ -193,6 +196,8 @@ size_t pn_lin_tc_scratch_bytes(const pn_handle* h);
 int pn_launch_lin_wsplit(pn_handle* h, cudaStream_t st);
 int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st);
 int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st);
+// pn_rollout.cu
+int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, cudaStream_t st);
 // pn_rmsprop.cu
 int pn_launch_rmsprop(pn_handle* h, int first_tensor, int n_tensors, bool complement, float lr, float decay,
                       float momentum, float eps, float clip, cudaStream_t st);

@@ -26,6 +26,7 @@
 // First call on a device.  It looks up the array's device address (cudaGetSymbolAddress, with the
 // device current) and caches it.  Issue that first call before any stream capture begins.
 #include "pn_internal.cuh"
+#include "pn_rms_core.cuh"
 
 #include <mutex>
 
@@ -45,64 +46,33 @@ struct NoallocTable {                       // passed by value (kernel parameter
     int len[PN_NOALLOC_MAX_TENSORS];
     long long off[PN_NOALLOC_MAX_TENSORS];
     unsigned char frozen[PN_NOALLOC_MAX_TENSORS];
+
+    // chunk -> the same description the handle form reads from its device tables, so both forms run the same
+    // kernel bodies (pn_rms_core.cuh) and give bit-identical results
+    __device__ __forceinline__ pnrms::ChunkRef chunk(int cid) const {
+        int lo = 0, hi = n - 1;             // last t with chunk0[t] <= cid
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (chunk0[mid] <= cid) lo = mid; else hi = mid - 1;
+        }
+        const int t = lo, c = cid - chunk0[t];
+        pnrms::ChunkRef r;
+        r.tensor = t;
+        r.off = off[t] + (long long)c * PN_RMS_CHUNK;
+        r.len = (int)min((long long)PN_RMS_CHUNK, (long long)len[t] - (long long)c * PN_RMS_CHUNK);
+        r.frozen = frozen[t] != 0;
+        r.chunk0 = chunk0[t];
+        r.nchunks = chunk0[t + 1] - chunk0[t];
+        return r;
+    }
 };
 
-constexpr int kThreads = 256;
-
-__device__ __forceinline__ int find_tensor(const NoallocTable& tb, int chunk) {
-    int lo = 0, hi = tb.n - 1;               // last t with chunk0[t] <= chunk
-    while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (tb.chunk0[mid] <= chunk) lo = mid; else hi = mid - 1;
-    }
-    return lo;
-}
-
-__device__ __forceinline__ float block_sum_na(float v, float* red) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (lane == 0) red[w] = v;
-    __syncthreads();
-    float s = 0.f;
-    if (threadIdx.x < 32) {
-        s = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    }
-    return s;
-}
+using pnrms::kThreads;
 
 __global__ void __launch_bounds__(kThreads)
 noalloc_sumsq_kernel(const float* __restrict__ grads, const __grid_constant__ NoallocTable tb,
                      float* __restrict__ chunk_ss) {
-    __shared__ float red[32];
-    const int t = find_tensor(tb, blockIdx.x);
-    if (tb.frozen[t]) return;
-    const int c = blockIdx.x - tb.chunk0[t];
-    const long long o = (long long)c * PN_RMS_CHUNK;
-    const int len = (int)min((long long)PN_RMS_CHUNK, (long long)tb.len[t] - o);
-    const float* g = grads + tb.off[t] + o;
-    const bool vec = ((tb.off[t] & 3) == 0);
-    const int n4 = vec ? (len >> 2) : 0;
-    float s = 0.f;
-    for (int i = threadIdx.x; i < n4; i += kThreads) {
-        const float4 v = reinterpret_cast<const float4*>(g)[i];
-        s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
-    }
-    for (int i = (n4 << 2) + threadIdx.x; i < len; i += kThreads) s = fmaf(g[i], g[i], s);
-    s = block_sum_na(s, red);
-    if (threadIdx.x == 0) chunk_ss[blockIdx.x] = s;
-}
-
-template <bool HAS_MOM>
-__device__ __forceinline__ void rms_elem_na(float g, float& var, float& ms, float& mom, float clip, float scale,
-                                            float lr, float omd, float momentum, float eps) {
-    const float gc = (g * clip) * scale;
-    ms = ms + (gc * gc - ms) * omd;
-    const float upd = (gc * lr) / sqrtf(eps + ms);
-    if (HAS_MOM) { mom = mom * momentum + upd; var -= mom; }
-    else { var -= upd; }
+    pnrms::sumsq_body(tb, (int)blockIdx.x, grads, chunk_ss);
 }
 
 template <bool HAS_MOM>
@@ -111,45 +81,7 @@ noalloc_update_kernel(float* __restrict__ params, float* __restrict__ msl, float
                       const float* __restrict__ grads, const __grid_constant__ NoallocTable tb,
                       const float* __restrict__ chunk_ss, float lr, float decay, float momentum, float eps,
                       float clip) {
-    __shared__ float s_scale;
-    const int t = find_tensor(tb, blockIdx.x);
-    if (tb.frozen[t]) return;
-    if (threadIdx.x == 0) {
-        float ss = 0.f;
-        for (int c = tb.chunk0[t]; c < tb.chunk0[t + 1]; ++c) ss += chunk_ss[c];
-        s_scale = fminf(1.0f / sqrtf(ss), 1.0f / clip);
-    }
-    __syncthreads();
-    const float scale = s_scale, omd = 1.0f - decay;
-    const int c = blockIdx.x - tb.chunk0[t];
-    const long long o = tb.off[t] + (long long)c * PN_RMS_CHUNK;
-    const int len = (int)min((long long)PN_RMS_CHUNK, (long long)tb.len[t] - (long long)c * PN_RMS_CHUNK);
-    float* pv = params + o;
-    float* pm = msl + o;
-    float* pq = HAS_MOM ? moml + o : nullptr;
-    const float* g = grads + o;
-    const bool vec = ((tb.off[t] & 3) == 0);
-    const int n4 = vec ? (len >> 2) : 0;
-    for (int i = threadIdx.x; i < n4; i += kThreads) {
-        const float4 gv = reinterpret_cast<const float4*>(g)[i];
-        float4 v = reinterpret_cast<float4*>(pv)[i];
-        float4 m = reinterpret_cast<float4*>(pm)[i];
-        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (HAS_MOM) q = reinterpret_cast<float4*>(pq)[i];
-        rms_elem_na<HAS_MOM>(gv.x, v.x, m.x, q.x, clip, scale, lr, omd, momentum, eps);
-        rms_elem_na<HAS_MOM>(gv.y, v.y, m.y, q.y, clip, scale, lr, omd, momentum, eps);
-        rms_elem_na<HAS_MOM>(gv.z, v.z, m.z, q.z, clip, scale, lr, omd, momentum, eps);
-        rms_elem_na<HAS_MOM>(gv.w, v.w, m.w, q.w, clip, scale, lr, omd, momentum, eps);
-        reinterpret_cast<float4*>(pv)[i] = v;
-        reinterpret_cast<float4*>(pm)[i] = m;
-        if (HAS_MOM) reinterpret_cast<float4*>(pq)[i] = q;
-    }
-    for (int i = (n4 << 2) + threadIdx.x; i < len; i += kThreads) {
-        float v = pv[i], m = pm[i], q = HAS_MOM ? pq[i] : 0.f;
-        rms_elem_na<HAS_MOM>(g[i], v, m, q, clip, scale, lr, omd, momentum, eps);
-        pv[i] = v; pm[i] = m;
-        if (HAS_MOM) pq[i] = q;
-    }
+    pnrms::update_body<HAS_MOM>(tb, (int)blockIdx.x, params, msl, moml, grads, chunk_ss, lr, decay, momentum, eps, clip);
 }
 
 std::mutex g_setup_mutex;
@@ -221,13 +153,14 @@ extern "C" PN_API int pn_rmsprop_apply_noalloc(float* params_dev, float* ms_dev,
     noalloc_sumsq_kernel<<<nblk, kThreads, 0, st>>>(grads_dev, tb, scratch);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return pn_fail_global(PN_ERR_CUDA, "noalloc_sumsq_kernel: %s", cudaGetErrorString(e));
+    // (launched so that its blocks may start their loads while the first kernel drains; see pn_rms_core.cuh)
     if (momentum != 0.0f)
-        noalloc_update_kernel<true><<<nblk, kThreads, 0, st>>>(params_dev, ms_dev, mom_dev, grads_dev, tb, scratch, lr,
-                                                               decay, momentum, epsilon, clip_norm);
+        e = pnrms::launch_pdl(noalloc_update_kernel<true>, nblk, st, params_dev, ms_dev, mom_dev, grads_dev, tb,
+                              (const float*)scratch, lr, decay, momentum, epsilon, clip_norm);
     else
-        noalloc_update_kernel<false><<<nblk, kThreads, 0, st>>>(params_dev, ms_dev, nullptr, grads_dev, tb, scratch,
-                                                                lr, decay, momentum, epsilon, clip_norm);
-    e = cudaGetLastError();
+        e = pnrms::launch_pdl(noalloc_update_kernel<false>, nblk, st, params_dev, ms_dev, (float*)nullptr, grads_dev, tb,
+                              (const float*)scratch, lr, decay, momentum, epsilon, clip_norm);
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return pn_fail_global(PN_ERR_CUDA, "noalloc_update_kernel: %s", cudaGetErrorString(e));
     return PN_OK;
 }

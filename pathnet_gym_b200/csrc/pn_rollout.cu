@@ -49,7 +49,48 @@ __global__ void nstep_returns_kernel(const float* __restrict__ rewards, const fl
     }
 }
 
+// ---- frame stacks from the rollout's unique planes ------------------------------------------------------------------
+// GameState keeps s_t as the stack of the C most recent preprocessed frames (game_state.py:62-66 reset: C copies of the
+// first frame; :75-81 step: s_t1 = append(s_t[:, :, 1:], x_t1)), so consecutive transitions of one rollout share C-1 of
+// their C channels.  A batch of B transitions therefore consists of only B + C - 1 distinct H x W planes per path:
+//     planes[p][0 .. C-1] = the channels of s_0 (after a reset: C copies of the first frame),  planes[p][C-1+i] = x_i
+//     frames[p][b][y][x][c] = planes[p][b + c][y][x]
+// The host ships the planes (3.7x fewer bytes over PCIe at B = 32, C = 4); this kernel rebuilds the stacks the layer-0
+// kernels read.  One thread = 4 pixels x C channels (C == 4: a 4x4 byte transpose, 16-byte coalesced stores).
+__global__ void __launch_bounds__(256)
+expand_planes_kernel(const uint8_t* __restrict__ planes, int P, int B, int HW, int C, uint8_t* __restrict__ frames) {
+    const int t = blockIdx.y;                                   // transition p * B + b
+    const int p = t / B, b = t - p * B;
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;        // group of 4 pixels
+    if (q * 4 >= HW) return;
+    const uint8_t* src = planes + ((size_t)p * (B + C - 1) + b) * HW + (size_t)q * 4;
+    uint8_t* dst = frames + ((size_t)t * HW + (size_t)q * 4) * C;
+    if (C == 4) {
+        const uint32_t a0 = *reinterpret_cast<const uint32_t*>(src), a1 = *reinterpret_cast<const uint32_t*>(src + HW);
+        const uint32_t a2 = *reinterpret_cast<const uint32_t*>(src + 2 * (size_t)HW), a3 = *reinterpret_cast<const uint32_t*>(src + 3 * (size_t)HW);
+        // byte k of plane word a_c is pixel k, channel c -> output word k holds bytes (a0.k, a1.k, a2.k, a3.k)
+        const uint32_t lo01 = __byte_perm(a0, a1, 0x5140), hi01 = __byte_perm(a0, a1, 0x7362);   // (a0.0 a1.0 a0.1 a1.1), (a0.2 a1.2 a0.3 a1.3)
+        const uint32_t lo23 = __byte_perm(a2, a3, 0x5140), hi23 = __byte_perm(a2, a3, 0x7362);
+        uint4 o;
+        o.x = __byte_perm(lo01, lo23, 0x5410); o.y = __byte_perm(lo01, lo23, 0x7632);
+        o.z = __byte_perm(hi01, hi23, 0x5410); o.w = __byte_perm(hi01, hi23, 0x7632);
+        *reinterpret_cast<uint4*>(dst) = o;
+    } else {
+        for (int k = 0; k < 4; ++k)
+            for (int c = 0; c < C; ++c) dst[k * C + c] = src[(size_t)c * HW + k];
+    }
+}
+
 }  // namespace
+
+int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, cudaStream_t st) {
+    const int HW = h->cfg.H * h->cfg.W, C = h->cfg.C;
+    if (HW % 4) return pn_fail(h, PN_ERR_INVALID, "H*W = %d must be a multiple of 4", HW);
+    dim3 grid((HW / 4 + 255) / 256, h->P * B);
+    expand_planes_kernel<<<grid, 256, 0, st>>>(planes_dev, h->P, B, HW, C, frames_dev);
+    PN_LAUNCH_CHECK(h, "expand_planes_kernel");
+    return PN_OK;
+}
 
 extern "C" PN_API int pn_sample_actions(const float* pi_dev, int n, int A, uint64_t seed, uint32_t epoch, uint32_t id0,
                                         int32_t* actions_dev, void* stream) {

@@ -224,6 +224,18 @@ class PathNetPopulation:
         nat.check(self.lib.pn_stage_inputs_host(self._h, int(slot), _ptr(frames), u8, _ptr(actions), _ptr(td), _ptr(r), B,
                                                 C.c_void_p(cs.cuda_stream)), self._h)
 
+    def stage_rollout_host(self, slot, planes, actions, td, r, copy_stream: Optional[torch.cuda.Stream] = None):
+        """Like stage_host for one rollout per path: `planes` [P, B + C - 1, H, W] u8 (pinned host) holds the distinct
+        planes of the B frame stacks (game_state.py:62-66,75-81); the stacks are rebuilt on the device."""
+        cfg = self.cfg
+        if planes.dtype != torch.uint8 or planes.dim() != 4 or planes.shape[0] != self.P or \
+                tuple(planes.shape[2:]) != (cfg.H, cfg.W) or not planes.is_contiguous():
+            raise ValueError("planes must be a contiguous uint8 [P=%d, B + %d, %d, %d] tensor" % (self.P, cfg.C - 1, cfg.H, cfg.W))
+        B = int(planes.shape[1]) - (cfg.C - 1)
+        cs = copy_stream if copy_stream is not None else torch.cuda.current_stream(self.device)
+        nat.check(self.lib.pn_stage_rollout_host(self._h, int(slot), _ptr(planes), _ptr(actions), _ptr(td), _ptr(r), B,
+                                                 C.c_void_p(cs.cuda_stream)), self._h)
+
     def train_step_staged(self, slot, entropy_beta=0.01, loss_out: Optional[torch.Tensor] = None):
         """Run the step on a staged slot; the D2H copy of the losses is enqueued, not awaited."""
         nat.check(self.lib.pn_train_step_staged(self._h, int(slot), float(entropy_beta), _ptr(loss_out), self._stream()),
@@ -315,6 +327,12 @@ class PathNetPopulation:
         return ((buf[..., None] >> np.arange(cfg.F, dtype=np.uint8)) & 1).astype(bool)
 
     # -- measurement support ---------------------------------------------------
+    def engine_paths(self) -> str:
+        """Which engine (tcgen05 or CUDA cores) every layer of this handle runs on."""
+        buf = C.create_string_buffer(512)
+        self.lib.pn_engine_paths(self._h, buf, 512)
+        return buf.value.decode()
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.pn_launch_count(self._h))

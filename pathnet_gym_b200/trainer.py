@@ -60,6 +60,16 @@ class OverlappedGradSum(object):
             self.peer = None
             self.peer_slabs = None
 
+    def path_name(self):
+        """Which exchange runs (for the bench line): nothing at one GPU; else the two regions' mechanisms."""
+        if not self.active:
+            return "none (1 GPU)"
+        small = "peer-memory kernel (pn_peer_sum_small)" if self.peer is not None else "NCCL all-reduce (grouped)"
+        lin = "peer-memory kernel (pn_peer_allreduce_lin)" if (self.peer is not None and self.peer_slabs is not None) \
+            else "NCCL all-reduce on a side stream"
+        err = getattr(self, "peer_error", None)
+        return "linear region: %s; conv + head regions: %s%s" % (lin, small, "; peer set-up failed: " + err if err else "")
+
     def sum_lin(self):
         """On the side stream (already waiting for the linear gradients): all-reduce them."""
         import os
@@ -160,9 +170,16 @@ class PipelinedHostTrainer(object):
         self.i = 0
         self.primed = False
 
+    def _stage(self, slot, batch):
+        # a 4-D first tensor is a rollout's plane sequence [P, B + C - 1, H, W], a 5-D one is full stacks [P, B, H, W, C]
+        if batch[0].dim() == 4:
+            self.pop.stage_rollout_host(slot, *batch, copy_stream=self.copy_stream)
+        else:
+            self.pop.stage_host(slot, *batch, copy_stream=self.copy_stream)
+
     def prime(self, batch):
-        """Stage the first batch (frames, actions, td, r)."""
-        self.pop.stage_host(self.i & 1, *batch, copy_stream=self.copy_stream)
+        """Stage the first batch (frames or planes, actions, td, r)."""
+        self._stage(self.i & 1, batch)
         self.primed = True
 
     def step(self, next_batch, lr, loss_out=None):
@@ -170,7 +187,7 @@ class PipelinedHostTrainer(object):
         assert self.primed, "call prime() with the first batch"
         cur = self.i & 1
         if next_batch is not None:
-            self.pop.stage_host(cur ^ 1, *next_batch, copy_stream=self.copy_stream)
+            self._stage(cur ^ 1, next_batch)
         self.pop.train_step_staged(cur, self.beta, loss_out)
         self.tail(lr)
         self.i += 1

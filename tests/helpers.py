@@ -58,3 +58,6 @@ def split_flat(cfg, flat):
         o += n
     assert o == len(flat)
     return out
+
+# BASELINE config C4: second-task transfer, L=4 M=10 N=4, 84x84x4 frames, 3-action head
+C4 = po.OracleConfig(L=4, M=10, N=4, H=84, W=84, C=4, A=3)

@@ -348,6 +348,41 @@ def test_pipelined_host_trainer_equals_device_steps(eng_mod):
     pop.close(); ref.close()
 
 
+def test_rollout_planes_staging_equals_full_stacks(eng_mod):
+    """pn_stage_rollout_host (the B + C - 1 distinct planes of each rollout cross PCIe, the stacks are rebuilt on the
+    device; game_state.py:62-66,75-81) == staging the full [P, B, H, W, C] stacks: bit-identical losses and weights.
+    Covers a B_max-sized and a shorter batch, C1 geometry (tensor-core layer 0) and a tiny one."""
+    from pathnet_gym_b200.trainer import PipelinedHostTrainer
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    for cfg, P, Bmax, Bs in ((hp.C1, 3, 8, (8, 5, 8)), (hp.TINY, 4, 6, (6, 1, 4))):
+        params = po.init_params(cfg, 4)
+        rng = np.random.Generator(np.random.PCG64(17))
+        masks = hp.synth_inputs(cfg, P, 1, 3)[4]
+        runs = []
+        for use_planes in (False, True):
+            pop = make_pop(eng_mod, cfg, P, Bmax, params, masks)
+            pipe = PipelinedHostTrainer(pop)
+            rng = np.random.Generator(np.random.PCG64(17))
+            hb = []
+            for B in Bs:
+                planes = rng.integers(0, 256, size=(P, B + cfg.C - 1, cfg.H, cfg.W), dtype=np.uint8)
+                stacks = np.stack([planes[:, b:b + cfg.C] for b in range(B)], axis=1).transpose(0, 1, 3, 4, 2)
+                a = rng.integers(0, cfg.A, size=(P, B)).astype(np.int32)
+                td = rng.normal(size=(P, B)).astype(np.float32)
+                r = rng.normal(size=(P, B)).astype(np.float32)
+                hb.append((pin(planes if use_planes else stacks), pin(a), pin(td), pin(r)))
+            outs = [torch.empty(P).pin_memory() for _ in Bs]
+            pipe.prime(hb[0])
+            for i in range(len(Bs)):
+                pipe.step(hb[i + 1] if i + 1 < len(Bs) else None, 7e-4, loss_out=outs[i])
+            torch.cuda.synchronize()
+            runs.append((outs, pop.params.clone(), pop.ms.clone()))
+            pop.close()
+        for a, b in zip(runs[0][0], runs[1][0]):
+            assert torch.equal(a, b)
+        assert torch.equal(runs[0][1], runs[1][1]) and torch.equal(runs[0][2], runs[1][2])
+
+
 def test_error_paths(eng_mod):
     from pathnet_gym_b200 import PathNetError
     cfg = hp.TINY
@@ -660,3 +695,74 @@ def test_population_scale_per_tensor_vs_fp64(eng_mod, cfgname, P, B):
     cfg = getattr(hp, cfgname)
     same, plain, f32, flips, total = _per_tensor_vs_fp64(eng_mod, cfg, P, B, 3, "pop_%s_%dx%d" % (cfgname, P, B))
     _check_population(same, flips, total)
+
+
+def test_c4_task_transfer_real_shape(eng_mod):
+    """BASELINE config C4 as stated: the L=4 / M=10 / N=4 net with the 3-action head; task 1 runs tournaments (so
+    mutations have already added and dropped modules), its winner's path is frozen (doom_pathnet.py:273-283), every
+    other tensor is re-initialised (:289-293), and task 2 starts fresh genotypes OR'ed with the frozen path (:213-221)
+    -- 4..8 active modules per layer.  Checks on that population: per-tensor parity of one step against the fp64
+    oracle, frozen tensors bit-identical after the update, non-frozen ones equal to the oracle's clipped RMSProp."""
+    from pathnet_gym_b200.controller import PopulationController
+    cfg, P, B = hp.C4, 12, 32
+    ecfg = hp.to_engine_cfg(cfg)
+    pop = eng_mod.PathNetPopulation(ecfg, P, B)
+    pop.init_params(5)
+    ctl = PopulationController(pop, P, Bcand=3, seed=21)
+    ctl.start_task()
+    for rnd in range(6):                                        # task 1: a few rounds of tournaments + mutation
+        ctl.report_scores(torch.arange(P, dtype=torch.float32).roll(rnd))
+        ctl.tournament_step()
+    fixed = ctl.end_task()                                      # freeze the winner's path, re-initialise the rest
+    ctl.start_task()                                            # task 2 population: genotype | fixed path
+    masks = pop.masks.copy()
+    fixed_bits = po.masks_from_gates(fixed)
+    assert np.all((masks & fixed_bits[None, :]) == fixed_bits[None, :])
+    pc = np.array([[bin(int(m)).count("1") for m in row] for row in masks])
+    assert pc.max() > 4 and pc.min() >= 4                       # the shapes the >4-module paths of every kernel see
+    _report["c4.active_modules_per_layer.max"] = int(pc.max())
+    params = pop.dump(pop.params)
+    frames, actions, td, r, _ = hp.synth_inputs(cfg, P, B, 41)
+    pre = [{} for _ in range(P)]
+    pi64, v64, l64, G64 = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", pre_out=pre)
+    loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
+    G = pop.dump(pop.grads)
+    dec = [pop.relu_decisions(l, B) for l in range(cfg.L)]
+    override, flips, total = [], [], 0
+    for p in range(P):
+        d = {}
+        for (l, j), pr in pre[p].items():
+            mk = dec[l][p, :, j].reshape(pr.shape)
+            d[(l, j)] = mk
+            diff = mk != (pr > 0)
+            total += pr.size
+            if diff.any():
+                flips += [float(x) for x in np.abs(pr[diff]) / np.sqrt(np.mean(pr ** 2))]
+        override.append(d)
+    piF, vF, lF, GF = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", relu_override=override)
+    same = {"pi": hp.rel_err(pi.cpu().numpy(), piF), "v": hp.rel_err(v.cpu().numpy(), vF),
+            "loss": hp.rel_err(loss.cpu().numpy(), lF)}
+    tt = po.tensor_table(cfg)
+    same.update({"grad/" + t["name"]: hp.rel_err(a, b) for t, a, b in zip(tt, G, GF)})
+    w = max(same, key=same.get)
+    _report["c4.cuda_same_decisions.worst"] = [w, same[w]]
+    _report["c4.relu_decisions_differing"] = len(flips)
+    _note("c4.relu_units", total)
+    _check_population(same, flips, total)
+    # the masked update: frozen tensors untouched (bit-identical), the rest = clip_by_norm + ApplyRMSProp of the oracle
+    frozen = po.frozen_flags(cfg, fixed)
+    assert np.array_equal(pop.frozen, frozen) and frozen.sum() > 0
+    p_before, ms_before = pop.params.clone(), pop.ms.clone()
+    ms0 = pop.dump(pop.ms)
+    pop.apply_gradients(7.0016e-4)
+    want_p, want_ms, _ = po.apply_gradients(params, ms0, [np.zeros_like(x) for x in params], G, frozen, 7.0016e-4)
+    got_p, got_ms = pop.dump(pop.params), pop.dump(pop.ms)
+    for i, t in enumerate(pop.tensors):
+        sl = slice(t["offset"], t["offset"] + t["length"])
+        if frozen[i]:
+            assert torch.equal(pop.params[sl], p_before[sl]) and torch.equal(pop.ms[sl], ms_before[sl]), tt[i]["name"]
+        else:
+            upd = np.abs(np.asarray(want_p[i], np.float64) - params[i]).max()
+            assert np.abs(got_p[i] - want_p[i]).max() <= REL_TOL * max(upd, 1e-30), tt[i]["name"]
+            assert hp.rel_err(got_ms[i], want_ms[i]) < 1e-5, tt[i]["name"]
+    pop.close()
