@@ -68,13 +68,21 @@ typedef struct pn_config {
     int32_t device;         /* CUDA device ordinal                                 */
     int32_t flags;          /* debug: bit 0 / bit 1 force the fp32 CUDA-core kernels for layer 0 / the linear modules,
                              * bit 2 the simple (untiled) kernels for the middle conv layers,
-                             * bit 3 the tiled CUDA-core kernels (instead of tcgen05) for the middle conv layers */
+                             * bit 3 the tiled CUDA-core kernels (instead of tcgen05) for the middle conv layers;
+                             * bit 4 (PN_FLAG_LSTM): the LSTM variant of the network, see pn_lstm_bind_state */
 } pn_config;
+
+/* cfg.flags bit 4: GameACPathNetLSTMNetwork (game_ac_network.py:303-521, the reference's default, constants.py:31):
+ * the last layer's module sum is not divided by M and feeds a BasicLSTMCell(256) unrolled over each path's B
+ * transitions (time order b = 0..B-1); the cell outputs feed the heads.  Two tensors are appended to the slab in
+ * get_vars() order: kind 8 = W_lstm [512, 1024] (rows 0..255 input, 256..511 previous output; gate order i, j, f, o)
+ * and kind 9 = b_lstm [1024]; neither is ever frozen.  Needs hidden = 256. */
+#define PN_FLAG_LSTM 16
 
 /* One row per trainable tensor, in get_vars() order with nothing frozen
  * (game_ac_network.py:239-253): for l<L-1, j<M: W_conv[l,j], b_conv[l,j];
  * for j<M: W_lin[j], b_lin[j]; W_fc2, b_fc2, W_fc3, b_fc3.
- * kind: 0 conv W (HWIO), 1 conv b, 2 lin W [in,hidden], 3 lin b, 4 fc2 W, 5 fc2 b,
+ * kind: 0 conv W (HWIO), 1 conv b, 2 lin W [in,hidden], 3 lin b, 4 fc2 W, 5 fc2 b, (8 / 9: W_lstm / b_lstm)
  * 6 fc3 W, 7 fc3 b.  offset/length are in floats into the slabs; every offset
  * is a multiple of 32 floats (the gaps are never read or written). */
 typedef struct pn_tensor_desc {
@@ -123,6 +131,14 @@ PN_API int pn_bind_slabs(pn_handle* h, float* params_dev, float* ms_dev, float* 
  * EFFECTIVE masks (genotype OR fixed path).  Rebuilds the module->path lists
  * used by the weight-gradient kernels.  Synchronises `stream`. */
 PN_API int pn_set_genotypes(pn_handle* h, const uint32_t* masks_host, void* stream);
+
+/* LSTM variant only: the cell state every path starts its sequence from, and where the state after the last
+ * step goes.  Both are caller-owned device arrays [P][2][256] = (c, h) per path (initial_lstm_state0 / 1,
+ * game_ac_network.py:403-406), borrowed until rebound; state_in NULL = zeros (reset_state, :441-443), state_out NULL =
+ * not written.  Acting (pn_forward with B = 1) carries the state by binding last call's output as the next input
+ * (run_policy_and_value, :448-456); run_value (:468-481) simply does not adopt its output; a training call binds
+ * the state the rollout started from (a3c_training_thread.py:113-114,200). */
+PN_API int pn_lstm_bind_state(pn_handle* h, const float* state_in_dev, float* state_out_dev);
 
 /* Replaces set_fixed_path + get_vars_idx + the op selection in process()
  * (game_ac_network.py:236-271, a3c_training_thread.py:205-209).
@@ -190,6 +206,12 @@ PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, floa
  * The other two regions are complete when the step's stream work is. */
 PN_API int pn_lin_grads_region(const pn_handle* h, int64_t* offset_floats, int64_t* count_floats);
 PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
+
+/* The exchange kernels wait for the other ranks' flags for at most 2 s; a rank that gives up records that in its own
+ * exchange buffer and finishes (the sums of that step are then wrong).  This synchronising call reads the record:
+ * PN_OK, or PN_ERR_STATE with a message naming the wait that timed out.  Call it whenever the host synchronises
+ * anyway (end of an epoch, before a checkpoint). */
+PN_API int pn_peer_check(pn_handle* h, const void* my_peer_buf_dev);
 
 /* Sum of the two small gradient regions (everything but the linear modules: conv layers + heads, ~140 KB) over the
  * GPUs of one node in ONE kernel over NVLink peer memory, instead of an all-reduce that would sit exposed at the end of

@@ -60,6 +60,7 @@ class OracleConfig:
     F: int = 8                                 # feature_num, game_ac_network.py:132
     hidden: int = 256                          # game_ac_network.py:146
     A: int = 18                                # max(ACTION_SIZEZ), game_ac_network.py:152
+    lstm: bool = False                         # GameACPathNetLSTMNetwork (game_ac_network.py:303-521): no /M, BasicLSTMCell(256)
 
     def conv_dims(self):
         """[(IH, IW, Cin, k, s, OH, OW)] for conv layers 0..L-2 (VALID padding)."""
@@ -100,6 +101,11 @@ def tensor_table(cfg: OracleConfig):
     t.append(dict(name="b_fc2", shape=(cfg.A,), layer=cfg.L, module=-1, kind=5))
     t.append(dict(name="W_fc3", shape=(cfg.hidden, 1), layer=cfg.L, module=-1, kind=6))
     t.append(dict(name="b_fc3", shape=(1,), layer=cfg.L, module=-1, kind=7))
+    if cfg.lstm:
+        # appended by the LSTM class's get_vars (game_ac_network.py:502-520); tf.contrib.rnn.BasicLSTMCell variables
+        # ".../basic_lstm_cell/kernel" [input + units, 4 * units] and ".../bias" [4 * units] (:437-438)
+        t.append(dict(name="W_lstm", shape=(2 * cfg.hidden, 4 * cfg.hidden), layer=cfg.L + 1, module=-1, kind=8))
+        t.append(dict(name="b_lstm", shape=(4 * cfg.hidden,), layer=cfg.L + 1, module=-1, kind=9))
     return t
 
 
@@ -115,6 +121,13 @@ def init_params(cfg: OracleConfig, seed: int = 1) -> List[np.ndarray]:
             d = 1.0 / math.sqrt(shp[2] * shp[0] * shp[1])
         elif t["kind"] in (2, 4, 6):
             d = 1.0 / math.sqrt(shp[0])
+        elif t["kind"] == 8:
+            # BasicLSTMCell creates its kernel with the variable scope's default initializer, glorot_uniform:
+            # U(-l, l), l = sqrt(6 / (fan_in + fan_out)); the bias is zeros_initializer (TF 1.x rnn_cell_impl.py)
+            d = math.sqrt(6.0 / (shp[0] + shp[1]))
+        if t["kind"] == 9:
+            out.append(np.zeros(shp, dtype=np.float32))
+            continue
         out.append(rng.uniform(-d, d, size=shp).astype(np.float32))
     return out
 
@@ -139,11 +152,30 @@ def frozen_flags(cfg: OracleConfig, fixed_path: np.ndarray) -> np.ndarray:
 # ----------------------------------------------------------------------------
 # Restatement #1: torch, literal graph (all M modules evaluated and gated)
 # ----------------------------------------------------------------------------
-def forward_torch(cfg: OracleConfig, params, frames, gates):
+def lstm_torch(x_seq, W, b, state):
+    """tf.contrib.rnn.BasicLSTMCell(256, state_is_tuple=True) under tf.nn.dynamic_rnn, batch 1 (game_ac_network.py:396-416):
+    [i | j | f | o] = [x_t, h] @ kernel + bias;  c' = c * sigmoid(f + 1.0) + sigmoid(i) * tanh(j);  h' = tanh(c') * sigmoid(o)
+    (TF 1.x rnn_cell_impl.py BasicLSTMCell.call, forget_bias = 1.0).  x_seq [T, units]; state = (c, h), each [units]."""
+    import torch
+    c, h = state
+    n = x_seq.shape[1]
+    outs = []
+    for t in range(x_seq.shape[0]):
+        a = torch.cat([x_seq[t], h]) @ W + b
+        i, j, f, o = a[:n], a[n:2 * n], a[2 * n:3 * n], a[3 * n:]
+        c = c * torch.sigmoid(f + 1.0) + torch.sigmoid(i) * torch.tanh(j)
+        h = torch.tanh(c) * torch.sigmoid(o)
+        outs.append(h)
+    return torch.stack(outs), (c, h)
+
+
+def forward_torch(cfg: OracleConfig, params, frames, gates, lstm_state=None, return_state=False):
     """game_ac_network.py:182-201.  `frames` [n,H,W,C] float, `gates` [L,M] 0/1.
 
     Every module of every layer is evaluated and multiplied by its scalar gate,
     summed in ascending j (np.sum over the object array), then /M, then heads.
+    cfg.lstm: the LSTM class (:381-426): no /M (:394), the n frames are ONE sequence in time order through the cell,
+    whose outputs feed the heads; lstm_state = (c, h) at the start (zeros if None, reset_state :441-443).
     """
     import torch
     import torch.nn.functional as Fn
@@ -165,10 +197,19 @@ def forward_torch(cfg: OracleConfig, params, frames, gates):
                 y = torch.relu(net @ params[idx[f"W_lin[{j}]"]] + params[idx[f"b_lin[{j}]"]]) * g
             acc = y if acc is None else acc + y
         net = acc
-    net = net / cfg.M                                           # :194
+    state = None
+    if cfg.lstm:
+        if lstm_state is None:
+            z0 = torch.zeros(cfg.hidden, dtype=net.dtype)
+            lstm_state = (z0, z0)
+        net, state = lstm_torch(net, params[idx["W_lstm"]], params[idx["b_lstm"]], lstm_state)
+    else:
+        net = net / cfg.M                                       # :194
     z = net @ params[idx["W_fc2"]] + params[idx["b_fc2"]]
     pi = torch.softmax(z, dim=1)                                # :198
     v = (net @ params[idx["W_fc3"]] + params[idx["b_fc3"]]).reshape(-1)  # :200-201
+    if return_state:
+        return pi, v, state
     return pi, v
 
 
@@ -182,7 +223,7 @@ def loss_torch(pi, v, a_onehot, td, r, entropy_beta=ENTROPY_BETA):
     return policy_loss + value_loss
 
 
-def path_grads_torch(cfg, params_np, frames_f, gates, actions, td, r, beta=ENTROPY_BETA, dtype="float64"):
+def path_grads_torch(cfg, params_np, frames_f, gates, actions, td, r, beta=ENTROPY_BETA, dtype="float64", lstm_state=None):
     """tf.gradients(total_loss, get_vars()) for ONE path (a3c_training_thread.py:55-60).
 
     Returns (pi, v, total_loss, [grad per tensor]) as NumPy arrays of `dtype`."""
@@ -191,7 +232,10 @@ def path_grads_torch(cfg, params_np, frames_f, gates, actions, td, r, beta=ENTRO
     ps = [torch.tensor(p, dtype=dt, requires_grad=True) for p in params_np]
     x = torch.tensor(np.asarray(frames_f), dtype=dt)
     g = torch.tensor(np.asarray(gates), dtype=dt)
-    pi, v = forward_torch(cfg, ps, x, g)
+    st = None
+    if lstm_state is not None:
+        st = (torch.tensor(np.asarray(lstm_state[0]), dtype=dt), torch.tensor(np.asarray(lstm_state[1]), dtype=dt))
+    pi, v = forward_torch(cfg, ps, x, g, lstm_state=st)
     a1h = torch.zeros(len(actions), cfg.A, dtype=dt)
     a1h[torch.arange(len(actions)), torch.tensor(np.asarray(actions), dtype=torch.long)] = 1.0
     loss = loss_torch(pi, v, a1h, torch.tensor(np.asarray(td), dtype=dt), torch.tensor(np.asarray(r), dtype=dt), beta)
@@ -212,8 +256,12 @@ def _im2col(x, k, s):
     return cols.reshape(n * oh * ow, k * k * C), oh, ow
 
 
+def _sigmoid(x):
+    return 1.0 / (1.0 + np.exp(-x))
+
+
 def forward_backward_numpy(cfg, params, frames_f, gates, actions, td, r, beta=ENTROPY_BETA, dtype=np.float64,
-                           want_grads=True, relu_override=None, pre_out=None):
+                           want_grads=True, relu_override=None, pre_out=None, lstm_state=None, state_out=None):
     """Closed-form forward + backward for ONE path.
 
     Only gated-on modules are evaluated: adding exact +0.0 terms does not change
@@ -259,7 +307,27 @@ def forward_backward_numpy(cfg, params, frames_f, gates, actions, td, r, beta=EN
         key = (cfg.L - 1, j)
         lmask[j] = np.asarray(relu_override[key]).reshape(pre.shape) if key in relu_override else pre > 0
         h = h + np.where(lmask[j], pre, 0)
-    h = h / cfg.M
+    lstm_saved = None
+    if cfg.lstm:
+        # no /M (game_ac_network.py:394); the n transitions are one sequence through BasicLSTMCell (see lstm_torch)
+        n_u = cfg.hidden
+        Wl, bl = P[idx["W_lstm"]], P[idx["b_lstm"]]
+        c = np.zeros(n_u, dtype=dtype) if lstm_state is None else np.asarray(lstm_state[0], dtype=dtype)
+        hp = np.zeros(n_u, dtype=dtype) if lstm_state is None else np.asarray(lstm_state[1], dtype=dtype)
+        x_seq, outs, lstm_saved = h, [], []
+        for t in range(n):
+            a = np.concatenate([x_seq[t], hp]) @ Wl + bl
+            ig, gg, fg, og = _sigmoid(a[:n_u]), np.tanh(a[n_u:2 * n_u]), _sigmoid(a[2 * n_u:3 * n_u] + 1.0), _sigmoid(a[3 * n_u:])
+            c_new = c * fg + ig * gg
+            tc = np.tanh(c_new)
+            lstm_saved.append((ig, gg, fg, og, c, tc, hp))
+            c, hp = c_new, tc * og
+            outs.append(hp)
+        if state_out is not None:
+            state_out[0], state_out[1] = c, hp
+        h = np.stack(outs)
+    else:
+        h = h / cfg.M
     z = h @ P[idx["W_fc2"]] + P[idx["b_fc2"]]
     zs = z - z.max(axis=1, keepdims=True)
     e = np.exp(zs)
@@ -285,7 +353,28 @@ def forward_backward_numpy(cfg, params, frames_f, gates, actions, td, r, beta=EN
     G[idx["b_fc2"]] = dz.sum(axis=0)
     G[idx["W_fc3"]] = h.T @ dv[:, None]
     G[idx["b_fc3"]] = dv.sum(keepdims=True)
-    dh = (dz @ P[idx["W_fc2"]].T + dv[:, None] * P[idx["W_fc3"]].T) / cfg.M
+    dh = dz @ P[idx["W_fc2"]].T + dv[:, None] * P[idx["W_fc3"]].T
+    if cfg.lstm:
+        # back-propagation through time; dh becomes the gradient at the cell INPUT (the module sum)
+        n_u = cfg.hidden
+        Wl = P[idx["W_lstm"]]
+        dW, db = np.zeros_like(Wl), np.zeros(4 * n_u, dtype=dtype)
+        dx = np.zeros_like(dh)
+        dh_next, dc_next = np.zeros(n_u, dtype=dtype), np.zeros(n_u, dtype=dtype)
+        for t in range(n - 1, -1, -1):
+            ig, gg, fg, og, c_prev, tc, h_prev = lstm_saved[t]
+            dht = dh[t] + dh_next
+            dc = dht * og * (1.0 - tc * tc) + dc_next
+            da = np.concatenate([dc * gg * ig * (1.0 - ig), dc * ig * (1.0 - gg * gg), dc * c_prev * fg * (1.0 - fg),
+                                 dht * tc * og * (1.0 - og)])
+            dW += np.outer(np.concatenate([x_seq[t], h_prev]), da)
+            db += da
+            dxh = Wl @ da
+            dx[t], dh_next, dc_next = dxh[:n_u], dxh[n_u:], dc * fg
+        G[idx["W_lstm"]], G[idx["b_lstm"]] = dW, db
+        dh = dx
+    else:
+        dh = dh / cfg.M
     dflat = np.zeros_like(flat)
     for j, mk in lmask.items():
         dpre = dh * mk
@@ -486,7 +575,7 @@ def masks_from_gates(g) -> np.ndarray:
 
 
 def population_step(cfg, params, frames_u8, masks, actions, td, r, beta=ENTROPY_BETA, dtype="float64",
-                    impl="torch", relu_override=None, pre_out=None):
+                    impl="torch", relu_override=None, pre_out=None, lstm_states=None):
     """Synchronous population gradient: per-path tf.gradients, summed over paths
     (the shared-module gradient the B200 design all-reduces).  frames_u8 [P,B,H,W,C].
     relu_override / pre_out (impl="numpy" only): lists with one dict per path, see forward_backward_numpy."""
@@ -497,12 +586,14 @@ def population_step(cfg, params, frames_u8, masks, actions, td, r, beta=ENTROPY_
         xf = frames_to_float(frames_u8[p]) if frames_u8.dtype == np.uint8 else frames_u8[p]
         gates = gates_from_masks(cfg, masks[p])
         if impl == "torch":
-            pi, v, ls, g = path_grads_torch(cfg, params, xf, gates, actions[p], td[p], r[p], beta, dtype)
+            pi, v, ls, g = path_grads_torch(cfg, params, xf, gates, actions[p], td[p], r[p], beta, dtype,
+                                            lstm_state=lstm_states[p] if lstm_states is not None else None)
         else:
             pi, v, ls, g = forward_backward_numpy(cfg, params, xf, gates, actions[p], td[p], r[p], beta,
                                                   np.dtype(dtype).type,
                                                   relu_override=relu_override[p] if relu_override is not None else None,
-                                                  pre_out=pre_out[p] if pre_out is not None else None)
+                                                  pre_out=pre_out[p] if pre_out is not None else None,
+                                                  lstm_state=lstm_states[p] if lstm_states is not None else None)
         pis.append(pi); vs.append(v); losses.append(ls)
         for a, b in zip(G, g):
             a += b

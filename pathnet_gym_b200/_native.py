@@ -14,6 +14,7 @@ PN_MAX_LAYERS = 8
 PN_MAX_MODULES = 32
 PN_ABI_VERSION = 1
 
+PN_FLAG_LSTM = 16
 PN_OK, PN_ERR_INVALID, PN_ERR_CUDA, PN_ERR_STATE, PN_ERR_NOMEM = 0, -1, -2, -3, -4
 
 
@@ -59,12 +60,14 @@ SIGNATURES = {
     "pn_lin_grads_region": (_i, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "pn_stream_wait_lin_grads": (_i, [_vp, _vp]),
     "pn_peer_buffer_bytes": (C.c_int64, [_vp]),
+    "pn_peer_check": (_i, [_vp, _vp]),
     "pn_peer_sum_small": (_i, [_vp, _vp, _i, _i, C.c_uint32, _vp]),
     "pn_peer_allreduce_lin": (_i, [_vp, _vp, _vp, _i, _i, C.c_uint32, _vp]),
     "pn_profile_enable": (_i, [_vp, _i]),
     "pn_profile_read": (_i, [_vp, C.POINTER(PnProfileEntry), _i]),
     "pn_bind_slabs": (_i, [_vp, _vp, _vp, _vp, _vp]),
     "pn_set_genotypes": (_i, [_vp, _vp, _vp]),
+    "pn_lstm_bind_state": (_i, [_vp, _vp, _vp]),
     "pn_set_frozen": (_i, [_vp, _vp]),
     "pn_forward": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "pn_train_step": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),

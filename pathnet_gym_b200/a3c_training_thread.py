@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from .constants import ACTION_SIZEZ, ENTROPY_BETA, GAMMA, LOCAL_T_MAX, ROMZ, USE_LSTM
-from .game_ac_network import GameACPathNetNetwork
+from .game_ac_network import GameACPathNetLSTMNetwork, GameACPathNetNetwork
 
 LOG_INTERVAL = 100
 PERFORMANCE_LOG_INTERVAL = 1000
@@ -53,10 +53,15 @@ class A3CTrainingThread(object):
         self.task_index = task_index
         self.learning_rate_input = learning_rate_input
         self.max_global_time_step = max_global_time_step
-        FLAGS.use_lstm = USE_LSTM
-        if USE_LSTM:
-            raise NotImplementedError("the LSTM variant (game_ac_network.py:303-521) is a next-row item")
-        self.local_network = GameACPathNetNetwork(training_stage, thread_index, device, FLAGS)
+        # the reference overwrites FLAGS.use_lstm with the constant (a3c_training_thread.py:46); a caller that set the
+        # field on its FLAGS object before is respected here so that both networks can be driven in one process
+        if not hasattr(FLAGS, "use_lstm"):
+            FLAGS.use_lstm = USE_LSTM
+        self.use_lstm = bool(FLAGS.use_lstm)
+        if self.use_lstm:
+            self.local_network = GameACPathNetLSTMNetwork(training_stage, thread_index, device, FLAGS)
+        else:
+            self.local_network = GameACPathNetNetwork(training_stage, thread_index, device, FLAGS)
         self.local_network.prepare_loss(ENTROPY_BETA)
         # tf.gradients + apply ops for the full variable list (fixed_path is all-zero here,
         # a3c_training_thread.py:55-64)
@@ -104,6 +109,8 @@ class A3CTrainingThread(object):
         terminal_end = False
         start_local_t = self.local_t
         net = self.local_network
+        if self.use_lstm:
+            start_lstm_state = net.lstm_state_out            # a3c_training_thread.py:113-114
         for i in range(LOCAL_T_MAX):
             pi_, value_ = net.run_policy_and_value(sess, self.game_state.s_t)
             action = self.choose_action(pi_)
@@ -123,6 +130,8 @@ class A3CTrainingThread(object):
                         op(self.episode_reward)
                 self.episode_reward = 0
                 self.game_state.reset()
+                if self.use_lstm:
+                    net.reset_state()                        # a3c_training_thread.py:148-149
                 break
         R = 0.0
         if not terminal_end:
@@ -135,6 +144,10 @@ class A3CTrainingThread(object):
             batch_td.append(R - Vi)
             batch_R.append(R)
         cur_learning_rate = self._anneal_learning_rate(global_t)
+        if self.use_lstm:
+            # the cell consumes the rollout in time order from the state it started with (a3c_training_thread.py:184-203)
+            batch_si.reverse(); batch_a.reverse(); batch_td.reverse(); batch_R.reverse()
+            net.pop.bind_lstm_state(start_lstm_state, None)
         # op selection = freeze mask (a3c_training_thread.py:205-209); then ONE call does
         # forward + loss + backward, and the selected apply ops run
         var_idx = net.get_vars_idx()

@@ -21,5 +21,5 @@ MAX_TIME_STEP = 4 * 10 ** 6
 GRAD_NORM_CLIP = 40.0
 NUM_GPUS = 3
 USE_GPU = True              # the reference ships False (constants.py:30); this build is GPU-only
-USE_LSTM = False            # the feed-forward net is the hot path (SURVEY 8f ranks the LSTM variant next)
+USE_LSTM = True             # as the reference ships it (constants.py:31): GameACPathNetLSTMNetwork
 USE_PATHNET = True

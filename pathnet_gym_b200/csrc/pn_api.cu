@@ -86,6 +86,16 @@ int build_layout(pn_handle* h) {
     off += align_up(c.hidden, PN_ALIGN);
     nd.fc3b = off; h->tensors.push_back(pn_tensor_desc{off, 1, c.L, -1, 7, 0});
     off += PN_ALIGN;
+    nd.out_div = (float)c.M;
+    nd.lstmW = nd.lstmb = 0;
+    if (c.flags & PN_FLAG_LSTM) {
+        // GameACPathNetLSTMNetwork.get_vars(): ..., W_fc3, b_fc3, W_lstm, b_lstm (game_ac_network.py:502-520); no /M (:394)
+        nd.out_div = 1.0f;
+        nd.lstmW = off; h->tensors.push_back(pn_tensor_desc{off, 2ll * c.hidden * 4 * c.hidden, c.L + 1, -1, 8, 0});
+        off += align_up(2ll * c.hidden * 4 * c.hidden, PN_ALIGN);
+        nd.lstmb = off; h->tensors.push_back(pn_tensor_desc{off, 4ll * c.hidden, c.L + 1, -1, 9, 0});
+        off += align_up(4ll * c.hidden, PN_ALIGN);
+    }
     h->slab_floats = off;
     return PN_OK;
 }
@@ -144,6 +154,8 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
     if (!h) return pn_fail_global(PN_ERR_NOMEM, "out of host memory");
     h->cfg = c;
     h->P = c.P; h->Bmax = c.B_max; h->T = c.P * c.B_max;
+    h->lstm = (c.flags & PN_FLAG_LSTM) != 0;
+    if (h->lstm && c.hidden != 256) { delete h; return pn_fail_global(PN_ERR_INVALID, "the LSTM variant needs hidden = 256"); }
     int rc = build_layout(h);
     if (rc) { pn_fail_global(rc, "%s", h->err.c_str()); delete h; return rc; }
     const PnNetDesc& nd = h->nd;
@@ -165,6 +177,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
     PN_TRY(dev_alloc(h, &h->dzv, T * 32));
     PN_TRY(dev_alloc(h, &h->dh, T * c.hidden));
     PN_TRY(dev_alloc(h, &h->loss_t, T));
+    if (h->lstm) PN_TRY(dev_alloc(h, &h->lstm_ws, pn_lstm_workspace_floats(h)));
     h->head_chunks = (int)((T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK);
     PN_TRY(dev_alloc(h, &h->head_part, (size_t)h->head_chunks * ((size_t)c.hidden * (c.A + 1) + c.A + 1)));
     PN_TRY(dev_alloc(h, &h->d_masks, (size_t)c.P * c.L));
@@ -233,7 +246,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     for (int l = 0; l < PN_MAX_LAYERS; ++l) {
         cudaFree(h->act[l]); cudaFree(h->dact[l]); cudaFree(h->rmask[l]); cudaFree(h->wpart[l]);
     }
-    cudaFree(h->hbuf); cudaFree(h->lmask); cudaFree(h->dzv); cudaFree(h->dh); cudaFree(h->loss_t);
+    cudaFree(h->lstm_ws); cudaFree(h->hbuf); cudaFree(h->lmask); cudaFree(h->dzv); cudaFree(h->dh); cudaFree(h->loss_t);
     cudaFree(h->head_part); cudaFree(h->d_masks); cudaFree(h->d_list); cudaFree(h->d_list_count);
     cudaFree(h->d_frozen); cudaFree(h->d_chunks); cudaFree(h->d_tensor_chunk0); cudaFree(h->d_tensor_nchunks);
     cudaFree(h->tc_w8); cudaFree(h->tc_dbg); cudaFree(h->tc_lin_buf);
@@ -334,7 +347,7 @@ extern "C" PN_API int pn_profile_read(pn_handle* h, pn_profile_entry* out, int c
         else {
             static const char* names[] = {"lin_fwd", "head_loss", "grad_reduce", "lin_dgrad", "lin_wgrad",
                                           "rms_sumsq", "rms_update", "conv0_wprep", "conv0_dquant", "lin_prep",
-                                          "conv_mid_prep", "lin_wprep", "rms_update_lin", "rms_update_small"};
+                                          "conv_mid_prep", "lin_wprep", "rms_update_lin", "rms_update_small", "lstm_fwd", "lstm_bwd"};
             base = names[slot - PN_PROF_LIN_FWD];
         }
         if (layer >= 0) snprintf(out[n].name, sizeof(out[n].name), "%s_l%d", base, layer);
@@ -404,6 +417,14 @@ extern "C" PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream) {
     return PN_OK;
 }
 
+extern "C" PN_API int pn_lstm_bind_state(pn_handle* h, const float* state_in_dev, float* state_out_dev) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "null handle");
+    if (!h->lstm) return pn_fail(h, PN_ERR_STATE, "this handle was not created with PN_FLAG_LSTM");
+    h->lstm_state_in = state_in_dev;
+    h->lstm_state_out = state_out_dev;
+    return PN_OK;
+}
+
 extern "C" PN_API int pn_set_frozen(pn_handle* h, const uint8_t* frozen_host) {
     if (!h || !frozen_host) return pn_fail_global(PN_ERR_INVALID, "pn_set_frozen: null argument");
     const int nt = (int)h->tensors.size();
@@ -423,6 +444,8 @@ extern "C" PN_API int pn_forward(pn_handle* h, const void* frames_dev, int frame
     PN_CUDA(h, cudaSetDevice(h->cfg.device));
     cudaStream_t st = (cudaStream_t)stream;
     if (int rc = pn_launch_forward(h, frames_dev, frames_are_u8, B, false, st)) return rc;
+    if (h->lstm)
+        if (int rc = pn_launch_lstm_fwd(h, B, st)) return rc;
     return pn_launch_heads(h, B, false, nullptr, nullptr, nullptr, 0.f, pi_dev, v_dev, nullptr, st);
 }
 
@@ -435,8 +458,12 @@ extern "C" PN_API int pn_train_step(pn_handle* h, const void* frames_dev, int fr
     PN_CUDA(h, cudaSetDevice(h->cfg.device));
     cudaStream_t st = (cudaStream_t)stream;
     if (int rc = pn_launch_forward(h, frames_dev, frames_are_u8, B, true, st)) return rc;
+    if (h->lstm)
+        if (int rc = pn_launch_lstm_fwd(h, B, st)) return rc;
     if (int rc = pn_launch_heads(h, B, true, actions_dev, td_dev, r_dev, entropy_beta, pi_dev, v_dev, loss_dev, st))
         return rc;
+    if (h->lstm)
+        if (int rc = pn_launch_lstm_bwd(h, B, st)) return rc;
     return pn_launch_backward(h, frames_dev, frames_are_u8, B, st);
 }
 

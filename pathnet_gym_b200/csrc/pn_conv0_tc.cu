@@ -239,10 +239,12 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     const int j = __fns(mask, 0, slot + 1);
                     // the module's digit rows arrive by one bulk copy (async proxy: no staging registers)
                     if (lane == 0) bulk_g2s(Bs + (size_t)slot * kSlotBytes, w8 + (size_t)j * kSlotBytes, kSlotBytes, b_full);
-                    // digit weights 1, 256, 65536 folded into the per-channel scale (exact: powers of two)
-                    if (lane < 24) sbuf[slot * 32 + lane] = wscale[j * 8 + (lane & 7)] * (float)(1 << (8 * (lane >> 3)));
-                    else
-                        sbuf[slot * 32 + lane] = params[nd.convW_base[0] + (long long)j * nd.conv_stride[0] + nd.convb_off[0] + lane - 24];
+                    // per slot: the 8 channel scales, then the 8 biases (the digit weights 256 and 65536 are immediates in
+                    // the epilogue: every shared-memory wavefront the epilogue spends competes with the tensor core's
+                    // operand fetch for the same port, and the scale table used to be half of the epilogue's loads)
+                    if (lane < 8) sbuf[slot * 32 + lane] = wscale[j * 8 + lane];
+                    else if (lane < 16)
+                        sbuf[slot * 32 + lane] = params[nd.convW_base[0] + (long long)j * nd.conv_stride[0] + nd.convb_off[0] + lane - 8];
                     if (lane == 0) jtab[slot] = j;
                 }
                 if (ns > 0) { mbar_wait(b_full, b_phase); b_phase ^= 1; }
@@ -408,11 +410,9 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                         tmem_ld8(tbase + sl * 24 + 16, d2);
                         const int slot = pass * kPassSlots + sl;
                         const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
-                        float s0[8], s1[8], s2[8], bi[8];
+                        float s0[8], bi[8];
                         *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
-                        *reinterpret_cast<float4*>(&s1[0]) = sb[2]; *reinterpret_cast<float4*>(&s1[4]) = sb[3];
-                        *reinterpret_cast<float4*>(&s2[0]) = sb[4]; *reinterpret_cast<float4*>(&s2[4]) = sb[5];
-                        *reinterpret_cast<float4*>(&bi[0]) = sb[6]; *reinterpret_cast<float4*>(&bi[4]) = sb[7];
+                        *reinterpret_cast<float4*>(&bi[0]) = sb[2]; *reinterpret_cast<float4*>(&bi[4]) = sb[3];
                         tmem_ld_wait();
                         if (dbg_epi) { const long long c = pinned_clock(); e_ld += c - e_t0; e_t0 = c; }
                         if (sl == nsl - 1) {        // last read of this accumulator stage: hand it back to the MMA warp
@@ -422,10 +422,11 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                         unsigned bits = 0;
 #pragma unroll
                         for (int c = 0; c < 8; ++c) {
-                            // |D| < 2^24: the int -> float conversions are exact; one rounding per fma
-                            float pre = fmaf((float)(int)d2[c], s2[c], bi[c]);
-                            pre = fmaf((float)(int)d1[c], s1[c], pre);
-                            pre = fmaf((float)(int)d0[c], s0[c], pre);
+                            // |D| < 2^24: the int -> float conversions are exact; Horner over the base-256 digits with
+                            // immediate multipliers, one rounding (2^-24 relative) per fma
+                            float acc = fmaf((float)(int)d2[c], 256.0f, (float)(int)d1[c]);
+                            acc = fmaf(acc, 256.0f, (float)(int)d0[c]);
+                            const float pre = fmaf(acc, s0[c], bi[c]);
                             if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
                         }
                         if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
@@ -954,8 +955,9 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
         const int cs = (B + nch - 1) / nch;
         if (cs > 32 || (B + cs - 1) / cs != nch) continue;
         const long long items = (long long)P * nch, rounds = (items + h->num_sms - 1) / h->num_sms;
-        // cost of an item ~ cs transitions of MMAs + one accumulator flush (~0.75 of a transition)
-        const double eff = (double)T / ((double)rounds * h->num_sms * (cs + 0.75));
+        // cost of an item ~ cs transitions of MMAs + one accumulator flush; measured (PN_TC_DEBUG=8, 256 paths x 32):
+        // ~12.6 K cycles per flush against ~3.9 K per transition, i.e. a flush costs about 3.3 transitions
+        const double eff = (double)T / ((double)rounds * h->num_sms * (cs + 3.3));
         if (eff > best_eff) { best_eff = eff; best_nch = nch; }
     }
     if (best_eff < 0) return pn_fail(h, PN_ERR_STATE, "no valid chunking for the conv0 weight-gradient kernel");

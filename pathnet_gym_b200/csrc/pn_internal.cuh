@@ -22,6 +22,9 @@ struct PnNetDesc {        // passed by value to kernels
     int convb_off[PN_MAX_LAYERS];          // b_conv[l,j] = W_conv[l,j] + convb_off[l]
     long long linW_base; int lin_stride; int linb_off;
     long long fc2W, fc2b, fc3W, fc3b;
+    long long lstmW, lstmb;                // LSTM variant only: kernel [512,1024], bias [1024] (game_ac_network.py:437-438)
+    float out_div;                         // the last layer's module sum is divided by this: M (feed-forward net,
+                                           // game_ac_network.py:194) or 1 (LSTM net, :394)
 };
 
 struct PnRmsChunk { int tensor; int len; long long off; };
@@ -46,6 +49,8 @@ enum PnProfSlot {
     PN_PROF_LIN_WPREP,
     PN_PROF_RMS_UPDATE_LIN,       // sumsq + update pair over the linear modules' tensors
     PN_PROF_RMS_UPDATE_SMALL,     // the same pair over everything else (conv + head tensors)
+    PN_PROF_LSTM_FWD,             // input projection + the per-step recurrence kernels
+    PN_PROF_LSTM_BWD,             // BPTT step kernels + weight / input gradient GEMMs
     PN_PROF_NSLOTS
 };
 #define PN_PROF_RING 64
@@ -120,6 +125,11 @@ struct pn_handle {
         bool used = false; int B = 0; int is_u8 = 1;
     } slot[2];
     long long workspace_bytes = 0;
+    // LSTM variant (cfg.flags bit 4; pn_lstm.cu)
+    bool lstm = false;
+    float* lstm_ws = nullptr;           // gx | gate activations | dA | c | tanh c | h_out | h_prev | dc carry
+    const float* lstm_state_in = nullptr;   // [P][2][256] (c, h) at the first step of every path, or null = zeros (borrowed)
+    float* lstm_state_out = nullptr;        // [P][2][256] state after the last step, or null (borrowed)
     long long launches = 0;             // kernels launched through this handle
     PnProf prof;
     std::string err;
@@ -196,6 +206,13 @@ size_t pn_lin_tc_scratch_bytes(const pn_handle* h);
 int pn_launch_lin_wsplit(pn_handle* h, cudaStream_t st);
 int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st);
 int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st);
+// pn_lstm.cu
+size_t pn_lstm_workspace_floats(const pn_handle* h);
+int pn_launch_lstm_fwd(pn_handle* h, int B, cudaStream_t st);
+int pn_launch_lstm_bwd(pn_handle* h, int B, cudaStream_t st);
+inline const float* pn_head_input(const pn_handle* h) {      // what the two heads read: the module sum, or the cell outputs
+    return h->lstm ? h->lstm_ws + (size_t)h->T * 1024 * 3 + (size_t)h->T * 256 * 2 : h->hbuf;
+}
 // pn_rollout.cu
 int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, cudaStream_t st);
 // pn_rmsprop.cu

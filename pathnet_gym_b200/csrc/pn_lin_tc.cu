@@ -344,7 +344,7 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
                     if (bg < B) Rl[(((size_t)p * B + bg) * g.M + j) * g.Hd + c] = on ? 1 : 0;   // 32 consecutive bytes per warp
                 }
             }
-            const float Mf = (float)g.M;
+            const float Mf = nd.out_div;
 #pragma unroll
             for (int b = 0; b < kNB; ++b) {
                 const int bg = bc * kNB + b;

@@ -167,7 +167,7 @@ lin_fwd_kernel(const float* __restrict__ X, const float* __restrict__ params, Pn
             }
         }
     }
-    const float Mf = (float)nd.M;
+    const float Mf = nd.out_div;
 #pragma unroll
     for (int a = 0; a < 2; ++a) {
         const int b = b0 + ty * 2 + a;
@@ -322,7 +322,7 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
     }
     if (!training) return;
     __syncthreads();
-    const float rM = 1.0f / (float)nd.M;
+    const float rM = 1.0f / nd.out_div;
     float* out = part ? part + (size_t)blockIdx.x * ((size_t)Hd * A1 + A1) : nullptr;
     for (int i = threadIdx.x; i < Hd; i += blockDim.x) {       // phase 3
         float2 wr[NP / 2], acc[NP / 2];
@@ -813,7 +813,7 @@ int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, 
     if (int rc = set_smem(h, kern, sm)) return rc;
     {
         PnProfScope prof(h, PN_PROF_HEAD, st);
-        kern<<<nchunks, 256, sm, st>>>(h->hbuf, h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v, h->dzv,
+        kern<<<nchunks, 256, sm, st>>>(pn_head_input(h), h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v, h->dzv,
                                        h->dh, h->loss_t, h->head_part);
     }
     PN_LAUNCH_CHECK(h, "head_kernel");

@@ -41,6 +41,28 @@ __device__ __forceinline__ float ld_peer(const float* p) {       // never from a
     return v;
 }
 
+// Bounded wait for a peer's flag.  Every rank must make the same call with the same step; if one does not (it raised an
+// error before launching, died, or passed another step), an unbounded spin would hold this GPU inside a kernel forever
+// with no host-side error.  After kSpinBudgetNs the waiter records the failure in control word kPeerErrWord of ITS OWN
+// buffer and goes on (the sums of that step are then garbage); pn_peer_check reports it to the host.  The loop backs off
+// with nanosleep so that the spinning CTAs leave issue slots to the kernels they share the SMs with.
+constexpr unsigned long long kSpinBudgetNs = 2000000000ull;     // 2 s
+constexpr int kPeerErrWord = 200;
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void wait_flag(const unsigned* f, unsigned target, unsigned* err_word, unsigned code) {
+    if ((int)(ld_acquire_sys(f) - target) >= 0) return;
+    const unsigned long long t0 = global_timer_ns();
+    unsigned it = 0;
+    while ((int)(ld_acquire_sys(f) - target) < 0) {
+        __nanosleep(64);
+        if ((++it & 255u) == 0 && global_timer_ns() - t0 > kSpinBudgetNs) { atomicExch(err_word, code); return; }
+    }
+}
+
 // slab index of element e of the small set: the conv region [0, lin_off) followed by the head region after the linear one
 __device__ __forceinline__ long long small_index(int e, long long lin_off, long long lin_cnt) {
     return e < lin_off ? (long long)e : (long long)e + lin_cnt;
@@ -68,8 +90,8 @@ peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long li
     }
     // B: wait until every rank has published this step
     if (threadIdx.x < world) {
-        const unsigned* f = reinterpret_cast<const unsigned*>(peers.buf[rank]) + threadIdx.x;
-        while ((int)(ld_acquire_sys(f) - (step + 1u)) < 0) { }
+        unsigned* mine_ctrl = reinterpret_cast<unsigned*>(peers.buf[rank]);
+        wait_flag(mine_ctrl + threadIdx.x, step + 1u, mine_ctrl + kPeerErrWord, 1u);
     }
     __syncthreads();
     // C: fixed-order sum over the ranks
@@ -100,10 +122,7 @@ peer_allreduce_lin_kernel(PeerPtrs slabs, PeerPtrs ctrl, long long lin_off, long
         __threadfence_system();
         st_release_sys(reinterpret_cast<unsigned*>(ctrl.buf[threadIdx.x]) + 64 + rank, step + 1u);
     }
-    if (threadIdx.x < world) {
-        const unsigned* f = my_ctrl + 64 + threadIdx.x;
-        while ((int)(ld_acquire_sys(f) - (step + 1u)) < 0) { }
-    }
+    if (threadIdx.x < world) wait_flag(my_ctrl + 64 + threadIdx.x, step + 1u, my_ctrl + kPeerErrWord, 2u);
     __syncthreads();
     // 2. my shard: float4 granularity
     const long long n4 = lin_cnt >> 2;
@@ -152,10 +171,7 @@ peer_allreduce_lin_kernel(PeerPtrs slabs, PeerPtrs ctrl, long long lin_off, long
     __syncthreads();
     if (last) __threadfence_system();
     if (last && threadIdx.x < world) st_release_sys(reinterpret_cast<unsigned*>(ctrl.buf[threadIdx.x]) + 96 + rank, step + 1u);
-    if (threadIdx.x < world) {
-        const unsigned* f = my_ctrl + 96 + threadIdx.x;
-        while ((int)(ld_acquire_sys(f) - (step + 1u)) < 0) { }
-    }
+    if (threadIdx.x < world) wait_flag(my_ctrl + 96 + threadIdx.x, step + 1u, my_ctrl + kPeerErrWord, 3u);
     __syncthreads();
 }
 
@@ -176,6 +192,18 @@ extern "C" PN_API int pn_peer_allreduce_lin(pn_handle* h, const uint64_t* peer_s
     const int grid = std::max(1, std::min(h->num_sms / 4, (int)((lin_cnt / world + 4095) / 4096)));
     peer_allreduce_lin_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(ps, pc, lin_off, lin_cnt, rank, world, step);
     PN_LAUNCH_CHECK(h, "peer_allreduce_lin_kernel");
+    return PN_OK;
+}
+
+extern "C" PN_API int pn_peer_check(pn_handle* h, const void* my_peer_buf_dev) {
+    if (!h || !my_peer_buf_dev) return pn_fail_global(PN_ERR_INVALID, "pn_peer_check: null argument");
+    unsigned code = 0;
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    PN_CUDA(h, cudaMemcpy(&code, reinterpret_cast<const unsigned*>(my_peer_buf_dev) + kPeerErrWord, sizeof(code), cudaMemcpyDeviceToHost));
+    if (code)
+        return pn_fail(h, PN_ERR_STATE, "a peer-memory exchange kernel gave up waiting for another rank after 2 s (wait %u: "
+                                        "1 = small regions published, 2 = linear gradients ready, 3 = linear sums written): "
+                                        "the ranks did not all make the same call with the same step", code);
     return PN_OK;
 }
 

@@ -89,6 +89,8 @@ class GameACPathNetNetwork(GameACNetwork):
     population (paths evaluated by this object, default 1), batch_max, gpu.
     """
 
+    LSTM = False
+
     def __init__(self, training_stage, thread_index, device="/cpu:0", FLAGS=""):
         GameACNetwork.__init__(self, training_stage, thread_index, device)
         self.task_index = FLAGS.task_index
@@ -96,7 +98,7 @@ class GameACPathNetNetwork(GameACNetwork):
         stride_size = tuple(int(x) for x in str(FLAGS.stride_size).split(","))
         self.cfg = PathNetConfig(L=FLAGS.L, M=FLAGS.M, N=getattr(FLAGS, "N", FLAGS.L), H=getattr(FLAGS, "H", 160),
                                  W=getattr(FLAGS, "W", 120), C=4, kernels=kernel_num, strides=stride_size, F=8,
-                                 hidden=256, A=max(ACTION_SIZEZ))
+                                 hidden=256, A=max(ACTION_SIZEZ), lstm=self.LSTM)
         self.P = int(getattr(FLAGS, "population", 1))
         self.pop = PathNetPopulation(self.cfg, self.P, int(getattr(FLAGS, "batch_max", 32)),
                                      device=int(getattr(FLAGS, "gpu", 0)))
@@ -197,3 +199,48 @@ class GameACPathNetNetwork(GameACNetwork):
     def get_vars_idx(self):
         """game_ac_network.py:255-271: 1 = update op is run, 0 = frozen; index-aligned with the FULL list."""
         return self._idx_full()
+
+
+class GameACPathNetLSTMNetwork(GameACPathNetNetwork):
+    """PathNet-LSTM actor-critic (game_ac_network.py:303-521), the reference's default (constants.py:31).
+
+    Same super-net without the /M (:394); the module sum feeds BasicLSTMCell(256) unrolled over the fed frames
+    (batch 1 per path, :396-416) whose outputs feed the heads.  Extra variables W_lstm / b_lstm are appended to
+    get_vars() and are never frozen (:437-438,502-520).  The cell state is carried on the host object exactly as the
+    reference does it: run_policy_and_value / run_policy adopt the new state, run_value rolls it back (:468-481),
+    reset_state zeroes it (:441-443)."""
+
+    LSTM = True
+
+    def __init__(self, training_stage, thread_index, device="/cpu:0", FLAGS=""):
+        GameACPathNetNetwork.__init__(self, training_stage, thread_index, device, FLAGS)
+        names = {(t["kind"]): i for i, t in enumerate(self.pop.tensors) if t["kind"] in (8, 9)}
+        self.W_lstm, self.b_lstm = SlabVar(self, names[8], "W_lstm"), SlabVar(self, names[9], "b_lstm")
+        self._state_next = torch.zeros(self.P, 2, self.cfg.hidden, dtype=torch.float32, device=self.pop.device)
+        self.initial_lstm_state = self.step_size = None     # feeds are plain arguments here
+        self.reset_state()
+
+    def reset_state(self):
+        """game_ac_network.py:441-443: zero (c, h)."""
+        self.lstm_state_out = torch.zeros(self.P, 2, self.cfg.hidden, dtype=torch.float32, device=self.pop.device)
+
+    def _forward_one(self, s_t, adopt_state=True):
+        x = torch.as_tensor(np.ascontiguousarray(s_t, dtype=np.float32)).to(self.pop.device)
+        x = x.view(1, 1, self.cfg.H, self.cfg.W, self.cfg.C).expand(self.P, 1, -1, -1, -1).contiguous()
+        nxt = torch.empty_like(self.lstm_state_out)
+        self.pop.bind_lstm_state(self.lstm_state_out, nxt)          # step_size = 1 from the carried state
+        pi, v = self.pop.forward(x)
+        if adopt_state:
+            self.lstm_state_out = nxt
+        k = 0 if self.P == 1 else self.task_index
+        return pi[k, 0].cpu().numpy(), float(v[k, 0])
+
+    def run_value(self, sess, s_t):
+        """game_ac_network.py:468-481: the bootstrap value does not advance the state."""
+        return self._forward_one(s_t, adopt_state=False)[1]
+
+    def all_vars(self):
+        return GameACPathNetNetwork.all_vars(self) + [self.W_lstm, self.b_lstm]
+
+    def _idx_full(self):
+        return GameACPathNetNetwork._idx_full(self) + [1, 1]

@@ -33,6 +33,7 @@ class PathNetConfig:
     F: int = 8                                  # feature_num (game_ac_network.py:132)
     hidden: int = 256                           # game_ac_network.py:146
     A: int = 18                                 # max(ACTION_SIZEZ) (game_ac_network.py:152)
+    lstm: bool = False                          # GameACPathNetLSTMNetwork (game_ac_network.py:303-521): no /M, BasicLSTMCell(256)
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -57,7 +58,7 @@ class PathNetPopulation:
         pc.L, pc.M, pc.H, pc.W, pc.C, pc.F, pc.hidden, pc.A = cfg.L, cfg.M, cfg.H, cfg.W, cfg.C, cfg.F, cfg.hidden, cfg.A
         for i in range(cfg.L - 1):
             pc.kernel[i], pc.stride[i] = cfg.kernels[i], cfg.strides[i]
-        pc.P, pc.B_max, pc.device, pc.flags = self.P, self.B_max, self.device_index, int(flags)
+        pc.P, pc.B_max, pc.device, pc.flags = self.P, self.B_max, self.device_index, int(flags) | (nat.PN_FLAG_LSTM if cfg.lstm else 0)
         h = C.c_void_p()
         nat.check(self.lib.pn_create(C.byref(pc), C.byref(h)))
         self._h = h
@@ -116,6 +117,10 @@ class PathNetPopulation:
                 shp.append((cfg.A,))
             elif k == 6:
                 shp.append((cfg.hidden, 1))
+            elif k == 8:
+                shp.append((2 * cfg.hidden, 4 * cfg.hidden))       # W_lstm (basic_lstm_cell/kernel)
+            elif k == 9:
+                shp.append((4 * cfg.hidden,))                      # b_lstm
             else:
                 shp.append((1,))
         return shp
@@ -148,6 +153,11 @@ class PathNetPopulation:
                 d = 1.0 / math.sqrt(shp[2] * shp[0] * shp[1])
             elif t["kind"] in (2, 4, 6):
                 d = 1.0 / math.sqrt(shp[0])
+            elif t["kind"] == 8:                # BasicLSTMCell kernel: glorot_uniform (the scope's default initializer)
+                d = math.sqrt(6.0 / (shp[0] + shp[1]))
+            if t["kind"] == 9:                  # BasicLSTMCell bias: zeros
+                out.append(np.zeros(shp, dtype=np.float32))
+                continue
             out.append(rng.uniform(-d, d, size=shp).astype(np.float32))
         self.load(self.params, out)
         return out
@@ -173,6 +183,17 @@ class PathNetPopulation:
                 row = t["layer"] if t["layer"] < self.cfg.L - 1 else -1
                 fl[i] = 1 if fp[row, t["module"]] == 1.0 else 0
         self.set_frozen(fl)
+
+    def bind_lstm_state(self, state_in: Optional[torch.Tensor], state_out: Optional[torch.Tensor] = None):
+        """LSTM variant: every path's cell state (c, h) at the start of its sequence, [P, 2, 256] fp32 on the device
+        (None = zeros, reset_state), and where the state after the last step is written (None = nowhere).  The
+        tensors are borrowed until the next call."""
+        for t in (state_in, state_out):
+            if t is not None and (t.dtype != torch.float32 or tuple(t.shape) != (self.P, 2, self.cfg.hidden)
+                                  or not t.is_contiguous() or t.device != self.device):
+                raise ValueError("LSTM state must be a contiguous fp32 [P=%d, 2, %d] tensor on %s" % (self.P, self.cfg.hidden, self.device))
+        self._lstm_state = (state_in, state_out)        # keep them alive while the library holds the pointers
+        nat.check(self.lib.pn_lstm_bind_state(self._h, _ptr(state_in), _ptr(state_out)), self._h)
 
     # -- hot path -------------------------------------------------------------
     def _check_frames(self, frames: torch.Tensor):
@@ -257,6 +278,10 @@ class PathNetPopulation:
 
     def peer_buffer_bytes(self) -> int:
         return int(self.lib.pn_peer_buffer_bytes(self._h))
+
+    def peer_check(self, my_peer_buf_ptr):
+        """Raises PathNetError if an exchange kernel of this rank gave up waiting for a peer (synchronises)."""
+        nat.check(self.lib.pn_peer_check(self._h, C.c_void_p(int(my_peer_buf_ptr))), self._h)
 
     def peer_sum_small(self, peer_ptrs, rank, world, step):
         """Conv + head gradient regions <- sum over the node's GPUs through peer memory (pn_peer_sum_small)."""

@@ -60,6 +60,11 @@ class OverlappedGradSum(object):
             self.peer = None
             self.peer_slabs = None
 
+    def check(self):
+        """Synchronising health check of the peer-memory exchange (a rank that waited 2 s for a peer's flag gave up)."""
+        if self.active and self.peer is not None:
+            self.pop.peer_check(self.peer[parallel.world()[0]])
+
     def path_name(self):
         """Which exchange runs (for the bench line): nothing at one GPU; else the two regions' mechanisms."""
         if not self.active:

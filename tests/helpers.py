@@ -36,7 +36,7 @@ def cfg_from_golden(arr):
 def to_engine_cfg(cfg):
     from pathnet_gym_b200.population import PathNetConfig
     return PathNetConfig(L=cfg.L, M=cfg.M, N=cfg.N, H=cfg.H, W=cfg.W, C=cfg.C, kernels=cfg.kernels,
-                         strides=cfg.strides, F=cfg.F, hidden=cfg.hidden, A=cfg.A)
+                         strides=cfg.strides, F=cfg.F, hidden=cfg.hidden, A=cfg.A, lstm=getattr(cfg, "lstm", False))
 
 
 def rel_err(x, ref):
@@ -61,3 +61,8 @@ def split_flat(cfg, flat):
 
 # BASELINE config C4: second-task transfer, L=4 M=10 N=4, 84x84x4 frames, 3-action head
 C4 = po.OracleConfig(L=4, M=10, N=4, H=84, W=84, C=4, A=3)
+
+# the LSTM variant (the reference's default network, constants.py:31) on the C2 / C3 nets and on a small geometry
+C1_LSTM = po.OracleConfig(L=3, M=10, N=3, H=84, W=84, C=4, A=18, lstm=True)
+C3_LSTM = po.OracleConfig(L=4, M=10, N=4, H=84, W=84, C=4, A=18, lstm=True)
+TC20_LSTM = po.OracleConfig(L=3, M=10, N=3, H=20, W=24, C=4, kernels=(8, 2, 3), strides=(4, 1, 1), F=8, hidden=256, A=6, lstm=True)

@@ -37,7 +37,7 @@ def test_network_thread_applier_like_the_reference_driver(native_lib):
     from pathnet_gym_b200.a3c_training_thread import A3CTrainingThread
     from pathnet_gym_b200.constants import GRAD_NORM_CLIP, MAX_TIME_STEP, RMSP_ALPHA, RMSP_EPSILON
     from pathnet_gym_b200.rmsprop_applier import RMSPropApplier
-    FLAGS = make_flags()
+    FLAGS = make_flags(use_lstm=False)            # the feed-forward class (the reference constant picks the LSTM class)
     np.random.seed(0)
     applier = RMSPropApplier(learning_rate=None, decay=RMSP_ALPHA, momentum=0.0, epsilon=RMSP_EPSILON,
                              clip_norm=GRAD_NORM_CLIP, device="/gpu:0")
@@ -72,6 +72,60 @@ def test_network_thread_applier_like_the_reference_driver(native_lib):
     assert not torch.equal(net.pop.params, before)
     assert applier.get_slot(net.W_fc2, "rms").shape == (256, 18)
     assert th._anneal_learning_rate(MAX_TIME_STEP * 2) == 0.0
+    net.pop.close()
+
+
+def test_lstm_network_and_thread_like_the_reference_driver(native_lib):
+    """The reference's default (constants.py:31 USE_LSTM = True): GameACPathNetLSTMNetwork through A3CTrainingThread.
+    State carry of run_policy_and_value, roll-back of run_value (game_ac_network.py:448-481), reset_state, the extra
+    variables in get_vars (:502-520), and one process() call whose training batch is fed in time order from the state
+    the rollout started with (a3c_training_thread.py:113-114,184-203) -- checked against the oracle's LSTM."""
+    import dataclasses
+    from pathnet_gym_b200 import constants, pathnet
+    from pathnet_gym_b200.a3c_training_thread import A3CTrainingThread
+    from pathnet_gym_b200.constants import GRAD_NORM_CLIP, MAX_TIME_STEP, RMSP_ALPHA, RMSP_EPSILON
+    from pathnet_gym_b200.game_ac_network import GameACPathNetLSTMNetwork
+    from pathnet_gym_b200.rmsprop_applier import RMSPropApplier
+    assert constants.USE_LSTM is True
+    FLAGS = make_flags()                            # no use_lstm field: the constant decides, as in the reference
+    np.random.seed(0)
+    applier = RMSPropApplier(learning_rate=None, decay=RMSP_ALPHA, momentum=0.0, epsilon=RMSP_EPSILON,
+                             clip_norm=GRAD_NORM_CLIP, device="/gpu:0")
+    th = A3CTrainingThread(0, "", 0, 7.0016e-4, None, applier, MAX_TIME_STEP, device="/gpu:0", FLAGS=FLAGS, task_index=0)
+    net = th.local_network
+    assert isinstance(net, GameACPathNetLSTMNetwork)
+    assert len(net.get_vars()) == 2 * (2 * 10 + 10) + 4 + 2 == len(th.apply_gradients)
+    assert net.W_lstm.get_shape() == (512, 1024) and net.b_lstm.get_shape() == (1024,)
+    assert net.get_vars_idx()[-6:] == [1, 1, 1, 1, 1, 1]
+    net.b_lstm.assign(np.random.default_rng(2).normal(size=1024) * 0.1)      # (the initial bias is all zero)
+    pathnet.seed(7)
+    geo = pathnet.get_geopath(FLAGS.L, FLAGS.M, FLAGS.N)
+    pathnet.geopath_insert(None, net.geopath_update_placeholders_set[0], net.geopath_update_ops_set[0], geo, FLAGS.L, FLAGS.M)
+    cfg = hp.C1_LSTM
+    params = net.pop.dump(net.pop.params)
+    frames = (np.random.randint(0, 256, size=(3, 84, 84, 4)).astype(np.float32)) * np.float32(1 / 255.0)
+    # three acting steps carry the state; the oracle runs the same three frames as one sequence from zeros
+    outs = [net.run_policy_and_value(None, f) for f in frames[:2]]
+    v_boot = net.run_value(None, frames[2])                     # does not advance the state ...
+    outs.append(net.run_policy_and_value(None, frames[2]))      # ... so the same frame gives the same value again
+    assert abs(outs[2][1] - v_boot) < 1e-6
+    st = {}
+    pi_r, v_r, _, _ = po.forward_backward_numpy(cfg, params, frames, geo, [0, 0, 0], [0.0] * 3, [0.0] * 3, want_grads=False,
+                                                state_out=st)
+    for i in range(3):
+        assert hp.rel_err(outs[i][0], pi_r[i]) < 1e-3 and abs(outs[i][1] - v_r[i]) < 1e-3 * max(1.0, abs(v_r[i]))
+    got = net.lstm_state_out.cpu().numpy()[0]
+    assert hp.rel_err(got[0], st[0]) < 1e-3 and hp.rel_err(got[1], st[1]) < 1e-3
+    net.reset_state()
+    assert float(net.lstm_state_out.abs().max()) == 0.0
+    th.set_training_stage(0)
+    before = net.pop.params.clone()
+    diff = th.process(None, 0, None, None, None, None, None, None, FLAGS, None, None)
+    assert diff == 20 and np.isfinite(th.last_loss)
+    t = net.pop.tensors[net.W_lstm.index]
+    sl = slice(t["offset"], t["offset"] + t["length"])
+    assert not torch.equal(net.pop.params[sl], before[sl])      # the cell's weights train
+    assert float(net.lstm_state_out.abs().max()) > 0.0          # and the acting state moved on with the rollout
     net.pop.close()
 
 

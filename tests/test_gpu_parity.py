@@ -766,3 +766,69 @@ def test_c4_task_transfer_real_shape(eng_mod):
             assert np.abs(got_p[i] - want_p[i]).max() <= REL_TOL * max(upd, 1e-30), tt[i]["name"]
             assert hp.rel_err(got_ms[i], want_ms[i]) < 1e-5, tt[i]["name"]
     pop.close()
+
+
+# ---------------------------------------------------------------------------
+# the LSTM variant (GameACPathNetLSTMNetwork, game_ac_network.py:303-521)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("cfgname,P,B,zero_state", [("TC20_LSTM", 5, 7, False), ("TC20_LSTM", 3, 1, True),
+                                                    ("C1_LSTM", 64, 20, False), ("C3_LSTM", 6, 20, False)])
+def test_lstm_variant_vs_oracle(eng_mod, cfgname, P, B, zero_state):
+    """Population-batched BasicLSTMCell(256) + BPTT against the fp64 oracle: pi, v, loss, every gradient tensor
+    (W_lstm / b_lstm included), the state after the last step, and one clipped RMSProp update -- up to the reference's
+    LOCAL_T_MAX = 20 steps on 64 paths of the C2 net."""
+    cfg = getattr(hp, cfgname)
+    params = po.init_params(cfg, 6)
+    rng = np.random.default_rng(8)
+    params[-1] = (rng.normal(size=params[-1].shape) * 0.1).astype(np.float32)          # (b_lstm is all zero at init)
+    frames, actions, td, r, masks = hp.synth_inputs(cfg, P, B, 60)
+    st_in = None if zero_state else (rng.normal(size=(P, 2, cfg.hidden)) * 0.5).astype(np.float32)
+    states = None if zero_state else [(st_in[p, 0], st_in[p, 1]) for p in range(P)]
+    pre = [{} for _ in range(P)]
+    pi64, v64, l64, G64 = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", pre_out=pre,
+                                             lstm_states=states)
+    pop = make_pop(eng_mod, cfg, P, B, params, masks)
+    assert len(pop.tensors) == len(po.tensor_table(cfg)) and pop.tensors[-2]["kind"] == 8
+    st_out = torch.zeros(P, 2, cfg.hidden, device="cuda")
+    pop.bind_lstm_state(None if zero_state else dev(st_in), st_out)
+    loss, pi, v = pop.train_step(dev(frames), dev(actions), dev(td), dev(r), 0.01, want_outputs=True)
+    G = pop.dump(pop.grads)
+    # evaluate the oracle with the CUDA path's ReLU decisions (see _per_tensor_vs_fp64)
+    dec = [pop.relu_decisions(l, B) for l in range(cfg.L)]
+    override, flips, total = [], [], 0
+    for p in range(P):
+        d = {}
+        for (l, j), pr in pre[p].items():
+            mk = dec[l][p, :, j].reshape(pr.shape)
+            d[(l, j)] = mk
+            diff = mk != (pr > 0)
+            total += pr.size
+            if diff.any():
+                flips += [float(x) for x in np.abs(pr[diff]) / np.sqrt(np.mean(pr ** 2))]
+        override.append(d)
+    piF, vF, lF, GF = po.population_step(cfg, params, frames, masks, actions, td, r, impl="numpy", relu_override=override,
+                                         lstm_states=states)
+    names = [t["name"] for t in po.tensor_table(cfg)]
+    same = {"pi": hp.rel_err(pi.cpu().numpy(), piF), "v": hp.rel_err(v.cpu().numpy(), vF),
+            "loss": hp.rel_err(loss.cpu().numpy(), lF)}
+    same.update({"grad/" + n: hp.rel_err(a, b) for n, a, b in zip(names, G, GF)})
+    w = max(same, key=same.get)
+    _report["lstm_%s_%dx%d.worst" % (cfgname, P, B)] = [w, same[w]]
+    _note("lstm_%s_%dx%d.relu_decisions_differing" % (cfgname, P, B), len(flips))
+    _check_population(same, flips, total)
+    # final state of path 0 (one more oracle pass that returns it)
+    so = {}
+    po.forward_backward_numpy(cfg, params, po.frames_to_float(frames[0]), po.gates_from_masks(cfg, masks[0]), actions[0], td[0],
+                              r[0], want_grads=False, lstm_state=None if zero_state else states[0], state_out=so)
+    got = st_out[0].cpu().numpy()
+    assert hp.rel_err(got[0], so[0]) < REL_TOL and hp.rel_err(got[1], so[1]) < REL_TOL
+    # the update: W_lstm / b_lstm are ordinary tensors of the slab (clipped per tensor like every other)
+    ms0 = pop.dump(pop.ms)
+    pop.apply_gradients(7.0016e-4)
+    fz = np.zeros(len(names), np.uint8)
+    want_p, want_ms, _ = po.apply_gradients(params, ms0, [np.zeros_like(x) for x in params], G, fz, 7.0016e-4)
+    got_p = pop.dump(pop.params)
+    for i in (len(names) - 2, len(names) - 1):
+        upd = np.abs(np.asarray(want_p[i], np.float64) - params[i]).max()
+        assert np.abs(got_p[i] - want_p[i]).max() <= REL_TOL * max(upd, 1e-30), names[i]
+    pop.close()

@@ -10,7 +10,7 @@ import torch
 import torch.distributed as dist
 
 from pathnet_gym_b200.population import PathNetConfig, PathNetPopulation, geopath_init
-from pathnet_gym_b200.trainer import OverlappedGradSum
+from pathnet_gym_b200.trainer import OverlappedGradSum, PopulationTrainer
 
 
 def main():
@@ -39,12 +39,35 @@ def main():
         torch.cuda.synchronize()
         err = float((pop.grads - ref).norm() / ref.norm())
         worst = max(worst, err)
+    gs.check()                      # no exchange kernel gave up waiting for a peer
+    # complete steps through the public trainer (exchange + clipped RMSProp): every rank must end with the same bits, and
+    # the same training with ONE plain all-reduce per step must agree
+    p0, ms0 = pop.params.clone(), pop.ms.clone()
+    tr = PopulationTrainer(pop)
+    for it in range(5):
+        tr.step(frames, actions, td, r, 7.0016e-4)
+    tr.tail.gradsum.check()
+    torch.cuda.synchronize()
+    trained = pop.params.clone()
+    pop.params.copy_(p0); pop.ms.copy_(ms0)
+    for it in range(5):
+        pop.train_step(frames, actions, td, r, 0.01)
+        dist.all_reduce(pop.grads)
+        pop.apply_gradients(7.0016e-4)
+    torch.cuda.synchronize()
+    train_err = float((trained - pop.params).norm() / (pop.params - p0).norm())
+    gathered = [torch.empty_like(trained) for _ in range(world)]
+    dist.all_gather(gathered, trained)
+    identical = all(torch.equal(g, trained) for g in gathered)
     if rank == 0:
         print(json.dumps({"world": world, "overlapped_vs_plain_allreduce_rel_err": worst,
+                          "params_identical_on_all_ranks": identical,
+                          "trained_vs_plain_allreduce_training_rel_err": train_err,
                           "small_regions_via_peer_memory": gs.peer is not None,
                           "linear_region_via_peer_memory": gs.peer_slabs is not None,
                           "peer_setup_error": getattr(gs, "peer_error", None)}))
     assert worst < 1e-6, worst
+    assert identical and train_err < 1e-6, (identical, train_err)
     pop.close()
     dist.destroy_process_group()
 
