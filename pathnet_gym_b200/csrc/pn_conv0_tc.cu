@@ -465,29 +465,44 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
 //   pixels of  x[t, oy*s+kh, ox*s+kw, ci] * dpre_j[t, oy, ox, co],   dpre_j = dY * relu_mask_j
 // (tf.gradients through Conv2D, a3c_training_thread.py:55-60).  Per tap (dy,dx) this is
 //   D_tap[64 x N] += A_tap^T[64 x m] * dq[m x N]      (m = block raster index, K of the MMA)
-// with A_tap^T the staged frame read MN-major through a shifted descriptor (same buffer as the forward
-// kernel) and dq the masked output gradient quantised to four signed base-256 digits of
-// round(dpre * 2^(30-e)), 2^e >= max|dY| over the batch (one global power-of-two scale, so the integer
-// accumulation is exact and order-independent; resolution 2^-30 of the largest gradient entry).
-// One work item = (path, chunk of its transitions); the four tap accumulators live in TMEM (M = 64,
-// N = 32 columns per module) for the whole chunk and are flushed once into the partial-sum buffer that
-// conv_wgrad_reduce_kernel adds up in a fixed order.
-// Warp roles (320 threads): warps 0-7 quantise dq and flush (two groups of four: a group flushes two of the
-// four tap accumulators), warp 8 frame producer, warp 9 MMA issue.
+// with A_tap^T the staged frame read MN-major through a shifted descriptor and dq the masked output gradient quantised to
+// kWgDigits signed base-256 digits of round(dpre * 2^(22-e_p)), 2^e_p >= max|dY| over the PATH's batch (one power-of-two
+// scale per path, so the integer accumulation is exact and order-independent; resolution 2^-22 of the path's largest
+// gradient entry).
+//
+// M = 128: the two taps of a kernel row share one MMA.  A tcgen05 instruction with M = 64 costs what one with M = 128
+// costs (the pipe time is the operand fetch, 128 B per clock), and it fills only half of the TMEM lanes.  Rows 64..127 of
+// the A operand must sit SBO * 4 bytes behind rows 0..63 in shared memory, so every frame is staged TWICE: copy 0 as it
+// is and copy 1 shifted by one block (the TMA load starts 4 u32 further right; the columns it then reads past the row end are
+// zero-filled, they only feed discarded positions).  One MMA per kernel row dy then covers (dy, dx = 0) in accumulator rows
+// 0..63 and (dy, dx = 1) in rows 64..127: 28 MMAs per transition instead of 56.  The TMA box carries one extra (zero-filled)
+// block row per region so that four regions are a multiple of 128 bytes and both copies start 128-byte aligned.
+//
+// One work item = (path, chunk of its transitions); the two accumulators (one per dy, N <= 96 columns each) live in
+// TMEM for the whole chunk.  There are TWO accumulator sets: the flush of item i (dedicated warps) runs underneath the
+// MMAs of item i+1, which used to wait for it (20 % of the kernel).
+// Warp roles (704 threads): warps 0-15 quantise dq, one raster row per thread (and keep the bias-gradient partial sums),
+// warps 16-19 flush (one TMEM lane quadrant each), warp 20 frame producer, warp 21 MMA issue (highest id = scheduler
+// priority).  With 8 quantiser warps the MMA warp waited for quantised operands 58 % of the time.
 // =====================================================================================================
-constexpr int kWgDigits = 4;
-constexpr int kWgSlotCols = 8 * kWgDigits;      // 32 accumulator columns per module
-constexpr int kWgTapCols = 128;                  // TMEM columns reserved per tap (4 modules per pass)
+constexpr int kWgDigits = 3;
+constexpr int kWgQuantWarps = 16;                // one raster row per quantiser thread (mq <= 512)
+constexpr int kWgThreads = (kWgQuantWarps + 6) * 32;
+constexpr int kWgSetCols = 256;                  // TMEM columns per accumulator set: two accumulators of 128
+constexpr int kWgAccCols = 128;
 
-__global__ void absmax_kernel(const float* __restrict__ x, size_t n4, unsigned* __restrict__ out) {
+// max |x| per path (x = the layer-0 output gradient [P][per_path floats]) when no earlier kernel has left it behind
+__global__ void absmax_kernel(const float* __restrict__ x, size_t n4_per_path, unsigned* __restrict__ out) {
+    const int p = blockIdx.y;
+    const float4* xp = reinterpret_cast<const float4*>(x) + (size_t)p * n4_per_path;
     float m = 0.f;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
-        const float4 v = reinterpret_cast<const float4*>(x)[i];
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4_per_path; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = xp[i];
         m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));   // non-negative floats order like uints
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out + p, __float_as_uint(m));   // non-negative floats order like uints
 }
 
 __device__ __forceinline__ uint32_t pack4(const int* d) {
@@ -499,26 +514,30 @@ __device__ __forceinline__ uint32_t nib_to_bytemask(unsigned nib) {
            ((nib & 8u) ? 0xFF000000u : 0u);
 }
 
-__global__ void __launch_bounds__(kTcThreads, 1)
+struct WgGeom {
+    int region_bytes;     // (Hs + 1) * row_bytes: one region of a staged frame copy (multiple of 32)
+    int stage_bytes;      // two copies of four regions + slack for the shifted reads
+    int region_q;         // mq * 16: one 16-column group of dq
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1)
 conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ dY, const uint8_t* __restrict__ R,
                       const unsigned* __restrict__ absmax, PnNetDesc nd, const uint32_t* __restrict__ masks, int B,
-                      int P, int cs, int nch, int nch_alloc, TcGeom gm, float* __restrict__ part, long long* __restrict__ dbg) {
+                      int P, int cs, int nch, int nch_alloc, TcGeom gm, WgGeom wg, float* __restrict__ part, long long* __restrict__ dbg) {
     const bool dbg8 = dbg && dbg[148 * 8] == 8;                 // PN_TC_DEBUG=8: where the weight-gradient kernel's roles wait
     const long long t_entry = dbg8 ? pinned_clock() : 0;
     extern __shared__ __align__(1024) uint8_t smem[];
-    const int region_q = gm.mq * 16;                       // bytes of one 16-column group of dq
-    const int dq_stage_bytes = 2 * kPassSlots * region_q;  // up to 4 modules x 2 groups
+    const int dq_stage_bytes = 2 * kWgDigits * wg.region_q;     // up to 4 modules: 3 digits x 32 columns = 6 groups of 16
     uint8_t* frame_s = smem;
-    uint8_t* dq_s = smem + 2 * (size_t)gm.stage_bytes;
-    // the dq ring doubles as the 16 KB scratch of the bias-gradient reduction at flush time
-    const int dq_total = max(2 * dq_stage_bytes, (256 + 8) * 32 * (int)sizeof(float));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(dq_s + dq_total);
+    uint8_t* dq_s = smem + 2 * (size_t)wg.stage_bytes;
+    float* bias_s = reinterpret_cast<float*>(dq_s + 2 * (size_t)dq_stage_bytes);     // [quantiser warps][32]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + kWgQuantWarps * 32);
     uint64_t* frame_full = bars;          // [2]
     uint64_t* frame_empty = bars + 2;     // [2]
     uint64_t* dq_full = bars + 4;         // [2]
     uint64_t* dq_empty = bars + 6;        // [2]
-    uint64_t* acc_full = bars + 8;
-    uint64_t* acc_empty = bars + 9;
+    uint64_t* acc_full = bars + 8;        // [2] accumulator set s holds a finished item
+    uint64_t* acc_empty = bars + 10;      // [2] ... and has been flushed
     __shared__ uint32_t tmem_base_s;
 
     // broadcast through a shuffle so that the compiler knows the warp index is warp-uniform (role branches
@@ -526,26 +545,25 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int npix = gm.OH * gm.OW;
     const int nitems = P * nch;      // round-robin over the CTAs: a path's chunks land on different CTAs, which spreads expensive
-                                     // paths by itself (a contiguous cost-balanced split measured worse here: 237 vs 214 us)
+                                     // paths by itself (a contiguous cost-balanced split measured worse here)
+    const int stride_part = nd.KK[0] * PN_F + PN_F;
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
             mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1);
-            mbar_init(&dq_full[i], 256); mbar_init(&dq_empty[i], 1);
+            mbar_init(&dq_full[i], kWgQuantWarps * 32); mbar_init(&dq_empty[i], 1);
+            mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128);
         }
-        mbar_init(acc_full, 1);
-        mbar_init(acc_empty, 256);
         fence_mbar_init();
     }
-    // roles: warps 0-7 quantise + flush, warp 8 frame producer, warp 9 MMA issue (highest id = scheduler priority)
-    if (warp == 9) tmem_alloc(&tmem_base_s, 512);
+    if (warp == kWgQuantWarps + 5) tmem_alloc(&tmem_base_s, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
 
-    if (warp == 8) {
-        // ================= frame producer =================
+    if (warp == kWgQuantWarps + 4) {
+        // ================= frame producer: two copies per frame (see above) =================
         if (lane == 0) tma_prefetch_desc(&tmap);
         int stage = 0;
         uint32_t phase = 0;
@@ -556,19 +574,23 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
             for (int pass = 0; pass < npass; ++pass)
                 for (int b = b_lo; b < b_hi; ++b) {
-                    const size_t t = (size_t)p * B + b;
+                    const int t = p * B + b;
                     mbar_wait(&frame_empty[stage], phase ^ 1);
-                    if (lane == 0)
-                        stage_frame_tma(frame_s + (size_t)stage * gm.stage_bytes, &tmap, (int)t, gm, &frame_full[stage]);
+                    if (lane == 0) {
+                        uint8_t* dst = frame_s + (size_t)stage * wg.stage_bytes;
+                        mbar_expect_tx(&frame_full[stage], (uint32_t)(8 * wg.region_bytes));
+                        tma_load_4d(dst, &tmap, 0, 0, 0, t, &frame_full[stage]);
+                        tma_load_4d(dst + 4 * wg.region_bytes, &tmap, 4, 0, 0, t, &frame_full[stage]);     // one block = 4 u32 further right
+                    }
                     __syncwarp();
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
         }
-    } else if (warp == 9) {
+    } else if (warp == kWgQuantWarps + 5) {
         // ================= MMA issue =================
         // whole-warp, warp-uniform code; only the tcgen05 instructions are elected to one lane
         int stage = 0;
-        uint32_t phase = 0, nflush = 0;
+        uint32_t phase = 0, nacc = 0;                           // nacc: (item, pass) accumulations started so far
         long long m_wframe = 0, m_wdq = 0, m_wacc = 0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int p = item / nch, ch = item % nch;
@@ -578,12 +600,14 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
             for (int pass = 0; pass < npass; ++pass) {
                 if (b_lo >= b_hi) continue;
                 const int nsl = min(kPassSlots, ns - pass * kPassSlots);
-                const int N = kWgSlotCols * nsl;
-                const uint32_t idesc = make_idesc_i8(64, N, 0, 1, 1, 1);
+                const int N = kWgDigits * 8 * ((nsl + 1) & ~1);                  // columns (digit, slot, channel), slots padded to even
+                const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 1, 1);
+                const uint32_t set = nacc & 1u;
                 const long long ca = dbg8 ? pinned_clock() : 0;
-                mbar_wait(acc_empty, (nflush & 1) ^ 1);       // previous flush has drained the accumulators
+                mbar_wait(&acc_empty[set], ((nacc >> 1) & 1u) ^ 1u);           // the flush of the item that used this set is done
                 if (dbg8) m_wacc += pinned_clock() - ca;
                 tc_fence_after();
+                const uint32_t d0 = td + set * kWgSetCols;
                 uint32_t accum = 0;
                 for (int b = b_lo; b < b_hi; ++b) {
                     const long long c0 = dbg8 ? pinned_clock() : 0;
@@ -592,22 +616,19 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     mbar_wait(&dq_full[stage], phase);
                     if (dbg8) { const long long c2 = pinned_clock(); m_wframe += c1 - c0; m_wdq += c2 - c1; }
                     tc_fence_after();
-                    const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
+                    const uint32_t fbase = smem_u32(frame_s + (size_t)stage * wg.stage_bytes);
                     const uint32_t qbase = smem_u32(dq_s + (size_t)stage * dq_stage_bytes);
                     // a K step advances both start addresses by 32 blocks (descriptor unit: 16 bytes): one add each
-                    uint32_t alo[4];
-#pragma unroll
-                    for (int tap = 0; tap < 4; ++tap) alo[tap] = desc_lo(fbase + (uint32_t)(((tap >> 1) * gm.Ws + (tap & 1)) * 16), 128);
+                    uint32_t alo0 = desc_lo(fbase, 128), alo1 = desc_lo(fbase + (uint32_t)(gm.Ws * 16), 128);
                     uint32_t blo = desc_lo(qbase, 128);
-                    const uint32_t ahi = desc_hi((uint32_t)gm.region_bytes), bhi = desc_hi((uint32_t)region_q);
+                    const uint32_t ahi = desc_hi((uint32_t)wg.region_bytes), bhi = desc_hi((uint32_t)wg.region_q);
                     for (int ks = 0; ks < gm.mq / 32; ++ks) {
                         const uint64_t bd = desc_join(blo, bhi);
-#pragma unroll
-                        for (int tap = 0; tap < 4; ++tap) {
-                            if (elect_one()) umma_i8(td + tap * kWgTapCols, desc_join(alo[tap], ahi), bd, idesc, accum);
-                            alo[tap] += 32;
+                        if (elect_one()) {
+                            umma_i8(d0, desc_join(alo0, ahi), bd, idesc, accum);
+                            umma_i8(d0 + kWgAccCols, desc_join(alo1, ahi), bd, idesc, accum);
                         }
-                        blo += 32;
+                        alo0 += 32; alo1 += 32; blo += 32;
                         accum = 1;
                     }
                     if (elect_one()) {
@@ -617,37 +638,93 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     __syncwarp();
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
-                if (elect_one()) umma_commit(acc_full);
+                if (elect_one()) umma_commit(&acc_full[set]);
                 __syncwarp();
-                ++nflush;
+                ++nacc;
             }
         }
         if (dbg8 && lane == 0) {
             dbg[blockIdx.x * 8 + 0] = m_wframe; dbg[blockIdx.x * 8 + 1] = m_wdq; dbg[blockIdx.x * 8 + 2] = m_wacc;
             dbg[blockIdx.x * 8 + 3] = pinned_clock() - t_entry;
         }
-    } else {
-        // ================= quantise dq per transition, flush the accumulators per (item, pass) =================
-        const int quad = warp & 3, fgroup = warp >> 2;         // TMEM lane quadrant; flush group (taps 2*fgroup, +1)
-        const int tid = threadIdx.x;                           // 0..255
-        int stage = 0;
-        uint32_t phase = 0, nflush = 0;
-        const unsigned am = *absmax;
-        int e = 0;
-        if (am) frexpf(__uint_as_float(am), &e);                // max = f * 2^e, f in [0.5, 1)  =>  2^e > max
-        const float qscale = am ? ldexpf(1.0f, 30 - e) : 0.f;
-        const double dscale = am ? ldexp(1.0, e - 30) / 255.0 : 0.0;
-        const int stride_part = nd.KK[0] * PN_F + PN_F;
-        long long q_wempty = 0, q_wfull = 0, q_flush = 0;
+    } else if (warp >= kWgQuantWarps) {
+        // ================= flush: TMEM lane = accumulator row = (dx, g, byte) =================
+        const int quad = warp & 3;
+        const int r = quad * 32 + lane;                         // 0..127
+        const int dx = r >> 6, g = (r >> 4) & 3, bb = r & 15;
+        uint32_t nacc = 0;
+        long long f_wait = 0, f_work = 0;
         for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
             const int p = item / nch, ch = item % nch;
             const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
             const uint32_t mask = masks[p * nd.L];
             const int ns = __popc(mask);
             const int npass = (ns + kPassSlots - 1) / kPassSlots;
+            const unsigned am = absmax[p];
+            int e = 0;
+            if (am) frexpf(__uint_as_float(am), &e);            // max = f * 2^e, f in [0.5, 1)  =>  2^e > max
+            const double dscale = am ? ldexp(1.0, e - (8 * kWgDigits - 2)) / 255.0 : 0.0;
             for (int pass = 0; pass < npass; ++pass) {
                 if (b_lo >= b_hi) continue;
                 const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                const int dstride = 8 * ((nsl + 1) & ~1);       // columns per digit
+                const uint32_t set = nacc & 1u;
+                const long long cf = dbg8 ? pinned_clock() : 0;
+                mbar_wait(&acc_full[set], (nacc >> 1) & 1u);
+                const long long cf1 = dbg8 ? pinned_clock() : 0;
+                tc_fence_after();
+                for (int dy = 0; dy < 2; ++dy) {
+                    const int kh = dy * gm.s + g, kw = dx * gm.s + bb / gm.C, ci = bb % gm.C;
+                    const int kk = (kh * nd.k[0] + kw) * gm.C + ci;
+                    for (int sl = 0; sl < nsl; ++sl) {
+                        uint32_t q0[8], q1[8], q2[8];
+                        const uint32_t ta = td + ((uint32_t)(quad * 32) << 16) + set * kWgSetCols + dy * kWgAccCols + sl * 8;
+                        tmem_ld8(ta, q0); tmem_ld8(ta + dstride, q1); tmem_ld8(ta + 2 * dstride, q2);
+                        tmem_ld_wait();
+                        float o[8];
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            // digits combined in 64-bit integers (exact), then ONE conversion
+                            const long long v = (long long)(int)q0[c] + ((long long)(int)q1[c] << 8) + ((long long)(int)q2[c] << 16);
+                            o[c] = (float)((double)v * dscale);
+                        }
+                        const int j = __fns(mask, 0, pass * kPassSlots + sl + 1);
+                        float4* dst = reinterpret_cast<float4*>(
+                            part + ((size_t)(p * nch_alloc + ch) * nd.M + j) * stride_part + (size_t)kk * PN_F);
+                        dst[0] = make_float4(o[0], o[1], o[2], o[3]);
+                        dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+                    }
+                }
+                tc_fence_before();
+                mbar_arrive(&acc_empty[set]);
+                if (dbg8) { f_wait += cf1 - cf; f_work += pinned_clock() - cf1; }
+                ++nacc;
+            }
+        }
+        if (dbg8 && threadIdx.x == kWgQuantWarps * 32) { dbg[blockIdx.x * 8 + 5] = f_wait; dbg[blockIdx.x * 8 + 6] = f_work; }
+    } else {
+        // ================= quantise dq per transition; bias-gradient partials per (item, pass) =================
+        const int m = threadIdx.x;                             // this thread's raster row, 0..511 (rows >= mq: nothing to do)
+        const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
+        const bool inside = m < gm.mq, valid = inside && ox < gm.OW && oy < gm.OH;
+        const int pix = oy * gm.OW + ox;
+        int stage = 0;
+        uint32_t phase = 0;
+        long long q_wempty = 0;
+        for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+            const int p = item / nch, ch = item % nch;
+            const int b_lo = ch * cs, b_hi = min(B, b_lo + cs);
+            const uint32_t mask = masks[p * nd.L];
+            const int ns = __popc(mask);
+            const int npass = (ns + kPassSlots - 1) / kPassSlots;
+            const unsigned am = absmax[p];
+            int e = 0;
+            if (am) frexpf(__uint_as_float(am), &e);
+            const float qscale = am ? ldexpf(1.0f, (8 * kWgDigits - 2) - e) : 0.f;     // |q| <= 2^22
+            for (int pass = 0; pass < npass; ++pass) {
+                if (b_lo >= b_hi) continue;
+                const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                const int npair = (nsl + 1) >> 1;               // 16-column groups per digit
                 int jl[kPassSlots];
 #pragma unroll
                 for (int sl = 0; sl < kPassSlots; ++sl) jl[sl] = sl < nsl ? __fns(mask, 0, pass * kPassSlots + sl + 1) : 0;
@@ -658,65 +735,58 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     for (int c = 0; c < 8; ++c) bsum[sl][c] = 0.f;
                 for (int b = b_lo; b < b_hi; ++b) {
                     const size_t t = (size_t)p * B + b;
+                    // loads first (they do not depend on the ring), then wait for the stage
+                    float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
+                    uint32_t rb = 0;
+                    if (valid) {
+                        const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pix) * PN_F);
+                        ga = __ldg(g4); gb = __ldg(g4 + 1);
+#pragma unroll
+                        for (int sl = 0; sl < kPassSlots; ++sl)
+                            if (sl < nsl) rb |= (uint32_t)__ldg(R + (t * nd.M + jl[sl]) * npix + pix) << (8 * sl);
+                    }
                     const long long cq = dbg8 ? pinned_clock() : 0;
                     mbar_wait(&dq_empty[stage], phase ^ 1);
                     if (dbg8) q_wempty += pinned_clock() - cq;
-                    uint8_t* dq = dq_s + (size_t)stage * dq_stage_bytes;
-                    for (int base = 0; base < gm.mq; base += 512) {
-                        // two raster rows per thread; all global loads are issued before either is processed
-                        int mm[2], pixv[2];
-                        bool val[2];
-                        float4 ga[2], gb[2];
-                        uint32_t rb[2];
+                    if (inside) {
+                        uint8_t* dq = dq_s + (size_t)stage * dq_stage_bytes + m * 16;
+                        const float dv[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+                        // balanced base-256 digits: the low byte of q is digit 0, of q1 = (q + 128) >> 8 digit 1, of
+                        // q2 = (q1 + 128) >> 8 digit 2 (two's complement bytes are what the s8 operand wants)
+                        int q0[8], q1[8], q2[8];
 #pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            const int m = base + u * 256 + tid;
-                            mm[u] = m;
-                            const int oy = m / gm.Ws, ox = m - oy * gm.Ws;
-                            val[u] = m < gm.mq && ox < gm.OW && oy < gm.OH;
-                            pixv[u] = oy * gm.OW + ox;
-                            ga[u] = gb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            rb[u] = 0;
-                            if (val[u]) {
-                                const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pixv[u]) * PN_F);
-                                ga[u] = g4[0]; gb[u] = g4[1];
-#pragma unroll
-                                for (int sl = 0; sl < kPassSlots; ++sl)
-                                    if (sl < nsl) rb[u] |= (uint32_t)R[(t * nd.M + jl[sl]) * npix + pixv[u]] << (8 * sl);
-                            }
+                        for (int c = 0; c < 8; ++c) {
+                            q0[c] = __float2int_rn(dv[c] * qscale);
+                            q1[c] = (q0[c] + 128) >> 8;
+                            q2[c] = (q1[c] + 128) >> 8;
                         }
+                        uint32_t w[kWgDigits][2];               // [digit][channels 0-3 / 4-7], byte k = channel
 #pragma unroll
-                        for (int u = 0; u < 2; ++u) {
-                            const int m = mm[u];
-                            if (m >= gm.mq) continue;
-                            const float dv[8] = {ga[u].x, ga[u].y, ga[u].z, ga[u].w, gb[u].x, gb[u].y, gb[u].z, gb[u].w};
-                            uint32_t w[4][2];                    // [digit][channels 0-3 / 4-7]
-                            int dg[4][8];
+                        for (int hf = 0; hf < 2; ++hf) {
+                            const int* a0 = &q0[4 * hf]; const int* a1 = &q1[4 * hf]; const int* a2 = &q2[4 * hf];
+                            w[0][hf] = __byte_perm(__byte_perm(a0[0], a0[1], 0x0040), __byte_perm(a0[2], a0[3], 0x0040), 0x5410);
+                            w[1][hf] = __byte_perm(__byte_perm(a1[0], a1[1], 0x0040), __byte_perm(a1[2], a1[3], 0x0040), 0x5410);
+                            w[2][hf] = __byte_perm(__byte_perm(a2[0], a2[1], 0x0040), __byte_perm(a2[2], a2[3], 0x0040), 0x5410);
+                        }
+                        // columns (digit, slot, channel): a 16-column group = two slots of one digit
+#pragma unroll
+                        for (int pr = 0; pr < kPassSlots / 2; ++pr) {
+                            if (pr >= npair) break;
+                            const unsigned bits0 = (rb >> (16 * pr)) & 255u, bits1 = (rb >> (16 * pr + 8)) & 255u;   // 0 outside the grid / for the pad slot
+                            // bit k -> byte k = 0xFF: spread the four bits to the bytes' low bits, then multiply by 255
+                            const uint32_t m0lo = (((bits0 & 15u) * 0x00204081u) & 0x01010101u) * 255u;
+                            const uint32_t m0hi = (((bits0 >> 4) * 0x00204081u) & 0x01010101u) * 255u;
+                            const uint32_t m1lo = (((bits1 & 15u) * 0x00204081u) & 0x01010101u) * 255u;
+                            const uint32_t m1hi = (((bits1 >> 4) * 0x00204081u) & 0x01010101u) * 255u;
+#pragma unroll
+                            for (int d = 0; d < kWgDigits; ++d) {
+                                const uint4 gq = make_uint4(w[d][0] & m0lo, w[d][1] & m0hi, w[d][0] & m1lo, w[d][1] & m1hi);
+                                *reinterpret_cast<uint4*>(dq + (size_t)(d * npair + pr) * wg.region_q) = gq;
+                            }
 #pragma unroll
                             for (int c = 0; c < 8; ++c) {
-                                int q = __float2int_rn(dv[c] * qscale);
-#pragma unroll
-                                for (int d = 0; d < 3; ++d) {
-                                    const int dd = ((q + 128) & 255) - 128;
-                                    dg[d][c] = dd;
-                                    q = (q - dd) >> 8;
-                                }
-                                dg[3][c] = q;
-                            }
-#pragma unroll
-                            for (int d = 0; d < 4; ++d) { w[d][0] = pack4(&dg[d][0]); w[d][1] = pack4(&dg[d][4]); }
-#pragma unroll
-                            for (int sl = 0; sl < kPassSlots; ++sl) {
-                                if (sl >= nsl) break;
-                                const unsigned bits = (rb[u] >> (8 * sl)) & 255u;     // 0 for rows outside the output grid
-                                const uint32_t mlo = nib_to_bytemask(bits & 15u), mhi = nib_to_bytemask(bits >> 4);
-                                const uint4 g0 = make_uint4(w[0][0] & mlo, w[0][1] & mhi, w[1][0] & mlo, w[1][1] & mhi);
-                                const uint4 g1 = make_uint4(w[2][0] & mlo, w[2][1] & mhi, w[3][0] & mlo, w[3][1] & mhi);
-                                *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl) * region_q + m * 16) = g0;
-                                *reinterpret_cast<uint4*>(dq + (size_t)(2 * sl + 1) * region_q + m * 16) = g1;
-#pragma unroll
-                                for (int c = 0; c < 8; ++c)
-                                    if ((bits >> c) & 1u) bsum[sl][c] += dv[c];
+                                if ((bits0 >> c) & 1u) bsum[2 * pr][c] += dv[c];
+                                if ((bits1 >> c) & 1u) bsum[2 * pr + 1][c] += dv[c];
                             }
                         }
                     }
@@ -724,77 +794,36 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     mbar_arrive(&dq_full[stage]);
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
-                // ---- flush ----
-                const long long cf = dbg8 ? pinned_clock() : 0;
-                mbar_wait(acc_full, nflush & 1);
-                const long long cf1 = dbg8 ? pinned_clock() : 0;
-                if (dbg8) q_wfull += cf1 - cf;
-                tc_fence_after();
-                const bool rowvalid = lane < 16;
-                const int r = quad * 16 + lane;                   // accumulator row = (g, byte) of the tap
-                const int g = r >> 4, bb = r & 15;
-                for (int tap = 2 * fgroup; tap < 2 * fgroup + 2; ++tap) {
-                    const int kh = (tap >> 1) * gm.s + g, kw = (tap & 1) * gm.s + bb / gm.C, ci = bb % gm.C;
-                    const int kk = (kh * nd.k[0] + kw) * gm.C + ci;
-                    for (int sl = 0; sl < nsl; ++sl) {
-                        uint32_t d0[8], d1[8], d2[8], d3[8];
-                        const uint32_t ta = td + ((uint32_t)(quad * 32) << 16) + tap * kWgTapCols + sl * kWgSlotCols;
-                        tmem_ld8(ta, d0); tmem_ld8(ta + 8, d1); tmem_ld8(ta + 16, d2); tmem_ld8(ta + 24, d3);
-                        tmem_ld_wait();
-                        if (rowvalid) {
-                            float o[8];
-#pragma unroll
-                            for (int c = 0; c < 8; ++c) {
-                                // digits combined in 64-bit integers (|sum| < 2^48: exact, and the same value the four
-                                // int -> double conversions gave), then ONE conversion: conversions are the slow instructions here
-                                const long long v = (long long)(int)d0[c] + ((long long)(int)d1[c] << 8) + ((long long)(int)d2[c] << 16) +
-                                                    ((long long)(int)d3[c] << 24);
-                                o[c] = (float)((double)v * dscale);
-                            }
-                            float4* dst = reinterpret_cast<float4*>(
-                                part + ((size_t)(p * nch_alloc + ch) * nd.M + jl[sl]) * stride_part + (size_t)kk * PN_F);
-                            dst[0] = make_float4(o[0], o[1], o[2], o[3]);
-                            dst[1] = make_float4(o[4], o[5], o[6], o[7]);
-                        }
-                    }
-                }
-                // bias gradient: fixed-order sum of the 256 per-thread partials (the dq ring is free now)
-                float* bred = reinterpret_cast<float*>(dq_s);
+                // ---- bias gradient of this (item, pass): warp shuffle trees, then the warp sums in warp order ----
+                float mine = 0.f;                               // lane l ends up with the warp's sum of value l = (slot, channel)
 #pragma unroll
                 for (int sl = 0; sl < kPassSlots; ++sl)
 #pragma unroll
-                    for (int c = 0; c < 8; ++c) bred[tid * 32 + sl * 8 + c] = bsum[sl][c];
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                {   // two levels, both in a fixed order: 8 groups of 32 thread-partials, then the 8 group sums
-                    float* red2 = bred + 256 * 32;
-                    const int grp = tid >> 5, o = tid & 31;
-                    float s8 = 0.f;
-#pragma unroll 8
-                    for (int i = 0; i < 32; ++i) s8 += bred[(grp * 32 + i) * 32 + o];
-                    red2[grp * 32 + o] = s8;
-                }
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                if (tid < nsl * 8) {
+                    for (int c = 0; c < 8; ++c) {
+                        float v = bsum[sl][c];
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                        if (lane == sl * 8 + c) mine = v;
+                    }
+                asm volatile("bar.sync 1, %0;" ::"n"(kWgQuantWarps * 32) : "memory");   // the previous (item, pass) has been read out of bias_s
+                bias_s[warp * 32 + lane] = mine;
+                asm volatile("bar.sync 1, %0;" ::"n"(kWgQuantWarps * 32) : "memory");
+                if (threadIdx.x < nsl * 8) {
                     float sacc = 0.f;
 #pragma unroll
-                    for (int q = 0; q < 8; ++q) sacc += bred[256 * 32 + q * 32 + tid];
-                    part[((size_t)(p * nch_alloc + ch) * nd.M + jl[tid >> 3]) * stride_part + (size_t)nd.KK[0] * PN_F + (tid & 7)] = sacc;
+                    for (int q = 0; q < kWgQuantWarps; ++q) sacc += bias_s[q * 32 + threadIdx.x];
+                    part[((size_t)(p * nch_alloc + ch) * nd.M + jl[threadIdx.x >> 3]) * stride_part + (size_t)nd.KK[0] * PN_F + (threadIdx.x & 7)] = sacc;
                 }
-                asm volatile("bar.sync 1, 256;" ::: "memory");
-                tc_fence_before();
-                mbar_arrive(acc_empty);
-                if (dbg8) q_flush += pinned_clock() - cf1;
-                ++nflush;
             }
         }
-        if (dbg8 && tid == 0) {
-            dbg[blockIdx.x * 8 + 4] = q_wempty; dbg[blockIdx.x * 8 + 5] = q_wfull; dbg[blockIdx.x * 8 + 6] = q_flush;
+        if (dbg8 && threadIdx.x == 0) {
+            dbg[blockIdx.x * 8 + 4] = q_wempty;
             dbg[blockIdx.x * 8 + 7] = pinned_clock() - t_entry;
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) tmem_dealloc(td, 512);
+    if (warp == kWgQuantWarps + 5) tmem_dealloc(td, 512);
 }
 
 bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
@@ -835,7 +864,7 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_
                                     const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T, CUtensorMap* out) {
+int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T, CUtensorMap* out, int extra_rows = 0) {
     static PFN_encodeTiled encode = nullptr;
     if (!encode) {
         void* fn = nullptr;
@@ -848,7 +877,8 @@ int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T,
     if (reinterpret_cast<uintptr_t>(frames) & 15) return pn_fail(h, PN_ERR_INVALID, "frames must be 16-byte aligned");
     const cuuint64_t dims[4] = {(cuuint64_t)(g.row_bytes / 4), (cuuint64_t)g.Hs, (cuuint64_t)g.s, (cuuint64_t)T};
     const cuuint64_t strides[3] = {(cuuint64_t)g.row_bytes * g.s, (cuuint64_t)g.row_bytes, (cuuint64_t)g.frame_bytes};
-    const cuuint32_t box[4] = {(cuuint32_t)(g.row_bytes / 4), (cuuint32_t)g.Hs, (cuuint32_t)g.s, 1};
+    // extra_rows > 0: the box is taller than the tensor; the rows past the end are zero-filled in shared memory
+    const cuuint32_t box[4] = {(cuuint32_t)(g.row_bytes / 4), (cuuint32_t)(g.Hs + extra_rows), (cuuint32_t)g.s, 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 4, const_cast<uint8_t*>(frames), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -896,13 +926,13 @@ bool pn_conv0_tc_supported(const pn_handle* h) {
 }
 
 size_t pn_conv0_tc_scratch_bytes(const pn_handle* h) {
-    // int8 weight digits + fp32 scales per module, then 16 bytes for the batch max |dY| of layer 0
-    return (((size_t)h->nd.M * (kSlotBytes + 8 * sizeof(float)) + 15) & ~(size_t)15) + 16;
+    // int8 weight digits + fp32 scales per module, then one word per path: max |dY| of layer 0 over the path's batch
+    return (((size_t)h->nd.M * (kSlotBytes + 8 * sizeof(float)) + 15) & ~(size_t)15) + (((size_t)h->P * 4 + 15) & ~(size_t)15);
 }
 
-unsigned* pn_conv0_absmax_slot(const pn_handle* h) {
+unsigned* pn_conv0_absmax_slot(const pn_handle* h) {        // [P] words
     if (!h->tc_conv0 || !h->tc_w8) return nullptr;
-    return reinterpret_cast<unsigned*>(h->tc_w8 + pn_conv0_tc_scratch_bytes(h) - 16);
+    return reinterpret_cast<unsigned*>(h->tc_w8 + (((size_t)h->nd.M * (kSlotBytes + 8 * sizeof(float)) + 15) & ~(size_t)15));
 }
 
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st) {
@@ -933,18 +963,41 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     return PN_OK;
 }
 
+// geometry of the weight-gradient kernel's staging; false if the frame does not fit its scheme
+static bool make_wg_geom(const TcGeom& g, WgGeom& w, size_t& smem_bytes) {
+    w.region_bytes = (g.Hs + 1) * g.row_bytes;                       // one zero-filled block row appended per region
+    if (w.region_bytes % 32) return false;                           // four regions must be a multiple of 128 bytes
+    // shifted reads reach block mq - 1 + Ws + 1 of the last region of copy 1
+    const int over = std::max(0, (g.mq + g.Ws + 2) * 16 - w.region_bytes);
+    w.stage_bytes = (8 * w.region_bytes + over + 1023) & ~1023;
+    w.region_q = g.mq * 16;
+    if (g.mq > 512) return false;                                    // the quantiser covers 512 raster rows per round
+    smem_bytes = 2 * (size_t)w.stage_bytes + 2 * (size_t)(2 * kWgDigits * w.region_q) + kWgQuantWarps * 32 * sizeof(float) + 16 * sizeof(uint64_t);
+    return smem_bytes <= 227 * 1024;
+}
+
+bool pn_conv0_wgrad_tc_supported(const pn_handle* h) {
+    TcGeom g;
+    WgGeom w;
+    size_t sm = 0;
+    return make_geom(h, g, sm) && make_wg_geom(g, w, sm);
+}
+
 int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st) {
     TcGeom g;
-    size_t fwd_smem = 0;
-    if (!make_geom(h, g, fwd_smem)) return pn_fail(h, PN_ERR_STATE, "tensor-core conv0 not supported for this geometry");
+    WgGeom wg;
+    size_t fwd_smem = 0, smem_bytes = 0;
+    if (!make_geom(h, g, fwd_smem) || !make_wg_geom(g, wg, smem_bytes))
+        return pn_fail(h, PN_ERR_STATE, "tensor-core conv0 weight gradient not supported for this geometry");
     const PnNetDesc& nd = h->nd;
     const int P = h->P, T = P * B;
     const int npix = g.OH * g.OW;
     unsigned* absmax = pn_conv0_absmax_slot(h);
-    if (!h->absmax_fused) {          // the layer-1 data-gradient kernel normally leaves the abs-max behind
-        PN_CUDA(h, cudaMemsetAsync(absmax, 0, sizeof(unsigned), st));
+    if (!h->absmax_fused) {          // the layer-1 data-gradient kernel normally leaves the per-path abs-max behind
+        PN_CUDA(h, cudaMemsetAsync(absmax, 0, (size_t)P * sizeof(unsigned), st));
         PnProfScope prof(h, PN_PROF_CONV0_DQUANT, st);
-        absmax_kernel<<<2 * h->num_sms, 256, 0, st>>>(h->dact[0], (size_t)T * npix * PN_F / 4, absmax);
+        dim3 grid(std::max(1, 2 * h->num_sms / P), P);
+        absmax_kernel<<<grid, 256, 0, st>>>(h->dact[0], (size_t)B * npix * PN_F / 4, absmax);
         PN_LAUNCH_CHECK(h, "absmax_kernel");
     }
     h->absmax_fused = false;
@@ -955,24 +1008,22 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
         const int cs = (B + nch - 1) / nch;
         if (cs > 32 || (B + cs - 1) / cs != nch) continue;
         const long long items = (long long)P * nch, rounds = (items + h->num_sms - 1) / h->num_sms;
-        // cost of an item ~ cs transitions of MMAs + one accumulator flush; measured (PN_TC_DEBUG=8, 256 paths x 32):
-        // ~12.6 K cycles per flush against ~3.9 K per transition, i.e. a flush costs about 3.3 transitions
-        const double eff = (double)T / ((double)rounds * h->num_sms * (cs + 3.3));
+        // cost of an item ~ cs transitions of MMAs; its flush runs underneath the next item's MMAs, so only the
+        // pipeline fill (~half a transition) is charged per item
+        const double eff = (double)T / ((double)rounds * h->num_sms * (cs + 0.5));
         if (eff > best_eff) { best_eff = eff; best_nch = nch; }
     }
     if (best_eff < 0) return pn_fail(h, PN_ERR_STATE, "no valid chunking for the conv0 weight-gradient kernel");
     const int nch = best_nch, cs = (B + nch - 1) / nch;
-    const size_t dq_total = std::max<size_t>(2 * (size_t)(2 * kPassSlots * g.mq * 16), (256 + 8) * 32 * sizeof(float));
-    const size_t smem_bytes = 2 * (size_t)g.stage_bytes + dq_total + 16 * sizeof(uint64_t);
     PN_SET_SMEM(h, conv0_wgrad_tc_kernel, smem_bytes);
     const int items = P * nch;
     const int grid = std::min(std::min(items, h->num_sms), kMaxCtas);
     CUtensorMap tmap;
-    if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
+    if (int rc = make_frame_tmap(h, g, frames, T, &tmap, 1)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + 0, st);
-        conv0_wgrad_tc_kernel<<<grid, kTcThreads, smem_bytes, st>>>(tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
-                                                                   B, P, cs, nch, h->nch, g, h->wpart[0], h->tc_dbg);
+        conv0_wgrad_tc_kernel<<<grid, kWgThreads, smem_bytes, st>>>(tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
+                                                                   B, P, cs, nch, h->nch, g, wg, h->wpart[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_wgrad_tc_kernel");
     h->last_wgrad_nch = nch;

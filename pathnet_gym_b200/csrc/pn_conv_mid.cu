@@ -278,7 +278,7 @@ conv_mid_dgrad_kernel(const float* __restrict__ dY, const uint8_t* __restrict__ 
         for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
         if ((threadIdx.x & 31) == 0) atomicMax(&blk_amax, __float_as_uint(amax));
         __syncthreads();
-        if (threadIdx.x == 0 && blk_amax) atomicMax(absmax_out, blk_amax);
+        if (threadIdx.x == 0 && blk_amax) atomicMax(absmax_out + p, blk_amax);          // one scale per path
     }
 }
 
@@ -447,7 +447,7 @@ int pn_launch_conv_mid_bwd(pn_handle* h, int l, int B, cudaStream_t st, int* nch
         dim3 grid(P, (B + kG - 1) / kG);
         // layer 1 writes the first conv layer's output gradient: fold the abs-max its quantiser needs into this pass
         unsigned* amax = l == 1 ? pn_conv0_absmax_slot(h) : nullptr;
-        if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, sizeof(unsigned), st));
+        if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, (size_t)h->P * sizeof(unsigned), st));
         PnProfScope prof(h, PN_PROF_CONV_DGRAD + l, st);
         conv_mid_dgrad_kernel<<<grid, threads, smem, st>>>(h->dact[l], h->rmask[l], h->params, nd, l, g, h->d_masks, B,
                                                           h->dact[l - 1], amax);

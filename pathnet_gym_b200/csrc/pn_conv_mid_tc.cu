@@ -435,7 +435,6 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
     const int d_hl = w_slots * g.chunk_bytes;                  // bytes of the hi (or lo) chunks of one stage
     uint8_t* d_s = w_s + (size_t)2 * w_slots * kModBytes;      // [kXStages][hl][w_slots][xrows] 16-byte rows
     __shared__ uint32_t tmem_base_s;
-    __shared__ unsigned blk_amax;
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const long long NT = (long long)P * ntile;
     const int g0 = (int)(NT * blockIdx.x / gridDim.x), g1 = (int)(NT * (blockIdx.x + 1) / gridDim.x);
@@ -447,7 +446,6 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
         for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
         mbar_init(w_full, 1); mbar_init(w_free, 1);
         fence_mbar_init();
-        blk_amax = 0u;
     }
     if (warp == 9) tmem_alloc(&tmem_base_s, 64);
     tc_fence_before();
@@ -590,11 +588,11 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
     } else if (warp < 4) {
         // ================= epilogue: thread = input raster row; 32 columns = (py, px, ci) =================
         int it = 0;
-        float amax = 0.f;
         for (int gt = g0; gt < g1; ++gt, ++it) {
             const int p = gt / ntile, tile = gt - p * ntile;
             const int ns = __popc(masks[p * nd.L + l]);
             const int Rr = tile * kTileM + warp * 32 + lane;
+            float amax = 0.f;                                 // max |dX| of this tile: the first conv layer's quantiser scale is per path
             int b, Yb, Xb;
             raster_split(Rr, g, b, Yb, Xb);
             const bool valid = Rr < NR;
@@ -637,17 +635,17 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
                     }
                 }
             }
-        }
-        if (absmax_out) {
+            if (absmax_out) {                                 // (a tile never straddles two paths)
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-            if (lane == 0) atomicMax(&blk_amax, __float_as_uint(amax));   // non-negative floats order like uints
+                for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                if (lane == 0 && amax > 0.f) atomicMax(absmax_out + p, __float_as_uint(amax));   // non-negative floats order like uints
+            }
         }
+
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 9) tmem_dealloc(td, 64);
-    if (threadIdx.x == 0 && absmax_out && blk_amax) atomicMax(absmax_out, blk_amax);
 }
 
 // =====================================================================================================
@@ -980,7 +978,7 @@ int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     const int grid = (int)std::min<long long>(NT, 3ll * h->num_sms);
     // layer 1 writes the first conv layer's output gradient: fold the abs-max its quantiser needs into this pass
     unsigned* amax = l == 1 ? pn_conv0_absmax_slot(h) : nullptr;
-    if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, sizeof(unsigned), st));
+    if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, (size_t)h->P * sizeof(unsigned), st));
     {
         PnProfScope prof(h, PN_PROF_CONV_DGRAD + l, st);
         conv_mid_dgrad_tc_kernel<<<grid, kFwdThreads, smem, st>>>(h->dact[l], h->rmask[l], wd, nd, l, g, h->d_masks, h->P, B,

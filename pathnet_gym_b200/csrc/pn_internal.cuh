@@ -186,6 +186,7 @@ bool pn_conv0_tc_supported(const pn_handle* h);
 size_t pn_conv0_tc_scratch_bytes(const pn_handle* h);
 unsigned* pn_conv0_absmax_slot(const pn_handle* h);   // nullptr when the tensor-core conv0 path is off
 int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
+bool pn_conv0_wgrad_tc_supported(const pn_handle* h);
 int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStream_t st);
 // pn_conv_mid_tc.cu
 bool pn_conv_mid_tc_supported(const pn_handle* h, int l);

@@ -870,7 +870,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
             add_job(l, nch_used);
             continue;
         }
-        if (l == 0 && is_u8 && h->tc_conv0) {
+        if (l == 0 && is_u8 && h->tc_conv0 && pn_conv0_wgrad_tc_supported(h)) {
             if (int rc = pn_launch_conv0_wgrad_tc(h, (const uint8_t*)frames, B, st)) return rc;
             add_job(l, h->last_wgrad_nch);
             continue;

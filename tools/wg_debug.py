@@ -16,6 +16,6 @@ torch.cuda.synchronize()
 buf = (C.c_longlong * (148 * 8))()
 n = pop.lib.pn_debug_read(pop._h, buf, 148 * 8)
 a = np.array(buf[:n]).reshape(-1, 8)
-names = ["mma: wait frame", "mma: wait dq", "mma: wait acc_empty", "mma: total", "quant: wait dq_empty", "quant: wait acc_full", "quant: flush", "quant: total"]
+names = ["mma: wait frame", "mma: wait dq", "mma: wait acc_empty", "mma: total", "quant: wait dq_empty", "flush: wait acc_full", "flush: work", "quant: total"]
 for i, nm in enumerate(names): print("%-24s mean %9.0f  max %9.0f" % (nm, a[:, i].mean(), a[:, i].max()))
 pop.close()
