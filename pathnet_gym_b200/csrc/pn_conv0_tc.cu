@@ -141,6 +141,11 @@ __device__ __forceinline__ long long pinned_clock() {
     return t;
 }
 
+// kFast: a frame is exactly one 128-row tile per accumulator stage and a tap is two K steps (84x84x4 frames, 8x8 / 4 filters);
+// the generic variant handles every other supported geometry.  Two instantiations instead of one kernel with both code
+// paths: the issuing warp keeps its descriptors in uniform registers, and with all variants in one body some of them
+// spilled to vector registers (an R2UR chain in front of every tile's MMAs: +8 % kernel time).
+template <bool kFast>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __restrict__ w8,
                     const float* __restrict__ wscale, const float* __restrict__ params, PnNetDesc nd,
@@ -173,6 +178,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < gm.nst; ++i) { mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1); }
+        // (one arrival per thread: electing one lane per warp after a __syncwarp measured 7 % SLOWER here)
         for (int i = 0; i < kAccStages; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
         mbar_init(path_ready, 1);
         mbar_init(drain, 1);
@@ -274,32 +280,57 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             const uint32_t ahi = desc_hi(128), bhi = desc_hi(2048);
             const int nmma = 4 * gm.ksteps;
             if (dbg_detail) w_desc += clock64() - cd0;
-            if (npass == 1 && gm.tiles == kAccStages && nmma == 8) {
-                // Common case (84x84x4 frames, at most 4 active modules): a frame is exactly one tile per
-                // accumulator stage.  This warp's scalar instruction stream is the critical path of the whole
-                // kernel (one warp, dependent uniform-datapath ops at ~7 cycles each: 120 instructions per tile were
-                // measured at ~870 cycles against 424 cycles of tensor time), so everything is hoisted: the 16
-                // descriptors are built once per frame as 64-bit values and a tile costs one add per MMA.
-                const int N = (24 * ns + 15) & ~15;
-                const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
+            if constexpr (kFast) {
+                // Common geometry (84x84x4 frames): a frame is exactly one tile per accumulator stage.  This warp's scalar
+                // instruction stream is the critical path of the whole kernel (one warp, dependent uniform-datapath ops at
+                // ~7 cycles each: 120 instructions per tile were measured at ~870 cycles against 424 cycles of tensor time),
+                // so everything is hoisted: the 16 descriptors are built once per frame as 64-bit values and a tile costs one
+                // add per MMA.  Paths with more than four active modules (mutation adds modules, task 2 ORs the frozen
+                // path in) take further passes over the same frame, pass-major: by the time stage t is filled again its
+                // epilogue group has drained the previous pass.
                 uint64_t a64[8], b64[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) { a64[i] = desc_join(alo[i], ahi); b64[i] = desc_join(blo[i], bhi); }
+                if (npass == 1) {
+                    // (kept apart from the multi-pass loop below: with the pass loop around it this code measured 6-10 %
+                    // slower for the common case -- the single issuing warp's instruction stream is that critical)
+                    const int N = (24 * ns + 15) & ~15;
+                    const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
 #pragma unroll
-                for (int tile = 0; tile < kAccStages; ++tile) {
-                    mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
-                    tc_fence_after();
-                    const uint32_t dcol = td + tile * kAccCols;
-                    if (!dbg_nomma && elect_one()) {
+                    for (int tile = 0; tile < kAccStages; ++tile) {
+                        mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
+                        tc_fence_after();
+                        const uint32_t dcol = td + tile * kAccCols;
+                        if (!dbg_nomma && elect_one()) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) umma_i8(dcol, a64[i] + (uint64_t)(tile * 128), b64[i], idesc, i ? 1u : 0u);
-                        umma_commit(&acc_full[tile]);
-                    } else if (dbg_nomma && elect_one()) {
-                        umma_commit(&acc_full[tile]);
+                            for (int i = 0; i < 8; ++i) umma_i8(dcol, a64[i] + (uint64_t)(tile * 128), b64[i], idesc, i ? 1u : 0u);
+                            umma_commit(&acc_full[tile]);
+                        } else if (dbg_nomma && elect_one()) {
+                            umma_commit(&acc_full[tile]);
+                        }
+                        __syncwarp();
                     }
-                    __syncwarp();
+                    fill_par ^= (1u << kAccStages) - 1u;
+                } else
+                for (int pass = 0; pass < npass; ++pass) {
+                    const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                    const int N = (24 * nsl + 15) & ~15;
+                    const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
+                    const uint64_t b_adv = (uint64_t)((pass * kPassSlots * kSlotBytes) >> 4);
+#pragma unroll
+                    for (int tile = 0; tile < kAccStages; ++tile) {
+                        mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
+                        tc_fence_after();
+                        const uint32_t dcol = td + tile * kAccCols;
+                        if (elect_one()) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) umma_i8(dcol, a64[i] + (uint64_t)(tile * 128), b64[i] + b_adv, idesc, i ? 1u : 0u);
+                            umma_commit(&acc_full[tile]);
+                        }
+                        __syncwarp();
+                    }
+                    fill_par ^= (1u << kAccStages) - 1u;
                 }
-                fill_par ^= (1u << kAccStages) - 1u;
                 tilec += kAccStages;
             } else
             for (int tile = 0; tile < gm.tiles && npass > 0; ++tile, ++tilec) {
@@ -551,8 +582,9 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2; ++i) {
             mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1);
-            mbar_init(&dq_full[i], kWgQuantWarps * 32); mbar_init(&dq_empty[i], 1);
-            mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128);
+            // one arrival per WARP (after __syncwarp): 512 threads arriving on one barrier serialise on its shared-memory word
+            mbar_init(&dq_full[i], kWgQuantWarps); mbar_init(&dq_empty[i], 1);
+            mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4);
         }
         fence_mbar_init();
     }
@@ -696,7 +728,8 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     }
                 }
                 tc_fence_before();
-                mbar_arrive(&acc_empty[set]);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[set]);
                 if (dbg8) { f_wait += cf1 - cf; f_work += pinned_clock() - cf1; }
                 ++nacc;
             }
@@ -733,18 +766,28 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 for (int sl = 0; sl < kPassSlots; ++sl)
 #pragma unroll
                     for (int c = 0; c < 8; ++c) bsum[sl][c] = 0.f;
-                for (int b = b_lo; b < b_hi; ++b) {
-                    const size_t t = (size_t)p * B + b;
-                    // loads first (they do not depend on the ring), then wait for the stage
-                    float4 ga = make_float4(0.f, 0.f, 0.f, 0.f), gb = ga;
-                    uint32_t rb = 0;
+                // Software pipeline over the transitions: the loads of transition b + 1 are issued before transition b is
+                // processed.  All quantiser warps run in lock step (they meet at the ring's barriers), so without this
+                // every warp sat out the same L2 round trip once per transition.
+                float4 ga_n = make_float4(0.f, 0.f, 0.f, 0.f), gb_n = ga_n;
+                uint32_t rb_n = 0;
+                auto fetch = [&](int b) {
+                    ga_n = gb_n = make_float4(0.f, 0.f, 0.f, 0.f);
+                    rb_n = 0;
                     if (valid) {
+                        const size_t t = (size_t)p * B + b;
                         const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pix) * PN_F);
-                        ga = __ldg(g4); gb = __ldg(g4 + 1);
+                        ga_n = __ldg(g4); gb_n = __ldg(g4 + 1);
 #pragma unroll
                         for (int sl = 0; sl < kPassSlots; ++sl)
-                            if (sl < nsl) rb |= (uint32_t)__ldg(R + (t * nd.M + jl[sl]) * npix + pix) << (8 * sl);
+                            if (sl < nsl) rb_n |= (uint32_t)__ldg(R + (t * nd.M + jl[sl]) * npix + pix) << (8 * sl);
                     }
+                };
+                fetch(b_lo);
+                for (int b = b_lo; b < b_hi; ++b) {
+                    const float4 ga = ga_n, gb = gb_n;
+                    const uint32_t rb = rb_n;
+                    if (b + 1 < b_hi) fetch(b + 1);
                     const long long cq = dbg8 ? pinned_clock() : 0;
                     mbar_wait(&dq_empty[stage], phase ^ 1);
                     if (dbg8) q_wempty += pinned_clock() - cq;
@@ -791,7 +834,8 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                         }
                     }
                     fence_proxy_async();
-                    mbar_arrive(&dq_full[stage]);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&dq_full[stage]);
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
                 // ---- bias gradient of this (item, pass): warp shuffle trees, then the warp sums in warp order ----
@@ -948,7 +992,9 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
         conv0_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, g.s, w8, wscale);
     }
     PN_LAUNCH_CHECK(h, "conv0_wprep_kernel");
-    PN_SET_SMEM(h, conv0_fwd_tc_kernel, smem_bytes);
+    const bool fast = g.tiles == kAccStages && 4 * g.ksteps == 8;
+    if (fast) PN_SET_SMEM(h, conv0_fwd_tc_kernel<true>, smem_bytes);
+    else PN_SET_SMEM(h, conv0_fwd_tc_kernel<false>, smem_bytes);
     const int grid = std::min(std::min(T, h->num_sms), kMaxCtas);
     TcBounds bounds;
     balance_units(h, kFwdCost, B, grid, bounds);
@@ -956,8 +1002,12 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + 0, st);
-        conv0_fwd_tc_kernel<<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g, bounds,
-                                                                 h->act[0], h->rmask[0], h->tc_dbg);
+        if (fast)
+            conv0_fwd_tc_kernel<true><<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g, bounds,
+                                                                           h->act[0], h->rmask[0], h->tc_dbg);
+        else
+            conv0_fwd_tc_kernel<false><<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g, bounds,
+                                                                            h->act[0], h->rmask[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_fwd_tc_kernel");
     return PN_OK;
