@@ -40,7 +40,7 @@ namespace {
 
 constexpr int kTcThreads = 320;          // weight-gradient kernel: 8 quantise/flush warps, producer, MMA
 constexpr int kEpiGroups = 4;            // forward kernel: 4 groups of 4 epilogue warps, then producer and MMA warps
-constexpr int kFwdThreads = (4 * kEpiGroups + 2) * 32;
+constexpr int kFwdThreads = (4 * kEpiGroups + 3) * 32;    // epilogue groups, producer, MMA warp A, MMA warp B
 // One TMEM accumulator stage per epilogue group: tile c -> group c%4 -> stage c%4.  (A stage must not be shared
 // between groups: mbarrier parity waits only distinguish the current from the preceding phase, so a group that
 // ran ahead would take another group's older phase for its own.)
@@ -177,7 +177,8 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
     const long long t_entry = dbg ? clock64() : 0;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < gm.nst; ++i) { mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1); }
+        // kFast: two warps issue MMAs (tiles 0, 2 and tiles 1, 3 of every frame), so a frame stage is free after two commits
+        for (int i = 0; i < gm.nst; ++i) { mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], kFast ? 2 : 1); }
         // (one arrival per thread: electing one lane per warp after a __syncwarp measured 7 % SLOWER here)
         for (int i = 0; i < kAccStages; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
         mbar_init(path_ready, 1);
@@ -297,7 +298,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     const int N = (24 * ns + 15) & ~15;
                     const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
 #pragma unroll
-                    for (int tile = 0; tile < kAccStages; ++tile) {
+                    for (int tile = 0; tile < kAccStages; tile += 2) {       // (tiles 1 and 3: warp B)
                         mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
                         tc_fence_after();
                         const uint32_t dcol = td + tile * kAccCols;
@@ -318,7 +319,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
                     const uint64_t b_adv = (uint64_t)((pass * kPassSlots * kSlotBytes) >> 4);
 #pragma unroll
-                    for (int tile = 0; tile < kAccStages; ++tile) {
+                    for (int tile = 0; tile < kAccStages; tile += 2) {       // (tiles 1 and 3: warp B)
                         mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
                         tc_fence_after();
                         const uint32_t dcol = td + tile * kAccCols;
@@ -380,6 +381,81 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
             dbg[blockIdx.x * 8 + 2] = w_desc; dbg[blockIdx.x * 8 + 3] = w_fend; dbg[blockIdx.x * 8 + 5] = clock64() - t_begin;
             dbg[blockIdx.x * 8 + 4] = w_path; dbg[blockIdx.x * 8 + 0] = dbg_detail ? w_issue : t_begin - t_entry;
             dbg[blockIdx.x * 8 + 1] = w_fence; dbg[blockIdx.x * 8 + 6] = dbg_detail ? w_commit : clock64();
+        }
+    } else if (warp == 4 * kEpiGroups + 2) {
+        // ================= second MMA-issue warp (kFast only): tiles 1 and 3 of every frame =================
+        // One issuing warp could not keep the tensor pipe fed: between two tiles it waits for the accumulator stage, fences,
+        // elects and commits, ~400 cycles during which the pipe drains (the kernel ran at 3300 cycles per frame with one
+        // module active against 1664 cycles of MMA time).  With two warps one warp's gap is covered by the other's MMAs.
+        // Warp A still owns the B operand: this warp learns about a new path from path_ready, like the epilogue warps.
+        if constexpr (kFast) {
+            int stage = 0, cur_path = -1, ns = 0;
+            uint32_t fphase = 0, path_phase = 0, fill_par = 0;
+            for (int t = t_lo; t < t_hi; ++t) {
+                const int p = t / B;
+                if (p != cur_path) {
+                    mbar_wait(path_ready, path_phase);
+                    path_phase ^= 1;
+                    cur_path = p;
+                    ns = __popc(__reduce_or_sync(0xffffffffu, masks[p * nd.L]));
+                }
+                mbar_wait(&frame_full[stage], fphase);
+                tc_fence_after();
+                const int npass = (ns + kPassSlots - 1) / kPassSlots;
+                const uint32_t fbase = smem_u32(frame_s + (size_t)stage * gm.stage_bytes);
+                const uint32_t bsm = smem_u32(Bs);
+                const uint32_t ahi = desc_hi(128), bhi = desc_hi(2048);
+                uint64_t a64[8], b64[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int tap = i >> 1, ks = i & 1;
+                    a64[i] = desc_join(desc_lo(fbase + (uint32_t)(2 * ks * gm.region_bytes + ((tap >> 1) * gm.Ws + (tap & 1)) * 16),
+                                               (uint32_t)gm.region_bytes), ahi);
+                    b64[i] = desc_join(desc_lo(bsm + (uint32_t)((tap * gm.s + 2 * ks) * 128), 128), bhi);
+                }
+                if (npass == 1) {
+                    const int N = (24 * ns + 15) & ~15;
+                    const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
+#pragma unroll
+                    for (int tile = 1; tile < kAccStages; tile += 2) {
+                        mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
+                        tc_fence_after();
+                        const uint32_t dcol = td + tile * kAccCols;
+                        if (elect_one()) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) umma_i8(dcol, a64[i] + (uint64_t)(tile * 128), b64[i], idesc, i ? 1u : 0u);
+                            umma_commit(&acc_full[tile]);
+                        }
+                        __syncwarp();
+                    }
+                    fill_par ^= (1u << kAccStages) - 1u;
+                } else
+                for (int pass = 0; pass < npass; ++pass) {
+                    const int nsl = min(kPassSlots, ns - pass * kPassSlots);
+                    const int N = (24 * nsl + 15) & ~15;
+                    const uint32_t idesc = make_idesc_i8(128, N, 0, 1, 0, 0);
+                    const uint64_t b_adv = (uint64_t)((pass * kPassSlots * kSlotBytes) >> 4);
+#pragma unroll
+                    for (int tile = 1; tile < kAccStages; tile += 2) {
+                        mbar_wait(&acc_empty[tile], ((fill_par >> tile) & 1u) ^ 1u);
+                        tc_fence_after();
+                        const uint32_t dcol = td + tile * kAccCols;
+                        if (elect_one()) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) umma_i8(dcol, a64[i] + (uint64_t)(tile * 128), b64[i] + b_adv, idesc, i ? 1u : 0u);
+                            umma_commit(&acc_full[tile]);
+                        }
+                        __syncwarp();
+                    }
+                    fill_par ^= (1u << kAccStages) - 1u;
+                }
+                if (elect_one()) {
+                    if (npass > 0) umma_commit(&frame_empty[stage]);
+                    else mbar_arrive(&frame_empty[stage]);
+                }
+                __syncwarp();
+                if (++stage == gm.nst) { stage = 0; fphase ^= 1; }
+            }
         }
     } else {
         // ================= epilogue: thread = TMEM lane = output pixel of the tile =================
@@ -932,7 +1008,7 @@ int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T,
 }
 
 // relative cost of one transition by the number of active layer-0 modules of its path (us per 8192 transitions, B200)
-const float kFwdCost[11] = {70.f, 96.f, 107.f, 123.f, 142.f, 338.f, 348.f, 364.f, 381.f, 520.f, 540.f};
+const float kFwdCost[11] = {66.f, 84.f, 101.f, 120.f, 140.f, 182.f, 194.f, 212.f, 230.f, 280.f, 300.f};
 
 // cut `units` work units (unit u belongs to path u / per_path) into `ctas` contiguous ranges of equal cumulative cost
 void balance_units(const pn_handle* h, const float* table, int per_path, int ctas, TcBounds& out) {
