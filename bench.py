@@ -291,6 +291,10 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_cpus = None
+    if world > 1:                                           # one process per GPU: keep its pinned buffers next to its GPU
+        from pathnet_gym_b200.parallel import bind_to_gpu_numa_node
+        numa_cpus = bind_to_gpu_numa_node(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -492,6 +496,7 @@ def run_b200(args):
                 "e2e": {"value": round(units * K / (e2e_ms * 1e-3), 1), "unit": UNIT,
                         "h2d_bytes_per_step": plane_bytes + 3 * P * B * 4, "d2h_bytes_per_step": P * 4,
                         "ms_per_step": round(e2e_ms / K, 4),
+                        "host_cpus_bound_to_gpu_numa_node": None if numa_cpus is None else len(numa_cpus),
                         "api": "PipelinedHostTrainer: pn_stage_rollout_host (pinned host buffers holding the B+C-1 distinct "
                                "planes of each path's rollout, copy stream, stacks rebuilt on the device) + "
                                "pn_train_step_staged + pn_rmsprop_apply; losses copied back every step",
@@ -518,41 +523,67 @@ def run_b200(args):
 
 
 def measure_rmsprop(pop, torch):
-    """pn_rmsprop_apply over the whole slab as ONE launch, timed alone with CUDA events: (a) back to back, slabs
-    L2-resident; (b) after evicting L2 (a 512 MB buffer is rewritten before every launch, outside the event pair)."""
+    """pn_rmsprop_apply over the whole slab, timed alone with CUDA events: (a) back to back, slabs L2-resident; (b) with the
+    slabs evicted from L2 before every launch.  The launches are queued behind a device-side sleep so that the events
+    bracket GPU time only (from Python a launch pair costs more host time than the kernels take)."""
     try:
         byts = rms_bytes(pop, 0, 0, True)
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         g = pop.grads
-        g.normal_(generator=None)
+        g.normal_()
         out = []
         for _ in range(5):
             pop.apply_gradients(1e-6)
         torch.cuda.synchronize()
         n = 20
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        torch.cuda._sleep(4_000_000)                       # ~2 ms: the queue fills while the GPU waits
         ev[0].record()
         for _ in range(n):
             pop.apply_gradients(1e-6)
         ev[1].record()
         torch.cuda.synchronize()
         t = ev[0].elapsed_time(ev[1]) / n * 1e-3
-        out.append({"kernel": "pn_rmsprop_apply (whole slab, one launch)", "regime": "slabs L2-resident (back to back)",
+        out.append({"kernel": "pn_rmsprop_apply (whole slab: rms_sumsq + rms_update, programmatic dependent launch)",
+                    "regime": "slabs L2-resident (back to back)",
                     "bound": "hbm", "bytes_per_launch": byts, "avg_launch_ms": round(t * 1e3, 5),
                     "achieved": round(byts / t / 1e9, 1), "unit": "GB/s"})
-        flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=pop.device)
-        tot = 0.0
-        for _ in range(n):
-            flush.fill_(1)
-            ev[0].record()
+        flush = torch.empty(384 * 1024 * 1024, dtype=torch.uint8, device=pop.device)
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        torch.cuda._sleep(4_000_000)
+        for a, b in evs:
+            flush.fill_(1)                                  # evicts params / rms / grads from the 126 MB L2
+            a.record()
             pop.apply_gradients(1e-6)
-            ev[1].record()
-            torch.cuda.synchronize()
-            tot += ev[0].elapsed_time(ev[1])
-        t = tot / n * 1e-3
-        out.append({"kernel": "pn_rmsprop_apply (whole slab, one launch)", "regime": "slabs evicted from L2 before every launch",
+            b.record()
+        torch.cuda.synchronize()
+        t = sum(a.elapsed_time(b) for a, b in evs) / n * 1e-3
+        out.append({"kernel": "pn_rmsprop_apply (whole slab: rms_sumsq + rms_update, programmatic dependent launch)",
+                    "regime": "slabs evicted from L2 before every launch",
                     "bound": "hbm", "bytes_per_launch": byts, "avg_launch_ms": round(t * 1e3, 5),
                     "achieved": round(byts / t / 1e9, 1), "unit": "GB/s"})
         del flush
+        # the same two kernels where HBM, not launch latency, is the bound: a 33.5 M-parameter synthetic slab (the largest
+        # input of the handle-free entry point: 128 tensors x 128 chunks; 402 MB of slabs, far beyond L2)
+        from pathnet_gym_b200.population import rmsprop_apply_noalloc
+        n_t, per = 128, 128 * 2048
+        nn = n_t * per
+        p_, s_, g_ = (torch.randn(nn, device=pop.device), torch.ones(nn, device=pop.device), torch.randn(nn, device=pop.device))
+        tensors = [dict(offset=i * per, length=per) for i in range(n_t)]
+        for _ in range(3):
+            rmsprop_apply_noalloc(p_, s_, g_, tensors, 1e-6)
+        torch.cuda.synchronize()
+        torch.cuda._sleep(2_000_000)
+        ev[0].record()
+        for _ in range(10):
+            rmsprop_apply_noalloc(p_, s_, g_, tensors, 1e-6)
+        ev[1].record()
+        torch.cuda.synchronize()
+        t = ev[0].elapsed_time(ev[1]) / 10 * 1e-3
+        out.append({"kernel": "rms_sumsq + rms_update through pn_rmsprop_apply_noalloc (same kernel bodies)",
+                    "regime": "33.5 M-parameter synthetic slab (402 MB of slabs, far beyond L2): HBM is the bound here, launch latency above",
+                    "bound": "hbm", "bytes_per_launch": 20.0 * nn, "avg_launch_ms": round(t * 1e3, 5),
+                    "achieved": round(20.0 * nn / t / 1e9, 1), "unit": "GB/s"})
+        del p_, s_, g_
         return out
     except Exception as e:  # noqa: BLE001
         return [{"error": repr(e)}]

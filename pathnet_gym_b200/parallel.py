@@ -38,3 +38,30 @@ def allgather_concat(t: torch.Tensor, sizes):
     out = [torch.empty_like(pad) for _ in range(ws)]
     dist.all_gather(out, pad)
     return torch.cat([o[:s] for o, s in zip(out, sizes)], dim=0)
+
+
+def bind_to_gpu_numa_node(device_index):
+    """Pin this process (and therefore the pinned host buffers it allocates afterwards) to the CPUs NVML reports as
+    local to the GPU.  With one process per GPU on a multi-socket host this keeps every rank's staging buffers on the
+    memory controller next to its PCIe root; without it the ranks' host-to-device copies share whichever node the
+    processes happened to start on.  Returns the CPU list, or None if NVML or the affinity call is unavailable."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = device_index
+        if vis:
+            parts = vis.split(",")
+            if device_index < len(parts) and parts[device_index].isdigit():
+                idx = int(parts[device_index])
+        h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [i for i in range(ncpu) if (int(words[i // 64]) >> (i % 64)) & 1]
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:  # noqa: BLE001  (no NVML, restricted container, ...)
+        return None
