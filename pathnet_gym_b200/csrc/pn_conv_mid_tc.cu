@@ -34,6 +34,7 @@ namespace {
 
 constexpr int kTileM = 128;
 constexpr int kXStages = 3;
+constexpr int kFwdStages = 4;          // forward kernel: two CTAs per SM, four operand stages each
 constexpr int kFwdThreads = 320;      // warps 0-3 epilogue, 4-8 operand converters, 9 MMA issue + weight loads
 constexpr int kConvWarps = 5;
 constexpr int kConvThreads = kConvWarps * 32;
@@ -193,19 +194,19 @@ conv_mid_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int l, int
 // =====================================================================================================
 // forward.  Work list = (path, tile of 128 raster rows), path-major; CTA c owns a contiguous range.
 // =====================================================================================================
-__global__ void __launch_bounds__(kFwdThreads, 3)
+__global__ void __launch_bounds__(kFwdThreads, 2)
 conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ wf, const float* __restrict__ params,
                        PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int P, int B, int ntile,
                        int w_slots, uint32_t tmem_cols, float* __restrict__ Y, uint8_t* __restrict__ R) {
     extern __shared__ __align__(128) uint8_t smem[];
-    uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kXStages]
-    uint64_t* x_empty = x_full + kXStages;                     // [kXStages]
-    uint64_t* acc_full = x_empty + kXStages;                   // [2]
+    uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kFwdStages]
+    uint64_t* x_empty = x_full + kFwdStages;                     // [kFwdStages]
+    uint64_t* acc_full = x_empty + kFwdStages;                   // [2]
     uint64_t* acc_empty = acc_full + 2;                        // [2]
     uint64_t* w_full = acc_empty + 2;
     uint64_t* w_free = w_full + 1;
     uint8_t* w_s = smem + 128;                                 // [hl][w_slots][kModBytes]
-    uint8_t* x_s = w_s + (size_t)2 * w_slots * kModBytes;      // [kXStages][stage_bytes]
+    uint8_t* x_s = w_s + (size_t)2 * w_slots * kModBytes;      // [kFwdStages][stage_bytes]
     __shared__ uint32_t tmem_base_s;
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const long long NT = (long long)P * ntile;
@@ -214,7 +215,7 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
     const uint32_t acc_stride = 8u * (uint32_t)w_slots;        // TMEM columns per accumulator stage
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kXStages; ++i) { mbar_init(&x_full[i], kConvWarps); mbar_init(&x_empty[i], 1); }
+        for (int i = 0; i < kFwdStages; ++i) { mbar_init(&x_full[i], kConvWarps); mbar_init(&x_empty[i], 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
         mbar_init(w_full, 1); mbar_init(w_free, 1);
         fence_mbar_init();
@@ -226,24 +227,27 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
     const uint32_t td = tmem_base_s;
 
     if (warp >= 4 && warp < 4 + kConvWarps) {
-        // ================= operand converters: global fp32 NHWC -> bf16 hi/lo chunks =================
+        // ================= operand converters: global fp32 NHWC -> fp16 hi/lo chunks =================
         const int cidx = threadIdx.x - 128;
-        int it = 0;
-        for (int gt = g0; gt < g1; ++gt, ++it) {
-            const int p = gt / ntile, tile = gt - p * ntile;
-            if (g.s1) {
-                // stride 1: one raster row = one pixel = one chunk, and the raster IS the NHWC tensor of the path
-                float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+        if (g.s1) {
+            // stride 1: one raster row = one pixel = one chunk, and the raster IS the NHWC tensor of the path.
+            // Software-pipelined like the stride-2 case below: tile i + 1 is being loaded while tile i is converted.
+            float4 a[2], c[2];
+            auto fetch = [&](int gt, int set) {
+                const int p = gt / ntile, tile = gt - p * ntile;
+                a[set] = c[set] = make_float4(0.f, 0.f, 0.f, 0.f);
                 const int Rr = tile * kTileM + cidx;
                 if (cidx < g.xrows && Rr < NR) {
                     const float4* src = reinterpret_cast<const float4*>(X + ((size_t)p * NR + Rr) * 8);
-                    a = __ldg(src); c = __ldg(src + 1);
+                    a[set] = __ldg(src); c[set] = __ldg(src + 1);
                 }
-                const int stage = it % kXStages;
-                mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
+            };
+            auto convert = [&](int set, int it) {
+                const int stage = it % kFwdStages;
+                mbar_wait(&x_empty[stage], ((it / kFwdStages) & 1) ^ 1);
                 if (cidx < g.xrows) {
                     uint4 hi, lo;
-                    split8_f16(a, c, kActScale, hi, lo);
+                    split8_f16(a[set], c[set], kActScale, hi, lo);
                     uint8_t* dst = x_s + (size_t)stage * g.stage_bytes + cidx * 16;
                     *reinterpret_cast<uint4*>(dst) = hi;
                     *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
@@ -251,48 +255,77 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&x_full[stage]);
-                continue;
-            }
-            float4 v[2][4];
-            int rr[2], pyy[2];
-#pragma unroll
-            for (int u = 0; u < 2; ++u) {
-                const int item = cidx + u * kConvThreads;
-                const int py = item >= g.xrows ? 1 : 0, r = item - py * g.xrows;
-                rr[u] = item < 2 * g.xrows ? r : -1;
-                pyy[u] = py;
-                const int Rr = tile * kTileM + r;
-                if (rr[u] >= 0 && Rr < NR) {
-                    int b, Yb, Xb;
-                    raster_split(Rr, g, b, Yb, Xb);
-                    const float4* src = reinterpret_cast<const float4*>(
-                        X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) v[u][q] = __ldg(src + q);
-                } else {
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) v[u][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+            };
+            if (g0 < g1) fetch(g0, 0);
+            int it2 = 0;
+            for (int gt = g0; gt < g1; gt += 2, it2 += 2) {
+                if (gt + 1 < g1) fetch(gt + 1, 1);
+                convert(0, it2);
+                if (gt + 1 < g1) {
+                    if (gt + 2 < g1) fetch(gt + 2, 0);
+                    convert(1, it2 + 1);
                 }
             }
-            const int stage = it % kXStages;
-            mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
-            uint8_t* xs = x_s + (size_t)stage * g.stage_bytes;
+        }
+        if (!g.s1) {
+            // stride 2, software-pipelined: the loads of tile i + 1 are in flight while tile i is converted.  One tile at a
+            // time left every converter thread waiting out a full memory round trip per tile (long-scoreboard stalls were
+            // half of this kernel's samples); two register sets cost the third resident CTA, which was worth less.
+            float4 v[2][2][4];
+            int rr[2][2], pyy[2][2];
+            auto fetch = [&](int gt, int set) {
+                const int p = gt / ntile, tile = gt - p * ntile;
 #pragma unroll
-            for (int u = 0; u < 2; ++u) {
-                if (rr[u] >= 0) {
+                for (int u = 0; u < 2; ++u) {
+                    const int item = cidx + u * kConvThreads;
+                    const int py = item >= g.xrows ? 1 : 0, r = item - py * g.xrows;
+                    rr[set][u] = item < 2 * g.xrows ? r : -1;
+                    pyy[set][u] = py;
+                    const int Rr = tile * kTileM + r;
+                    if (rr[set][u] >= 0 && Rr < NR) {
+                        int b, Yb, Xb;
+                        raster_split(Rr, g, b, Yb, Xb);
+                        const float4* src = reinterpret_cast<const float4*>(
+                            X + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
 #pragma unroll
-                    for (int px = 0; px < 2; ++px) {
-                        uint4 hi, lo;
-                        split8_f16(v[u][2 * px], v[u][2 * px + 1], kActScale, hi, lo);
-                        uint8_t* dst = xs + (size_t)(pyy[u] * 2 + px) * g.chunk_bytes + rr[u] * 16;
-                        *reinterpret_cast<uint4*>(dst) = hi;
-                        *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
+                        for (int q = 0; q < 4; ++q) v[set][u][q] = __ldg(src + q);
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) v[set][u][q] = make_float4(0.f, 0.f, 0.f, 0.f);
                     }
                 }
+            };
+            auto convert = [&](int set, int it) {
+                const int stage = it % kFwdStages;
+                mbar_wait(&x_empty[stage], ((it / kFwdStages) & 1) ^ 1);
+                uint8_t* xs = x_s + (size_t)stage * g.stage_bytes;
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    if (rr[set][u] >= 0) {
+#pragma unroll
+                        for (int px = 0; px < 2; ++px) {
+                            uint4 hi, lo;
+                            split8_f16(v[set][u][2 * px], v[set][u][2 * px + 1], kActScale, hi, lo);
+                            uint8_t* dst = xs + (size_t)(pyy[set][u] * 2 + px) * g.chunk_bytes + rr[set][u] * 16;
+                            *reinterpret_cast<uint4*>(dst) = hi;
+                            *reinterpret_cast<uint4*>(dst + g.hl_bytes) = lo;
+                        }
+                    }
+                }
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&x_full[stage]);
+            };
+            if (g0 < g1) fetch(g0, 0);
+            int it2 = 0;
+            for (int gt = g0; gt < g1; gt += 2, it2 += 2) {      // unrolled by two so that the register sets are static
+                if (gt + 1 < g1) fetch(gt + 1, 1);
+                convert(0, it2);
+                if (gt + 1 < g1) {
+                    if (gt + 2 < g1) fetch(gt + 2, 0);
+                    convert(1, it2 + 1);
+                }
             }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&x_full[stage]);
         }
     } else if (warp == 9) {
         // ================= weight loads + MMA issue (whole warp, uniform values, elected instructions) =================
@@ -300,6 +333,17 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
         uint32_t wphase = 0, fphase = 0, idesc = 0;
         const uint32_t ws = smem_u32(w_s);
         const uint32_t w_hl = (uint32_t)w_slots * kModBytes;
+        // Descriptor templates, built ONCE: this warp's dependent uniform-datapath instructions (~7 cycles each) are the
+        // pace of the kernel's MMA stream, and building four descriptors from the geometry tables inside the tile loop
+        // cost ~25 such instructions per K step.  Per tile only the stage offset is added (descriptor unit: 16 bytes).
+        uint64_t a_t[8], b_t[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            a_t[i] = make_smem_desc(smem_u32(x_s) + (uint32_t)g.a_off[i < g.nk ? i : 0], (uint32_t)g.a_lbo[i < g.nk ? i : 0], 128);
+            b_t[i] = make_smem_desc(ws + (uint32_t)g.b_off[i < g.nk ? i : 0], 128, kModBytes);
+        }
+        const uint64_t a_lo_adv = (uint64_t)(g.hl_bytes >> 4), b_lo_adv = (uint64_t)(w_hl >> 4);
+        const uint64_t stage_adv = (uint64_t)(g.stage_bytes >> 4);
         for (int gt = g0; gt < g1; ++gt, ++it) {
             const int p = gt / ntile;
             if (p != cur_p) {
@@ -328,30 +372,27 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
                 idesc = make_idesc_f16(kTileM, 8 * ((ns + 1) & ~1), 0, 0, 0, 0);   // fp16 x fp16, both K-major
                 cur_p = p;
             }
-            const int stage = it % kXStages, as = it & 1;
+            const int stage = it % kFwdStages, as = it & 1;
             mbar_wait(&acc_empty[as], ((it >> 1) & 1) ^ 1);
-            mbar_wait(&x_full[stage], (it / kXStages) & 1);
+            mbar_wait(&x_full[stage], (it / kFwdStages) & 1);
             tc_fence_after();
             if (ns > 0) {
-                const uint32_t xs = smem_u32(x_s + (size_t)stage * g.stage_bytes);
+                const uint64_t s_adv = stage_adv * (uint64_t)stage;
                 const uint32_t dcol = td + as * acc_stride;
+                if (elect_one()) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {              // K steps of the layer's geometry (g.nk of them)
-                    if (i < g.nk) {
-                        const uint32_t a_addr = xs + (uint32_t)g.a_off[i];
-                        const uint32_t b_addr = ws + (uint32_t)g.b_off[i];
-                        const uint64_t a_hi = make_smem_desc(a_addr, (uint32_t)g.a_lbo[i], 128);
-                        const uint64_t a_lo = make_smem_desc(a_addr + g.hl_bytes, (uint32_t)g.a_lbo[i], 128);
-                        const uint64_t b_hi = make_smem_desc(b_addr, 128, kModBytes);
-                        const uint64_t b_lo = make_smem_desc(b_addr + w_hl, 128, kModBytes);
-                        if (elect_one()) {
+                    for (int i = 0; i < 8; ++i) {              // K steps of the layer's geometry (g.nk of them)
+                        if (i < g.nk) {
+                            const uint64_t a_hi = a_t[i] + s_adv, a_lo = a_hi + a_lo_adv;
+                            const uint64_t b_hi = b_t[i], b_lo = b_hi + b_lo_adv;
                             umma_f16(dcol, a_hi, b_hi, idesc, i ? 1u : 0u);
                             umma_f16(dcol, a_hi, b_lo, idesc, 1u);
                             umma_f16(dcol, a_lo, b_hi, idesc, 1u);
                         }
                     }
+                    umma_commit(&x_empty[stage]);
+                    umma_commit(&acc_full[as]);
                 }
-                if (elect_one()) { umma_commit(&x_empty[stage]); umma_commit(&acc_full[as]); }
             } else {
                 if (elect_one()) { mbar_arrive(&x_empty[stage]); mbar_arrive(&acc_full[as]); }
             }
@@ -359,11 +400,28 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
         }
     } else if (warp < 4) {
         // ================= epilogue: thread = raster row of the tile =================
-        int it = 0;
+        // The path's first four biases and module ids live in registers and are reloaded only when the path changes:
+        // fetched per tile, the two dependent global loads per module sat in front of every tile's arithmetic.
+        int it = 0, cur_p = -1, ns = 0;
+        uint32_t mask = 0;
+        float bias4[4][8];
+        int j4[4] = {0, 0, 0, 0};
         for (int gt = g0; gt < g1; ++gt, ++it) {
             const int p = gt / ntile, tile = gt - p * ntile;
-            const uint32_t mask = masks[p * nd.L + l];
-            const int ns = __popc(mask);
+            if (p != cur_p) {
+                cur_p = p;
+                mask = masks[p * nd.L + l];
+                ns = __popc(mask);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    j4[q] = q < ns ? __fns(mask, 0, q + 1) : 0;
+                    const float4* bp = reinterpret_cast<const float4*>(
+                        params + nd.convW_base[l] + (long long)j4[q] * nd.conv_stride[l] + nd.convb_off[l]);
+                    const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1);
+                    bias4[q][0] = b0.x; bias4[q][1] = b0.y; bias4[q][2] = b0.z; bias4[q][3] = b0.w;
+                    bias4[q][4] = b1.x; bias4[q][5] = b1.y; bias4[q][6] = b1.z; bias4[q][7] = b1.w;
+                }
+            }
             const int Rr = tile * kTileM + warp * 32 + lane;
             int b, Yb, Xb;
             raster_split(Rr, g, b, Yb, Xb);
@@ -376,7 +434,27 @@ conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ 
             for (int c = 0; c < 8; ++c) sum[c] = 0.f;
             mbar_wait(&acc_full[as], (it >> 1) & 1);
             tc_fence_after();
-            for (int s0 = 0; s0 < ns; s0 += 2) {
+#pragma unroll
+            for (int s0 = 0; s0 < 4; s0 += 2) {                 // slots 0..3 from the registers
+                if (s0 < ns) {
+                    uint32_t d[16];
+                    tmem_ld16(td + ((uint32_t)(warp * 32) << 16) + as * acc_stride + s0 * 8, d);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        if (s0 + u < ns) {
+                            unsigned bits = 0;
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {
+                                const float pre = fmaf(__uint_as_float(d[u * 8 + c]), kFwdUnscale, bias4[s0 + u][c]);
+                                if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
+                            }
+                            if (valid) R[(t * nd.M + j4[s0 + u]) * g.npix + pix] = (uint8_t)bits;
+                        }
+                    }
+                }
+            }
+            for (int s0 = 4; s0 < ns; s0 += 2) {                // further slots (a mutated or OR'ed path): biases from global memory
                 uint32_t d[16];
                 tmem_ld16(td + ((uint32_t)(warp * 32) << 16) + as * acc_stride + s0 * 8, d);
                 tmem_ld_wait();
@@ -921,8 +999,8 @@ bool pn_conv_mid_tc_supported(const pn_handle* h, int l) {
     MidTcGeom g;
     if (!make_mid_tc_geom(h->nd, l, g)) return false;
     const int w_slots = (h->nd.M + 1) & ~1;
-    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * g.stage_bytes;
-    return smem <= 200 * 1024 && 16 * w_slots <= 512 && h->nd.convb_off[l] % 4 == 0;
+    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kFwdStages * g.stage_bytes;
+    return smem <= 113 * 1024 && 16 * w_slots <= 512 && h->nd.convb_off[l] % 4 == 0;
 }
 
 size_t pn_conv_mid_tc_scratch_bytes(const pn_handle* h, int l) {
@@ -951,11 +1029,11 @@ int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     const uint8_t* wf = h->tc_mid_buf[l];
     const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
     const uint32_t tmem_cols = pow2_cols(16u * w_slots);
-    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * g.stage_bytes;
+    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kFwdStages * g.stage_bytes;
     PN_SET_SMEM(h, conv_mid_fwd_tc_kernel, smem);
     const int ntile = (B * g.RB + kTileM - 1) / kTileM;
     const long long NT = (long long)h->P * ntile;
-    const int grid = (int)std::min<long long>(NT, 3ll * h->num_sms);
+    const int grid = (int)std::min<long long>(NT, 2ll * h->num_sms);
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + l, st);
         conv_mid_fwd_tc_kernel<<<grid, kFwdThreads, smem, st>>>(h->act[l - 1], wf, h->params, nd, l, g, h->d_masks, h->P, B,

@@ -91,6 +91,7 @@ struct pn_handle {
     float* pending_loss = nullptr;      // per-path loss output of the step in flight (written by the head reduce launch)
     float* head_part = nullptr;         // [head_chunks][hidden*(A+1) + (A+1)]
     int head_chunks = 0;
+    int head_ctas = 0;                  // CTAs of the last head-kernel launch = partial slices it wrote
     // rmsprop
     std::vector<PnRmsChunk> h_chunks;
     std::vector<int> h_tensor_chunk0;   // host copy of d_tensor_chunk0

@@ -208,20 +208,11 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
     float* hs = b2s + 32;                      // [16][hpitch]
     float* zs = hs + PN_HEAD_CHUNK * hpitch;   // [16][32] logits (k < A), value (k == A)
     float* dzs = zs + PN_HEAD_CHUNK * 32;      // [16][32]
-    const int t0 = blockIdx.x * PN_HEAD_CHUNK, nt = min(PN_HEAD_CHUNK, T - t0);
+    // A CTA walks over several 16-transition chunks (chunk = blockIdx.x, + gridDim.x, ...): the head weights are staged once
+    // per CTA, and the CTA's partial of the head weight gradient is accumulated over its chunks (first chunk writes, later
+    // chunks add, same CTA, fixed order), so the reduction that follows reads one partial per CTA instead of one per chunk.
+    const int nchunks_all = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
     {
-        const int m4 = Hd >> 2;
-        if ((Hd & 3) == 0) {
-            for (int i = threadIdx.x; i < nt * m4; i += blockDim.x) {
-                const int tt = i / m4, c = i - tt * m4;
-                pntc::cp_async16(hs + tt * hpitch + 4 * c, Hin + (size_t)(t0 + tt) * Hd + 4 * c);
-            }
-        } else {
-            for (int i = threadIdx.x; i < nt * Hd; i += blockDim.x) {
-                const int tt = i / Hd, c = i - tt * Hd;
-                hs[tt * hpitch + c] = Hin[(size_t)(t0 + tt) * Hd + c];
-            }
-        }
         for (int i = threadIdx.x; i < Hd; i += blockDim.x) {       // one weight row per thread, loads issued together
             float wr[NP];
             const float* src = params + nd.fc2W + (size_t)i * A;
@@ -244,11 +235,29 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
         }
         if (threadIdx.x < 32) b2s[threadIdx.x] = threadIdx.x < A ? params[nd.fc2b + threadIdx.x]
                                                                   : (threadIdx.x == A ? params[nd.fc3b] : 0.f);
+    }
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    bool first = true;
+    for (int chunk = blockIdx.x; chunk < nchunks_all; chunk += gridDim.x, first = false) {
+    const int t0 = chunk * PN_HEAD_CHUNK, nt = min(PN_HEAD_CHUNK, T - t0);
+    __syncthreads();                                               // the previous chunk's readers are done with hs / zs / dzs
+    {
+        const int m4 = Hd >> 2;
+        if ((Hd & 3) == 0) {
+            for (int i = threadIdx.x; i < nt * m4; i += blockDim.x) {
+                const int tt = i / m4, c = i - tt * m4;
+                pntc::cp_async16(hs + tt * hpitch + 4 * c, Hin + (size_t)(t0 + tt) * Hd + 4 * c);
+            }
+        } else {
+            for (int i = threadIdx.x; i < nt * Hd; i += blockDim.x) {
+                const int tt = i / Hd, c = i - tt * Hd;
+                hs[tt * hpitch + c] = Hin[(size_t)(t0 + tt) * Hd + c];
+            }
+        }
         for (int i = threadIdx.x; i < PN_HEAD_CHUNK * 32; i += blockDim.x) dzs[i] = 0.f;
         pntc::cp_async_wait_all();
     }
     __syncthreads();
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     {   // phase 1
         const int tt = threadIdx.x >> 4, ks = threadIdx.x & 15;
         float2 acc[NP / 2];
@@ -320,7 +329,7 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
             if (lane == 0) loss_t[t] = a < 0 ? 0.f : loss;
         }
     }
-    if (!training) return;
+    if (!training) continue;
     __syncthreads();
     const float rM = 1.0f / nd.out_div;
     float* out = part ? part + (size_t)blockIdx.x * ((size_t)Hd * A1 + A1) : nullptr;
@@ -351,16 +360,17 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
         if (out) {
 #pragma unroll
             for (int k = 0; k < NP / 2; ++k) {
-                if (2 * k < A1) out[(size_t)i * A1 + 2 * k] = acc[k].x;
-                if (2 * k + 1 < A1) out[(size_t)i * A1 + 2 * k + 1] = acc[k].y;
+                if (2 * k < A1) out[(size_t)i * A1 + 2 * k] = (first ? 0.f : out[(size_t)i * A1 + 2 * k]) + acc[k].x;
+                if (2 * k + 1 < A1) out[(size_t)i * A1 + 2 * k + 1] = (first ? 0.f : out[(size_t)i * A1 + 2 * k + 1]) + acc[k].y;
             }
         }
     }
     if (out && threadIdx.x < A1) {
         float s = 0.f;
         for (int tt = 0; tt < nt; ++tt) s += dzs[tt * 32 + threadIdx.x];
-        out[(size_t)Hd * A1 + threadIdx.x] = s;
+        out[(size_t)Hd * A1 + threadIdx.x] = (first ? 0.f : out[(size_t)Hd * A1 + threadIdx.x]) + s;
     }
+    }   // chunks of this CTA
 }
 
 // stage 2: fixed-order sum over chunks, scatter into W_fc2/b_fc2/W_fc3/b_fc3.
@@ -383,8 +393,18 @@ __device__ __forceinline__ void head_reduce_body(int bid, const float* __restric
     const int el = threadIdx.x & 31, grp = threadIdx.x >> 5;
     const int e = bid * 32 + el;
     float s = 0.f;
-    if (e < n)
-        for (int c = grp; c < nchunks; c += 8) s += part[(size_t)c * n + e];
+    if (e < n) {
+        // four independent partial sums (chunks c, c+8, c+16, c+24 of this group's sequence): four loads in flight
+        // instead of a chain of dependent round trips; combined in a fixed order
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        int c = grp;
+        for (; c + 24 < nchunks; c += 32) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) s4[u] += part[(size_t)(c + 8 * u) * n + e];
+        }
+        for (int u = 0; c < nchunks; c += 8, ++u) s4[u] += part[(size_t)c * n + e];
+        s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+    }
     red[grp][el] = s;
     __syncthreads();
     if (grp != 0 || e >= n) return;
@@ -676,12 +696,21 @@ __device__ __forceinline__ void conv_reduce_body(int j, int by, const float* __r
         __syncthreads();
     }
     float s = 0.f;
-    if (e < n)
-        for (int i = grp; i < nterms; i += 8) {
+    if (e < n) {
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four loads in flight (see head_reduce_body); fixed combination order
+        auto term = [&](int i) {
             const int pi = i / nch_active, c = i - pi * nch_active;
             const int p = staged ? lst_s[pi] : lst[pi];
-            s += part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
+            return part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
+        };
+        int i = grp;
+        for (; i + 24 < nterms; i += 32) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) s4[u] += term(i + 8 * u);
         }
+        for (int u = 0; i < nterms; i += 8, ++u) s4[u] += term(i);
+        s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+    }
     red[grp][el] = s;
     __syncthreads();
     if (grp != 0 || e >= n) return;
@@ -808,7 +837,10 @@ int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, 
     const size_t hpitch = (((size_t)nd.hidden + 3) & ~(size_t)3) + 16;
     const int np = nd.A + 1 <= 8 ? 8 : (nd.A + 1 <= 20 ? 20 : 32);
     const size_t sm = ((size_t)nd.hidden * np + 32 + PN_HEAD_CHUNK * hpitch + 2 * PN_HEAD_CHUNK * 32) * sizeof(float);
-    const int nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
+    // one CTA per chunk while they all fit the partial buffer (measured: letting a CTA walk over several chunks to amortise
+    // the weight staging made the kernel slower, 35 -> 41 us at 8192 transitions: it is latency-, not traffic-bound)
+    const int nchunks = std::min((T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK, h->head_chunks);
+    h->head_ctas = nchunks;
     auto kern = np == 8 ? head_kernel<8> : (np == 20 ? head_kernel<20> : head_kernel<32>);
     if (int rc = set_smem(h, kern, sm)) return rc;
     {
@@ -910,7 +942,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         const int nh = nd.hidden * (nd.A + 1) + nd.A + 1;
         jobs.head_blk0 = blk;
         jobs.head_nred = (nh + 31) / 32;
-        jobs.head_nchunks = (T + PN_HEAD_CHUNK - 1) / PN_HEAD_CHUNK;
+        jobs.head_nchunks = h->head_ctas;               // one partial of the head weight gradient per CTA of the head kernel
         const int nloss = h->pending_loss ? (P + 255) / 256 : 0;
         PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
         grad_reduce_kernel<<<blk + jobs.head_nred + nloss, 256, 0, st>>>(jobs, nd, h->d_list, h->d_list_count, P, B, h->nch,
