@@ -727,6 +727,293 @@ conv_mid_dgrad_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict
 }
 
 // =====================================================================================================
+// data gradient of the 3x3 / stride-1 layers ("col2im" form).  In raster form
+//     dX[R][(py, px, ci)] = sum over taps (dy, dx), slots, co of  dpre_slot[R - shift_tap][co] * W_slot[tap][(py,px,ci)][co]
+// with dpre = dY * relu-mask on the output raster (junk rows, rows before the path's first transition and rows
+// past its last are zero) and shift_tap = dy * Xp + dx (stride 2) or kh * IW + kw (stride 1).
+// Round 1 issued one GEMM per tap with the A operand shifted BACK by the tap (N = 32 or 8 columns: 24 .. 54 MMAs per
+// 128-row tile, each costing its 4 KB A fetch).  Here the taps are COLUMNS of one GEMM on the unshifted rows,
+//     D[R'][tap * nb + (py,px,ci)] = sum over (slot, co) of dpre_slot[R'][co] * W_slot[tap][(py,px,ci)][co]       (nb = 32 / 8)
+// K = 8 * slots, N = 4 * 32 = 128 (stride 2) or 9 * 8 = 72 -> 80 (stride 1): 3 * slots / 2 MMAs per tile, and the epilogue
+// adds the shifted rows:  dX[R] = sum over taps of D[R - shift_tap][tap block]  (through shared memory, one tap group at
+// a time).  A tile computes D for 128 consecutive rows starting `lead` = max shift rows before its first output row and
+// produces 128 - lead output rows.  The weight operand blocks are the ones round 1 used (block = tap, [ci][co]).
+// Measured (256 paths x 32): 61 -> 40 us for the stride-1 layer.  For the 4x4 / stride-2 layer the same form reads four
+// times as many accumulator columns out of TMEM (128 per row) and measured SLOWER (61 -> 88 us): that layer keeps the
+// per-tap kernel above, whose tap sum happens inside the tensor core.
+// =====================================================================================================
+__global__ void __launch_bounds__(kFwdThreads, 2)
+conv_mid_dgrad_col2im_tc_kernel(const float* __restrict__ dY, const uint8_t* __restrict__ R, const uint8_t* __restrict__ wd,
+                         PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int P, int B, int ntile,
+                         int w_slots, float* __restrict__ dX, unsigned* __restrict__ absmax_out) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kXStages]
+    uint64_t* x_empty = x_full + kXStages;                     // [kXStages]
+    uint64_t* acc_full = x_empty + kXStages;                   // [2]
+    uint64_t* acc_empty = acc_full + 2;                        // [2]
+    uint64_t* w_full = acc_empty + 2;
+    uint64_t* w_free = w_full + 1;
+    uint8_t* w_s = smem + 128;                                 // [hl][w_slots][kModBytes]
+    const int d_chunk = kTileM * 16;                           // bytes of one slot's chunk of a stage (128 rows)
+    const int d_hl = w_slots * d_chunk;                        // bytes of the hi (or lo) chunks of one stage
+    uint8_t* d_s = w_s + (size_t)2 * w_slots * kModBytes;      // [kXStages][hl][w_slots][128] 16-byte rows
+    float* c_s = reinterpret_cast<float*>(d_s + (size_t)kXStages * 2 * d_hl);    // [128][pitch] tap group of D for the shifted sum
+    __shared__ uint32_t tmem_base_s;
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    const long long NT = (long long)P * ntile;
+    const int g0 = (int)(NT * blockIdx.x / gridDim.x), g1 = (int)(NT * (blockIdx.x + 1) / gridDim.x);
+    const int NR = B * g.RB;
+    const int lead = g.max_shift, tstride = kTileM - lead;    // output rows per tile
+    const int ncols = g.s1 ? 80 : 128;                         // accumulator columns (stride 1: 72 used)
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kXStages; ++i) { mbar_init(&x_full[i], kConvWarps); mbar_init(&x_empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 128); }
+        mbar_init(w_full, 1); mbar_init(w_free, 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) tmem_alloc(&tmem_base_s, 256);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t td = tmem_base_s;
+
+    if (warp >= 4 && warp < 4 + kConvWarps) {
+        // ================= converters: masked output gradient -> bf16 hi/lo chunks, one raster row per thread =================
+        const int r = threadIdx.x - 128;
+        int it = 0, cur_p = -1, ns = 0, ns_pad = 0;
+        uint32_t mask = 0;
+        int jq[4] = {0, 0, 0, 0};
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile, tile = gt - p * ntile;
+            if (p != cur_p) {
+                mask = masks[p * nd.L + l];
+                ns = __popc(mask); ns_pad = (ns + 1) & ~1;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) jq[q] = q < ns ? __fns(mask, 0, q + 1) : 0;
+                cur_p = p;
+            }
+            const int m = tile * tstride - lead + r;
+            bool valid = r < kTileM && m >= 0 && m < NR;
+            int b = 0, pix = 0;
+            if (valid) {
+                int oy, ox;
+                raster_split(m, g, b, oy, ox);
+                valid = oy < g.OH && ox < g.OW;
+                pix = oy * g.OW + ox;
+            }
+            const size_t t = (size_t)p * B + b;
+            float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+            unsigned mk[4] = {0, 0, 0, 0};
+            if (valid) {
+                const float4* src = reinterpret_cast<const float4*>(dY + (t * g.npix + pix) * 8);
+                v0 = __ldg(src); v1 = __ldg(src + 1);
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (q < ns) mk[q] = R[(t * nd.M + jq[q]) * g.npix + pix];
+            }
+            const int stage = it % kXStages;
+            mbar_wait(&x_empty[stage], ((it / kXStages) & 1) ^ 1);
+            if (r < kTileM) {
+                uint8_t* dst = d_s + (size_t)stage * 2 * d_hl + r * 16;
+                for (int slot = 0; slot < ns_pad; ++slot) {
+                    unsigned bits = 0;
+                    if (slot < 4) bits = slot == 0 ? mk[0] : (slot == 1 ? mk[1] : (slot == 2 ? mk[2] : mk[3]));
+                    else if (valid && slot < ns) bits = R[(t * nd.M + __fns(mask, 0, slot + 1)) * g.npix + pix];
+                    const float4 a = make_float4((bits & 1u) ? v0.x : 0.f, (bits & 2u) ? v0.y : 0.f, (bits & 4u) ? v0.z : 0.f,
+                                                 (bits & 8u) ? v0.w : 0.f);
+                    const float4 c = make_float4((bits & 16u) ? v1.x : 0.f, (bits & 32u) ? v1.y : 0.f, (bits & 64u) ? v1.z : 0.f,
+                                                 (bits & 128u) ? v1.w : 0.f);
+                    uint4 hi, lo;
+                    split8(a, c, hi, lo);
+                    *reinterpret_cast<uint4*>(dst + (size_t)slot * d_chunk) = hi;
+                    *reinterpret_cast<uint4*>(dst + d_hl + (size_t)slot * d_chunk) = lo;
+                }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&x_full[stage]);
+        }
+    } else if (warp == 9) {
+        // ================= weight loads + MMA issue =================
+        int cur_p = -1, ns = 0, it = 0;
+        uint32_t wphase = 0, fphase = 0;
+        const uint32_t ws = smem_u32(w_s);
+        const uint32_t w_hl = (uint32_t)w_slots * kModBytes;
+        // B: rows n = tap block * 8 + ci (stride 2: tap * 32 + (py,px,ci): 16 consecutive blocks of the module's operand
+        // buffer), K = (slot, co): 8-row groups 128 B apart, the two slots of a K step kModBytes apart
+        const uint32_t idesc = make_idesc_f16(kTileM, ncols, 1, 1, 0, 0);
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile;
+            if (p != cur_p) {
+                const uint32_t mask = __reduce_or_sync(0xffffffffu, masks[p * nd.L + l]);
+                ns = __popc(mask);
+                if (it > 0) {
+                    if (elect_one()) umma_commit(w_free);
+                    __syncwarp();
+                    mbar_wait(w_free, fphase);
+                    fphase ^= 1;
+                }
+                if (ns > 0) {
+                    if (ns & 1) {                   // zero the pad slot (its A chunk is zero too; stale bits could be NaN)
+                        uint4* z0 = reinterpret_cast<uint4*>(w_s + (size_t)ns * kModBytes);
+                        uint4* z1 = reinterpret_cast<uint4*>(w_s + w_hl + (size_t)ns * kModBytes);
+                        for (int i = lane; i < kModBytes / 16; i += 32) { z0[i] = make_uint4(0, 0, 0, 0); z1[i] = make_uint4(0, 0, 0, 0); }
+                        fence_proxy_async();
+                        __syncwarp();
+                    }
+                    if (elect_one()) {
+                        mbar_expect_tx(w_full, (uint32_t)(ns * 2 * kModBytes));
+                        for (int slot = 0; slot < ns; ++slot) {
+                            const int j = __fns(mask, 0, slot + 1);
+                            bulk_g2s(w_s + (size_t)slot * kModBytes, wd + (size_t)j * 2 * kModBytes, kModBytes, w_full);
+                            bulk_g2s(w_s + w_hl + (size_t)slot * kModBytes, wd + (size_t)j * 2 * kModBytes + kModBytes,
+                                     kModBytes, w_full);
+                        }
+                    }
+                    __syncwarp();
+                    mbar_wait(w_full, wphase);
+                    wphase ^= 1;
+                }
+                cur_p = p;
+            }
+            const int stage = it % kXStages, as = it & 1;
+            mbar_wait(&acc_empty[as], ((it >> 1) & 1) ^ 1);
+            mbar_wait(&x_full[stage], (it / kXStages) & 1);
+            tc_fence_after();
+            if (ns > 0) {
+                const uint32_t ds = smem_u32(d_s + (size_t)stage * 2 * d_hl);
+                const uint32_t dcol = td + as * 128;
+                const int nk = (ns + 1) >> 1;
+                if (elect_one()) {
+                    for (int kk = 0; kk < nk; ++kk) {
+                        const uint32_t a_addr = ds + (uint32_t)(2 * kk) * d_chunk;
+                        const uint32_t b_addr = ws + (uint32_t)(2 * kk) * kModBytes;
+                        const uint64_t a_hi = make_smem_desc(a_addr, d_chunk, 128);
+                        const uint64_t a_lo = make_smem_desc(a_addr + d_hl, d_chunk, 128);
+                        const uint64_t b_hi = make_smem_desc(b_addr, kModBytes, 128);
+                        const uint64_t b_lo = make_smem_desc(b_addr + w_hl, kModBytes, 128);
+                        umma_f16(dcol, a_hi, b_hi, idesc, kk ? 1u : 0u);
+                        umma_f16(dcol, a_hi, b_lo, idesc, 1u);
+                        umma_f16(dcol, a_lo, b_hi, idesc, 1u);
+                    }
+                    umma_commit(&x_empty[stage]);
+                    umma_commit(&acc_full[as]);
+                }
+            } else {
+                if (elect_one()) { mbar_arrive(&x_empty[stage]); mbar_arrive(&acc_full[as]); }
+            }
+            __syncwarp();
+        }
+    } else if (warp < 4) {
+        // ================= epilogue: thread = row of D; output row o = thread (o < tstride) =================
+        const int rD = warp * 32 + lane;
+        const int pitch = g.s1 ? 28 : 36;                      // floats per row of c_s (16-byte aligned, conflict-free for LDS.128 / STS.128)
+        int it = 0;
+        for (int gt = g0; gt < g1; ++gt, ++it) {
+            const int p = gt / ntile, tile = gt - p * ntile;
+            const int ns = __popc(masks[p * nd.L + l]);
+            const int Rr = tile * tstride + rD;                 // output raster row of this thread
+            const bool valid = rD < tstride && Rr < NR;
+            const int as = it & 1;
+            float amax = 0.f;                                 // max |dX| of this tile: the first conv layer's quantiser scale is per path
+            mbar_wait(&acc_full[as], (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t ta = td + ((uint32_t)(warp * 32) << 16) + as * 128;
+            if (g.s1) {
+                float acc[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+                for (int kh = 0; kh < 3; ++kh) {
+                    if (ns > 0) {
+                        uint32_t d[24];
+                        tmem_ld8(ta + kh * 24, *reinterpret_cast<uint32_t(*)[8]>(&d[0]));
+                        tmem_ld8(ta + kh * 24 + 8, *reinterpret_cast<uint32_t(*)[8]>(&d[8]));
+                        tmem_ld8(ta + kh * 24 + 16, *reinterpret_cast<uint32_t(*)[8]>(&d[16]));
+                        tmem_ld_wait();
+                        float4* row = reinterpret_cast<float4*>(c_s + rD * pitch);
+#pragma unroll
+                        for (int q = 0; q < 6; ++q)
+                            row[q] = make_float4(__uint_as_float(d[4 * q]), __uint_as_float(d[4 * q + 1]), __uint_as_float(d[4 * q + 2]),
+                                                 __uint_as_float(d[4 * q + 3]));
+                    }
+                    if (kh == 2) { tc_fence_before(); mbar_arrive(&acc_empty[as]); }      // the accumulator stage has been read
+                    asm volatile("bar.sync 2, 128;" ::: "memory");
+                    if (valid && ns > 0) {
+#pragma unroll
+                        for (int kw = 0; kw < 3; ++kw) {
+                            const float4* src = reinterpret_cast<const float4*>(c_s + (rD + lead - (kh * g.Xp + kw)) * pitch + kw * 8);
+                            const float4 a = src[0], b4 = src[1];
+                            acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w;
+                            acc[4] += b4.x; acc[5] += b4.y; acc[6] += b4.z; acc[7] += b4.w;
+                        }
+                    }
+                    asm volatile("bar.sync 2, 128;" ::: "memory");
+                }
+                if (valid) {
+                    // stride 1: the raster is the NHWC tensor of the path itself
+                    float4* o = reinterpret_cast<float4*>(dX + ((size_t)p * NR + Rr) * 8);
+                    o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                    o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) amax = fmaxf(amax, fabsf(acc[c]));
+                }
+            } else {
+                float acc[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) acc[c] = 0.f;
+                for (int tap = 0; tap < 4; ++tap) {
+                    if (ns > 0) {
+                        uint32_t d[32];
+                        tmem_ld16(ta + tap * 32, *reinterpret_cast<uint32_t(*)[16]>(&d[0]));
+                        tmem_ld16(ta + tap * 32 + 16, *reinterpret_cast<uint32_t(*)[16]>(&d[16]));
+                        tmem_ld_wait();
+                        float4* row = reinterpret_cast<float4*>(c_s + rD * pitch);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            row[q] = make_float4(__uint_as_float(d[4 * q]), __uint_as_float(d[4 * q + 1]), __uint_as_float(d[4 * q + 2]),
+                                                 __uint_as_float(d[4 * q + 3]));
+                    }
+                    if (tap == 3) { tc_fence_before(); mbar_arrive(&acc_empty[as]); }
+                    asm volatile("bar.sync 2, 128;" ::: "memory");
+                    if (valid && ns > 0) {
+                        const float4* src = reinterpret_cast<const float4*>(c_s + (rD + lead - ((tap >> 1) * g.Xp + (tap & 1))) * pitch);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const float4 a = src[q];
+                            acc[4 * q] += a.x; acc[4 * q + 1] += a.y; acc[4 * q + 2] += a.z; acc[4 * q + 3] += a.w;
+                        }
+                    }
+                    asm volatile("bar.sync 2, 128;" ::: "memory");
+                }
+                if (valid) {
+                    int b, Yb, Xb;
+                    raster_split(Rr, g, b, Yb, Xb);
+#pragma unroll
+                    for (int py = 0; py < 2; ++py) {
+                        float4* o = reinterpret_cast<float4*>(
+                            dX + ((((size_t)p * B + b) * g.IH + 2 * Yb + py) * g.IW + 2 * Xb) * 8);
+#pragma unroll
+                        for (int q = 0; q < 4; ++q)
+                            o[q] = make_float4(acc[py * 16 + q * 4], acc[py * 16 + q * 4 + 1], acc[py * 16 + q * 4 + 2], acc[py * 16 + q * 4 + 3]);
+                    }
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) amax = fmaxf(amax, fabsf(acc[c]));
+                }
+            }
+            if (absmax_out) {                                 // (a tile never straddles two paths)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                if (lane == 0 && amax > 0.f) atomicMax(absmax_out + p, __float_as_uint(amax));   // non-negative floats order like uints
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) tmem_dealloc(td, 256);
+}
+
+// =====================================================================================================
 // weight gradient.  d W_slot[(2dy+py, 2dx+px)][ci][co] = sum over raster rows m of  dpre_slot[m][co] * Xs2d[m + dy*Xp + dx][(py,px,ci)]
 // as D[(hl, slot, co) = 64 rows][tap * 32 + (py, px, ci) = 128 columns], accumulated in TMEM over all tiles of
 // one (path, chunk) item: A = dpre chunks (MN-major, chunk = hi slot 0..3 | lo slot 0..3), B = the forward's X
@@ -1043,10 +1330,38 @@ int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     return PN_OK;
 }
 
+static int launch_dgrad_col2im(pn_handle* h, int l, int B, cudaStream_t st) {
+    const PnNetDesc& nd = h->nd;
+    MidTcGeom g;
+    if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+    const uint8_t* wd = h->tc_mid_buf[l] + (size_t)nd.M * 2 * kModBytes;     // written by this step's forward launch
+    const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
+    const int pitch = g.s1 ? 28 : 36;
+    const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * 2 * w_slots * (kTileM * 16) +
+                        (size_t)kTileM * pitch * sizeof(float);
+    PN_SET_SMEM(h, conv_mid_dgrad_col2im_tc_kernel, smem);
+    const int tstride = kTileM - g.max_shift;                                // output rows per tile (see the kernel)
+    const int ntile = (B * g.RB + tstride - 1) / tstride;
+    const long long NT = (long long)h->P * ntile;
+    const int grid = (int)std::min<long long>(NT, 2ll * h->num_sms);
+    // layer 1 writes the first conv layer's output gradient: fold the abs-max its quantiser needs into this pass
+    unsigned* amax = l == 1 ? pn_conv0_absmax_slot(h) : nullptr;
+    if (amax) PN_CUDA(h, cudaMemsetAsync(amax, 0, (size_t)h->P * sizeof(unsigned), st));
+    {
+        PnProfScope prof(h, PN_PROF_CONV_DGRAD + l, st);
+        conv_mid_dgrad_col2im_tc_kernel<<<grid, kFwdThreads, smem, st>>>(h->dact[l], h->rmask[l], wd, nd, l, g, h->d_masks, h->P, B,
+                                                                  ntile, w_slots, h->dact[l - 1], amax);
+    }
+    h->absmax_fused = amax != nullptr;
+    PN_LAUNCH_CHECK(h, "conv_mid_dgrad_col2im_tc_kernel");
+    return PN_OK;
+}
+
 int pn_launch_conv_mid_dgrad_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     const PnNetDesc& nd = h->nd;
     MidTcGeom g;
     if (!make_mid_tc_geom(nd, l, g)) return pn_fail(h, PN_ERR_STATE, "tensor-core middle conv layer not supported");
+    if (g.s1) return launch_dgrad_col2im(h, l, B, st);
     const uint8_t* wd = h->tc_mid_buf[l] + (size_t)nd.M * 2 * kModBytes;     // written by this step's forward launch
     const int w_slots = std::max(2, (h->max_active[l] + 1) & ~1);
     const size_t smem = 128 + (size_t)2 * w_slots * kModBytes + (size_t)kXStages * 2 * w_slots * g.chunk_bytes;

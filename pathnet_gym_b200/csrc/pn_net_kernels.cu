@@ -341,6 +341,7 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
             wr[2 * q] = make_float2(wv.x, wv.y); wr[2 * q + 1] = make_float2(wv.z, wv.w);
             acc[2 * q] = acc[2 * q + 1] = make_float2(0.f, 0.f);
         }
+#pragma unroll 4
         for (int tt = 0; tt < nt; ++tt) {
             const float hv = hs[tt * hpitch + i];
             const float2 h2 = make_float2(hv, hv);
@@ -394,16 +395,25 @@ __device__ __forceinline__ void head_reduce_body(int bid, const float* __restric
     const int e = bid * 32 + el;
     float s = 0.f;
     if (e < n) {
-        // four independent partial sums (chunks c, c+8, c+16, c+24 of this group's sequence): four loads in flight
-        // instead of a chain of dependent round trips; combined in a fixed order
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};
-        int c = grp;
-        for (; c + 24 < nchunks; c += 32) {
+        // sixteen independent partial sums (chunks c, c+8, ..., c+120 of this group's sequence): sixteen loads in flight
+        // instead of a chain of dependent round trips (512 partials per element at 8192 transitions: the chain WAS this
+        // launch's duration); combined in a fixed order
+        float s16[16];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) s4[u] += part[(size_t)(c + 8 * u) * n + e];
+        for (int u = 0; u < 16; ++u) s16[u] = 0.f;
+        int c = grp;
+        for (; c + 120 < nchunks; c += 128) {
+#pragma unroll
+            for (int u = 0; u < 16; ++u) s16[u] += part[(size_t)(c + 8 * u) * n + e];
         }
-        for (int u = 0; c < nchunks; c += 8, ++u) s4[u] += part[(size_t)c * n + e];
-        s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+#pragma unroll
+        for (int u = 0; u < 16; ++u)
+            if (c + 8 * u < nchunks) s16[u] += part[(size_t)(c + 8 * u) * n + e];
+#pragma unroll
+        for (int w = 8; w > 0; w >>= 1)
+#pragma unroll
+            for (int u = 0; u < w; ++u) s16[u] += s16[u + w];
+        s = s16[0];
     }
     red[grp][el] = s;
     __syncthreads();
@@ -697,18 +707,21 @@ __device__ __forceinline__ void conv_reduce_body(int j, int by, const float* __r
     }
     float s = 0.f;
     if (e < n) {
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four loads in flight (see head_reduce_body); fixed combination order
-        auto term = [&](int i) {
-            const int pi = i / nch_active, c = i - pi * nch_active;
+        // group g adds terms g, g + 8, ... (term i = (path lst[i / nch], chunk i % nch)); the (path, chunk) pair is advanced
+        // incrementally -- an integer division per term made this loop the launch's whole instruction count -- and four
+        // loads are kept in flight; the four partial sums are combined in a fixed order
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        const float* part_je = part + (size_t)j * n + e;
+        const size_t stride_pc = (size_t)nd.M * n;
+        const int dpi = 8 / nch_active, dc = 8 % nch_active;
+        int pi = grp / nch_active, c = grp % nch_active, u = 0;
+        for (int i = grp; i < nterms; i += 8) {
             const int p = staged ? lst_s[pi] : lst[pi];
-            return part[((size_t)(p * nch_alloc + c) * nd.M + j) * n + e];
-        };
-        int i = grp;
-        for (; i + 24 < nterms; i += 32) {
-#pragma unroll
-            for (int u = 0; u < 4; ++u) s4[u] += term(i + 8 * u);
+            s4[u] += part_je[(size_t)(p * nch_alloc + c) * stride_pc];
+            u = (u + 1) & 3;
+            pi += dpi; c += dc;
+            if (c >= nch_active) { c -= nch_active; ++pi; }
         }
-        for (int u = 0; i < nterms; i += 8, ++u) s4[u] += term(i);
         s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
     }
     red[grp][el] = s;
