@@ -900,8 +900,37 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     const int nch_simt = std::min(h->nch, std::max(1, (296 + P - 1) / P));
     const int cs = (B + nch_simt - 1) / nch_simt;
     int nch_active = (B + cs - 1) / cs;
+    // The partials of the middle conv layers and of the heads are complete before the first conv layer's weight-gradient
+    // kernel starts: their reduction runs on the side stream underneath it (that kernel is the longest of the step), and
+    // only layer 0's own partials are reduced after it.
+    bool early_done = false;
+    auto launch_reduce = [&](PnReduceJobs& jb, bool with_head, cudaStream_t rs) -> int {
+        int blk = 0;
+        for (int q = 0; q < jb.nconv; ++q) { jb.blk0[q] = blk; blk += nd.M * jb.nby[q]; }
+        const int nh = nd.hidden * (nd.A + 1) + nd.A + 1;
+        jb.head_blk0 = blk;
+        jb.head_nred = with_head ? (nh + 31) / 32 : 0;
+        jb.head_nchunks = h->head_ctas;               // one partial of the head weight gradient per CTA of the head kernel
+        const int nloss = (with_head && h->pending_loss) ? (P + 255) / 256 : 0;
+        if (blk + jb.head_nred + nloss == 0) return PN_OK;
+        PnProfScope prof(h, PN_PROF_HEAD_WGRAD, rs);
+        grad_reduce_kernel<<<blk + jb.head_nred + nloss, 256, 0, rs>>>(jb, nd, h->d_list, h->d_list_count, P, B, h->nch,
+                                                                      h->head_part, h->loss_t, h->pending_loss, h->grads);
+        if (with_head) h->pending_loss = nullptr;
+        PN_LAUNCH_CHECK(h, "grad_reduce_kernel");
+        return PN_OK;
+    };
     for (int l = nd.nconv - 1; l >= 0; --l) {
         const int npix = nd.OH[l] * nd.OW[l];
+        if (l == 0 && nd.nconv > 1 && !h->prof.on) {
+            // fork: everything launched so far on `st` has produced the partials below
+            PN_CUDA(h, cudaEventRecord(h->ev_fork, st));
+            PN_CUDA(h, cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+            if (int rc = launch_reduce(jobs, true, h->side)) return rc;
+            PN_CUDA(h, cudaEventRecord(h->ev_join, h->side));
+            jobs.nconv = 0;
+            early_done = true;
+        }
         if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
             int nch_used = 1;
             const bool wg_tc = pn_conv_mid_wgrad_tc_usable(h, l);
@@ -949,19 +978,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
             PN_LAUNCH_CHECK(h, "conv_dgrad_kernel");
         }
     }
-    {
-        int blk = 0;
-        for (int q = 0; q < jobs.nconv; ++q) { jobs.blk0[q] = blk; blk += nd.M * jobs.nby[q]; }
-        const int nh = nd.hidden * (nd.A + 1) + nd.A + 1;
-        jobs.head_blk0 = blk;
-        jobs.head_nred = (nh + 31) / 32;
-        jobs.head_nchunks = h->head_ctas;               // one partial of the head weight gradient per CTA of the head kernel
-        const int nloss = h->pending_loss ? (P + 255) / 256 : 0;
-        PnProfScope prof(h, PN_PROF_HEAD_WGRAD, st);
-        grad_reduce_kernel<<<blk + jobs.head_nred + nloss, 256, 0, st>>>(jobs, nd, h->d_list, h->d_list_count, P, B, h->nch,
-                                                                         h->head_part, h->loss_t, h->pending_loss, h->grads);
-        h->pending_loss = nullptr;
-        PN_LAUNCH_CHECK(h, "grad_reduce_kernel");
-    }
+    if (int rc = launch_reduce(jobs, !early_done, st)) return rc;
+    if (early_done) PN_CUDA(h, cudaStreamWaitEvent(st, h->ev_join, 0));
     return PN_OK;
 }
