@@ -78,6 +78,9 @@ typedef struct pn_config {
  * get_vars() order: kind 8 = W_lstm [512, 1024] (rows 0..255 input, 256..511 previous output; gate order i, j, f, o)
  * and kind 9 = b_lstm [1024]; neither is ever frozen.  Needs hidden = 256. */
 #define PN_FLAG_LSTM 16
+/* cfg.flags bit 6 (debug / comparison): keep every backward kernel on the caller's stream instead of running the middle
+ * conv layers' weight-gradient kernels on the handle's side stream beside the data-gradient chain. */
+#define PN_FLAG_SERIAL_BWD 64
 
 /* One row per trainable tensor, in get_vars() order with nothing frozen
  * (game_ac_network.py:239-253): for l<L-1, j<M: W_conv[l,j], b_conv[l,j];

@@ -903,7 +903,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     // The partials of the middle conv layers and of the heads are complete before the first conv layer's weight-gradient
     // kernel starts: their reduction runs on the side stream underneath it (that kernel is the longest of the step), and
     // only layer 0's own partials are reduced after it.
-    bool early_done = false;
+    bool early_done = false, side_used = false;
     auto launch_reduce = [&](PnReduceJobs& jb, bool with_head, cudaStream_t rs) -> int {
         int blk = 0;
         for (int q = 0; q < jb.nconv; ++q) { jb.blk0[q] = blk; blk += nd.M * jb.nby[q]; }
@@ -934,9 +934,19 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         if (l >= 1 && !(h->cfg.flags & 4) && pn_conv_mid_supported(h, l)) {
             int nch_used = 1;
             const bool wg_tc = pn_conv_mid_wgrad_tc_usable(h, l);
-            if (wg_tc)
-                if (int rc = pn_launch_conv_mid_wgrad_tc(h, l, B, st, &nch_used)) return rc;
             const bool dg_tc = pn_conv_mid_tc_has_bwd(h, l);
+            // The layer's weight gradient and data gradient both need only dact[l]: the weight gradient goes to the side
+            // stream and runs beside the data-gradient chain (they stress different units: MMA pipe vs converters / epilogue).
+            // With per-kernel timing on, everything stays on one stream so that the event pairs mean what they say.
+            cudaStream_t wst = st;
+            if (wg_tc && dg_tc && !h->prof.on && !(h->cfg.flags & PN_FLAG_SERIAL_BWD)) {
+                PN_CUDA(h, cudaEventRecord(h->ev_fork, st));
+                PN_CUDA(h, cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+                wst = h->side;
+                side_used = true;
+            }
+            if (wg_tc)
+                if (int rc = pn_launch_conv_mid_wgrad_tc(h, l, B, wst, &nch_used)) return rc;
             if (!wg_tc || !dg_tc)
                 if (int rc = pn_launch_conv_mid_bwd(h, l, B, st, &nch_used, !wg_tc, !dg_tc)) return rc;
             if (dg_tc)
@@ -977,6 +987,10 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
                                                    h->dact[l - 1]);
             PN_LAUNCH_CHECK(h, "conv_dgrad_kernel");
         }
+    }
+    if (side_used && !early_done) {                      // (cannot happen today: a middle layer implies nconv > 1)
+        PN_CUDA(h, cudaEventRecord(h->ev_join, h->side));
+        PN_CUDA(h, cudaStreamWaitEvent(st, h->ev_join, 0));
     }
     if (int rc = launch_reduce(jobs, !early_done, st)) return rc;
     if (early_done) PN_CUDA(h, cudaStreamWaitEvent(st, h->ev_join, 0));
