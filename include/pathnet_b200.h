@@ -195,7 +195,9 @@ PN_API int pn_stage_inputs_host(pn_handle* h, int slot, const void* frames_host,
  *     planes_host [P][B + C - 1][H][W] u8;  planes[p][0..C-1] = the channels of the rollout's first state (after a
  *     reset: C copies of the first frame), planes[p][C-1+i] = the frame observed after step i;
  *     frames[p][b][y][x][c] = planes[p][b + c][y][x].
- * 3.7x fewer bytes over PCIe at B = 32, C = 4.  Then call pn_train_step_staged as for pn_stage_inputs_host. */
+ * 3.7x fewer bytes over PCIe at B = 32, C = 4.  Then call pn_train_step_staged as for pn_stage_inputs_host.
+ * Every read of the host arrays is enqueued on `copy_stream` (once it has drained they may be reused); the stacks are
+ * rebuilt on a stream of the handle's own, a group of paths at a time, while the next group's planes are in flight. */
 PN_API int pn_stage_rollout_host(pn_handle* h, int slot, const uint8_t* planes_host, const int32_t* actions_host,
                                  const float* td_host, const float* r_host, int B, void* copy_stream);
 PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, float* loss_host, void* stream);

@@ -257,7 +257,9 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
         cudaFree(sl.frames); cudaFree(sl.planes); cudaFree(sl.actions); cudaFree(sl.td); cudaFree(sl.r); cudaFree(sl.loss);
         if (sl.copied) cudaEventDestroy(sl.copied);
         if (sl.consumed) cudaEventDestroy(sl.consumed);
+        for (auto& e : sl.part) if (e) cudaEventDestroy(e);
     }
+    if (h->stage_aux) cudaStreamDestroy(h->stage_aux);
     if (h->side) cudaStreamDestroy(h->side);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -573,13 +575,26 @@ extern "C" PN_API int pn_stage_rollout_host(pn_handle* h, int slot, const uint8_
         s.planes_bytes = pwant;
         h->workspace_bytes += (long long)pwant;
     }
+    if (!h->stage_aux) PN_CUDA(h, cudaStreamCreateWithFlags(&h->stage_aux, cudaStreamNonBlocking));
+    for (auto& e : s.part)
+        if (!e) PN_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     if (s.used) PN_CUDA(h, cudaStreamWaitEvent(cs, s.consumed, 0));
-    PN_CUDA(h, cudaMemcpyAsync(s.planes, planes_host, pbytes, cudaMemcpyHostToDevice, cs));
     PN_CUDA(h, cudaMemcpyAsync(s.actions, actions_host, T * sizeof(int32_t), cudaMemcpyHostToDevice, cs));
     PN_CUDA(h, cudaMemcpyAsync(s.td, td_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
     PN_CUDA(h, cudaMemcpyAsync(s.r, r_host, T * sizeof(float), cudaMemcpyHostToDevice, cs));
-    if (int rc = pn_launch_expand_planes(h, s.planes, B, (uint8_t*)s.frames, cs)) return rc;
-    PN_CUDA(h, cudaEventRecord(s.copied, cs));
+    // All host reads are on `cs`; the stacks of one group of paths are rebuilt on the auxiliary stream while the next
+    // group's planes cross PCIe.  `copied` (what pn_train_step_staged waits for) follows the last rebuild.
+    const size_t per_path = (size_t)(B + C - 1) * HW;
+    const int parts = h->P < PN_STAGE_PARTS ? h->P : PN_STAGE_PARTS;
+    for (int j = 0; j < parts; ++j) {
+        const int p0 = (int)((long long)h->P * j / parts), p1 = (int)((long long)h->P * (j + 1) / parts);
+        PN_CUDA(h, cudaMemcpyAsync(s.planes + p0 * per_path, planes_host + p0 * per_path, (p1 - p0) * per_path,
+                                   cudaMemcpyHostToDevice, cs));
+        PN_CUDA(h, cudaEventRecord(s.part[j], cs));
+        PN_CUDA(h, cudaStreamWaitEvent(h->stage_aux, s.part[j], 0));
+        if (int rc = pn_launch_expand_planes(h, s.planes, B, (uint8_t*)s.frames, p0, p1 - p0, h->stage_aux)) return rc;
+    }
+    PN_CUDA(h, cudaEventRecord(s.copied, h->stage_aux));
     s.B = B; s.is_u8 = 1; s.used = true;
     return PN_OK;
 }

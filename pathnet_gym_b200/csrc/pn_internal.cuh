@@ -60,6 +60,8 @@ struct PnProf {
     int count[PN_PROF_NSLOTS] = {};
 };
 
+#define PN_STAGE_PARTS 4
+
 struct pn_handle {
     pn_config cfg{};
     PnNetDesc nd{};
@@ -118,11 +120,13 @@ struct pn_handle {
     void* st_frames = nullptr; size_t st_frames_bytes = 0;
     int32_t* st_actions = nullptr; float* st_td = nullptr; float* st_r = nullptr; float* st_loss = nullptr;
     // double-buffered staging for the pipelined host path (pn_stage_inputs_host / pn_train_step_staged)
+    cudaStream_t stage_aux = nullptr;   // rebuilds the stacks of one group of paths while the next group crosses PCIe
     struct StageSlot {
         void* frames = nullptr; size_t frames_bytes = 0;
         uint8_t* planes = nullptr; size_t planes_bytes = 0;     // pn_stage_rollout_host: the rollout's unique planes
         int32_t* actions = nullptr; float* td = nullptr; float* r = nullptr; float* loss = nullptr;
         cudaEvent_t copied = nullptr, consumed = nullptr;
+        cudaEvent_t part[PN_STAGE_PARTS] = {};                  // pn_stage_rollout_host: one per group of paths copied
         bool used = false; int B = 0; int is_u8 = 1;
     } slot[2];
     long long workspace_bytes = 0;
@@ -216,7 +220,7 @@ inline const float* pn_head_input(const pn_handle* h) {      // what the two hea
     return h->lstm ? h->lstm_ws + (size_t)h->T * 1024 * 3 + (size_t)h->T * 256 * 2 : h->hbuf;
 }
 // pn_rollout.cu
-int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, cudaStream_t st);
+int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, int p0, int np, cudaStream_t st);
 // pn_rmsprop.cu
 int pn_launch_rmsprop(pn_handle* h, int first_tensor, int n_tensors, bool complement, float lr, float decay,
                       float momentum, float eps, float clip, cudaStream_t st);

@@ -83,11 +83,14 @@ expand_planes_kernel(const uint8_t* __restrict__ planes, int P, int B, int HW, i
 
 }  // namespace
 
-int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, cudaStream_t st) {
+// paths [p0, p0 + np) of the slot's plane and frame buffers
+int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, int p0, int np, cudaStream_t st) {
     const int HW = h->cfg.H * h->cfg.W, C = h->cfg.C;
     if (HW % 4) return pn_fail(h, PN_ERR_INVALID, "H*W = %d must be a multiple of 4", HW);
-    dim3 grid((HW / 4 + 255) / 256, h->P * B);
-    expand_planes_kernel<<<grid, 256, 0, st>>>(planes_dev, h->P, B, HW, C, frames_dev);
+    if (np <= 0) return PN_OK;
+    dim3 grid((HW / 4 + 255) / 256, np * B);
+    expand_planes_kernel<<<grid, 256, 0, st>>>(planes_dev + (size_t)p0 * (B + C - 1) * HW, np, B, HW, C,
+                                               frames_dev + (size_t)p0 * B * HW * C);
     PN_LAUNCH_CHECK(h, "expand_planes_kernel");
     return PN_OK;
 }
