@@ -208,9 +208,15 @@ PN_API int pn_train_step_staged(pn_handle* h, int slot, float entropy_beta, floa
  * the host can start summing that region over the GPUs while the rest of the step still runs:
  *   pn_lin_grads_region    -> offset / length (in floats) of the W_lin, b_lin region inside the gradient slab
  *   pn_stream_wait_lin_grads -> `stream` waits until the most recent pn_train_step* has written that region
- * The other two regions are complete when the step's stream work is. */
+ * The other two regions are complete when the step's stream work is -- and all of them except the first conv layer's
+ * tensors (the first *late_floats floats of the slab) already before that layer's weight-gradient kernel, the longest
+ * of the step, starts:
+ *   pn_stream_wait_early_grads -> `stream` waits until the most recent pn_train_step* has written every gradient
+ *                                 outside [0, *late_floats)  (late_floats may be NULL)
+ * No counterpart in the reference. */
 PN_API int pn_lin_grads_region(const pn_handle* h, int64_t* offset_floats, int64_t* count_floats);
 PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream);
+PN_API int pn_stream_wait_early_grads(pn_handle* h, void* stream, int64_t* late_floats);
 
 /* The exchange kernels wait for the other ranks' flags for at most 2 s; a rank that gives up records that in its own
  * exchange buffer and finishes (the sums of that step are then wrong).  This synchronising call reads the record:
@@ -227,6 +233,14 @@ PN_API int pn_peer_check(pn_handle* h, const void* my_peer_buf_dev);
  * counted PER SET OF BUFFERS (a fresh zeroed set starts again at 0), identical on all ranks.  No counterpart in the reference (single process per parameter server). */
 PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h);
 PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, void* stream);
+
+/* pn_peer_sum_small in two parts, so that only the first conv layer's gradients are exchanged after the step's last
+ * kernel: part 1 = the small regions outside [0, late_floats) (enqueue it on a stream that waits with
+ * pn_stream_wait_early_grads: it then runs underneath the first layer's weight-gradient kernel), part 2 = [0, late_floats)
+ * (on the compute stream after the step), part 0 = both (= pn_peer_sum_small).  Each part keeps its own flags in the
+ * exchange buffers and its own step count; a host uses either part 0 or parts 1 + 2 on one set of buffers. */
+PN_API int pn_peer_sum_part(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, int part,
+                            void* stream);
 
 /* All-reduce of the linear modules' gradient region (pn_lin_grads_region) in place over NVLink peer memory, for hosts
  * whose GRADIENT SLABS are themselves symmetric memory (peer_slabs_host[r] = rank r's slab base in this process,

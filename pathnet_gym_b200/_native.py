@@ -62,6 +62,8 @@ SIGNATURES = {
     "pn_peer_buffer_bytes": (C.c_int64, [_vp]),
     "pn_peer_check": (_i, [_vp, _vp]),
     "pn_peer_sum_small": (_i, [_vp, _vp, _i, _i, C.c_uint32, _vp]),
+    "pn_peer_sum_part": (_i, [_vp, _vp, _i, _i, C.c_uint32, _i, _vp]),
+    "pn_stream_wait_early_grads": (_i, [_vp, _vp, _vp]),
     "pn_peer_allreduce_lin": (_i, [_vp, _vp, _vp, _i, _i, C.c_uint32, _vp]),
     "pn_profile_enable": (_i, [_vp, _i]),
     "pn_profile_read": (_i, [_vp, C.POINTER(PnProfileEntry), _i]),

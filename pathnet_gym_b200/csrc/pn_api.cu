@@ -228,6 +228,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_lin_grads, cudaEventDisableTiming));
+    PN_TRYC(cudaEventCreateWithFlags(&h->ev_early_grads, cudaEventDisableTiming));
     // staging for the host-pointer entry point
     PN_TRY(dev_alloc(h, &h->st_actions, T));
     PN_TRY(dev_alloc(h, &h->st_td, T));
@@ -264,6 +265,7 @@ extern "C" PN_API void pn_destroy(pn_handle* h) {
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->ev_lin_grads) cudaEventDestroy(h->ev_lin_grads);
+    if (h->ev_early_grads) cudaEventDestroy(h->ev_early_grads);
     for (auto& e : h->prof.ev) cudaEventDestroy(e);
     delete h;
 }
@@ -416,6 +418,16 @@ extern "C" PN_API int pn_stream_wait_lin_grads(pn_handle* h, void* stream) {
     if (!h) return pn_fail_global(PN_ERR_INVALID, "pn_stream_wait_lin_grads: null handle");
     PN_CUDA(h, cudaSetDevice(h->cfg.device));
     PN_CUDA(h, cudaStreamWaitEvent((cudaStream_t)stream, h->ev_lin_grads, 0));
+    return PN_OK;
+}
+
+long long pn_late_grads_floats(const pn_handle* h) { return h->nd.nconv > 1 ? h->nd.convW_base[1] : h->nd.linW_base; }
+
+extern "C" PN_API int pn_stream_wait_early_grads(pn_handle* h, void* stream, int64_t* late_floats) {
+    if (!h) return pn_fail_global(PN_ERR_INVALID, "pn_stream_wait_early_grads: null handle");
+    PN_CUDA(h, cudaSetDevice(h->cfg.device));
+    PN_CUDA(h, cudaStreamWaitEvent((cudaStream_t)stream, h->ev_early_grads, 0));
+    if (late_floats) *late_floats = pn_late_grads_floats(h);
     return PN_OK;
 }
 

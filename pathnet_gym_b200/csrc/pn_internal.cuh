@@ -107,6 +107,7 @@ struct pn_handle {
     int max_active[PN_MAX_LAYERS] = {}; // largest number of active modules of any path, per layer (from pn_set_genotypes)
     cudaStream_t side = nullptr;        // weight-operand preparation runs here, beside the first conv layer
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaEvent_t ev_early_grads = nullptr;   // every gradient except the first conv layer's is final (see pn_stream_wait_early_grads)
     cudaEvent_t ev_lin_grads = nullptr; // recorded after the linear weight-gradient launch of every training step
     bool absmax_fused = false;          // the layer-1 data-gradient launch of this step already wrote max |dY0|
     bool tc_conv0 = false;              // geometry supported and not disabled by cfg.flags bit 0
@@ -220,6 +221,7 @@ inline const float* pn_head_input(const pn_handle* h) {      // what the two hea
     return h->lstm ? h->lstm_ws + (size_t)h->T * 1024 * 3 + (size_t)h->T * 256 * 2 : h->hbuf;
 }
 // pn_rollout.cu
+long long pn_late_grads_floats(const pn_handle* h);   // floats at the start of the slab that ev_early_grads does not cover
 int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, int p0, int np, cudaStream_t st);
 // pn_rmsprop.cu
 int pn_launch_rmsprop(pn_handle* h, int first_tensor, int n_tensors, bool complement, float lr, float decay,

@@ -928,6 +928,7 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
             PN_CUDA(h, cudaStreamWaitEvent(h->side, h->ev_fork, 0));
             if (int rc = launch_reduce(jobs, true, h->side)) return rc;
             PN_CUDA(h, cudaEventRecord(h->ev_join, h->side));
+            PN_CUDA(h, cudaEventRecord(h->ev_early_grads, h->side));
             jobs.nconv = 0;
             early_done = true;
         }
@@ -994,5 +995,6 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
     }
     if (int rc = launch_reduce(jobs, !early_done, st)) return rc;
     if (early_done) PN_CUDA(h, cudaStreamWaitEvent(st, h->ev_join, 0));
+    else PN_CUDA(h, cudaEventRecord(h->ev_early_grads, st));
     return PN_OK;
 }

@@ -8,7 +8,8 @@
 // for the peers' flags, and adds up all copies itself in rank order -- one launch, and bit-identical on every rank.
 //
 //   exchange buffer of a rank: [256 x u32 control words][slot 0: n floats][slot 1: n floats]
-//   control words: [0..31] flags of the small-region sum, [32] its CTA counter;
+//   control words: [0..31] flags of the small-region sum, [32] its CTA counter ([136..151], [152] and [160..175], [176] for its
+//                  early and late parts when the sum is split: pn_peer_sum_part);
 //                  [64..95] / [96..127] "gradients ready" / "sums written" flags of the linear-region all-reduce, [128] its CTA counter
 //   flags[r] = number of steps rank r has published (monotonic).  Step s uses slot s & 1: a rank publishes step s + 1 only
 //   after it has finished reading every peer's step-s slot, and nobody can overwrite slot s & 1 (step s + 2) before all
@@ -69,14 +70,21 @@ __device__ __forceinline__ long long small_index(int e, long long lin_off, long 
 }
 
 __global__ void __launch_bounds__(256)
-peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long lin_cnt, int n, PeerPtrs peers, int rank, int world,
-                      unsigned step) {
+peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long lin_cnt, int n, int e_lo, int e_hi, int flag_word,
+                      int counter_word, PeerPtrs peers, int rank, int world, unsigned step) {
+    // elements [e_lo, e_hi) of the small set; flags and the CTA counter of this part at control words flag_word / counter_word
     const int slot = step & 1u;
-    unsigned* cta_counter = reinterpret_cast<unsigned*>(peers.buf[rank]) + 32;   // lives in the buffer: one count per buffer
+    unsigned* cta_counter = reinterpret_cast<unsigned*>(peers.buf[rank]) + counter_word;   // lives in the buffer: one count per buffer
     float* mine = reinterpret_cast<float*>(peers.buf[rank]) + kPeerFlagWords + (size_t)slot * n;
     const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
-    // A: publish my values
-    for (int e = tid; e < n; e += nthreads) mine[e] = grads[small_index(e, lin_off, lin_cnt)];
+    // A: publish my values (16 bytes per thread when the regions allow it: n, lin_off, lin_cnt multiples of 4)
+    const bool vec = ((n | lin_off | lin_cnt | e_lo | e_hi) & 3) == 0;
+    if (vec) {
+        for (int e = e_lo + tid * 4; e < e_hi; e += nthreads * 4)
+            *reinterpret_cast<float4*>(mine + e) = *reinterpret_cast<const float4*>(grads + small_index(e, lin_off, lin_cnt));
+    } else {
+        for (int e = e_lo + tid; e < e_hi; e += nthreads) mine[e] = grads[small_index(e, lin_off, lin_cnt)];
+    }
     __threadfence_system();
     __syncthreads();
     __shared__ unsigned last;
@@ -85,21 +93,47 @@ peer_sum_small_kernel(float* __restrict__ grads, long long lin_off, long long li
     if (last) __threadfence_system();     // every CTA's values (fenced before its atomicAdd) are ordered before the flag
     if (last && threadIdx.x < world) {
         // the last CTA to finish writing raises my flag on every rank (including myself)
-        unsigned* f = reinterpret_cast<unsigned*>(peers.buf[threadIdx.x]) + rank;
+        unsigned* f = reinterpret_cast<unsigned*>(peers.buf[threadIdx.x]) + flag_word + rank;
         st_release_sys(f, step + 1u);
     }
     // B: wait until every rank has published this step
     if (threadIdx.x < world) {
         unsigned* mine_ctrl = reinterpret_cast<unsigned*>(peers.buf[rank]);
-        wait_flag(mine_ctrl + threadIdx.x, step + 1u, mine_ctrl + kPeerErrWord, 1u);
+        wait_flag(mine_ctrl + flag_word + threadIdx.x, step + 1u, mine_ctrl + kPeerErrWord, 1u);
     }
     __syncthreads();
-    // C: fixed-order sum over the ranks
-    for (int e = tid; e < n; e += nthreads) {
-        float s = 0.f;
-        for (int r = 0; r < world; ++r)
-            s += ld_peer(reinterpret_cast<const float*>(peers.buf[r]) + kPeerFlagWords + (size_t)slot * n + e);
-        grads[small_index(e, lin_off, lin_cnt)] = s;
+    // C: fixed-order sum over the ranks.  All ranks' loads are issued before the first add (an NVLink round trip is
+    // ~2 us: summing rank by rank would pay it `world` times per element).
+    if (vec) {
+        for (int e = e_lo + tid * 4; e < e_hi; e += nthreads * 4) {
+            float4 v[kPeerMaxWorld];
+#pragma unroll
+            for (int r = 0; r < kPeerMaxWorld; ++r) {
+                v[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (r < world)
+                    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(v[r].x), "=f"(v[r].y), "=f"(v[r].z), "=f"(v[r].w)
+                                 : "l"(reinterpret_cast<const float*>(peers.buf[r]) + kPeerFlagWords + (size_t)slot * n + e)
+                                 : "memory");
+            }
+            float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int r = 0; r < kPeerMaxWorld; ++r)
+                if (r < world) { s4.x += v[r].x; s4.y += v[r].y; s4.z += v[r].z; s4.w += v[r].w; }
+            *reinterpret_cast<float4*>(grads + small_index(e, lin_off, lin_cnt)) = s4;
+        }
+    } else {
+        for (int e = e_lo + tid; e < e_hi; e += nthreads) {
+            float v[kPeerMaxWorld];
+#pragma unroll
+            for (int r = 0; r < kPeerMaxWorld; ++r)
+                v[r] = r < world ? ld_peer(reinterpret_cast<const float*>(peers.buf[r]) + kPeerFlagWords + (size_t)slot * n + e) : 0.f;
+            float s1 = 0.f;
+#pragma unroll
+            for (int r = 0; r < kPeerMaxWorld; ++r)
+                if (r < world) s1 += v[r];
+            grads[small_index(e, lin_off, lin_cnt)] = s1;
+        }
     }
 }
 
@@ -213,19 +247,38 @@ extern "C" PN_API int64_t pn_peer_buffer_bytes(const pn_handle* h) {
     return (int64_t)(kPeerFlagWords * 4 + 2 * n * 4);
 }
 
-extern "C" PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step,
-                                        void* stream) {
-    if (!h || !peer_bufs_host) return pn_fail_global(PN_ERR_INVALID, "pn_peer_sum_small: null argument");
+namespace {
+// part 0: all small regions; part 1: those final before the first conv layer's weight-gradient kernel (middle conv layers,
+// heads, LSTM); part 2: the first conv layer's tensors.  Each part has its own flags and CTA counter.
+int launch_peer_sum(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, int part, cudaStream_t st) {
+    if (!h || !peer_bufs_host) return pn_fail_global(PN_ERR_INVALID, "pn_peer_sum: null argument");
     if (world < 1 || world > kPeerMaxWorld || rank < 0 || rank >= world)
-        return pn_fail(h, PN_ERR_INVALID, "pn_peer_sum_small: rank %d of %d (at most %d ranks)", rank, world, kPeerMaxWorld);
+        return pn_fail(h, PN_ERR_INVALID, "pn_peer_sum: rank %d of %d (at most %d ranks)", rank, world, kPeerMaxWorld);
+    if (part < 0 || part > 2) return pn_fail(h, PN_ERR_INVALID, "pn_peer_sum: part %d (0, 1 or 2)", part);
     if (!h->grads) return pn_fail(h, PN_ERR_STATE, "gradient slab not bound");
     const long long lin_off = h->nd.linW_base, lin_cnt = h->nd.fc2W - h->nd.linW_base;
     const int n = (int)(h->slab_floats - lin_cnt);
+    const int late = (int)pn_late_grads_floats(h);
+    const int e_lo = part == 1 ? late : 0, e_hi = part == 2 ? late : n;
+    if (e_hi <= e_lo) return PN_OK;
+    static const int kFlagWord[3] = {0, 136, 160}, kCounterWord[3] = {32, 152, 176};
     PeerPtrs pp;
     for (int r = 0; r < kPeerMaxWorld; ++r) pp.buf[r] = r < world ? peer_bufs_host[r] : 0;
-    if (world > 32) return pn_fail(h, PN_ERR_INVALID, "pn_peer_sum_small: at most 32 ranks");
-    const int grid = std::max(1, std::min(h->num_sms / 4, (n + 1023) / 1024));      // a function of the handle only: the same every step
-    peer_sum_small_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(h->grads, lin_off, lin_cnt, n, pp, rank, world, step);
+    // a function of the handle and the part only: the same every step (the CTA counter relies on it)
+    const int grid = std::max(1, std::min(h->num_sms / 2, (e_hi - e_lo + 1023) / 1024));
+    peer_sum_small_kernel<<<grid, 256, 0, st>>>(h->grads, lin_off, lin_cnt, n, e_lo, e_hi, kFlagWord[part], kCounterWord[part], pp,
+                                                rank, world, step);
     PN_LAUNCH_CHECK(h, "peer_sum_small_kernel");
     return PN_OK;
+}
+}  // namespace
+
+extern "C" PN_API int pn_peer_sum_small(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step,
+                                        void* stream) {
+    return launch_peer_sum(h, peer_bufs_host, rank, world, step, 0, (cudaStream_t)stream);
+}
+
+extern "C" PN_API int pn_peer_sum_part(pn_handle* h, const uint64_t* peer_bufs_host, int rank, int world, uint32_t step, int part,
+                                       void* stream) {
+    return launch_peer_sum(h, peer_bufs_host, rank, world, step, part, (cudaStream_t)stream);
 }

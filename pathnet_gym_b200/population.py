@@ -289,6 +289,13 @@ class PathNetPopulation:
         arr = (C.c_uint64 * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
         nat.check(self.lib.pn_peer_sum_small(self._h, arr, int(rank), int(world), int(step), self._stream()), self._h)
 
+    def peer_sum_part(self, peer_ptrs, rank, world, step, part):
+        """One part of peer_sum_small (pn_peer_sum_part): 1 = the regions final before the first conv layer's weight
+        gradient, 2 = that layer's own tensors."""
+        import ctypes as C
+        arr = (C.c_uint64 * len(peer_ptrs))(*[int(p) for p in peer_ptrs])
+        nat.check(self.lib.pn_peer_sum_part(self._h, arr, int(rank), int(world), int(step), int(part), self._stream()), self._h)
+
     def peer_allreduce_lin(self, peer_slabs, peer_ptrs, rank, world, step):
         """Linear-module gradient region <- sum over the node's GPUs, in place through peer memory (pn_peer_allreduce_lin)."""
         import ctypes as C
@@ -306,6 +313,14 @@ class PathNetPopulation:
         """`stream` waits until the latest train_step has written the W_lin/b_lin gradients."""
         import ctypes as C
         nat.check(self.lib.pn_stream_wait_lin_grads(self._h, C.c_void_p(stream.cuda_stream)), self._h)
+
+    def stream_wait_early_grads(self, stream: "torch.cuda.Stream"):
+        """`stream` waits until the latest train_step has written every gradient except the first conv layer's; returns
+        the number of floats at the start of the slab that are NOT covered (that layer's tensors)."""
+        import ctypes as C
+        late = C.c_int64(0)
+        nat.check(self.lib.pn_stream_wait_early_grads(self._h, C.c_void_p(stream.cuda_stream), C.byref(late)), self._h)
+        return int(late.value)
 
     def apply_gradients(self, lr, decay=0.99, momentum=0.0, epsilon=0.1, clip_norm=40.0):
         """Per-tensor clip_by_norm + RMSProp on the non-frozen tensors (rmsprop_applier.py:79-106)."""

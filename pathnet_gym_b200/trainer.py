@@ -10,6 +10,7 @@ class OverlappedGradSum(object):
     small regions (conv, heads) follow on the compute stream."""
 
     def __init__(self, pop):
+        import os
         import torch
         self.pop = pop
         self.active = parallel.world()[1] > 1
@@ -17,6 +18,8 @@ class OverlappedGradSum(object):
         g = pop.grads
         self.lin, self.head, self.conv = g[off:off + cnt], g[off + cnt:], g[:off]
         self.comm = torch.cuda.Stream(device=pop.device)
+        self.comm_early = torch.cuda.Stream(device=pop.device)
+        self.split = os.environ.get("PN_PEER_SPLIT", "0") == "1"      # PN_PEER_SPLIT=1: exchange all but the first layer early
         self.peer = None
         self.peer_slabs = None
         self.step = 0
@@ -69,7 +72,10 @@ class OverlappedGradSum(object):
         """Which exchange runs (for the bench line): nothing at one GPU; else the two regions' mechanisms."""
         if not self.active:
             return "none (1 GPU)"
-        small = "peer-memory kernel (pn_peer_sum_small)" if self.peer is not None else "NCCL all-reduce (grouped)"
+        small = "NCCL all-reduce (grouped)"
+        if self.peer is not None:
+            small = "peer-memory kernel, middle conv + heads underneath the first layer's weight gradient, first layer " \
+                    "after the step (pn_peer_sum_part)" if self.split else "peer-memory kernel (pn_peer_sum_small)"
         lin = "peer-memory kernel (pn_peer_allreduce_lin)" if (self.peer is not None and self.peer_slabs is not None) \
             else "NCCL all-reduce on a side stream"
         err = getattr(self, "peer_error", None)
@@ -94,7 +100,17 @@ class OverlappedGradSum(object):
             return
         if self.peer is not None:
             rank, world = parallel.world()
-            self.pop.peer_sum_small(self.peer, rank, world, self.step)
+            if self.split:
+                import torch
+                # everything but the first conv layer's tensors is final before that layer's weight-gradient kernel:
+                # that part is exchanged on its own stream underneath it, only the rest after the step
+                self.pop.stream_wait_early_grads(self.comm_early)
+                with torch.cuda.stream(self.comm_early):
+                    self.pop.peer_sum_part(self.peer, rank, world, self.step, 1)
+                self.pop.peer_sum_part(self.peer, rank, world, self.step, 2)
+                torch.cuda.current_stream(self.pop.device).wait_stream(self.comm_early)
+            else:
+                self.pop.peer_sum_small(self.peer, rank, world, self.step)
             self.step += 1
             return
         import torch.distributed as dist
