@@ -593,8 +593,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
 // priority).  With 8 quantiser warps the MMA warp waited for quantised operands 58 % of the time.
 // =====================================================================================================
 constexpr int kWgDigits = 3;
-constexpr int kWgQuantWarps = 16;                // one raster row per quantiser thread (mq <= 512)
-constexpr int kWgThreads = (kWgQuantWarps + 6) * 32;
+constexpr int kWgQuantWarps = 16;                // at most: one raster row per quantiser thread (mq <= 512)
 constexpr int kWgSetCols = 256;                  // TMEM columns per accumulator set: two accumulators of 128
 constexpr int kWgAccCols = 128;
 
@@ -627,7 +626,10 @@ struct WgGeom {
     int region_q;         // mq * 16: one 16-column group of dq
 };
 
-__global__ void __launch_bounds__(kWgThreads, 1)
+// QW = quantiser warps: 14 cover the 84x84 frame's 448 raster rows; then the block has 20 warps and 96 registers per thread
+// (22 warps are allocated as 24: 80 registers, at which the quantisers had no room to keep their loads in flight).
+template <int QW>
+__global__ void __launch_bounds__((QW + 6) * 32, 1)
 conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ dY, const uint8_t* __restrict__ R,
                       const unsigned* __restrict__ absmax, PnNetDesc nd, const uint32_t* __restrict__ masks, int B,
                       int P, int cs, int nch, int nch_alloc, TcGeom gm, WgGeom wg, float* __restrict__ part, long long* __restrict__ dbg) {
@@ -659,18 +661,18 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
         for (int i = 0; i < 2; ++i) {
             mbar_init(&frame_full[i], 1); mbar_init(&frame_empty[i], 1);
             // one arrival per WARP (after __syncwarp): 512 threads arriving on one barrier serialise on its shared-memory word
-            mbar_init(&dq_full[i], kWgQuantWarps); mbar_init(&dq_empty[i], 1);
+            mbar_init(&dq_full[i], QW); mbar_init(&dq_empty[i], 1);
             mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4);
         }
         fence_mbar_init();
     }
-    if (warp == kWgQuantWarps + 5) tmem_alloc(&tmem_base_s, 512);
+    if (warp == QW + 5) tmem_alloc(&tmem_base_s, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
 
-    if (warp == kWgQuantWarps + 4) {
+    if (warp == QW + 4) {
         // ================= frame producer: two copies per frame (see above) =================
         if (lane == 0) tma_prefetch_desc(&tmap);
         int stage = 0;
@@ -694,7 +696,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                     if (++stage == 2) { stage = 0; phase ^= 1; }
                 }
         }
-    } else if (warp == kWgQuantWarps + 5) {
+    } else if (warp == QW + 5) {
         // ================= MMA issue =================
         // whole-warp, warp-uniform code; only the tcgen05 instructions are elected to one lane
         int stage = 0;
@@ -755,7 +757,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
             dbg[blockIdx.x * 8 + 0] = m_wframe; dbg[blockIdx.x * 8 + 1] = m_wdq; dbg[blockIdx.x * 8 + 2] = m_wacc;
             dbg[blockIdx.x * 8 + 3] = pinned_clock() - t_entry;
         }
-    } else if (warp >= kWgQuantWarps) {
+    } else if (warp >= QW) {
         // ================= flush: TMEM lane = accumulator row = (dx, g, byte) =================
         const int quad = warp & 3;
         const int r = quad * 32 + lane;                         // 0..127
@@ -810,7 +812,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 ++nacc;
             }
         }
-        if (dbg8 && threadIdx.x == kWgQuantWarps * 32) { dbg[blockIdx.x * 8 + 5] = f_wait; dbg[blockIdx.x * 8 + 6] = f_work; }
+        if (dbg8 && threadIdx.x == QW * 32) { dbg[blockIdx.x * 8 + 5] = f_wait; dbg[blockIdx.x * 8 + 6] = f_work; }
     } else {
         // ================= quantise dq per transition; bias-gradient partials per (item, pass) =================
         const int m = threadIdx.x;                             // this thread's raster row, 0..511 (rows >= mq: nothing to do)
@@ -845,24 +847,29 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                 // Software pipeline over the transitions: the loads of transition b + 1 are issued before transition b is
                 // processed.  All quantiser warps run in lock step (they meet at the ring's barriers), so without this
                 // every warp sat out the same L2 round trip once per transition.
+                // (The mask bytes stay in their own registers until the next iteration: any arithmetic on a loaded value right
+                // here -- the shift that packs them was the top stall of the kernel -- makes the warp wait for the load.)
                 float4 ga_n = make_float4(0.f, 0.f, 0.f, 0.f), gb_n = ga_n;
-                uint32_t rb_n = 0;
+                uint32_t rraw_n[kPassSlots];
                 auto fetch = [&](int b) {
                     ga_n = gb_n = make_float4(0.f, 0.f, 0.f, 0.f);
-                    rb_n = 0;
+#pragma unroll
+                    for (int sl = 0; sl < kPassSlots; ++sl) rraw_n[sl] = 0;
                     if (valid) {
                         const size_t t = (size_t)p * B + b;
                         const float4* g4 = reinterpret_cast<const float4*>(dY + (t * npix + pix) * PN_F);
                         ga_n = __ldg(g4); gb_n = __ldg(g4 + 1);
 #pragma unroll
                         for (int sl = 0; sl < kPassSlots; ++sl)
-                            if (sl < nsl) rb_n |= (uint32_t)__ldg(R + (t * nd.M + jl[sl]) * npix + pix) << (8 * sl);
+                            if (sl < nsl) rraw_n[sl] = __ldg(R + (t * nd.M + jl[sl]) * npix + pix);
                     }
                 };
                 fetch(b_lo);
                 for (int b = b_lo; b < b_hi; ++b) {
                     const float4 ga = ga_n, gb = gb_n;
-                    const uint32_t rb = rb_n;
+                    uint32_t rb = 0;
+#pragma unroll
+                    for (int sl = 0; sl < kPassSlots; ++sl) rb |= rraw_n[sl] << (8 * sl);
                     if (b + 1 < b_hi) fetch(b + 1);
                     const long long cq = dbg8 ? pinned_clock() : 0;
                     mbar_wait(&dq_empty[stage], phase ^ 1);
@@ -925,13 +932,13 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
                         for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
                         if (lane == sl * 8 + c) mine = v;
                     }
-                asm volatile("bar.sync 1, %0;" ::"n"(kWgQuantWarps * 32) : "memory");   // the previous (item, pass) has been read out of bias_s
+                asm volatile("bar.sync 1, %0;" ::"n"(QW * 32) : "memory");   // the previous (item, pass) has been read out of bias_s
                 bias_s[warp * 32 + lane] = mine;
-                asm volatile("bar.sync 1, %0;" ::"n"(kWgQuantWarps * 32) : "memory");
+                asm volatile("bar.sync 1, %0;" ::"n"(QW * 32) : "memory");
                 if (threadIdx.x < nsl * 8) {
                     float sacc = 0.f;
 #pragma unroll
-                    for (int q = 0; q < kWgQuantWarps; ++q) sacc += bias_s[q * 32 + threadIdx.x];
+                    for (int q = 0; q < QW; ++q) sacc += bias_s[q * 32 + threadIdx.x];
                     part[((size_t)(p * nch_alloc + ch) * nd.M + jl[threadIdx.x >> 3]) * stride_part + (size_t)nd.KK[0] * PN_F + (threadIdx.x & 7)] = sacc;
                 }
             }
@@ -943,7 +950,7 @@ conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __r
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == kWgQuantWarps + 5) tmem_dealloc(td, 512);
+    if (warp == QW + 5) tmem_dealloc(td, 512);
 }
 
 bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
@@ -973,7 +980,7 @@ bool make_geom(const pn_handle* h, TcGeom& g, size_t& smem_bytes) {
     if (g.row_bytes % 16 || g.row_bytes / 4 > 256 || g.Hs > 256) return false;
     const size_t fixed = (size_t)(nd.M + 1) * kSlotBytes + (size_t)nd.M * 32 * sizeof(float) +
                          (size_t)(nd.M + 2) * sizeof(int) + 64 * sizeof(uint64_t);
-    for (g.nst = 3; g.nst >= 2; --g.nst) {
+    for (g.nst = 3; g.nst >= 2; --g.nst) {      // (5 stages measured no faster: the frame loads are not the limit)
         smem_bytes = (size_t)g.nst * g.stage_bytes + fixed;
         if (smem_bytes <= 220 * 1024) return true;
     }
@@ -1141,15 +1148,21 @@ int pn_launch_conv0_wgrad_tc(pn_handle* h, const uint8_t* frames, int B, cudaStr
     }
     if (best_eff < 0) return pn_fail(h, PN_ERR_STATE, "no valid chunking for the conv0 weight-gradient kernel");
     const int nch = best_nch, cs = (B + nch - 1) / nch;
-    PN_SET_SMEM(h, conv0_wgrad_tc_kernel, smem_bytes);
+    const bool narrow = g.mq <= 14 * 32;
+    if (narrow) PN_SET_SMEM(h, conv0_wgrad_tc_kernel<14>, smem_bytes);
+    else PN_SET_SMEM(h, conv0_wgrad_tc_kernel<kWgQuantWarps>, smem_bytes);
     const int items = P * nch;
     const int grid = std::min(std::min(items, h->num_sms), kMaxCtas);
     CUtensorMap tmap;
     if (int rc = make_frame_tmap(h, g, frames, T, &tmap, 1)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_WGRAD + 0, st);
-        conv0_wgrad_tc_kernel<<<grid, kWgThreads, smem_bytes, st>>>(tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
-                                                                   B, P, cs, nch, h->nch, g, wg, h->wpart[0], h->tc_dbg);
+        if (narrow)
+            conv0_wgrad_tc_kernel<14><<<grid, (14 + 6) * 32, smem_bytes, st>>>(tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks,
+                                                                             B, P, cs, nch, h->nch, g, wg, h->wpart[0], h->tc_dbg);
+        else
+            conv0_wgrad_tc_kernel<kWgQuantWarps><<<grid, (kWgQuantWarps + 6) * 32, smem_bytes, st>>>(
+                tmap, h->dact[0], h->rmask[0], absmax, nd, h->d_masks, B, P, cs, nch, h->nch, g, wg, h->wpart[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_wgrad_tc_kernel");
     h->last_wgrad_nch = nch;
