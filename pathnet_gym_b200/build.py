@@ -43,6 +43,9 @@ def build_library(force=False, verbose=False):
            "-I", os.path.join(ROOT, "include"), "-I", CSRC]
     if verbose:
         cmd += ["-Xptxas", "-v"]
+    # PN_BUILD_DEFINES="PN_TC_DEBUG_BUILD": compile the role-timing instrumentation of the tensor-core kernels in
+    # (read with PN_TC_DEBUG=<mode> at run time; off in the product build: predicated-off instructions still take issue slots)
+    cmd += ["-D" + d for d in os.environ.get("PN_BUILD_DEFINES", "").split() if d]
     cmd += sources()
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:

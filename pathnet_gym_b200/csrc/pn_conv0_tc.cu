@@ -150,7 +150,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1)
 conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __restrict__ w8,
                     const float* __restrict__ wscale, const float* __restrict__ params, PnNetDesc nd,
                     const uint32_t* __restrict__ masks, int B, int T, TcGeom gm, const __grid_constant__ TcBounds bounds,
-                    float* __restrict__ Y, uint8_t* __restrict__ R, long long* __restrict__ dbg) {
+                    float* __restrict__ Y, uint8_t* __restrict__ R, long long* __restrict__ dbg_arg) {
+    long long* const dbg = kTcDebugBuild ? dbg_arg : nullptr;   // the instrumentation below compiles away in the product build
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* frame_s = smem;
     uint8_t* Bs = smem + (size_t)gm.nst * gm.stage_bytes;
@@ -632,7 +633,8 @@ template <int QW>
 __global__ void __launch_bounds__((QW + 6) * 32, 1)
 conv0_wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmap, const float* __restrict__ dY, const uint8_t* __restrict__ R,
                       const unsigned* __restrict__ absmax, PnNetDesc nd, const uint32_t* __restrict__ masks, int B,
-                      int P, int cs, int nch, int nch_alloc, TcGeom gm, WgGeom wg, float* __restrict__ part, long long* __restrict__ dbg) {
+                      int P, int cs, int nch, int nch_alloc, TcGeom gm, WgGeom wg, float* __restrict__ part, long long* __restrict__ dbg_arg) {
+    long long* const dbg = kTcDebugBuild ? dbg_arg : nullptr;   // the instrumentation below compiles away in the product build
     const bool dbg8 = dbg && dbg[148 * 8] == 8;                 // PN_TC_DEBUG=8: where the weight-gradient kernel's roles wait
     const long long t_entry = dbg8 ? pinned_clock() : 0;
     extern __shared__ __align__(1024) uint8_t smem[];

@@ -7,6 +7,15 @@
 // for 1-byte elements (16 elements per 16-byte row of a core matrix).
 #pragma once
 #include <cuda_runtime.h>
+
+// -DPN_TC_DEBUG_BUILD (PN_BUILD_DEFINES=PN_TC_DEBUG_BUILD python pathnet_gym_b200/build.py) compiles the kernels' role-timing
+// instrumentation in; PN_TC_DEBUG=<mode> then selects what it records (tools/wg_debug.py, tools/fwd_debug.py).
+#ifdef PN_TC_DEBUG_BUILD
+constexpr bool kTcDebugBuild = true;
+#else
+constexpr bool kTcDebugBuild = false;
+#endif
+
 #include <stdint.h>
 
 namespace pntc {
