@@ -510,17 +510,26 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                         mbar_arrive(&acc_empty[acc]);
                         continue;
                     }
-#pragma unroll 1
-                    for (int sl = 0; sl < nsl; ++sl) {
+                    // This loop is the kernel: the epilogue warps are issue-bound (ncu: 2.6 of 4 warp instructions per cycle
+                    // and SM).  It is unrolled over the pass's slots so that the TMEM column, the scale / bias rows and the
+                    // module index are immediates off per-tile bases, and it spends 5 instructions per digit triple:
+                    // lo = d1 * 256 + d0 stays inside int32 (|d| <= 256 * 255 * 128, so |lo| < 2^31) and costs one LEA
+                    // instead of a conversion and an fma; two conversions, fma(d2, 65536, lo), fma(.., scale, bias).
+                    uint8_t* const rrow = R + (size_t)t * nd.M * npix + pix;
+                    const float* const sbp = sbuf + pass * kPassSlots * 32;
+                    const int* const jtp = jtab + pass * kPassSlots;
+#pragma unroll
+                    for (int sl = 0; sl < kPassSlots; ++sl) {
+                        if (sl >= nsl) break;
                         uint32_t d0[8], d1[8], d2[8];
                         tmem_ld8(tbase + sl * 24, d0);
                         tmem_ld8(tbase + sl * 24 + 8, d1);
                         tmem_ld8(tbase + sl * 24 + 16, d2);
-                        const int slot = pass * kPassSlots + sl;
-                        const float4* sb = reinterpret_cast<const float4*>(sbuf + slot * 32);
+                        const float4* sb = reinterpret_cast<const float4*>(sbp + sl * 32);
                         float s0[8], bi[8];
                         *reinterpret_cast<float4*>(&s0[0]) = sb[0]; *reinterpret_cast<float4*>(&s0[4]) = sb[1];
                         *reinterpret_cast<float4*>(&bi[0]) = sb[2]; *reinterpret_cast<float4*>(&bi[4]) = sb[3];
+                        const int j = jtp[sl];
                         tmem_ld_wait();
                         if (dbg_epi) { const long long c = pinned_clock(); e_ld += c - e_t0; e_t0 = c; }
                         if (sl == nsl - 1) {        // last read of this accumulator stage: hand it back to the MMA warp
@@ -530,14 +539,12 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                         unsigned bits = 0;
 #pragma unroll
                         for (int c = 0; c < 8; ++c) {
-                            // |D| < 2^24: the int -> float conversions are exact; Horner over the base-256 digits with
-                            // immediate multipliers, one rounding (2^-24 relative) per fma
-                            float acc = fmaf((float)(int)d2[c], 256.0f, (float)(int)d1[c]);
-                            acc = fmaf(acc, 256.0f, (float)(int)d0[c]);
+                            const int lo = (int)d1[c] * 256 + (int)d0[c];
+                            const float acc = fmaf((float)(int)d2[c], 65536.0f, (float)lo);
                             const float pre = fmaf(acc, s0[c], bi[c]);
                             if (pre > 0.f) { sum[c] += pre; bits |= 1u << c; }
                         }
-                        if (valid) R[((size_t)t * nd.M + jtab[slot]) * npix + pix] = (uint8_t)bits;
+                        if (valid) rrow[(size_t)j * npix] = (uint8_t)bits;
                         if (dbg_epi) { const long long c = pinned_clock(); e_math += c - e_t0; e_t0 = c; }
                     }
                 }
