@@ -485,8 +485,10 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                 for (int i = threadIdx.x; i < npix * 2; i += 128 * kEpiGroups) yo[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 continue;
             }
-            for (int tile = 0; tile < gm.tiles; ++tile, ++tilec) {
-                if ((int)(tilec & (kEpiGroups - 1)) != group) continue;
+            // kFast: a frame is exactly one tile per epilogue group, so the group's tile (and with it the thread's pixel)
+            // never changes -- no loop, no per-frame index arithmetic
+            for (int tile = kFast ? group : 0; tile < (kFast ? group + 1 : gm.tiles); ++tile, ++tilec) {
+                if (!kFast && (int)(tilec & (kEpiGroups - 1)) != group) continue;
                 const int m = tile * 128 + L;
                 const int oy = (int)(((uint32_t)m * (uint32_t)gm.rcp_ws) >> 16), ox = m - oy * gm.Ws;   // m / Ws
                 const bool valid = ox < gm.OW && oy < gm.OH;
