@@ -224,8 +224,9 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         long long w_frame = 0, w_acc = 0, w_path = 0, w_issue = 0, w_fence = 0, w_commit = 0, w_desc = 0, w_fend = 0;
         const bool dbg_nomma = dbg && __reduce_or_sync(0xffffffffu, (unsigned)(dbg[gridDim.x * 8] == 6));   // experiment: no MMAs at all
         const bool dbg_twice = dbg && __reduce_or_sync(0xffffffffu, (unsigned)(dbg[gridDim.x * 8] == 3));   // experiment: every MMA twice
-        for (int t = t_lo; t < t_hi; ++t) {
-            const int p = t / B;
+        // (path index by counting: an integer division per frame is ~25 dependent instructions on these roles' critical paths)
+        for (int t = t_lo, p = t_lo / B, p_next = (t_lo / B + 1) * B; t < t_hi; ++t) {
+            if (t == p_next) { ++p; p_next += B; }
             const long long cp0 = dbg_detail ? clock64() : 0;
             if (p != cur_path) {
                 if (cur_path >= 0) {
@@ -392,8 +393,9 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         if constexpr (kFast) {
             int stage = 0, cur_path = -1, ns = 0;
             uint32_t fphase = 0, path_phase = 0, fill_par = 0;
-            for (int t = t_lo; t < t_hi; ++t) {
-                const int p = t / B;
+            // (path index by counting: an integer division per frame is ~25 dependent instructions on these roles' critical paths)
+            for (int t = t_lo, p = t_lo / B, p_next = (t_lo / B + 1) * B; t < t_hi; ++t) {
+                if (t == p_next) { ++p; p_next += B; }
                 if (p != cur_path) {
                     mbar_wait(path_ready, path_phase);
                     path_phase ^= 1;
@@ -467,8 +469,9 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
         uint32_t path_phase = 0, mask = 0, tilec = 0, gi = 0;   // gi: items this group has consumed from its stage
         long long w_full = 0, t_begin = clock64(), e_ld = 0, e_math = 0, e_t0 = 0, e_path = 0, e_ystore = 0;
         const bool dbg_epi = dbg && dbg[gridDim.x * 8] == 7;
-        for (int t = t_lo; t < t_hi; ++t) {
-            const int p = t / B;
+        // (path index by counting: an integer division per frame is ~25 dependent instructions on these roles' critical paths)
+        for (int t = t_lo, p = t_lo / B, p_next = (t_lo / B + 1) * B; t < t_hi; ++t) {
+            if (t == p_next) { ++p; p_next += B; }
             if (p != cur_path) {
                 if (cur_path >= 0) mbar_arrive(epi_idle);
                 const long long cpw = dbg_epi ? pinned_clock() : 0;
