@@ -194,7 +194,7 @@ lin_fwd_kernel(const float* __restrict__ X, const float* __restrict__ params, Pn
 // Wc[i][0..A-1] = W_fc2[i][:], Wc[i][A] = W_fc3[i], zero up to NP (a multiple of 4): every inner loop is
 // float4 shared loads feeding packed fp32x2 FMAs with no per-column predicate.
 template <int NP>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)       // 64 registers: all 512 chunks of an 8192-transition step are resident at once
 head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnNetDesc nd, int T, int training,
             const int32_t* __restrict__ actions, const float* __restrict__ td, const float* __restrict__ r,
             float beta, float* __restrict__ pi_out, float* __restrict__ v_out, float* __restrict__ dzv,
@@ -360,9 +360,10 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
         }
         if (out) {
 #pragma unroll
+            // column-major partial (element k * Hd + i): consecutive threads write consecutive floats
             for (int k = 0; k < NP / 2; ++k) {
-                if (2 * k < A1) out[(size_t)i * A1 + 2 * k] = (first ? 0.f : out[(size_t)i * A1 + 2 * k]) + acc[k].x;
-                if (2 * k + 1 < A1) out[(size_t)i * A1 + 2 * k + 1] = (first ? 0.f : out[(size_t)i * A1 + 2 * k + 1]) + acc[k].y;
+                if (2 * k < A1) out[(size_t)(2 * k) * Hd + i] = (first ? 0.f : out[(size_t)(2 * k) * Hd + i]) + acc[k].x;
+                if (2 * k + 1 < A1) out[(size_t)(2 * k + 1) * Hd + i] = (first ? 0.f : out[(size_t)(2 * k + 1) * Hd + i]) + acc[k].y;
             }
         }
     }
@@ -422,7 +423,7 @@ __device__ __forceinline__ void head_reduce_body(int bid, const float* __restric
 #pragma unroll
     for (int q = 0; q < 8; ++q) s += red[q][el];
     if (e < Hd * A1) {
-        const int i = e / A1, kx = e % A1;
+        const int kx = e / Hd, i = e - kx * Hd;          // the partials are column-major (see head_kernel)
         if (kx < A) grads[nd.fc2W + (long long)i * A + kx] = s;
         else grads[nd.fc3W + i] = s;
     } else {
@@ -708,21 +709,30 @@ __device__ __forceinline__ void conv_reduce_body(int j, int by, const float* __r
     float s = 0.f;
     if (e < n) {
         // group g adds terms g, g + 8, ... (term i = (path lst[i / nch], chunk i % nch)); the (path, chunk) pair is advanced
-        // incrementally -- an integer division per term made this loop the launch's whole instruction count -- and four
-        // loads are kept in flight; the four partial sums are combined in a fixed order
-        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        // incrementally -- an integer division per term made this loop the launch's whole instruction count -- and eight
+        // loads are kept in flight; the eight partial sums are combined in a fixed order
+        float s8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const float* part_je = part + (size_t)j * n + e;
         const size_t stride_pc = (size_t)nd.M * n;
         const int dpi = 8 / nch_active, dc = 8 % nch_active;
-        int pi = grp / nch_active, c = grp % nch_active, u = 0;
-        for (int i = grp; i < nterms; i += 8) {
+        int pi = grp / nch_active, c = grp % nch_active;
+        auto next_term = [&]() -> const float* {
             const int p = staged ? lst_s[pi] : lst[pi];
-            s4[u] += part_je[(size_t)(p * nch_alloc + c) * stride_pc];
-            u = (u + 1) & 3;
+            const float* a = part_je + (size_t)(p * nch_alloc + c) * stride_pc;
             pi += dpi; c += dc;
             if (c >= nch_active) { c -= nch_active; ++pi; }
+            return a;
+        };
+        int i = grp;
+        for (; i + 56 < nterms; i += 64) {      // eight independent loads per round trip
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldg(next_term());
+#pragma unroll
+            for (int u = 0; u < 8; ++u) s8[u] += v[u];
         }
-        s = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        for (int u = 0; i < nterms; i += 8, ++u) s8[u] += __ldg(next_term());
+        s = ((s8[0] + s8[1]) + (s8[2] + s8[3])) + ((s8[4] + s8[5]) + (s8[6] + s8[7]));
     }
     red[grp][el] = s;
     __syncthreads();
