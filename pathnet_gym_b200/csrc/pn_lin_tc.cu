@@ -34,8 +34,8 @@ namespace {
 
 constexpr int kBlk = 128;                  // bytes of one 8x8 bf16 block
 constexpr int kNB = 32;                    // batch rows per GEMM (N of forward / dgrad)
-constexpr int kWChunkKb = 8;               // k-blocks per forward W stage (64 k)
-constexpr int kWStages = 3;
+constexpr int kWChunkKb = 6;               // k-blocks per forward W stage: 3 K steps, one per hi*hi accumulator (see lin_fwd_tc_kernel)
+constexpr int kWStages = 5;
 
 struct LinGeom {
     int K, KB, Hd, M, L;                   // last_lin, K/8 + 1, hidden, modules, layers
@@ -244,7 +244,14 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
         uint32_t wphase = 0, it = 0, sc = 0;                              // sc: slots issued so far (ring position)
         long long d_wx = 0, d_ww = 0;
         const uint32_t idesc = make_idesc_f16(128, kNB, 0, 0, 1, 0);      // fp16 x fp16, A MN-major, B K-major
-        const uint32_t xs = smem_u32(x_s);
+        // The issuing warp's own instruction stream limited this kernel (ncu: tensor pipe 21 % active, ~100 cycles per MMA):
+        // it rebuilt four descriptors per K step on the uniform datapath.  Now a stage is exactly three K steps -- the hi*hi
+        // accumulator of a step is a compile-time column -- and every descriptor is a per-stage base plus an immediate.
+        // B: Xp blocks [kb][bb]: b-groups 128 B apart, k-groups 512 B apart
+        const uint64_t b_hi0 = make_smem_desc(smem_u32(x_s), 4 * kBlk, kBlk);
+        const uint64_t b_lo_off = (uint64_t)((g.xp_chunk / 2) >> 4);
+        constexpr uint64_t kAStep = (2 * 16 * kBlk) >> 4, kBStep = (2 * 4 * kBlk) >> 4, kALoOff = (uint64_t)(kWChunkKb * 16 * kBlk) >> 4;
+        static_assert(kWChunkKb == 6, "a W stage must hold exactly three K steps");
         for (int item = blockIdx.x; item < nitems; item += gridDim.x, ++it) {
             const int p = (item >> 1) / g.nbc;
             const int ns = __popc(__reduce_or_sync(0xffffffffu, masks[p * g.L + g.L - 1]));
@@ -257,29 +264,28 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
                 mbar_wait(&slot_empty[ring], ((sc / kAccRing) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t dcol = td + ring * kSlotCols;
+                uint64_t b_hi = b_hi0;
                 for (int c = 0; c < nchunk; ++c) {
                     const long long cw = dbg9 ? lin_clock() : 0;
                     mbar_wait(&w_full[stage], wphase);
                     if (dbg9) d_ww += lin_clock() - cw;
                     tc_fence_after();
-                    const uint32_t ws = smem_u32(w_s + (size_t)stage * w_stage_bytes);
+                    // A: Wp blocks [kb][cb16]: mn-groups (c) 128 B apart, k-groups 2048 B apart
+                    const uint64_t a_hi = make_smem_desc(smem_u32(w_s + (size_t)stage * w_stage_bytes), 16 * kBlk, kBlk);
+                    const uint64_t a_lo = a_hi + kALoOff, b_lo = b_hi + b_lo_off;
+                    const int nk = min(3, nkstep - c * 3);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int kk = 0; kk < kWChunkKb / 2; ++kk) {
-                        const int ks = c * (kWChunkKb / 2) + kk;              // global K step
-                        // A: Wp blocks [kb][cb16]: mn-groups (c) 128 B apart, k-groups 2048 B apart
-                        const uint64_t a_hi = make_smem_desc(ws + (uint32_t)(kk * 2 * 16 * kBlk), 16 * kBlk, kBlk);
-                        const uint64_t a_lo = make_smem_desc(ws + (uint32_t)(w_stage_bytes / 2 + kk * 2 * 16 * kBlk), 16 * kBlk, kBlk);
-                        // B: Xp blocks [kb][bb]: b-groups 128 B apart, k-groups 512 B apart
-                        const uint64_t b_hi = make_smem_desc(xs + (uint32_t)(ks * 2 * 4 * kBlk), 4 * kBlk, kBlk);
-                        const uint64_t b_lo = make_smem_desc(xs + (uint32_t)(g.xp_chunk / 2 + ks * 2 * 4 * kBlk), 4 * kBlk, kBlk);
-                        const uint32_t hh = dcol + (uint32_t)(1 + ks % 3) * kNB;
-                        if (ks < nkstep && elect_one()) {
-                            umma_f16(hh, a_hi, b_hi, idesc, ks >= 3 ? 1u : 0u);
-                            umma_f16(dcol, a_hi, b_lo, idesc, ks ? 1u : 0u);
-                            umma_f16(dcol, a_lo, b_hi, idesc, 1u);
+                        for (int kk = 0; kk < 3; ++kk) {
+                            if (kk < nk) {
+                                umma_f16(dcol + (uint32_t)(1 + kk) * kNB, a_hi + kk * kAStep, b_hi + kk * kBStep, idesc, c ? 1u : 0u);
+                                umma_f16(dcol, a_hi + kk * kAStep, b_lo + kk * kBStep, idesc, (c | kk) ? 1u : 0u);
+                                umma_f16(dcol, a_lo + kk * kAStep, b_hi + kk * kBStep, idesc, 1u);
+                            }
                         }
+                        umma_commit(&w_empty[stage]);
                     }
-                    if (elect_one()) umma_commit(&w_empty[stage]);
+                    b_hi += 3 * kBStep;
                     __syncwarp();
                     if (++stage == kWStages) { stage = 0; wphase ^= 1; }
                 }
