@@ -1029,7 +1029,7 @@ int make_frame_tmap(pn_handle* h, const TcGeom& g, const uint8_t* frames, int T,
 }
 
 // relative cost of one transition by the number of active layer-0 modules of its path (us per 8192 transitions, B200)
-const float kFwdCost[11] = {66.f, 84.f, 101.f, 120.f, 140.f, 182.f, 194.f, 212.f, 230.f, 280.f, 300.f};
+const float kFwdCost[11] = {50.f, 62.f, 75.f, 87.f, 101.f, 148.f, 155.f, 164.f, 179.f, 226.f, 240.f};   // tools/layer0_cost.py, current kernel
 
 // cut `units` work units (unit u belongs to path u / per_path) into `ctas` contiguous ranges of equal cumulative cost
 void balance_units(const pn_handle* h, const float* table, int per_path, int ctas, TcBounds& out) {
