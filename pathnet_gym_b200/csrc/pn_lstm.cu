@@ -24,116 +24,177 @@ namespace {
 constexpr int kH = 256;          // cell width (game_ac_network.py:397)
 constexpr int kG = 4 * kH;       // gate columns
 
-// ---- generic fp32 GEMM: C[M x N] = A[M x K] * B[K x N] (+ bias[N]) with arbitrary element strides -------------------
-// 64 x 64 tile, 16-deep K slices, 256 threads, 4 x 4 outputs per thread.
-struct GemmArgs {
-    const float* A; long long a_m, a_k;       // A(m, k) = A[m * a_m + k * a_k]
-    const float* B; long long b_k, b_n;       // B(k, n) = B[k * b_k + n * b_n]
-    float* C; long long c_m;                  // C(m, n) = C[m * c_m + n]
-    const float* bias;                        // optional, per column
-    int M, N, K;
+// ---- fp32 tile GEMM core: acc[TM][TN] += A[m0.., k] * B[k, n0..] over k in [k_lo, k_hi) --------------------------------
+// 256 threads as 16 x 16, thread (ty, tx) owns rows ty*TM.. and columns tx*TN.. of a (16 TM) x (16 TN) tile; 16-deep K
+// slices.  The loads of slice s + 1 are in flight (in registers) while slice s is multiplied out of shared memory: the
+// first version fetched, synchronised and multiplied one slice at a time, and every kernel built on it ran at one
+// exposed memory round trip per slice (the K = 8192 weight-gradient GEMM: 512 slices = 0.56 ms).
+// Operands are addressed with element strides, so one core serves A x B, A^T x B and A x B^T; the loader walks whichever
+// dimension is contiguous.  Fixed summation order (k ascending), so results are run-to-run reproducible.
+struct Operand {
+    const float* p; long long s_mn, s_k;      // element (mn, k) at p[mn * s_mn + k * s_k]
+    int n_mn;                                  // rows (A) / columns (B) that exist: the rest reads as zero
+    int gate_stride;                           // != 0: column mn stands for gate (mn & 3) of unit (mn >> 2), at offset
+                                               // (mn & 3) * gate_stride + (mn >> 2) (the four gates of a unit side by side)
+};
+__device__ __forceinline__ long long operand_mn_offset(const Operand& o, int mn) {
+    return o.gate_stride ? (long long)(mn & 3) * o.gate_stride + (mn >> 2) : (long long)mn * o.s_mn;
+}
+
+template <int TM, int TN>
+struct TileGemm {
+    static constexpr int BM = 16 * TM, BN = 16 * TN, KS = 16;
+    static constexpr int LA = BM * KS / 256, LB = BN * KS / 256;      // elements per thread and slice
+    float (*As)[BM + 4];
+    float (*Bs)[BN + 4];
+    float ra[LA], rb[LB];
+
+    template <int BT, int L>
+    __device__ __forceinline__ void fetch(const Operand& o, int mn0, int k0, int k_hi, float (&r)[L]) {
+        const bool kfast = o.s_k == 1;
+#pragma unroll
+        for (int q = 0; q < L; ++q) {
+            const int e = threadIdx.x + q * 256;
+            int kk, mm;
+            if (kfast) { kk = e % KS; mm = e / KS; } else { mm = e % BT; kk = e / BT; }
+            const int mn = mn0 + mm, k = k0 + kk;
+            r[q] = (mn < o.n_mn && k < k_hi) ? __ldg(o.p + operand_mn_offset(o, mn) + (long long)k * o.s_k) : 0.f;
+        }
+    }
+    template <int BT, int L>
+    __device__ __forceinline__ void stash(const Operand& o, const float (&r)[L], float (*S)[BT + 4]) {
+        const bool kfast = o.s_k == 1;
+#pragma unroll
+        for (int q = 0; q < L; ++q) {
+            const int e = threadIdx.x + q * 256;
+            int kk, mm;
+            if (kfast) { kk = e % KS; mm = e / KS; } else { mm = e % BT; kk = e / BT; }
+            S[kk][mm] = r[q];
+        }
+    }
+    __device__ __forceinline__ void run(const Operand& A, const Operand& B, int m0, int n0, int k_lo, int k_hi,
+                                        float (&acc)[TM][TN]) {
+        const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+        if (k_lo >= k_hi) return;
+        fetch<BM, LA>(A, m0, k_lo, k_hi, ra);
+        fetch<BN, LB>(B, n0, k_lo, k_hi, rb);
+        for (int k0 = k_lo; k0 < k_hi; k0 += KS) {
+            __syncthreads();                                   // the previous slice has been read out of shared memory
+            stash<BM, LA>(A, ra, As);
+            stash<BN, LB>(B, rb, Bs);
+            __syncthreads();
+            if (k0 + KS < k_hi) {
+                fetch<BM, LA>(A, m0, k0 + KS, k_hi, ra);
+                fetch<BN, LB>(B, n0, k0 + KS, k_hi, rb);
+            }
+#pragma unroll
+            for (int kk = 0; kk < KS; ++kk) {
+                float av[TM], bv[TN];
+                if constexpr (TM % 4 == 0) {
+#pragma unroll
+                    for (int i = 0; i < TM; i += 4) *reinterpret_cast<float4*>(&av[i]) = *reinterpret_cast<const float4*>(&As[kk][ty * TM + i]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < TM; i += 2) *reinterpret_cast<float2*>(&av[i]) = *reinterpret_cast<const float2*>(&As[kk][ty * TM + i]);
+                }
+                if constexpr (TN % 4 == 0) {
+#pragma unroll
+                    for (int j = 0; j < TN; j += 4) *reinterpret_cast<float4*>(&bv[j]) = *reinterpret_cast<const float4*>(&Bs[kk][tx * TN + j]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < TN; j += 2) *reinterpret_cast<float2*>(&bv[j]) = *reinterpret_cast<const float2*>(&Bs[kk][tx * TN + j]);
+                }
+#pragma unroll
+                for (int i = 0; i < TM; ++i)
+#pragma unroll
+                    for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+            }
+        }
+    }
 };
 
+// ---- generic GEMM launch: C[M x N] = A * B (+ bias[N]); blockIdx.z = K split (partials [z][M][N], summed by splitk_sum_kernel) ---
+struct GemmArgs {
+    Operand A, B;                              // A.n_mn = M, B.n_mn = N
+    float* C; long long c_m;                   // C(m, n) = C[m * c_m + n]   (split z: C + z * M * c_m)
+    const float* bias;                        // optional, per column (only without K split)
+    int M, N, K, k_per_split;
+};
+
+template <int TM, int TN>
 __global__ void __launch_bounds__(256)
 gemm_kernel(GemmArgs g) {
-    __shared__ float As[16][64 + 4];
-    __shared__ float Bs[16][64 + 4];
-    const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    using TG = TileGemm<TM, TN>;
+    __shared__ __align__(16) float As[TG::KS][TG::BM + 4];
+    __shared__ __align__(16) float Bs[TG::KS][TG::BN + 4];
+    TG tg;
+    tg.As = As; tg.Bs = Bs;
+    const int m0 = blockIdx.y * TG::BM, n0 = blockIdx.x * TG::BN;
+    const int k_lo = blockIdx.z * g.k_per_split, k_hi = min(g.K, k_lo + g.k_per_split);
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = 0.f;
+    tg.run(g.A, g.B, m0, n0, k_lo, k_hi, acc);
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    float acc[4][4];
+    float* C = g.C + (size_t)blockIdx.z * g.M * g.c_m;
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    // loaders: choose the thread mapping so that the contiguous dimension of each operand is the fast one
-    const bool a_kfast = g.a_k == 1, b_nfast = g.b_n == 1;
-    for (int k0 = 0; k0 < g.K; k0 += 16) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int e = threadIdx.x + q * 256;                       // 1024 elements per tile
-            int mm, kk;
-            if (a_kfast) { kk = e & 15; mm = e >> 4; } else { mm = e & 63; kk = e >> 6; }
-            const int m = m0 + mm, k = k0 + kk;
-            As[kk][mm] = (m < g.M && k < g.K) ? g.A[m * g.a_m + k * g.a_k] : 0.f;
-            int nn, kb;
-            if (b_nfast) { nn = e & 63; kb = e >> 6; } else { kb = e & 15; nn = e >> 4; }
-            const int n = n0 + nn, k2 = k0 + kb;
-            Bs[kb][nn] = (n < g.N && k2 < g.K) ? g.B[k2 * g.b_k + n * g.b_n] : 0.f;
-        }
-        __syncthreads();
-#pragma unroll
-        for (int kk = 0; kk < 16; ++kk) {
-            const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
-            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
-            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
-        }
-        __syncthreads();
-    }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int m = m0 + ty * 4 + i;
+    for (int i = 0; i < TM; ++i) {
+        const int m = m0 + ty * TM + i;
         if (m >= g.M) continue;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int n = n0 + tx * 4 + j;
-            if (n < g.N) g.C[m * g.c_m + n] = acc[i][j] + (g.bias ? g.bias[n] : 0.f);
+        for (int j = 0; j < TN; ++j) {
+            const int n = n0 + tx * TN + j;
+            if (n < g.N) C[(long long)m * g.c_m + n] = acc[i][j] + (g.bias ? g.bias[n] : 0.f);
         }
     }
+}
+
+// out[e] = sum over the K splits, in split order (fixed summation order)
+__global__ void __launch_bounds__(256)
+splitk_sum_kernel(const float* __restrict__ part, int nsplit, long long n, float* __restrict__ out) {
+    const long long i = ((long long)blockIdx.x * 256 + threadIdx.x) * 4;
+    if (i >= n) return;
+    float4 s = *reinterpret_cast<const float4*>(part + i);
+    for (int z = 1; z < nsplit; ++z) {
+        const float4 v = *reinterpret_cast<const float4*>(part + (long long)z * n + i);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    *reinterpret_cast<float4*>(out + i) = s;
 }
 
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 // ---- one time step of the recurrence, all paths ------------------------------------------------------------------------
-// block = 64 paths x 16 cell units (x 4 gates); thread (ty, tx): paths 4*ty..4*ty+3, unit u0 + tx.
+// block = 32 paths x 16 cell units (x 4 gates, side by side as GEMM columns); thread (ty, tx): paths 2*ty, 2*ty+1, unit u0 + tx.
 // gates = gx[t] + h_{t-1} @ Wh;  writes the activated gates (i, g = tanh(j), f, o), c_t, tanh(c_t), h_t and h_{t-1}.
 __global__ void __launch_bounds__(256)
 lstm_step_fwd_kernel(const float* __restrict__ gx, const float* __restrict__ Wh, const float* __restrict__ state_in,
                      int P, int B, int t, float* __restrict__ act, float* __restrict__ cbuf, float* __restrict__ tcbuf,
                      float* __restrict__ hout, float* __restrict__ hprev_buf, float* __restrict__ state_out) {
-    __shared__ float Hs[16][64 + 4];
-    __shared__ float Ws[16][64 + 4];           // [k][gate * 16 + unit]
-    const int p0 = blockIdx.y * 64, u0 = blockIdx.x * 16;
+    using TG = TileGemm<2, 4>;
+    __shared__ __align__(16) float As[TG::KS][TG::BM + 4];
+    __shared__ __align__(16) float Bs[TG::KS][TG::BN + 4];
+    TG tg;
+    tg.As = As; tg.Bs = Bs;
+    const int p0 = blockIdx.y * TG::BM, u0 = blockIdx.x * 16;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    float acc[4][4];                            // [path][gate]
+    float acc[2][4];                            // [path][gate]
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 2; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    for (int k0 = 0; k0 < kH; k0 += 16) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const int e = threadIdx.x + q * 256;
-            const int kk = e & 15, pp = e >> 4, p = p0 + pp;
-            float hv = 0.f;
-            if (p < P) {
-                if (t == 0) hv = state_in ? state_in[((size_t)p * 2 + 1) * kH + k0 + kk] : 0.f;
-                else hv = hout[((size_t)p * B + t - 1) * kH + k0 + kk];
-            }
-            Hs[kk][pp] = hv;
-            const int nn = e & 63, kb = e >> 6;
-            Ws[kb][nn] = Wh[(size_t)(k0 + kb) * kG + (nn >> 4) * kH + u0 + (nn & 15)];
-        }
-        __syncthreads();
-#pragma unroll
-        for (int kk = 0; kk < 16; ++kk) {
-            const float4 a = *reinterpret_cast<const float4*>(&Hs[kk][ty * 4]);
-            const float av[4] = {a.x, a.y, a.z, a.w};
-            const float w[4] = {Ws[kk][tx], Ws[kk][16 + tx], Ws[kk][32 + tx], Ws[kk][48 + tx]};
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], w[j], acc[i][j]);
-        }
-        __syncthreads();
+    if (t > 0 || state_in) {
+        // A = h_{t-1}: the previous step's outputs, or the bound initial state (c, h per path)
+        const Operand A{t > 0 ? hout + (size_t)(t - 1) * kH : state_in + kH, t > 0 ? (long long)B * kH : 2LL * kH, 1, P, 0};
+        const Operand Bm{Wh + u0, 0, kG, kG, kH};      // column n = gate (n & 3) of unit u0 + (n >> 2)
+        tg.run(A, Bm, p0, 0, 0, kH, acc);
     }
     const int u = u0 + tx;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int p = p0 + ty * 4 + i;
+    for (int i = 0; i < 2; ++i) {
+        const int p = p0 + ty * 2 + i;
         if (p >= P) continue;
         const size_t row = (size_t)p * B + t;
         const float* gr = gx + row * kG;
@@ -159,51 +220,36 @@ lstm_step_fwd_kernel(const float* __restrict__ gx, const float* __restrict__ Wh,
 }
 
 // ---- one step of BPTT, all paths: dA_t (gradient at the gate pre-activations) ----------------------------------------
-// dh_t = dh_out[t] + dA_{t+1} @ Wh^T;  block = 64 paths x 64 units, K = 1024 gate columns.
+// dh_t = dh_out[t] + dA_{t+1} @ Wh^T;  block = 32 paths x 32 units, K = 1024 gate columns.
 __global__ void __launch_bounds__(256)
 lstm_step_bwd_kernel(const float* __restrict__ dh_out, const float* __restrict__ Wh, const float* __restrict__ act,
                      const float* __restrict__ cbuf, const float* __restrict__ tcbuf, const float* __restrict__ state_in,
                      int P, int B, int t, float* __restrict__ dA, float* __restrict__ dc_carry) {
-    __shared__ float As[16][64 + 4];
-    __shared__ float Bs[16][64 + 4];
-    const int p0 = blockIdx.y * 64, u0 = blockIdx.x * 64;
+    using TG = TileGemm<2, 2>;
+    __shared__ __align__(16) float As[TG::KS][TG::BM + 4];
+    __shared__ __align__(16) float Bs[TG::KS][TG::BN + 4];
+    TG tg;
+    tg.As = As; tg.Bs = Bs;
+    const int p0 = blockIdx.y * TG::BM, u0 = blockIdx.x * TG::BN;
     const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    float acc[4][4];
+    float acc[2][2];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 2; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+        for (int j = 0; j < 2; ++j) acc[i][j] = 0.f;
     if (t < B - 1) {
-        for (int k0 = 0; k0 < kG; k0 += 16) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int e = threadIdx.x + q * 256;
-                const int kk = e & 15, mm = e >> 4, p = p0 + mm;
-                As[kk][mm] = p < P ? dA[((size_t)p * B + t + 1) * kG + k0 + kk] : 0.f;
-                Bs[kk][mm] = Wh[(size_t)(u0 + mm) * kG + k0 + kk];        // Wh^T: (k = gate column, n = unit)
-            }
-            __syncthreads();
-#pragma unroll
-            for (int kk = 0; kk < 16; ++kk) {
-                const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
-                const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
-                const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
-            }
-            __syncthreads();
-        }
+        const Operand A{dA + (size_t)(t + 1) * kG, (long long)B * kG, 1, P, 0};       // dA_{t+1}[p][k]
+        const Operand Bm{Wh, kG, 1, kH, 0};                                          // Wh^T: (k = gate column, n = unit) = Wh[n][k]
+        tg.run(A, Bm, p0, u0, 0, kG, acc);
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int p = p0 + ty * 4 + i;
+    for (int i = 0; i < 2; ++i) {
+        const int p = p0 + ty * 2 + i;
         if (p >= P) continue;
         const size_t row = (size_t)p * B + t;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int u = u0 + tx * 4 + j;
+        for (int j = 0; j < 2; ++j) {
+            const int u = u0 + tx * 2 + j;
             const float dh = dh_out[row * kH + u] + acc[i][j];
             const float* a = act + row * kG;
             const float ig = a[u], gg = a[kH + u], fg = a[2 * kH + u], og = a[3 * kH + u];
@@ -221,36 +267,66 @@ lstm_step_bwd_kernel(const float* __restrict__ dh_out, const float* __restrict__
     }
 }
 
-// column sums of dA [T][1024] in a fixed order: block = 32 columns, 8 row groups, then the 8 partials in order
+// column sums of dA [T][1024] in a fixed order, two levels: block (x, y) adds rows y, y + gridDim.y, ... of 32 columns in 8 row
+// groups (then the 8 partials in order) into part[y][c]; colsum_finish_kernel adds the gridDim.y partials in order.
+constexpr int kColsumChunks = 32;
 __global__ void __launch_bounds__(256)
-colsum_kernel(const float* __restrict__ dA, int T, float* __restrict__ out) {
+colsum_kernel(const float* __restrict__ dA, int T, float* __restrict__ part) {
     __shared__ float red[8][33];
     const int c = blockIdx.x * 32 + (threadIdx.x & 31), g = threadIdx.x >> 5;
     float s = 0.f;
-    for (int r = g; r < T; r += 8) s += dA[(size_t)r * kG + c];
+    for (int r = blockIdx.y * 8 + g; r < T; r += 8 * gridDim.y) s += dA[(size_t)r * kG + c];
     red[g][threadIdx.x & 31] = s;
     __syncthreads();
     if (g == 0) {
         float tot = 0.f;
 #pragma unroll
         for (int q = 0; q < 8; ++q) tot += red[q][threadIdx.x & 31];
-        out[c] = tot;
+        part[(size_t)blockIdx.y * kG + c] = tot;
     }
 }
+__global__ void __launch_bounds__(256)
+colsum_finish_kernel(const float* __restrict__ part, int nchunks, float* __restrict__ out) {
+    const int c = blockIdx.x * 256 + threadIdx.x;
+    if (c >= kG) return;
+    float s = 0.f;
+    for (int y = 0; y < nchunks; ++y) s += part[(size_t)y * kG + c];
+    out[c] = s;
+}
 
-int gemm(pn_handle* h, const GemmArgs& g, cudaStream_t st, const char* what) {
-    dim3 grid((g.N + 63) / 64, (g.M + 63) / 64);
-    gemm_kernel<<<grid, 256, 0, st>>>(g);
+// C = A * B (+ bias).  Big tiles (128 x 128, 8 x 8 per thread) when the output has enough of them to fill the GPU, else
+// 64 x 64; nsplit > 1 cuts K into equal pieces whose partial products go to `partials` and are added in split order.
+int gemm(pn_handle* h, GemmArgs g, int nsplit, float* partials, cudaStream_t st, const char* what) {
+    float* out = g.C;
+    g.k_per_split = ((g.K + nsplit - 1) / nsplit + 15) & ~15;
+    nsplit = (g.K + g.k_per_split - 1) / g.k_per_split;
+    if (nsplit > 1) { g.C = partials; g.c_m = g.N; g.bias = nullptr; }
+    const long long big_tiles = (long long)((g.M + 127) / 128) * ((g.N + 127) / 128) * nsplit;
+    if (big_tiles >= h->num_sms) {
+        dim3 grid((g.N + 127) / 128, (g.M + 127) / 128, nsplit);
+        gemm_kernel<8, 8><<<grid, 256, 0, st>>>(g);
+    } else {
+        dim3 grid((g.N + 63) / 64, (g.M + 63) / 64, nsplit);
+        gemm_kernel<4, 4><<<grid, 256, 0, st>>>(g);
+    }
     PN_LAUNCH_CHECK(h, what);
+    if (nsplit > 1) {
+        const long long n = (long long)g.M * g.N;
+        splitk_sum_kernel<<<(int)((n / 4 + 255) / 256), 256, 0, st>>>(partials, nsplit, n, out);
+        PN_LAUNCH_CHECK(h, "splitk_sum_kernel");
+    }
     return PN_OK;
 }
 
 }  // namespace
 
+constexpr int kLstmSplitK = 16;
+
 size_t pn_lstm_workspace_floats(const pn_handle* h) {
-    // gx / dA share nothing: gx [T,1024], act [T,1024], dA [T,1024], c, tanh c, h_out, h_prev [T,256] each, dc carry [P,256]
+    // gx [T,1024], act [T,1024], dA [T,1024], c, tanh c, h_out, h_prev [T,256] each, dc carry [P,256],
+    // split-K partials of a weight-gradient GEMM [16][256][1024], column-sum partials [32][1024]
     const size_t T = (size_t)h->T;
-    return T * kG * 3 + T * kH * 4 + (size_t)h->P * kH;
+    return T * kG * 3 + T * kH * 4 + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG;
 }
 
 // hbuf (module sum, no /M) -> lstm_out; reads the bound initial state, writes the final state if one is bound
@@ -266,10 +342,11 @@ int pn_launch_lstm_fwd(pn_handle* h, int B, cudaStream_t st) {
     float* hout = tcbuf + (size_t)h->T * kH;
     float* hprev = hout + (size_t)h->T * kH;
     PnProfScope prof(h, PN_PROF_LSTM_FWD, st);
-    GemmArgs g{h->hbuf, kH, 1, W, kG, 1, gx, kG, h->params + nd.lstmb, T, kG, kH};      // rows 0..255 of the kernel: the input
-    if (int rc = gemm(h, g, st, "lstm input projection")) return rc;
+    // rows 0..255 of the kernel multiply the input: gx = X @ W[0:256] + b
+    GemmArgs g{{h->hbuf, kH, 1, T, 0}, {W, 1, kG, kG, 0}, gx, kG, h->params + nd.lstmb, T, kG, kH, 0};
+    if (int rc = gemm(h, g, 1, nullptr, st, "lstm input projection")) return rc;
     const float* Wh = W + (size_t)kH * kG;
-    dim3 grid(kH / 16, (P + 63) / 64);
+    dim3 grid(kH / 16, (P + 31) / 32);
     for (int t = 0; t < B; ++t) {
         lstm_step_fwd_kernel<<<grid, 256, 0, st>>>(gx, Wh, h->lstm_state_in, P, B, t, act, cbuf, tcbuf, hout, hprev,
                                                   h->lstm_state_out);
@@ -292,22 +369,27 @@ int pn_launch_lstm_bwd(pn_handle* h, int B, cudaStream_t st) {
     float* hout = tcbuf + (size_t)h->T * kH;
     float* hprev = hout + (size_t)h->T * kH;
     float* dcc = hprev + (size_t)h->T * kH;
+    float* partials = dcc + (size_t)h->P * kH;
+    float* colpart = partials + (size_t)kLstmSplitK * kH * kG;
     (void)hout;
     PnProfScope prof(h, PN_PROF_LSTM_BWD, st);
-    dim3 grid(kH / 64, (P + 63) / 64);
+    dim3 grid(kH / 32, (P + 31) / 32);
     for (int t = B - 1; t >= 0; --t) {
         lstm_step_bwd_kernel<<<grid, 256, 0, st>>>(h->dh, Wh, act, cbuf, tcbuf, h->lstm_state_in, P, B, t, dA, dcc);
         PN_LAUNCH_CHECK(h, "lstm_step_bwd_kernel");
     }
     float* gW = h->grads + nd.lstmW;
-    // dW rows 0..255 = X^T dA, rows 256..511 = Hprev^T dA (sum over every transition of every path)
-    GemmArgs gw1{h->hbuf, 1, kH, dA, kG, 1, gW, kG, nullptr, kH, kG, T};
-    if (int rc = gemm(h, gw1, st, "lstm weight gradient (input rows)")) return rc;
-    GemmArgs gw2{hprev, 1, kH, dA, kG, 1, gW + (size_t)kH * kG, kG, nullptr, kH, kG, T};
-    if (int rc = gemm(h, gw2, st, "lstm weight gradient (recurrent rows)")) return rc;
-    colsum_kernel<<<kG / 32, 256, 0, st>>>(dA, T, h->grads + nd.lstmb);
+    // dW rows 0..255 = X^T dA, rows 256..511 = Hprev^T dA (sum over every transition of every path): K = T is cut into
+    // pieces so that the 8 output tiles become 128 blocks
+    GemmArgs gw1{{h->hbuf, 1, kH, kH, 0}, {dA, 1, kG, kG, 0}, gW, kG, nullptr, kH, kG, T, 0};
+    if (int rc = gemm(h, gw1, kLstmSplitK, partials, st, "lstm weight gradient (input rows)")) return rc;
+    GemmArgs gw2{{hprev, 1, kH, kH, 0}, {dA, 1, kG, kG, 0}, gW + (size_t)kH * kG, kG, nullptr, kH, kG, T, 0};
+    if (int rc = gemm(h, gw2, kLstmSplitK, partials, st, "lstm weight gradient (recurrent rows)")) return rc;
+    colsum_kernel<<<dim3(kG / 32, kColsumChunks), 256, 0, st>>>(dA, T, colpart);
     PN_LAUNCH_CHECK(h, "colsum_kernel");
+    colsum_finish_kernel<<<kG / 256, 256, 0, st>>>(colpart, kColsumChunks, h->grads + nd.lstmb);
+    PN_LAUNCH_CHECK(h, "colsum_finish_kernel");
     // gradient at the cell input = dA @ Wx^T, overwriting dh (every step has consumed its dh_out by now)
-    GemmArgs gd{dA, kG, 1, W, 1, kG, h->dh, kH, nullptr, T, kH, kG};
-    return gemm(h, gd, st, "lstm input gradient");
+    GemmArgs gd{{dA, kG, 1, T, 0}, {W, kG, 1, kH, 0}, h->dh, kH, nullptr, T, kH, kG, 0};
+    return gemm(h, gd, 1, nullptr, st, "lstm input gradient");
 }

@@ -7,7 +7,7 @@ from pathnet_gym_b200.trainer import PopulationTrainer
 
 L, M, N, P, B = [int(x) for x in sys.argv[1:6]]
 A = int(sys.argv[6]) if len(sys.argv) > 6 else 18
-cfg = PathNetConfig(L=L, M=M, N=N, A=A)
+cfg = PathNetConfig(L=L, M=M, N=N, A=A, lstm=bool(os.environ.get("PN_LSTM")))      # PN_LSTM=1: the LSTM variant
 pop = PathNetPopulation(cfg, P, B); pop.init_params(1)
 pop.set_genotypes(geopath_init(P, L, M, N, 7, 0).cpu().numpy().view("uint32"))
 dev = pop.device
