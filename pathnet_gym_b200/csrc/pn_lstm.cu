@@ -164,42 +164,207 @@ splitk_sum_kernel(const float* __restrict__ part, int nsplit, long long n, float
     *reinterpret_cast<float4*>(out + i) = s;
 }
 
+// ---- tile GEMM core for the per-step kernels: acc[TM][TN] += sum_k A[m][k] * B[n][k], both operands k-contiguous ---------
+// A time step's GEMM is tiny (134 MFLOP over the whole GPU) and strictly ordered after the previous step, so what it costs is
+// memory round trips: with one K slice in flight a block paid one per slice (K = 1024: 64 of them, 55 us per step).  Here the
+// slices stream through NS shared-memory stages with 16-byte cp.async copies, NS - 1 slices in flight per block.
+// Thread (ty, tx) owns rows ty*TM.. of A and rows tx, tx + 16, .. of B (acc[i][j] = row ty*TM + i x row tx + 16 j).
+// Rows past n_rows read as zero.  K is a multiple of 16, row strides are multiples of 4 floats.  Fixed summation order.
+__device__ __forceinline__ void cp_async_16(void* dst_smem, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <int TM, int TN, int NS>
+struct TileGemmNT {
+    static constexpr int BM = 16 * TM, BN = 16 * TN, KS = 16, LD = KS + 4;
+    static constexpr size_t kSmemFloats = (size_t)NS * (BM + BN) * LD;
+    float* smem;                                                          // [NS][BM + BN][LD]
+    __device__ __forceinline__ float* a_row(int stage, int m) { return smem + ((size_t)stage * (BM + BN) + m) * LD; }
+    __device__ __forceinline__ float* b_row(int stage, int n) { return smem + ((size_t)stage * (BM + BN) + BM + n) * LD; }
+    __device__ __forceinline__ void issue(const float* A, long long lda, int a_rows, int m0, const float* Bm, long long ldb,
+                                          int b_rows, int n0, int k0, int stage) {
+        for (int c = threadIdx.x; c < (BM + BN) * 4; c += 256) {
+            const int r = c >> 2, k4 = (c & 3) * 4;
+            float* dst = smem + ((size_t)stage * (BM + BN) + r) * LD + k4;
+            const bool isA = r < BM;
+            const int row = isA ? m0 + r : n0 + r - BM;
+            const bool ok = row < (isA ? a_rows : b_rows);
+            const float* src = isA ? A + (long long)row * lda + k0 + k4 : Bm + (long long)row * ldb + k0 + k4;
+            if (ok) cp_async_16(dst, src);
+            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    __device__ __forceinline__ void run(const float* A, long long lda, int a_rows, int m0, const float* Bm, long long ldb,
+                                        int b_rows, int n0, int K, float (&acc)[TM][TN]) {
+        const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+        const int nslice = K / KS;
+#pragma unroll
+        for (int s = 0; s < NS - 1; ++s) {
+            if (s < nslice) issue(A, lda, a_rows, m0, Bm, ldb, b_rows, n0, s * KS, s);
+            cp_async_commit();
+        }
+        for (int s = 0; s < nslice; ++s) {
+            cp_async_wait<NS - 2>();                 // this thread's copies of slice s have landed
+            __syncthreads();                         // ... everybody's, and everybody has finished multiplying slice s - 1
+            if (s + NS - 1 < nslice) issue(A, lda, a_rows, m0, Bm, ldb, b_rows, n0, (s + NS - 1) * KS, (s + NS - 1) % NS);
+            cp_async_commit();
+            const int st = s % NS;
+#pragma unroll
+            for (int kq = 0; kq < KS; kq += 4) {
+                float4 a4[TM], b4[TN];
+#pragma unroll
+                for (int i = 0; i < TM; ++i) a4[i] = *reinterpret_cast<const float4*>(a_row(st, ty * TM + i) + kq);
+#pragma unroll
+                for (int j = 0; j < TN; ++j) b4[j] = *reinterpret_cast<const float4*>(b_row(st, tx + 16 * j) + kq);   // (rows 20 floats apart: 8 lanes, 8 bank groups)
+#pragma unroll
+                for (int i = 0; i < TM; ++i)
+#pragma unroll
+                    for (int j = 0; j < TN; ++j) {
+                        float v = acc[i][j];
+                        v = fmaf(a4[i].x, b4[j].x, v); v = fmaf(a4[i].y, b4[j].y, v);
+                        v = fmaf(a4[i].z, b4[j].z, v); v = fmaf(a4[i].w, b4[j].w, v);
+                        acc[i][j] = v;
+                    }
+            }
+        }
+        cp_async_wait<0>();
+    }
+};
+
+// ---- the same product with K split over the block's 8 warps ----------------------------------------------------------------
+// out[32 x BN] = sum_k A[m][k] * B[n][k] for one 32-row x BN-column tile (BN = 32 or 64); warp w multiplies k in
+// [w K/8, (w+1) K/8) for the WHOLE tile, streaming its operands through its own ring of shared-memory stages, then the 8
+// partial tiles are added in warp order (fixed summation order).  A block's serial chain is K/8 deep instead of K: the
+// step kernels are latency-bound (one block per SM, 64-128 blocks per step), so this is what their time follows.
+// Lane (ly = lane / 4, lx = lane % 4) owns rows ly + 8 i (i < 4) and columns lx + 4 j (j < BN / 4): with rows 20 floats apart
+// the 8 (4) distinct rows of a 128-bit load fall into distinct bank groups, equal addresses broadcast.
+template <int BN, int NSW>
+struct WarpSplitGemmNT {
+    static constexpr int BM = 32, KS = 16, LD = KS + 4, TJ = BN / 4;
+    static constexpr int kStageFloats = (BM + BN) * LD;
+    static constexpr size_t kSmemBytes = sizeof(float) * (size_t)8 * NSW * kStageFloats;      // >= 8 * BM * BN floats for the partial tiles
+    // returns with part[w][m][n] (w < 8) in `smem` (layout [8][BM][BN]); the caller sums over w
+    __device__ __forceinline__ void run(float* smem, const float* A, long long lda, int a_rows, int m0, const float* Bm, long long ldb,
+                                        int b_rows, int n0, int K) {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, ly = lane >> 2, lx = lane & 3;
+        float* ws = smem + (size_t)warp * NSW * kStageFloats;
+        const int kw = K / 8, k_lo = warp * kw, nslice = kw / KS;
+        auto issue = [&](int slice, int stage) {
+            float* base = ws + (size_t)stage * kStageFloats;
+            const int k0 = k_lo + slice * KS;
+#pragma unroll
+            for (int q = 0; q < (BM + BN) * 4 / 32; ++q) {
+                const int c = lane + q * 32, r = c >> 2, k4 = (c & 3) * 4;
+                const bool isA = r < BM;
+                const int row = isA ? m0 + r : n0 + r - BM;
+                float* dst = base + r * LD + k4;
+                if (row < (isA ? a_rows : b_rows)) cp_async_16(dst, isA ? A + (long long)row * lda + k0 + k4 : Bm + (long long)row * ldb + k0 + k4);
+                else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
+        float acc[4][TJ];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < TJ; ++j) acc[i][j] = 0.f;
+#pragma unroll
+        for (int s = 0; s < NSW - 1; ++s) {
+            if (s < nslice) issue(s, s);
+            cp_async_commit();
+        }
+        for (int s = 0; s < nslice; ++s) {
+            cp_async_wait<NSW - 2>();
+            __syncwarp();                            // the whole warp's copies of slice s have landed; slice s - 1 has been multiplied
+            if (s + NSW - 1 < nslice) issue(s + NSW - 1, (s + NSW - 1) % NSW);
+            cp_async_commit();
+            const float* base = ws + (size_t)(s % NSW) * kStageFloats;
+#pragma unroll
+            for (int kq = 0; kq < KS; kq += 4) {
+                float4 a4[4], b4[TJ];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) a4[i] = *reinterpret_cast<const float4*>(base + (ly + 8 * i) * LD + kq);
+#pragma unroll
+                for (int j = 0; j < TJ; ++j) b4[j] = *reinterpret_cast<const float4*>(base + (BM + lx + 4 * j) * LD + kq);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < TJ; ++j) {
+                        float v = acc[i][j];
+                        v = fmaf(a4[i].x, b4[j].x, v); v = fmaf(a4[i].y, b4[j].y, v);
+                        v = fmaf(a4[i].z, b4[j].z, v); v = fmaf(a4[i].w, b4[j].w, v);
+                        acc[i][j] = v;
+                    }
+            }
+        }
+        cp_async_wait<0>();
+        __syncthreads();                             // every warp is done with its stages: they become the partial tiles
+        float* part = smem + (size_t)warp * BM * BN;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < TJ; ++j) part[(ly + 8 * i) * BN + lx + 4 * j] = acc[i][j];
+        __syncthreads();
+    }
+    // sum over the 8 warps' partials of element (m, n), in warp order
+    __device__ __forceinline__ static float total(const float* smem, int m, int n) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += smem[(size_t)w * BM * BN + m * BN + n];
+        return s;
+    }
+};
+
+// Wh [256 k][4 gates x 256 units] -> WhR [(unit / 16) * 64 + gate * 16 + unit % 16][256 k]: the forward step's B operand,
+// k-contiguous; a block's 64 rows are the four gates of its 16 units, gate-major, so that thread tx owns rows tx + 16 * gate.
+// 32 x 32 tile transpose per gate.
+__global__ void __launch_bounds__(256)
+lstm_wh_reorder_kernel(const float* __restrict__ Wh, float* __restrict__ WhR) {
+    __shared__ float tile[32][33];
+    const int g = blockIdx.z, u0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) tile[r][tx] = Wh[(size_t)(k0 + r) * kG + g * kH + u0 + tx];
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int u = u0 + r;
+        WhR[((size_t)(u >> 4) * 64 + g * 16 + (u & 15)) * kH + k0 + tx] = tile[tx][r];
+    }
+}
+
 __device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
 
 // ---- one time step of the recurrence, all paths ------------------------------------------------------------------------
 // block = 32 paths x 16 cell units (x 4 gates, side by side as GEMM columns); thread (ty, tx): paths 2*ty, 2*ty+1, unit u0 + tx.
 // gates = gx[t] + h_{t-1} @ Wh;  writes the activated gates (i, g = tanh(j), f, o), c_t, tanh(c_t), h_t and h_{t-1}.
 __global__ void __launch_bounds__(256)
-lstm_step_fwd_kernel(const float* __restrict__ gx, const float* __restrict__ Wh, const float* __restrict__ state_in,
+lstm_step_fwd_kernel(const float* __restrict__ gx, const float* __restrict__ WhR, const float* __restrict__ state_in,
                      int P, int B, int t, float* __restrict__ act, float* __restrict__ cbuf, float* __restrict__ tcbuf,
                      float* __restrict__ hout, float* __restrict__ hprev_buf, float* __restrict__ state_out) {
-    using TG = TileGemm<2, 4>;
-    __shared__ __align__(16) float As[TG::KS][TG::BM + 4];
-    __shared__ __align__(16) float Bs[TG::KS][TG::BN + 4];
-    TG tg;
-    tg.As = As; tg.Bs = Bs;
-    const int p0 = blockIdx.y * TG::BM, u0 = blockIdx.x * 16;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    float acc[2][4];                            // [path][gate]
-#pragma unroll
-    for (int i = 0; i < 2; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-    if (t > 0 || state_in) {
-        // A = h_{t-1}: the previous step's outputs, or the bound initial state (c, h per path)
-        const Operand A{t > 0 ? hout + (size_t)(t - 1) * kH : state_in + kH, t > 0 ? (long long)B * kH : 2LL * kH, 1, P, 0};
-        const Operand Bm{Wh + u0, 0, kG, kG, kH};      // column n = gate (n & 3) of unit u0 + (n >> 2)
-        tg.run(A, Bm, p0, 0, 0, kH, acc);
+    using WG = WarpSplitGemmNT<64, 3>;
+    extern __shared__ __align__(16) float tile_s[];
+    const int p0 = blockIdx.y * WG::BM, u0 = blockIdx.x * 16;
+    const bool have_h = t > 0 || state_in;
+    if (have_h) {
+        // A = h_{t-1}: the previous step's outputs, or the bound initial state (c, h per path);
+        // B = WhR: row u0 * 4 + 16 * gate + ul = gate `gate` of unit u0 + ul
+        const float* A = t > 0 ? hout + (size_t)(t - 1) * kH : state_in + kH;
+        WG wg;
+        wg.run(tile_s, A, t > 0 ? (long long)B * kH : 2LL * kH, P, p0, WhR, kH, kG, u0 * 4, kH);
     }
-    const int u = u0 + tx;
+    const int ul = threadIdx.x & 15, u = u0 + ul;
 #pragma unroll
     for (int i = 0; i < 2; ++i) {
-        const int p = p0 + ty * 2 + i;
+        const int m = (threadIdx.x >> 4) + 16 * i, p = p0 + m;
         if (p >= P) continue;
         const size_t row = (size_t)p * B + t;
         const float* gr = gx + row * kG;
-        const float ai = acc[i][0] + gr[u], aj = acc[i][1] + gr[kH + u], af = acc[i][2] + gr[2 * kH + u],
-                    ao = acc[i][3] + gr[3 * kH + u];
+        float ai = gr[u], aj = gr[kH + u], af = gr[2 * kH + u], ao = gr[3 * kH + u];
+        if (have_h) {
+            ai += WG::total(tile_s, m, ul); aj += WG::total(tile_s, m, 16 + ul);
+            af += WG::total(tile_s, m, 32 + ul); ao += WG::total(tile_s, m, 48 + ul);
+        }
         const float c_prev = t == 0 ? (state_in ? state_in[(size_t)p * 2 * kH + u] : 0.f) : cbuf[(row - 1) * kH + u];
         const float h_prev = t == 0 ? (state_in ? state_in[((size_t)p * 2 + 1) * kH + u] : 0.f) : hout[(row - 1) * kH + u];
         const float ig = sigmoidf_(ai), gg = tanhf(aj), fg = sigmoidf_(af + 1.0f), og = sigmoidf_(ao);   // forget_bias = 1.0
@@ -225,32 +390,22 @@ __global__ void __launch_bounds__(256)
 lstm_step_bwd_kernel(const float* __restrict__ dh_out, const float* __restrict__ Wh, const float* __restrict__ act,
                      const float* __restrict__ cbuf, const float* __restrict__ tcbuf, const float* __restrict__ state_in,
                      int P, int B, int t, float* __restrict__ dA, float* __restrict__ dc_carry) {
-    using TG = TileGemm<2, 2>;
-    __shared__ __align__(16) float As[TG::KS][TG::BM + 4];
-    __shared__ __align__(16) float Bs[TG::KS][TG::BN + 4];
-    TG tg;
-    tg.As = As; tg.Bs = Bs;
-    const int p0 = blockIdx.y * TG::BM, u0 = blockIdx.x * TG::BN;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-    float acc[2][2];
-#pragma unroll
-    for (int i = 0; i < 2; ++i)
-#pragma unroll
-        for (int j = 0; j < 2; ++j) acc[i][j] = 0.f;
+    using WG = WarpSplitGemmNT<32, 3>;
+    extern __shared__ __align__(16) float tile_s[];
+    const int p0 = blockIdx.y * WG::BM, u0 = blockIdx.x * 32;
+    // dA_{t+1}[p][k] x Wh^T: (k = gate column, n = unit) = Wh[n][k], both k-contiguous
     if (t < B - 1) {
-        const Operand A{dA + (size_t)(t + 1) * kG, (long long)B * kG, 1, P, 0};       // dA_{t+1}[p][k]
-        const Operand Bm{Wh, kG, 1, kH, 0};                                          // Wh^T: (k = gate column, n = unit) = Wh[n][k]
-        tg.run(A, Bm, p0, u0, 0, kG, acc);
+        WG wg;
+        wg.run(tile_s, dA + (size_t)(t + 1) * kG, (long long)B * kG, P, p0, Wh, kG, kH, u0, kG);
     }
+    {
+        const int n = threadIdx.x & 31, u = u0 + n;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int p = p0 + ty * 2 + i;
-        if (p >= P) continue;
-        const size_t row = (size_t)p * B + t;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int u = u0 + tx * 2 + j;
-            const float dh = dh_out[row * kH + u] + acc[i][j];
+        for (int i = 0; i < 4; ++i) {
+            const int m = (threadIdx.x >> 5) + 8 * i, p = p0 + m;
+            if (p >= P) continue;
+            const size_t row = (size_t)p * B + t;
+            const float dh = dh_out[row * kH + u] + (t < B - 1 ? WG::total(tile_s, m, n) : 0.f);
             const float* a = act + row * kG;
             const float ig = a[u], gg = a[kH + u], fg = a[2 * kH + u], og = a[3 * kH + u];
             const float tc = tcbuf[row * kH + u];
@@ -326,7 +481,8 @@ size_t pn_lstm_workspace_floats(const pn_handle* h) {
     // gx [T,1024], act [T,1024], dA [T,1024], c, tanh c, h_out, h_prev [T,256] each, dc carry [P,256],
     // split-K partials of a weight-gradient GEMM [16][256][1024], column-sum partials [32][1024]
     const size_t T = (size_t)h->T;
-    return T * kG * 3 + T * kH * 4 + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG;
+    return T * kG * 3 + T * kH * 4 + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG +
+           (size_t)kH * kG;                          // + the recurrent weights reordered for the forward step (WhR)
 }
 
 // hbuf (module sum, no /M) -> lstm_out; reads the bound initial state, writes the final state if one is bound
@@ -346,9 +502,14 @@ int pn_launch_lstm_fwd(pn_handle* h, int B, cudaStream_t st) {
     GemmArgs g{{h->hbuf, kH, 1, T, 0}, {W, 1, kG, kG, 0}, gx, kG, h->params + nd.lstmb, T, kG, kH, 0};
     if (int rc = gemm(h, g, 1, nullptr, st, "lstm input projection")) return rc;
     const float* Wh = W + (size_t)kH * kG;
+    float* WhR = hprev + (size_t)h->T * kH + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG;
+    lstm_wh_reorder_kernel<<<dim3(kH / 32, kH / 32, 4), 256, 0, st>>>(Wh, WhR);
+    PN_LAUNCH_CHECK(h, "lstm_wh_reorder_kernel");
     dim3 grid(kH / 16, (P + 31) / 32);
+    const size_t smem = WarpSplitGemmNT<64, 3>::kSmemBytes;
+    PN_SET_SMEM(h, lstm_step_fwd_kernel, smem);
     for (int t = 0; t < B; ++t) {
-        lstm_step_fwd_kernel<<<grid, 256, 0, st>>>(gx, Wh, h->lstm_state_in, P, B, t, act, cbuf, tcbuf, hout, hprev,
+        lstm_step_fwd_kernel<<<grid, 256, smem, st>>>(gx, WhR, h->lstm_state_in, P, B, t, act, cbuf, tcbuf, hout, hprev,
                                                   h->lstm_state_out);
         PN_LAUNCH_CHECK(h, "lstm_step_fwd_kernel");
     }
@@ -374,8 +535,10 @@ int pn_launch_lstm_bwd(pn_handle* h, int B, cudaStream_t st) {
     (void)hout;
     PnProfScope prof(h, PN_PROF_LSTM_BWD, st);
     dim3 grid(kH / 32, (P + 31) / 32);
+    const size_t smem = WarpSplitGemmNT<32, 3>::kSmemBytes;
+    PN_SET_SMEM(h, lstm_step_bwd_kernel, smem);
     for (int t = B - 1; t >= 0; --t) {
-        lstm_step_bwd_kernel<<<grid, 256, 0, st>>>(h->dh, Wh, act, cbuf, tcbuf, h->lstm_state_in, P, B, t, dA, dcc);
+        lstm_step_bwd_kernel<<<grid, 256, smem, st>>>(h->dh, Wh, act, cbuf, tcbuf, h->lstm_state_in, P, B, t, dA, dcc);
         PN_LAUNCH_CHECK(h, "lstm_step_bwd_kernel");
     }
     float* gW = h->grads + nd.lstmW;
