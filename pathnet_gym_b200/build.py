@@ -8,7 +8,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libpathnet_b200.so")
-SOURCES = ["pn_api.cu", "pn_net_kernels.cu", "pn_rmsprop.cu", "pn_genotype.cu", "pn_noalloc.cu", "pn_conv0_tc.cu", "pn_lin_tc.cu", "pn_conv_mid.cu", "pn_conv_mid_tc.cu", "pn_rollout.cu", "pn_peer.cu", "pn_lstm.cu"]
+SOURCES = ["pn_api.cu", "pn_net_kernels.cu", "pn_rmsprop.cu", "pn_genotype.cu", "pn_noalloc.cu", "pn_conv0_tc.cu", "pn_lin_tc.cu", "pn_conv_mid.cu", "pn_conv_mid_tc.cu", "pn_rollout.cu", "pn_peer.cu", "pn_lstm.cu", "pn_gemm_tc.cu"]
 HEADERS = [os.path.join(CSRC, "pn_internal.cuh"), os.path.join(CSRC, "pn_tc.cuh"), os.path.join(CSRC, "pn_rms_core.cuh"), os.path.join(ROOT, "include", "pathnet_b200.h")]
 
 

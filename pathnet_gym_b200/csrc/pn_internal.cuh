@@ -221,6 +221,13 @@ inline const float* pn_head_input(const pn_handle* h) {      // what the two hea
     return h->lstm ? h->lstm_ws + (size_t)h->T * 1024 * 3 + (size_t)h->T * 256 * 2 : h->hbuf;
 }
 // pn_rollout.cu
+// pn_gemm_tc.cu: plain GEMMs on the tensor cores (bf16 hi/lo block planes), used by the LSTM variant
+struct PnGemmOperand { const uint8_t* planes; int R, C; bool mn; };
+size_t pn_gemm_planes_bytes(int R, int C);
+int pn_gemm_split(pn_handle* h, const float* S, int R, int C, long long ld, uint8_t* planes, cudaStream_t st);
+bool pn_gemm_tc_usable(int M, int N, int K, int nsplit);
+int pn_gemm_tc(pn_handle* h, const PnGemmOperand& A, const PnGemmOperand& B, float* C, long long ldc, const float* bias, int M,
+               int N, int K, int nsplit, cudaStream_t st);
 long long pn_late_grads_floats(const pn_handle* h);   // floats at the start of the slab that ev_early_grads does not cover
 int pn_launch_expand_planes(pn_handle* h, const uint8_t* planes_dev, int B, uint8_t* frames_dev, int p0, int np, cudaStream_t st);
 // pn_rmsprop.cu

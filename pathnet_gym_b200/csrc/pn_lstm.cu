@@ -477,12 +477,29 @@ int gemm(pn_handle* h, GemmArgs g, int nsplit, float* partials, cudaStream_t st,
 
 constexpr int kLstmSplitK = 16;
 
+namespace {
+struct LstmPlanes { uint8_t *x, *hp, *da, *wx; };
+LstmPlanes lstm_planes(const pn_handle* h) {
+    const size_t T = (size_t)h->T;
+    float* base = h->lstm_ws + T * kG * 3 + T * kH * 4 + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG +
+                  (size_t)kH * kG;
+    LstmPlanes p;
+    p.x = reinterpret_cast<uint8_t*>(base);
+    p.hp = p.x + pn_gemm_planes_bytes((int)T, kH);
+    p.da = p.hp + pn_gemm_planes_bytes((int)T, kH);
+    p.wx = p.da + pn_gemm_planes_bytes((int)T, kG);
+    return p;
+}
+}  // namespace
+
 size_t pn_lstm_workspace_floats(const pn_handle* h) {
     // gx [T,1024], act [T,1024], dA [T,1024], c, tanh c, h_out, h_prev [T,256] each, dc carry [P,256],
     // split-K partials of a weight-gradient GEMM [16][256][1024], column-sum partials [32][1024]
     const size_t T = (size_t)h->T;
     return T * kG * 3 + T * kH * 4 + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG +
-           (size_t)kH * kG;                          // + the recurrent weights reordered for the forward step (WhR)
+           (size_t)kH * kG +                         // + the recurrent weights reordered for the forward step (WhR)
+           // + bf16 hi/lo block planes of X, Hprev [T,256], dA [T,1024] and the input half of the kernel (pn_gemm_tc.cu)
+           (pn_gemm_planes_bytes((int)T, kH) * 2 + pn_gemm_planes_bytes((int)T, kG) + pn_gemm_planes_bytes(kH, kG)) / sizeof(float);
 }
 
 // hbuf (module sum, no /M) -> lstm_out; reads the bound initial state, writes the final state if one is bound
@@ -499,8 +516,13 @@ int pn_launch_lstm_fwd(pn_handle* h, int B, cudaStream_t st) {
     float* hprev = hout + (size_t)h->T * kH;
     PnProfScope prof(h, PN_PROF_LSTM_FWD, st);
     // rows 0..255 of the kernel multiply the input: gx = X @ W[0:256] + b
-    GemmArgs g{{h->hbuf, kH, 1, T, 0}, {W, 1, kG, kG, 0}, gx, kG, h->params + nd.lstmb, T, kG, kH, 0};
-    if (int rc = gemm(h, g, 1, nullptr, st, "lstm input projection")) return rc;
+    const LstmPlanes pl = lstm_planes(h);
+    // the planes of X are made whenever the weight-gradient GEMM of this step could use them, too
+    if (int rc = pn_gemm_split(h, h->hbuf, T, kH, kH, pl.x, st)) return rc;
+    if (int rc = pn_gemm_split(h, W, kH, kG, kG, pl.wx, st)) return rc;
+    if (int rc = pn_gemm_tc(h, PnGemmOperand{pl.x, T, kH, false}, PnGemmOperand{pl.wx, kH, kG, true}, gx, kG, h->params + nd.lstmb, T,
+                            kG, kH, 1, st))
+        return rc;
     const float* Wh = W + (size_t)kH * kG;
     float* WhR = hprev + (size_t)h->T * kH + (size_t)h->P * kH + (size_t)kLstmSplitK * kH * kG + (size_t)kColsumChunks * kG;
     lstm_wh_reorder_kernel<<<dim3(kH / 32, kH / 32, 4), 256, 0, st>>>(Wh, WhR);
@@ -544,15 +566,35 @@ int pn_launch_lstm_bwd(pn_handle* h, int B, cudaStream_t st) {
     float* gW = h->grads + nd.lstmW;
     // dW rows 0..255 = X^T dA, rows 256..511 = Hprev^T dA (sum over every transition of every path): K = T is cut into
     // pieces so that the 8 output tiles become 128 blocks
-    GemmArgs gw1{{h->hbuf, 1, kH, kH, 0}, {dA, 1, kG, kG, 0}, gW, kG, nullptr, kH, kG, T, 0};
-    if (int rc = gemm(h, gw1, kLstmSplitK, partials, st, "lstm weight gradient (input rows)")) return rc;
-    GemmArgs gw2{{hprev, 1, kH, kH, 0}, {dA, 1, kG, kG, 0}, gW + (size_t)kH * kG, kG, nullptr, kH, kG, T, 0};
-    if (int rc = gemm(h, gw2, kLstmSplitK, partials, st, "lstm weight gradient (recurrent rows)")) return rc;
+    const LstmPlanes pl = lstm_planes(h);
+    if (int rc = pn_gemm_split(h, dA, T, kG, kG, pl.da, st)) return rc;
+    int nsplit = 0;                                 // tensor-core weight gradient: K = T in pieces of whole 64-deep chunks
+    for (int s2 = kLstmSplitK; s2 >= 1; --s2)
+        if (T % (64 * s2) == 0 && 16 * s2 <= 2 * h->num_sms) { nsplit = s2; break; }
+    if (nsplit) {
+        if (int rc = pn_gemm_split(h, hprev, T, kH, kH, pl.hp, st)) return rc;
+        const uint8_t* a_planes[2] = {pl.x, pl.hp};
+        for (int half = 0; half < 2; ++half) {
+            float* out = gW + (size_t)half * kH * kG;
+            if (int rc = pn_gemm_tc(h, PnGemmOperand{a_planes[half], T, kH, true}, PnGemmOperand{pl.da, T, kG, true},
+                                    nsplit > 1 ? partials : out, kG, nullptr, kH, kG, T, nsplit, st))
+                return rc;
+            if (nsplit > 1) {
+                const long long n = (long long)kH * kG;
+                splitk_sum_kernel<<<(int)((n / 4 + 255) / 256), 256, 0, st>>>(partials, nsplit, n, out);
+                PN_LAUNCH_CHECK(h, "splitk_sum_kernel");
+            }
+        }
+    } else {
+        GemmArgs gw1{{h->hbuf, 1, kH, kH, 0}, {dA, 1, kG, kG, 0}, gW, kG, nullptr, kH, kG, T, 0};
+        if (int rc = gemm(h, gw1, kLstmSplitK, partials, st, "lstm weight gradient (input rows)")) return rc;
+        GemmArgs gw2{{hprev, 1, kH, kH, 0}, {dA, 1, kG, kG, 0}, gW + (size_t)kH * kG, kG, nullptr, kH, kG, T, 0};
+        if (int rc = gemm(h, gw2, kLstmSplitK, partials, st, "lstm weight gradient (recurrent rows)")) return rc;
+    }
     colsum_kernel<<<dim3(kG / 32, kColsumChunks), 256, 0, st>>>(dA, T, colpart);
     PN_LAUNCH_CHECK(h, "colsum_kernel");
     colsum_finish_kernel<<<kG / 256, 256, 0, st>>>(colpart, kColsumChunks, h->grads + nd.lstmb);
     PN_LAUNCH_CHECK(h, "colsum_finish_kernel");
     // gradient at the cell input = dA @ Wx^T, overwriting dh (every step has consumed its dh_out by now)
-    GemmArgs gd{{dA, kG, 1, T, 0}, {W, kG, 1, kH, 0}, h->dh, kH, nullptr, T, kH, kG, 0};
-    return gemm(h, gd, 1, nullptr, st, "lstm input gradient");
+    return pn_gemm_tc(h, PnGemmOperand{pl.da, T, kG, false}, PnGemmOperand{pl.wx, kH, kG, false}, h->dh, kH, nullptr, T, kH, kG, 1, st);
 }
