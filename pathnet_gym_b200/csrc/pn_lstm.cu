@@ -164,6 +164,28 @@ splitk_sum_kernel(const float* __restrict__ part, int nsplit, long long n, float
     *reinterpret_cast<float4*>(out + i) = s;
 }
 
+// Programmatic dependent launch for the chains of per-step kernels: step t + 1 is launched while step t still runs and waits
+// (griddepcontrol.wait, first thing in the kernel) until step t has completed, so the launch latency between two dependent
+// steps (~3 us, 64 times per training step) overlaps with the step before.
+__device__ __forceinline__ void pdl_trigger_then_wait() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <class... KArgs, class... Args>
+cudaError_t launch_step_pdl(void (*kernel)(KArgs...), dim3 grid, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(256);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---- tile GEMM core for the per-step kernels: acc[TM][TN] += sum_k A[m][k] * B[n][k], both operands k-contiguous ---------
 // A time step's GEMM is tiny (134 MFLOP over the whole GPU) and strictly ordered after the previous step, so what it costs is
 // memory round trips: with one K slice in flight a block paid one per slice (K = 1024: 64 of them, 55 us per step).  Here the
@@ -235,15 +257,15 @@ struct TileGemmNT {
 };
 
 // ---- the same product with K split over the block's 8 warps ----------------------------------------------------------------
-// out[32 x BN] = sum_k A[m][k] * B[n][k] for one 32-row x BN-column tile (BN = 32 or 64); warp w multiplies k in
+// out[BM x BN] = sum_k A[m][k] * B[n][k] for one BM-row x BN-column tile (BM = 16 or 32, BN = 32 or 64); warp w multiplies k in
 // [w K/8, (w+1) K/8) for the WHOLE tile, streaming its operands through its own ring of shared-memory stages, then the 8
 // partial tiles are added in warp order (fixed summation order).  A block's serial chain is K/8 deep instead of K: the
 // step kernels are latency-bound (one block per SM, 64-128 blocks per step), so this is what their time follows.
-// Lane (ly = lane / 4, lx = lane % 4) owns rows ly + 8 i (i < 4) and columns lx + 4 j (j < BN / 4): with rows 20 floats apart
+// Lane (ly = lane / 4, lx = lane % 4) owns rows ly + 8 i (i < BM / 8) and columns lx + 4 j (j < BN / 4): with rows 20 floats apart
 // the 8 (4) distinct rows of a 128-bit load fall into distinct bank groups, equal addresses broadcast.
-template <int BN, int NSW>
+template <int BM, int BN, int NSW>
 struct WarpSplitGemmNT {
-    static constexpr int BM = 32, KS = 16, LD = KS + 4, TJ = BN / 4;
+    static constexpr int KS = 16, LD = KS + 4, TI = BM / 8, TJ = BN / 4;
     static constexpr int kStageFloats = (BM + BN) * LD;
     static constexpr size_t kSmemBytes = sizeof(float) * (size_t)8 * NSW * kStageFloats;      // >= 8 * BM * BN floats for the partial tiles
     // returns with part[w][m][n] (w < 8) in `smem` (layout [8][BM][BN]); the caller sums over w
@@ -265,9 +287,9 @@ struct WarpSplitGemmNT {
                 else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
-        float acc[4][TJ];
+        float acc[TI][TJ];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < TI; ++i)
 #pragma unroll
             for (int j = 0; j < TJ; ++j) acc[i][j] = 0.f;
 #pragma unroll
@@ -283,13 +305,13 @@ struct WarpSplitGemmNT {
             const float* base = ws + (size_t)(s % NSW) * kStageFloats;
 #pragma unroll
             for (int kq = 0; kq < KS; kq += 4) {
-                float4 a4[4], b4[TJ];
+                float4 a4[TI], b4[TJ];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) a4[i] = *reinterpret_cast<const float4*>(base + (ly + 8 * i) * LD + kq);
+                for (int i = 0; i < TI; ++i) a4[i] = *reinterpret_cast<const float4*>(base + (ly + 8 * i) * LD + kq);
 #pragma unroll
                 for (int j = 0; j < TJ; ++j) b4[j] = *reinterpret_cast<const float4*>(base + (BM + lx + 4 * j) * LD + kq);
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < TI; ++i)
 #pragma unroll
                     for (int j = 0; j < TJ; ++j) {
                         float v = acc[i][j];
@@ -303,7 +325,7 @@ struct WarpSplitGemmNT {
         __syncthreads();                             // every warp is done with its stages: they become the partial tiles
         float* part = smem + (size_t)warp * BM * BN;
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int i = 0; i < TI; ++i)
 #pragma unroll
             for (int j = 0; j < TJ; ++j) part[(ly + 8 * i) * BN + lx + 4 * j] = acc[i][j];
         __syncthreads();
@@ -342,9 +364,10 @@ __global__ void __launch_bounds__(256)
 lstm_step_fwd_kernel(const float* __restrict__ gx, const float* __restrict__ WhR, const float* __restrict__ state_in,
                      int P, int B, int t, float* __restrict__ act, float* __restrict__ cbuf, float* __restrict__ tcbuf,
                      float* __restrict__ hout, float* __restrict__ hprev_buf, float* __restrict__ state_out) {
-    using WG = WarpSplitGemmNT<64, 3>;
+    using WG = WarpSplitGemmNT<32, 64, 3>;
     extern __shared__ __align__(16) float tile_s[];
-    const int p0 = blockIdx.y * WG::BM, u0 = blockIdx.x * 16;
+    pdl_trigger_then_wait();
+    const int p0 = blockIdx.y * 32, u0 = blockIdx.x * 16;
     const bool have_h = t > 0 || state_in;
     if (have_h) {
         // A = h_{t-1}: the previous step's outputs, or the bound initial state (c, h per path);
@@ -385,14 +408,15 @@ lstm_step_fwd_kernel(const float* __restrict__ gx, const float* __restrict__ WhR
 }
 
 // ---- one step of BPTT, all paths: dA_t (gradient at the gate pre-activations) ----------------------------------------
-// dh_t = dh_out[t] + dA_{t+1} @ Wh^T;  block = 32 paths x 32 units, K = 1024 gate columns.
+// dh_t = dh_out[t] + dA_{t+1} @ Wh^T;  block = 16 paths x 32 units (128 blocks at 256 paths: every SM gets one), K = 1024 gate columns.
 __global__ void __launch_bounds__(256)
 lstm_step_bwd_kernel(const float* __restrict__ dh_out, const float* __restrict__ Wh, const float* __restrict__ act,
                      const float* __restrict__ cbuf, const float* __restrict__ tcbuf, const float* __restrict__ state_in,
                      int P, int B, int t, float* __restrict__ dA, float* __restrict__ dc_carry) {
-    using WG = WarpSplitGemmNT<32, 3>;
+    using WG = WarpSplitGemmNT<16, 32, 4>;
     extern __shared__ __align__(16) float tile_s[];
-    const int p0 = blockIdx.y * WG::BM, u0 = blockIdx.x * 32;
+    pdl_trigger_then_wait();
+    const int p0 = blockIdx.y * 16, u0 = blockIdx.x * 32;
     // dA_{t+1}[p][k] x Wh^T: (k = gate column, n = unit) = Wh[n][k], both k-contiguous
     if (t < B - 1) {
         WG wg;
@@ -401,7 +425,7 @@ lstm_step_bwd_kernel(const float* __restrict__ dh_out, const float* __restrict__
     {
         const int n = threadIdx.x & 31, u = u0 + n;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
+        for (int i = 0; i < 2; ++i) {
             const int m = (threadIdx.x >> 5) + 8 * i, p = p0 + m;
             if (p >= P) continue;
             const size_t row = (size_t)p * B + t;
@@ -528,11 +552,12 @@ int pn_launch_lstm_fwd(pn_handle* h, int B, cudaStream_t st) {
     lstm_wh_reorder_kernel<<<dim3(kH / 32, kH / 32, 4), 256, 0, st>>>(Wh, WhR);
     PN_LAUNCH_CHECK(h, "lstm_wh_reorder_kernel");
     dim3 grid(kH / 16, (P + 31) / 32);
-    const size_t smem = WarpSplitGemmNT<64, 3>::kSmemBytes;
+    const size_t smem = WarpSplitGemmNT<32, 64, 3>::kSmemBytes;
     PN_SET_SMEM(h, lstm_step_fwd_kernel, smem);
     for (int t = 0; t < B; ++t) {
-        lstm_step_fwd_kernel<<<grid, 256, smem, st>>>(gx, WhR, h->lstm_state_in, P, B, t, act, cbuf, tcbuf, hout, hprev,
-                                                  h->lstm_state_out);
+        cudaError_t e = launch_step_pdl(lstm_step_fwd_kernel, grid, smem, st, gx, WhR, h->lstm_state_in, P, B, t, act, cbuf, tcbuf, hout,
+                                        hprev, h->lstm_state_out);
+        if (e != cudaSuccess) return pn_fail(h, PN_ERR_CUDA, "launch of lstm_step_fwd_kernel failed: %s", cudaGetErrorString(e));
         PN_LAUNCH_CHECK(h, "lstm_step_fwd_kernel");
     }
     return PN_OK;
@@ -556,11 +581,13 @@ int pn_launch_lstm_bwd(pn_handle* h, int B, cudaStream_t st) {
     float* colpart = partials + (size_t)kLstmSplitK * kH * kG;
     (void)hout;
     PnProfScope prof(h, PN_PROF_LSTM_BWD, st);
-    dim3 grid(kH / 32, (P + 31) / 32);
-    const size_t smem = WarpSplitGemmNT<32, 3>::kSmemBytes;
+    dim3 grid(kH / 32, (P + 15) / 16);
+    const size_t smem = WarpSplitGemmNT<16, 32, 4>::kSmemBytes;
     PN_SET_SMEM(h, lstm_step_bwd_kernel, smem);
     for (int t = B - 1; t >= 0; --t) {
-        lstm_step_bwd_kernel<<<grid, 256, smem, st>>>(h->dh, Wh, act, cbuf, tcbuf, h->lstm_state_in, P, B, t, dA, dcc);
+        cudaError_t e = launch_step_pdl(lstm_step_bwd_kernel, grid, smem, st, h->dh, Wh, act, cbuf, tcbuf, h->lstm_state_in, P, B, t, dA,
+                                        dcc);
+        if (e != cudaSuccess) return pn_fail(h, PN_ERR_CUDA, "launch of lstm_step_bwd_kernel failed: %s", cudaGetErrorString(e));
         PN_LAUNCH_CHECK(h, "lstm_step_bwd_kernel");
     }
     float* gW = h->grads + nd.lstmW;
