@@ -186,14 +186,14 @@ def synthetic_scores(P_total, rnd, device):
     return torch.rand(P_total, generator=g).to(device) * 100.0
 
 
-def build_population(name, P, rank, world, local, pre_rounds=20):
+def build_population(name, P, rank, world, local, pre_rounds=20, lstm=False):
     """Population + controller in the state the configuration describes."""
     import numpy as np
     import torch
     from pathnet_gym_b200.controller import PopulationController
     from pathnet_gym_b200.population import PathNetConfig, PathNetPopulation, geopath_init
     c = CONFIGS[name]
-    cfg = PathNetConfig(L=c["L"], N=c["N"], A=c["A"])
+    cfg = PathNetConfig(L=c["L"], N=c["N"], A=c["A"], lstm=lstm)
     pop = PathNetPopulation(cfg, P, BATCH, device=local)
     pop.init_params(1)                                      # same seed on every rank: replicated parameters
     ctl = None
@@ -220,11 +220,11 @@ def build_population(name, P, rank, world, local, pre_rounds=20):
 class Workload(object):
     """Device-resident inputs + the step closure (train step -> gradient sum -> update [-> tournament])."""
 
-    def __init__(self, name, P, rank, world, local, seed_off=0):
+    def __init__(self, name, P, rank, world, local, seed_off=0, lstm=False):
         import torch
         from pathnet_gym_b200.trainer import PopulationTrainer
         self.name, self.P, self.rank, self.world = name, P, rank, world
-        self.cfg, self.pop, self.ctl = build_population(name, P, rank, world, local)
+        self.cfg, self.pop, self.ctl = build_population(name, P, rank, world, local, lstm=lstm)
         dev = self.pop.device
         gen = torch.Generator(device=dev)
         gen.manual_seed(1234 + rank + seed_off)
@@ -410,6 +410,20 @@ def run_b200(args):
         wl2.close()
         del masks_main
 
+    # ---- the same configuration with the reference's default network (constants.py:31 USE_LSTM = True): SURVEY 8f rank 1 ----
+    lstm_obj = None
+    if not args.no_lstm and world == 1:
+        wl3 = Workload(args.config, P, rank, world, local, seed_off=200, lstm=True)
+        for _ in range(W):
+            wl3.step()
+        barrier()
+        ms6, nt6 = timed(wl3, K, barrier, torch)
+        lstm_obj = {"workload": "%s with GameACPathNetLSTMNetwork (game_ac_network.py:303-521): BasicLSTMCell(256) over each path's "
+                                "%d transitions, BPTT, W_lstm / b_lstm in the slab" % (args.config, B),
+                    "value": round(P * B * K / (ms6 * 1e-3), 1), "unit": UNIT, "ms_per_step": round(ms6 / K, 4),
+                    "tournaments_in_timed_region": nt6}
+        wl3.close()
+
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
@@ -510,7 +524,7 @@ def run_b200(args):
                 "roofline": roof, "roofline_layer0": layer0, "roofline_rmsprop": roof_rms,
                 "roofline_rmsprop_alone": rms_alone, "roofline_tensor_kernels": tensor_rows, "kernels": kern,
                 "ms_per_step_instrumented": round(ms_instr / K, 4),
-                "workspace_mb": round(pop.workspace_bytes / 1e6, 1), "c5_strong": c5}
+                "workspace_mb": round(pop.workspace_bytes / 1e6, 1), "c5_strong": c5, "lstm_variant": lstm_obj}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(name, target_seconds=12.0)
         else:
@@ -691,6 +705,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-c5", action="store_true", help="skip the 512-path strong-scaling object")
+    ap.add_argument("--no-lstm", action="store_true", help="skip the LSTM-variant object")
     ap.add_argument("--no-stack-e2e", action="store_true", help="skip the full-stack end-to-end form")
     args = ap.parse_args()
     if args.impl == "reference":
