@@ -25,13 +25,22 @@ def tensor_names(cfg):
             names += ["W_conv[%d,%d]" % (l, j), "b_conv[%d,%d]" % (l, j)]
     for j in range(cfg.M):
         names += ["W_lin[%d]" % j, "b_lin[%d]" % j]
-    return names + ["W_fc2", "b_fc2", "W_fc3", "b_fc3"]
+    names += ["W_fc2", "b_fc2", "W_fc3", "b_fc3"]
+    if getattr(cfg, "lstm", False):                 # GameACPathNetLSTMNetwork.get_vars appends them (game_ac_network.py:502-506)
+        names += ["W_lstm", "b_lstm"]
+    return names
 
 
 def tf_saver_names(cfg, thread_index=0):
-    """Name each tensor has in a reference tf.train.Saver checkpoint (creation order == get_vars() order)."""
-    n = len(tensor_names(cfg))
-    return ["net_%d/Variable" % thread_index if k == 0 else "net_%d/Variable_%d" % (thread_index, k) for k in range(n)]
+    """Name each tensor has in a reference tf.train.Saver checkpoint: the conv / linear / head tensors are anonymous
+    tf.Variables created in get_vars() order (`Variable`, `Variable_1`, ...), the LSTM cell's two are created by
+    dynamic_rnn under their own names (game_ac_network.py:411-416,436-438)."""
+    lstm = bool(getattr(cfg, "lstm", False))
+    n = len(tensor_names(cfg)) - (2 if lstm else 0)
+    names = ["net_%d/Variable" % thread_index if k == 0 else "net_%d/Variable_%d" % (thread_index, k) for k in range(n)]
+    if lstm:
+        names += ["net_%d/basic_lstm_cell/kernel" % thread_index, "net_%d/basic_lstm_cell/bias" % thread_index]
+    return names
 
 
 def save_checkpoint(path, cfg, params, rms, momentum=None, genotypes=None, fixed_path=None, global_t=0, extra=None):
@@ -40,7 +49,7 @@ def save_checkpoint(path, cfg, params, rms, momentum=None, genotypes=None, fixed
     if len(params) != len(names) or len(rms) != len(names):
         raise ValueError("expected %d tensors, got %d params / %d rms" % (len(names), len(params), len(rms)))
     out = {"__format__": np.asarray(FORMAT), "__names__": np.asarray(names), "__tf_names__": np.asarray(tf_saver_names(cfg)),
-           "__config__": np.asarray(json.dumps({k: getattr(cfg, k) for k in ("L", "M", "H", "W", "C", "F", "hidden", "A")
+           "__config__": np.asarray(json.dumps({k: getattr(cfg, k) for k in ("L", "M", "H", "W", "C", "F", "hidden", "A", "lstm")
                                                 if hasattr(cfg, k)})),
            "__global_t__": np.asarray(int(global_t), dtype=np.int64)}
     for k, nm in enumerate(names):
@@ -65,7 +74,7 @@ def load_checkpoint(path, cfg):
         raise ValueError("not a %s file: %s" % (FORMAT, path))
     names = tensor_names(cfg)
     if [str(x) for x in z["__names__"]] != names:
-        raise ValueError("checkpoint tensor table does not match this configuration (L, M differ)")
+        raise ValueError("checkpoint tensor table does not match this configuration (L, M or the LSTM flag differ)")
     has_mom = ("momentum/" + names[0]) in z.files
     return dict(params=[z["param/" + nm] for nm in names], rms=[z["rms/" + nm] for nm in names],
                 momentum=[z["momentum/" + nm] for nm in names] if has_mom else None,

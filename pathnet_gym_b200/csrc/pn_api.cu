@@ -577,7 +577,7 @@ extern "C" PN_API int pn_stage_rollout_host(pn_handle* h, int slot, const uint8_
     const size_t Tmax = (size_t)h->T, T = (size_t)h->P * B;
     const size_t HW = (size_t)h->cfg.H * h->cfg.W, C = (size_t)h->cfg.C;
     if (int rc = prepare_slot(h, s, Tmax * HW * C)) return rc;
-    const size_t pwant = (size_t)h->P * (h->Bmax + C - 1) * HW, pbytes = (size_t)h->P * (B + C - 1) * HW;
+    const size_t pwant = (size_t)h->P * (h->Bmax + C - 1) * HW;
     if (s.planes_bytes < pwant) {
         PN_CUDA(h, cudaDeviceSynchronize());
         cudaFree(s.planes);

@@ -38,7 +38,6 @@ using namespace pntc;
 
 namespace {
 
-constexpr int kTcThreads = 320;          // weight-gradient kernel: 8 quantise/flush warps, producer, MMA
 constexpr int kEpiGroups = 4;            // forward kernel: 4 groups of 4 epilogue warps, then producer and MMA warps
 constexpr int kFwdThreads = (4 * kEpiGroups + 3) * 32;    // epilogue groups, producer, MMA warp A, MMA warp B
 // One TMEM accumulator stage per epilogue group: tile c -> group c%4 -> stage c%4.  (A stage must not be shared
@@ -507,8 +506,8 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
                     tc_fence_after();
                     const int nsl = min(kPassSlots, ns - pass * kPassSlots);
                     const uint32_t tbase = td + ((uint32_t)(quad * 32) << 16) + acc * kAccCols;
-                    // The TMEM read-out is this kernel's bottleneck (64 B/clk): a warp whose 32 raster rows all lie past the
-                    // end of the frame's raster (the last tile covers 36 useful rows of 128) skips it.
+                    // A warp whose 32 raster rows all lie past the end of the frame's raster (the last tile covers 36 useful
+                    // rows of 128) skips the read-out and the arithmetic.
                     const bool warp_all_junk = tile * 128 + quad * 32 >= gm.OH * gm.Ws;
                     if (warp_all_junk || (dbg && dbg[gridDim.x * 8] == 2)) {          // (debug mode 2: handshake only)
                         tc_fence_before();
@@ -622,15 +621,6 @@ __global__ void absmax_kernel(const float* __restrict__ x, size_t n4_per_path, u
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out + p, __float_as_uint(m));   // non-negative floats order like uints
-}
-
-__device__ __forceinline__ uint32_t pack4(const int* d) {
-    return (uint32_t)(d[0] & 255) | ((uint32_t)(d[1] & 255) << 8) | ((uint32_t)(d[2] & 255) << 16) |
-           ((uint32_t)(d[3] & 255) << 24);
-}
-__device__ __forceinline__ uint32_t nib_to_bytemask(unsigned nib) {
-    return ((nib & 1u) ? 0xFFu : 0u) | ((nib & 2u) ? 0xFF00u : 0u) | ((nib & 4u) ? 0xFF0000u : 0u) |
-           ((nib & 8u) ? 0xFF000000u : 0u);
 }
 
 struct WgGeom {

@@ -596,6 +596,35 @@ def test_peer_sum_small_single_rank(eng_mod):
     pop.close()
 
 
+def test_peer_sum_parts_single_rank(eng_mod):
+    """pn_peer_sum_part with world = 1: part 1 (everything but the first conv layer's tensors, exchanged early after
+    pn_stream_wait_early_grads) and part 2 (the first conv layer) publish disjoint pieces of the same slots with their own
+    flags; together they must leave the slab unchanged and the slots equal to the small regions, for several steps."""
+    cfg = hp.TINY
+    pop = make_pop(eng_mod, cfg, 1, 1, po.init_params(cfg, 1), np.zeros((1, cfg.L), np.uint32))
+    rng = np.random.default_rng(9)
+    buf = torch.zeros((pop.peer_buffer_bytes() + 3) // 4, dtype=torch.float32, device="cuda")
+    off, cnt = pop.lin_grads_region()
+    side = torch.cuda.Stream()
+    late = pop.stream_wait_early_grads(side)
+    assert 0 < late <= off
+    for step in range(4):
+        g0 = torch.from_numpy(rng.normal(size=pop.slab_floats).astype(np.float32)).cuda()
+        pop.grads.copy_(g0)
+        pop.peer_sum_part([buf.data_ptr()], 0, 1, step, 1)
+        pop.peer_sum_part([buf.data_ptr()], 0, 1, step, 2)
+        torch.cuda.synchronize()
+        assert torch.equal(pop.grads, g0)
+        slot = buf[256 + (step & 1) * (pop.slab_floats - cnt):][:pop.slab_floats - cnt]
+        assert torch.equal(slot[:off], g0[:off]) and torch.equal(slot[off:], g0[off + cnt:])
+    flags = buf[:256].view(torch.int32)
+    assert int(flags[136]) == 4 and int(flags[160]) == 4 and int(flags[0]) == 0
+    from pathnet_gym_b200 import PathNetError
+    with pytest.raises(PathNetError):
+        pop.peer_sum_part([buf.data_ptr()], 0, 1, 4, 3)
+    pop.close()
+
+
 def test_tensor_core_matches_cuda_core_path_l4(eng_mod):
     """L = 4 (third conv layer 3x3 / stride 1 on the tensor cores too): all tensor-core kernels against all CUDA-core
     kernels at a size where the raster tiles straddle transitions (81 rows per transition, 128-row tiles) and the weight

@@ -88,3 +88,16 @@ def test_checkpoint_roundtrip_and_tf_names(tmp_path):
     import pytest
     with pytest.raises(ValueError):
         ck.load_checkpoint(path, hp.TINY4)
+    # the LSTM network appends W_lstm / b_lstm (game_ac_network.py:502-506), saved by TF under the cell's own names
+    lcfg = hp.TC20_LSTM
+    ltt = po.tensor_table(lcfg)
+    assert ck.tensor_names(lcfg) == [t["name"] for t in ltt] and ck.tensor_names(lcfg)[-2:] == ["W_lstm", "b_lstm"]
+    lnames = ck.tf_saver_names(lcfg, 2)
+    assert lnames[-2:] == ["net_2/basic_lstm_cell/kernel", "net_2/basic_lstm_cell/bias"] and lnames[-3] == "net_2/Variable_%d" % (len(ltt) - 3)
+    lparams = po.init_params(lcfg, 5)
+    lpath = str(tmp_path / "ck_lstm.npz")
+    ck.save_checkpoint(lpath, lcfg, lparams, lparams)
+    lgot = ck.load_checkpoint(lpath, lcfg)
+    assert all(np.array_equal(a, b) for a, b in zip(lgot["params"], lparams))
+    with pytest.raises(ValueError):                         # a feed-forward configuration refuses the LSTM checkpoint
+        ck.load_checkpoint(lpath, po.OracleConfig(**{**lcfg.__dict__, "lstm": False}))
