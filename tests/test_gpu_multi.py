@@ -31,12 +31,13 @@ def _run(nproc, env_extra, port):
     return json.loads(lines[-1])
 
 
-@pytest.mark.parametrize("mode", ["default", "nccl_only", "peer_lin", "peer_split"])
+@pytest.mark.parametrize("mode", ["default", "nccl_only", "peer_lin", "peer_split", "lstm"])
 def test_overlapped_exchange_equals_plain_allreduce(native_lib, mode):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    env = {"default": {}, "nccl_only": {"PN_PEER_SUM": "0"}, "peer_lin": {"PN_PEER_LIN": "1"}, "peer_split": {"PN_PEER_SPLIT": "1"}}[mode]
-    out = _run(2, env, 29610 + {"default": 0, "nccl_only": 1, "peer_lin": 2, "peer_split": 3}[mode])
+    env = {"default": {}, "nccl_only": {"PN_PEER_SUM": "0"}, "peer_lin": {"PN_PEER_LIN": "1"}, "peer_split": {"PN_PEER_SPLIT": "1"},
+           "lstm": {"PN_CHECK_LSTM": "1"}}[mode]
+    out = _run(2, env, 29610 + {"default": 0, "nccl_only": 1, "peer_lin": 2, "peer_split": 3, "lstm": 4}[mode])
     assert out["world"] == 2
     assert out["overlapped_vs_plain_allreduce_rel_err"] < 1e-6
     assert out["params_identical_on_all_ranks"] is True

@@ -18,7 +18,7 @@ def main():
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    cfg, P, B = PathNetConfig(), 16, 32
+    cfg, P, B = PathNetConfig(lstm=bool(os.environ.get("PN_CHECK_LSTM"))), 16, 32      # PN_CHECK_LSTM=1: the LSTM variant
     pop = PathNetPopulation(cfg, P, B, device=local)
     pop.init_params(1)
     masks = geopath_init(P * world, cfg.L, cfg.M, 3, 7, 0, device=local)[rank * P:(rank + 1) * P]
