@@ -16,6 +16,8 @@ Configurations (BASELINE.json `configs`):
       with the frozen path, 64 paths x 32, tournament every 1000 steps
   c5  = `--gpus N`: the main line is weak scaling (the chosen config on every GPU); the `c5_strong` object in
       the same line holds 512 paths of the L=4 net IN TOTAL split over the N GPUs.
+At one GPU the line also carries `lstm_variant`: the same configuration with the reference's default network
+(GameACPathNetLSTMNetwork, constants.py:31 USE_LSTM = True), device-timed like the main value.
 
 For N > 1 launch with torchrun (RANK / LOCAL_RANK / WORLD_SIZE from the env); rank 0 prints ONE JSON line.
 """
