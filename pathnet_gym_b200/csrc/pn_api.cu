@@ -224,6 +224,7 @@ extern "C" PN_API int pn_create(const pn_config* cfg, pn_handle** out) {
             PN_TRYC(cudaMemcpy(h->tc_dbg + (size_t)h->num_sms * 8, &mode, sizeof(mode), cudaMemcpyHostToDevice));
         }
     }
+    h->no_pdl = getenv("PN_NO_PDL") != nullptr;
     PN_TRYC(cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking));
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
     PN_TRYC(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));

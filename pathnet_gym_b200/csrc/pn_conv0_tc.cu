@@ -196,6 +196,7 @@ conv0_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmap, const int8_t* __re
     __syncthreads();
     tc_fence_after();
     const uint32_t td = tmem_base_s;
+    pn_pdl_sync();                // everything above touches this CTA's shared memory and TMEM only
 
     if (warp == 4 * kEpiGroups) {
         // ================= producer: one TMA load per frame =================
@@ -1089,12 +1090,13 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     if (int rc = make_frame_tmap(h, g, frames, T, &tmap)) return rc;
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + 0, st);
+        // (programmatic dependent launch behind the weight-digit kernel: see pn_pdl_sync)
         if (fast)
-            conv0_fwd_tc_kernel<true><<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g, bounds,
-                                                                           h->act[0], h->rmask[0], h->tc_dbg);
+            pn_launch(pn_use_pdl(h), conv0_fwd_tc_kernel<true>, dim3(grid), dim3(kFwdThreads), smem_bytes, st, tmap, w8, wscale, h->params, nd,
+                      h->d_masks, B, T, g, bounds, h->act[0], h->rmask[0], h->tc_dbg);
         else
-            conv0_fwd_tc_kernel<false><<<grid, kFwdThreads, smem_bytes, st>>>(tmap, w8, wscale, h->params, nd, h->d_masks, B, T, g, bounds,
-                                                                            h->act[0], h->rmask[0], h->tc_dbg);
+            pn_launch(pn_use_pdl(h), conv0_fwd_tc_kernel<false>, dim3(grid), dim3(kFwdThreads), smem_bytes, st, tmap, w8, wscale, h->params, nd,
+                      h->d_masks, B, T, g, bounds, h->act[0], h->rmask[0], h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "conv0_fwd_tc_kernel");
     return PN_OK;

@@ -198,6 +198,7 @@ __global__ void __launch_bounds__(kFwdThreads, 2)
 conv_mid_fwd_tc_kernel(const float* __restrict__ X, const uint8_t* __restrict__ wf, const float* __restrict__ params,
                        PnNetDesc nd, int l, MidTcGeom g, const uint32_t* __restrict__ masks, int P, int B, int ntile,
                        int w_slots, uint32_t tmem_cols, float* __restrict__ Y, uint8_t* __restrict__ R) {
+    pn_pdl_sync();
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t* x_full = reinterpret_cast<uint64_t*>(smem);      // [kFwdStages]
     uint64_t* x_empty = x_full + kFwdStages;                     // [kFwdStages]
@@ -1323,8 +1324,8 @@ int pn_launch_conv_mid_fwd_tc(pn_handle* h, int l, int B, cudaStream_t st) {
     const int grid = (int)std::min<long long>(NT, 2ll * h->num_sms);
     {
         PnProfScope prof(h, PN_PROF_CONV_FWD + l, st);
-        conv_mid_fwd_tc_kernel<<<grid, kFwdThreads, smem, st>>>(h->act[l - 1], wf, h->params, nd, l, g, h->d_masks, h->P, B,
-                                                                ntile, w_slots, tmem_cols, h->act[l], h->rmask[l]);
+        pn_launch(pn_use_pdl(h), conv_mid_fwd_tc_kernel, dim3(grid), dim3(kFwdThreads), smem, st, (const float*)h->act[l - 1], wf,
+                  (const float*)h->params, nd, l, g, (const uint32_t*)h->d_masks, h->P, B, ntile, w_slots, tmem_cols, h->act[l], h->rmask[l]);
     }
     PN_LAUNCH_CHECK(h, "conv_mid_fwd_tc_kernel");
     return PN_OK;

@@ -136,6 +136,7 @@ struct pn_handle {
     float* lstm_ws = nullptr;           // gx | gate activations | dA | c | tanh c | h_out | h_prev | dc carry
     const float* lstm_state_in = nullptr;   // [P][2][256] (c, h) at the first step of every path, or null = zeros (borrowed)
     float* lstm_state_out = nullptr;        // [P][2][256] state after the last step, or null (borrowed)
+    bool no_pdl = false;                // PN_NO_PDL: ordinary launches everywhere (comparison)
     long long launches = 0;             // kernels launched through this handle
     PnProf prof;
     std::string err;
@@ -172,6 +173,32 @@ int pn_set_smem_cached(pn_handle* h, const void* kern, int bytes);
     do {                                                                                   \
         if (int rc__ = pn_set_smem_cached((h), (const void*)(kern), (int)(bytes))) return rc__; \
     } while (0)
+
+// Programmatic dependent launch along a chain of kernels on one stream: the next kernel is launched while this one runs
+// and waits -- pn_pdl_sync(), the first thing it does -- until this one has completed and its writes are visible, so
+// the launch latency between two dependent kernels (~2.7 us) overlaps with the kernel before.  A kernel launched the
+// ordinary way executes pn_pdl_sync() as a no-op.  Off while per-kernel timing is on and with PN_NO_PDL set.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pn_pdl_sync() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <class... KArgs, class... Args>
+inline cudaError_t pn_launch(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+inline bool pn_use_pdl(const pn_handle* h) { return !h->prof.on && !h->no_pdl; }
 
 #define PN_LAUNCH_CHECK(h, name)                                                              \
     do {                                                                                      \

@@ -146,6 +146,7 @@ __global__ void __launch_bounds__(256)
 lin_prep_kernel(const float* __restrict__ params, PnNetDesc nd, LinGeom g, uint8_t* __restrict__ wp,
                 uint8_t* __restrict__ wph, int wblocks, const float* __restrict__ X, int P, int B, uint8_t* __restrict__ xp,
                 uint8_t* __restrict__ xph) {
+    pn_pdl_sync();
     if ((int)blockIdx.x < wblocks) wsplit_item((long long)blockIdx.x * 256 + threadIdx.x, params, nd, g, wp, wph);
     else xsplit_item((long long)(blockIdx.x - wblocks) * 256 + threadIdx.x, X, g, P, B, xp, xph);
 }
@@ -173,6 +174,7 @@ __global__ void __launch_bounds__(192, 1)
 lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp, const float* __restrict__ params,
                   PnNetDesc nd, LinGeom g, const uint32_t* __restrict__ masks, int P, int B, float* __restrict__ Hout,
                   uint8_t* __restrict__ Rl, long long* __restrict__ dbg_arg) {
+    pn_pdl_sync();
     long long* const dbg = kTcDebugBuild ? dbg_arg : nullptr;   // the instrumentation below compiles away in the product build
     const bool dbg9 = dbg && dbg[148 * 8] == 9;              // PN_TC_DEBUG=9: where the forward GEMM's roles wait
     const long long t_entry = dbg9 ? lin_clock() : 0;
@@ -371,6 +373,7 @@ lin_fwd_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ xp
 __global__ void __launch_bounds__(256)
 lin_dsplit_kernel(const float* __restrict__ dh, const uint8_t* __restrict__ Rl, LinGeom g, const uint32_t* __restrict__ masks,
                   int P, int B, uint8_t* __restrict__ dp) {
+    pn_pdl_sync();
     const int p = blockIdx.z, slot = blockIdx.y;
     const uint32_t mask = masks[p * g.L + g.L - 1];
     if (slot >= __popc(mask)) return;
@@ -570,6 +573,7 @@ __global__ void __launch_bounds__(192, 1)
 lin_wgrad_tc_kernel(const uint8_t* __restrict__ xp, const uint8_t* __restrict__ dp, PnNetDesc nd, LinGeom g,
                     const uint32_t* __restrict__ masks, const int* __restrict__ list, const int* __restrict__ list_count,
                     int P, int KT, float* __restrict__ grads) {
+    pn_pdl_sync();
     extern __shared__ __align__(1024) uint8_t smem[];
     constexpr int kStages = 4;
     const int a_bytes = 16 * 4 * kBlk, b_bytes = 16 * 4 * kBlk;      // per hl: 16 kb (or cb) x 4 bb blocks = 8 KB
@@ -774,7 +778,8 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
         PnProfScope prof(h, PN_PROF_LIN_PREP, st);
         const long long xthreads = (long long)h->P * g.nbc * ((g.KB + 3) / 4) * 128;
         const int xblocks = (int)((xthreads + 255) / 256);
-        lin_prep_kernel<<<xblocks, 256, 0, st>>>(h->params, nd, g, wp, wph, 0, h->act[nd.nconv - 1], h->P, B, xp, xph);
+        pn_launch(pn_use_pdl(h), lin_prep_kernel, dim3(xblocks), dim3(256), 0, st, (const float*)h->params, nd, g, wp, wph, 0,
+                  (const float*)h->act[nd.nconv - 1], h->P, B, xp, xph);
     }
     PN_LAUNCH_CHECK(h, "lin_prep_kernel");
     const size_t smem = (size_t)kWStages * 2 * kWChunkKb * 16 * kBlk + g.xp_chunk + 256;
@@ -783,7 +788,8 @@ int pn_launch_lin_fwd_tc(pn_handle* h, int B, cudaStream_t st) {
     const int grid = items < h->num_sms ? items : h->num_sms;
     {
         PnProfScope prof(h, PN_PROF_LIN_FWD, st);
-        lin_fwd_tc_kernel<<<grid, 192, smem, st>>>(wph, xph, h->params, nd, g, h->d_masks, h->P, B, h->hbuf, h->lmask, h->tc_dbg);
+        pn_launch(pn_use_pdl(h), lin_fwd_tc_kernel, dim3(grid), dim3(192), smem, st, (const uint8_t*)wph, (const uint8_t*)xph,
+                  (const float*)h->params, nd, g, (const uint32_t*)h->d_masks, h->P, B, h->hbuf, h->lmask, h->tc_dbg);
     }
     PN_LAUNCH_CHECK(h, "lin_fwd_tc_kernel");
     return PN_OK;
@@ -799,7 +805,8 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
     {
         PnProfScope prof(h, PN_PROF_LIN_PREP, st);
         dim3 dgrid((g.nbc * (g.Hd / 32) * 128 + 255) / 256, g.M, h->P);
-        lin_dsplit_kernel<<<dgrid, 256, 0, st>>>(h->dh, h->lmask, g, h->d_masks, h->P, B, dp);
+        pn_launch(pn_use_pdl(h), lin_dsplit_kernel, dgrid, dim3(256), 0, st, (const float*)h->dh, (const uint8_t*)h->lmask, g,
+                  (const uint32_t*)h->d_masks, h->P, B, dp);
     }
     PN_LAUNCH_CHECK(h, "lin_dsplit_kernel");
     const int KT = (g.K / 8 + 1 + 15) / 16;          // tiles of 16 k-blocks covering the K rows plus the ones row
@@ -811,7 +818,8 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
         const int items = g.M * KT * 2;
         const int grid = items < h->num_sms ? items : h->num_sms;
         PnProfScope prof(h, PN_PROF_LIN_WGRAD, st);
-        lin_wgrad_tc_kernel<<<grid, 192, smem, st>>>(xp, dp, nd, g, h->d_masks, h->d_list, h->d_list_count, h->P, KT, h->grads);
+        pn_launch(pn_use_pdl(h), lin_wgrad_tc_kernel, dim3(grid), dim3(192), smem, st, (const uint8_t*)xp, (const uint8_t*)dp, nd, g,
+                  (const uint32_t*)h->d_masks, (const int*)h->d_list, (const int*)h->d_list_count, h->P, KT, h->grads);
     }
     PN_LAUNCH_CHECK(h, "lin_wgrad_tc_kernel");
     PN_CUDA(h, cudaEventRecord(h->ev_lin_grads, st));     // W_lin / b_lin gradients are final from here on

@@ -199,6 +199,7 @@ head_kernel(const float* __restrict__ Hin, const float* __restrict__ params, PnN
             const int32_t* __restrict__ actions, const float* __restrict__ td, const float* __restrict__ r,
             float beta, float* __restrict__ pi_out, float* __restrict__ v_out, float* __restrict__ dzv,
             float* __restrict__ dh, float* __restrict__ loss_t, float* __restrict__ part) {
+    pn_pdl_sync();
     static_assert(PN_HEAD_CHUNK == 16 && NP % 4 == 0 && NP <= 32, "phase 1 maps 16 transitions x 16 slices onto 256 threads");
     extern __shared__ __align__(16) float hsm[];
     const int Hd = nd.hidden, A = nd.A, A1 = A + 1;
@@ -868,8 +869,8 @@ int pn_launch_heads(pn_handle* h, int B, bool training, const int32_t* actions, 
     if (int rc = set_smem(h, kern, sm)) return rc;
     {
         PnProfScope prof(h, PN_PROF_HEAD, st);
-        kern<<<nchunks, 256, sm, st>>>(pn_head_input(h), h->params, nd, T, training ? 1 : 0, actions, td, r, beta, pi, v, h->dzv,
-                                       h->dh, h->loss_t, h->head_part);
+        pn_launch(pn_use_pdl(h), kern, dim3(nchunks), dim3(256), sm, st, (const float*)pn_head_input(h), (const float*)h->params, nd, T,
+                  training ? 1 : 0, actions, td, r, beta, pi, v, h->dzv, h->dh, h->loss_t, h->head_part);
     }
     PN_LAUNCH_CHECK(h, "head_kernel");
     h->pending_loss = training ? loss : nullptr;     // summed per path by the head-gradient reduce launch
