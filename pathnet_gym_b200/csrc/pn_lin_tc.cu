@@ -411,6 +411,7 @@ lin_dsplit_kernel(const float* __restrict__ dh, const uint8_t* __restrict__ Rl, 
 __global__ void __launch_bounds__(192, 1)
 lin_dgrad_tc_kernel(const uint8_t* __restrict__ wp, const uint8_t* __restrict__ dp, LinGeom g,
                     const uint32_t* __restrict__ masks, int P, int B, int KT, float* __restrict__ dflat) {
+    pn_pdl_sync();
     extern __shared__ __align__(1024) uint8_t smem[];
     const int w_stage_bytes = 2 * 16 * 16 * kBlk;                    // (hi + lo) x 16 kb x 16 cb16 = 64 KB
     uint8_t* w_s = smem;                                             // 2 stages, one per (slot, half)
@@ -829,7 +830,8 @@ int pn_launch_lin_bwd_tc(pn_handle* h, int B, cudaStream_t st) {
         const int items = h->P * g.nbc * KT;
         const int grid = items < h->num_sms ? items : h->num_sms;
         PnProfScope prof(h, PN_PROF_LIN_DGRAD, st);
-        lin_dgrad_tc_kernel<<<grid, 192, smem, st>>>(wp, dp, g, h->d_masks, h->P, B, KT, h->dact[nd.nconv - 1]);
+        pn_launch(pn_use_pdl(h), lin_dgrad_tc_kernel, dim3(grid), dim3(192), smem, st, (const uint8_t*)wp, (const uint8_t*)dp, g,
+                  (const uint32_t*)h->d_masks, h->P, B, KT, h->dact[nd.nconv - 1]);
     }
     PN_LAUNCH_CHECK(h, "lin_dgrad_tc_kernel");
     return PN_OK;

@@ -760,6 +760,7 @@ __global__ void __launch_bounds__(256)
 grad_reduce_kernel(PnReduceJobs jobs, PnNetDesc nd, const int* __restrict__ list, const int* __restrict__ list_count, int P,
                    int B, int nch_alloc, const float* __restrict__ head_part, const float* __restrict__ loss_t,
                    float* __restrict__ loss, float* __restrict__ grads) {
+    pn_pdl_sync();
     __shared__ float red[8][33];
     const int bid = blockIdx.x;
     if (bid >= jobs.head_blk0) {
@@ -925,8 +926,8 @@ int pn_launch_backward(pn_handle* h, const void* frames, int is_u8, int B, cudaS
         const int nloss = (with_head && h->pending_loss) ? (P + 255) / 256 : 0;
         if (blk + jb.head_nred + nloss == 0) return PN_OK;
         PnProfScope prof(h, PN_PROF_HEAD_WGRAD, rs);
-        grad_reduce_kernel<<<blk + jb.head_nred + nloss, 256, 0, rs>>>(jb, nd, h->d_list, h->d_list_count, P, B, h->nch,
-                                                                      h->head_part, h->loss_t, h->pending_loss, h->grads);
+        pn_launch(pn_use_pdl(h), grad_reduce_kernel, dim3(blk + jb.head_nred + nloss), dim3(256), 0, rs, jb, nd, (const int*)h->d_list,
+                  (const int*)h->d_list_count, P, B, h->nch, (const float*)h->head_part, (const float*)h->loss_t, h->pending_loss, h->grads);
         if (with_head) h->pending_loss = nullptr;
         PN_LAUNCH_CHECK(h, "grad_reduce_kernel");
         return PN_OK;

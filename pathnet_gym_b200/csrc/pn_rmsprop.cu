@@ -22,6 +22,7 @@ struct HandleTab {
 // two chunk segments in one launch: [c0, c0 + n0) then [c1, ...)
 __global__ void __launch_bounds__(kThreads)
 rms_sumsq_kernel(HandleTab tb, const float* __restrict__ grads, float* __restrict__ chunk_ss, int c0, int n0, int c1) {
+    pnrms::pdl_wait();          // launched programmatically behind the kernel that finishes the gradients (pn_pdl_sync)
     const int cid = (int)blockIdx.x < n0 ? c0 + (int)blockIdx.x : c1 + ((int)blockIdx.x - n0);
     pnrms::sumsq_body(tb, cid, grads, chunk_ss);
 }
@@ -64,7 +65,7 @@ int pn_launch_rmsprop(pn_handle* h, int first_tensor, int n_tensors, bool comple
     const int slot = is_lin ? (complement ? PN_PROF_RMS_UPDATE_SMALL : PN_PROF_RMS_UPDATE_LIN) : PN_PROF_RMS_UPDATE;
     const HandleTab tb{h->d_chunks, h->d_frozen, h->d_tensor_chunk0, h->d_tensor_nchunks};
     PnProfScope prof(h, slot, st);                  // ONE bracket around the pair: an event between them would undo the overlap
-    rms_sumsq_kernel<<<nchunks, kThreads, 0, st>>>(tb, h->grads, h->d_chunk_ss, c0, n0, c1);
+    pn_launch(pn_use_pdl(h), rms_sumsq_kernel, dim3(nchunks), dim3(kThreads), 0, st, tb, (const float*)h->grads, h->d_chunk_ss, c0, n0, c1);
     PN_LAUNCH_CHECK(h, "rms_sumsq_kernel");
     cudaError_t e;
     if (momentum != 0.0f)
