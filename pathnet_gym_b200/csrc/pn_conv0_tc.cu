@@ -76,6 +76,7 @@ struct TcGeom {
 __global__ void __launch_bounds__(256)
 conv0_wprep_kernel(const float* __restrict__ params, PnNetDesc nd, int s, int8_t* __restrict__ w8,
                    float* __restrict__ wscale) {
+    pn_pdl_sync();                // the weights may have been written by the kernel just before (the RMSProp update)
     __shared__ float red[8][8];
     __shared__ float mx[8];
     const int j = blockIdx.x, KK = nd.KK[0], C = nd.Cin[0], k = nd.k[0];
@@ -1077,7 +1078,7 @@ int pn_launch_conv0_fwd_tc(pn_handle* h, const uint8_t* frames, int B, cudaStrea
     float* wscale = reinterpret_cast<float*>(h->tc_w8 + (size_t)nd.M * kSlotBytes);
     {
         PnProfScope prof(h, PN_PROF_CONV0_WPREP, st);
-        conv0_wprep_kernel<<<nd.M, 256, 0, st>>>(h->params, nd, g.s, w8, wscale);
+        pn_launch(pn_use_pdl(h), conv0_wprep_kernel, dim3(nd.M), dim3(256), 0, st, (const float*)h->params, nd, g.s, w8, wscale);
     }
     PN_LAUNCH_CHECK(h, "conv0_wprep_kernel");
     const bool fast = g.tiles == kAccStages && 4 * g.ksteps == 8;
